@@ -1,0 +1,206 @@
+"""Generates the committed fixtures under tests/golden/ by running the UNMODIFIED reference code
+(/root/reference, imported through oracle/ref_shim.py) and, for the un-vendored DAC dependency, the
+arithmetic-equivalent implementation in the installed `transformers`.
+
+Run in the build container only (the reference does not travel to the GPU box):
+    python -m oracle.gen_golden
+Weights are never stored: they are regenerated from seeds by oracle.decoder_oracle.random_decoder_state /
+oracle.dac_oracle.random_dac_state, so a fixture = (seeds, inputs, reference outputs).
+"""
+import os
+import sys
+import warnings
+
+import numpy as np
+import torch
+
+HERE = os.path.dirname(os.path.abspath(__file__))
+ROOT = os.path.dirname(HERE)
+sys.path.insert(0, ROOT)
+GOLD = os.path.join(ROOT, "tests", "golden")
+
+from oracle import dac_oracle, decoder_oracle, generate_oracle  # noqa: E402
+from oracle.ref_shim import import_reference  # noqa: E402
+
+warnings.filterwarnings("ignore")
+
+TINY = dict(
+    vocab_size=96, hidden_size=128, num_hidden_layers=2, num_attention_heads=2, ffn_dim=256, num_codebooks=4,
+    max_position_embeddings=64, pad_token_id=32, eos_token_id=32, bos_token_id=33,
+)
+
+
+def gen_delay(ref):
+    cases = {}
+    # known-answer pattern of the reference docstring (modeling_parler_tts.py:84-87): K=4, M=8, B=9, P=8
+    specs = [
+        ("kat", 1, 4, 8, 1, 9, 8),
+        ("mini", 2, 9, 20, 1, 1025, 1024),
+        ("mini_long", 3, 9, 181, 1, 1025, 1024),
+        ("short", 2, 9, 16, 1, 1025, 1024),  # M < 2K-1: all -1
+        ("edge", 1, 9, 17, 1, 1025, 1024),  # M == 2K-1
+        ("prompt3", 2, 4, 12, 3, 33, 32),  # audio-prompt continuation
+        ("prompt5", 1, 9, 30, 5, 1025, 1024),
+    ]
+    rng = np.random.default_rng(7)
+    for name, B, K, M, T, bos, pad in specs:
+        if T == 1:
+            ids = np.full((B * K, 1), bos, dtype=np.int64)
+        else:
+            ids = rng.integers(0, pad, size=(B * K, T)).astype(np.int64)
+            ids[:, 0] = bos
+        out_ids, mask = ref.build_delay_pattern_mask(torch.from_numpy(ids), bos, pad, M, K)
+        cases[name + "_in"] = ids
+        cases[name + "_meta"] = np.array([B, K, M, T, bos, pad], dtype=np.int64)
+        cases[name + "_ids"] = out_ids.numpy()
+        cases[name + "_mask"] = mask.numpy()
+        gen = rng.integers(0, pad + 2, size=(B * K, min(M, 11))).astype(np.int64)
+        cases[name + "_gen"] = gen
+        cases[name + "_applied"] = ref.apply_delay_pattern_mask(torch.from_numpy(gen), mask).numpy()
+    np.savez_compressed(os.path.join(GOLD, "delay_patterns.npz"), **cases)
+    print("delay_patterns.npz:", len(specs), "cases")
+
+
+def _ref_decoder(ref, dims, sd):
+    cfg = ref.ParlerTTSDecoderConfig(
+        vocab_size=dims.vocab_size, max_position_embeddings=dims.max_position_embeddings,
+        num_hidden_layers=dims.num_hidden_layers, ffn_dim=dims.ffn_dim, num_attention_heads=dims.num_attention_heads,
+        hidden_size=dims.hidden_size, num_codebooks=dims.num_codebooks, pad_token_id=dims.pad_token_id,
+        eos_token_id=dims.eos_token_id, bos_token_id=dims.bos_token_id, dropout=0.1,
+    )
+    m = ref.ParlerTTSForCausalLM(cfg).eval()
+    missing = m.load_state_dict(sd, strict=True)
+    assert not missing.missing_keys and not missing.unexpected_keys
+    return m
+
+
+def gen_decoder(ref):
+    dims = decoder_oracle.DecoderDims(**TINY)
+    sd = decoder_oracle.random_decoder_state(dims, seed=11, ln_jitter=0.1)
+    model = _ref_decoder(ref, dims, sd)
+    g = torch.Generator().manual_seed(12)
+    B, S, P, K = 3, 5, 4, dims.num_codebooks
+    enc = torch.randn(B, S, dims.hidden_size, generator=g)
+    prm = torch.randn(B, P, dims.hidden_size, generator=g) * 0.5
+    enc_mask = torch.tensor([[1, 1, 1, 1, 1], [1, 1, 1, 0, 0], [1, 1, 1, 1, 0]])
+    prm_mask = torch.tensor([[1, 1, 1, 1], [0, 1, 1, 1], [1, 1, 0, 0]])
+    out = {"meta": np.array([B, S, P], dtype=np.int64)}
+    for tag, em, pm in (("nomask", None, None), ("masked", enc_mask, prm_mask)):
+        e = enc if em is None else enc * em[..., None]
+        ids = torch.full((B * K, 1), dims.bos_token_id)
+        steps = torch.randint(0, dims.vocab_size, (3, B * K, 1), generator=g)
+        with torch.no_grad():
+            o = model(input_ids=ids, encoder_hidden_states=e, encoder_attention_mask=em, prompt_hidden_states=prm,
+                      prompt_attention_mask=pm, use_cache=True)
+            out[f"{tag}_prefill_logits"] = o.logits.numpy()
+            past = o.past_key_values
+            for t in range(3):
+                o = model(input_ids=steps[t], encoder_hidden_states=e, encoder_attention_mask=em,
+                          prompt_attention_mask=pm, past_key_values=past, use_cache=True)
+                past = o.past_key_values
+                out[f"{tag}_step{t}_logits"] = o.logits.numpy()
+        out[f"{tag}_step_ids"] = steps.numpy()
+        out[f"{tag}_k_self_l1"] = past[1][0].numpy()
+        out[f"{tag}_v_cross_l0"] = past[0][3].numpy()
+    out["enc"], out["prm"], out["enc_mask"], out["prm_mask"] = enc.numpy(), prm.numpy(), enc_mask.numpy(), prm_mask.numpy()
+    # teacher-forced multi-token forward without cache (ParlerTTSForCausalLM.forward on a whole sequence)
+    seq = torch.randint(0, dims.vocab_size, (B * K, 6), generator=g)
+    with torch.no_grad():
+        o = model(input_ids=seq, encoder_hidden_states=enc, prompt_hidden_states=prm, use_cache=False)
+    out["tf_ids"], out["tf_logits"] = seq.numpy(), o.logits.numpy()
+    np.savez_compressed(os.path.join(GOLD, "decoder_tiny.npz"), **out)
+    print("decoder_tiny.npz written")
+    return dims, sd, model
+
+
+def gen_loop(ref, dims, sd, model):
+    """Drives the reference decoder + the reference mask functions through the restated loop (greedy), so that the
+    fixture pins prepare_inputs/apply-mask/cache semantics end to end on the reference's own forward."""
+    g = torch.Generator().manual_seed(21)
+    B, S, P = 2, 6, 3
+    enc = torch.randn(B, S, dims.hidden_size, generator=g)
+    prm = torch.randn(B, P, dims.hidden_size, generator=g) * 0.5
+    out = {"enc": enc.numpy(), "prm": prm.numpy()}
+    for tag, max_length, suppress in (("free", 24, None), ("noeos", 20, dims.pad_token_id)):
+        def fwd(inp, prompt, past):
+            with torch.no_grad():
+                o = model(input_ids=inp, encoder_hidden_states=enc, prompt_hidden_states=prompt,
+                          past_key_values=past, use_cache=True)
+            return o.logits, o.past_key_values
+
+        # the loop with reference functions substituted for the oracle's
+        res = generate_oracle.generate_codes(sd, dims, enc, prompt_hidden_states=prm, max_length=max_length,
+                                             do_sample=False, suppress_from=suppress, forward_fn=fwd, return_trace=True)
+        # cross-check mask/apply with the reference implementation
+        start = torch.full((B * dims.num_codebooks, 1), dims.bos_token_id)
+        _, rmask = ref.build_delay_pattern_mask(start, dims.bos_token_id, dims.pad_token_id, max_length, dims.num_codebooks)
+        assert np.array_equal(rmask.numpy(), res["pattern_mask"])
+        applied = ref.apply_delay_pattern_mask(torch.from_numpy(res["sequences"]), rmask)
+        _, m2 = ref.build_delay_pattern_mask(start, dims.bos_token_id, dims.pad_token_id, applied.shape[1], dims.num_codebooks)
+        keep = (m2 != dims.bos_token_id) & (m2 != dims.pad_token_id)
+        codes = applied[keep].reshape(B, dims.num_codebooks, -1).numpy()
+        assert np.array_equal(codes, res["codes"])
+        out[f"{tag}_sequences"], out[f"{tag}_codes"] = res["sequences"], codes
+        out[f"{tag}_scores"] = res["scores"].numpy()
+        out[f"{tag}_meta"] = np.array([max_length, -1 if suppress is None else suppress, res["steps"]], dtype=np.int64)
+        print(f"loop {tag}: Lout={res['sequences'].shape[1]} codes={codes.shape}")
+    np.savez_compressed(os.path.join(GOLD, "loop_tiny.npz"), **out)
+
+
+def gen_dac():
+    """transformers' DacModel (arithmetic-equivalent to descript DAC) on the oracle's random weights."""
+    from transformers import DacConfig, DacModel
+
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+    sd = dac_oracle.random_dac_state(cfg, seed=31)
+    hf_cfg = DacConfig(encoder_hidden_size=8, downsampling_ratios=[2, 4, 8, 8], decoder_hidden_size=64,
+                       n_codebooks=3, codebook_size=32, codebook_dim=4, sampling_rate=44100)
+    assert hf_cfg.hidden_size == 128
+    hf = DacModel(hf_cfg).eval()
+    new = {}
+    for i in range(3):
+        new[f"quantizer.quantizers.{i}.codebook.weight"] = sd[f"quantizer.quantizers.{i}.codebook.weight"]
+        w, b = dac_oracle.wn(sd, f"quantizer.quantizers.{i}.out_proj")
+        new[f"quantizer.quantizers.{i}.out_proj.weight"], new[f"quantizer.quantizers.{i}.out_proj.bias"] = w, b
+    w, b = dac_oracle.wn(sd, "decoder.model.0")
+    new["decoder.conv1.weight"], new["decoder.conv1.bias"] = w, b
+    for bi in range(4):
+        p, h = f"decoder.model.{bi + 1}.block", f"decoder.block.{bi}"
+        new[h + ".snake1.alpha"] = sd[p + ".0.alpha"]
+        w, b = dac_oracle.wn(sd, p + ".1")
+        new[h + ".conv_t1.weight"], new[h + ".conv_t1.bias"] = w, b
+        for ri in range(3):
+            r, hr = f"{p}.{ri + 2}.block", f"{h}.res_unit{ri + 1}"
+            new[hr + ".snake1.alpha"], new[hr + ".snake2.alpha"] = sd[r + ".0.alpha"], sd[r + ".2.alpha"]
+            w, b = dac_oracle.wn(sd, r + ".1")
+            new[hr + ".conv1.weight"], new[hr + ".conv1.bias"] = w, b
+            w, b = dac_oracle.wn(sd, r + ".3")
+            new[hr + ".conv2.weight"], new[hr + ".conv2.bias"] = w, b
+    new["decoder.snake1.alpha"] = sd["decoder.model.5.alpha"]
+    w, b = dac_oracle.wn(sd, "decoder.model.6")
+    new["decoder.conv2.weight"], new["decoder.conv2.bias"] = w, b
+    res = hf.load_state_dict(new, strict=False)
+    assert not res.unexpected_keys, res.unexpected_keys
+    assert all(k.startswith(("encoder.", "quantizer.quantizers.0.in_proj", "quantizer.quantizers.1.in_proj",
+                             "quantizer.quantizers.2.in_proj")) for k in res.missing_keys), res.missing_keys
+    g = torch.Generator().manual_seed(32)
+    codes = torch.randint(0, 32, (2, 3, 7), generator=g)
+    with torch.no_grad():
+        wav = hf.decode(audio_codes=codes).audio_values
+        z = hf.quantizer.from_codes(codes)[0]
+    np.savez_compressed(os.path.join(GOLD, "dac_tiny.npz"), codes=codes.numpy(), wav=wav.numpy(), z=z.numpy(),
+                        cfg=np.array([3, 32, 4, 128, 64, 8, 8, 4, 2], dtype=np.int64))
+    print("dac_tiny.npz:", wav.shape)
+
+
+def main():
+    os.makedirs(GOLD, exist_ok=True)
+    ref = import_reference()
+    gen_delay(ref)
+    dims, sd, model = gen_decoder(ref)
+    gen_loop(ref, dims, sd, model)
+    gen_dac()
+
+
+if __name__ == "__main__":
+    main()
