@@ -1,0 +1,192 @@
+/*
+ * parler_b200.h - C ABI of libparler_b200.so: the B200 (sm_100a) codec-token generation path of Parler-TTS.
+ *
+ * The reference (danlyth/parler-tts, /root/reference) is pure Python and has NO FFI; every entry point below
+ * names the reference Python function (file:line under /root/reference/parler_tts/) whose device work it
+ * replaces.  INTEGRATION.md shows the ctypes binding a maintainer of the reference would add.
+ *
+ * Conventions
+ *   - extern "C", plain pointers and sizes.  All tensor pointers are DEVICE pointers owned by the caller (PyTorch
+ *     allocates; the library never allocates, frees or keeps a pointer after the call returns).
+ *   - ptts_stream_t is a cudaStream_t (torch.cuda.current_stream().cuda_stream).  No call synchronises the host;
+ *     no host-side state changes per call, so every call is CUDA-graph capturable and replayable.
+ *   - return value: 0 = ok; non-zero = PTTS_E_* (argument or launch error), text in ptts_last_error_string().
+ *   - "T" tensors have the element type named by a PTTS_F32 / PTTS_BF16 enum; accumulation is always fp32.
+ *   - dynamic scalars that change between graph replays (current sequence length) live in the device-resident
+ *     control block PttsCtrl.
+ */
+#ifndef PARLER_B200_H
+#define PARLER_B200_H
+
+#include <stdint.h>
+
+#ifdef __cplusplus
+extern "C" {
+#endif
+
+typedef void* ptts_stream_t;
+
+#if defined(__GNUC__)
+#define PTTS_API __attribute__((visibility("default")))
+#else
+#define PTTS_API
+#endif
+
+enum { PTTS_F32 = 0, PTTS_BF16 = 1 };
+enum { PTTS_ACT_NONE = 0, PTTS_ACT_GELU = 1, PTTS_ACT_RELU = 2, PTTS_ACT_SILU = 3, PTTS_ACT_GELU_TANH = 4 };
+enum { PTTS_OK = 0, PTTS_E_ARG = 1, PTTS_E_LAUNCH = 2, PTTS_E_UNSUPPORTED = 3 };
+enum { PTTS_IMPL_SIMPLE = 0, PTTS_IMPL_FAST = 1 };
+
+#define PTTS_ABI_VERSION 1
+#define PTTS_MAX_CODEBOOKS 16
+
+/* Device-resident control block (int32 words), one per generation state.  Written only by kernels. */
+typedef struct {
+  int32_t len;          /* columns filled in `ids` (the next token goes to column `len`) */
+  int32_t done;         /* 1 once every row has finished or len reached max_len */
+  int32_t stop_len;     /* value of len at which the reference loop would have returned */
+  int32_t n_unfinished; /* rows (of B*K) still unfinished (transformers greedy_search/sample bookkeeping) */
+  int32_t ticket;       /* internal: block arrival counter of the epilogue kernel */
+  int32_t steps;        /* decode-step epilogues executed (diagnostic) */
+  int32_t reserved[2];  /* Philox key (seed lo, hi) of the sampling epilogue; written by the host at reset */
+} PttsCtrl;
+
+/* One decoder layer, weights packed row-major [out_features][in_features], element type = PttsModel.wdtype.
+ * Reference keys: model.decoder.layers.{i}.* (modeling_parler_tts.py:386-413). */
+typedef struct {
+  const void* w_qkv;   /* [3H][H]   self_attn q_proj | k_proj | v_proj stacked */
+  const void* w_o;     /* [H][H]    self_attn.out_proj */
+  const void* w_qc;    /* [H][H]    encoder_attn.q_proj */
+  const void* w_kvc;   /* [2H][H]   encoder_attn k_proj | v_proj stacked (prefill only) */
+  const void* w_oc;    /* [H][H]    encoder_attn.out_proj */
+  const void* w_fc1;   /* [F][H] */
+  const void* w_fc2;   /* [H][F] */
+  const float *ln1_g, *ln1_b; /* self_attn_layer_norm */
+  const float *ln2_g, *ln2_b; /* encoder_attn_layer_norm */
+  const float *ln3_g, *ln3_b; /* final_layer_norm */
+} PttsLayer;
+
+typedef struct {
+  int32_t n_layers, hidden, n_heads, head_dim, ffn, n_codebooks, vocab, max_pos;
+  int32_t wdtype;      /* PTTS_F32 | PTTS_BF16: matrices, KV caches and GEMM-input activations */
+  int32_t act_fn;      /* PTTS_ACT_* */
+  int32_t pad_id, eos_id, bos_id, reserved0;
+  const float* embed;  /* [K][vocab+1][H] fp32  model.decoder.embed_tokens.{k}.weight */
+  const float* pos;    /* [max_pos][H] fp32     model.decoder.embed_positions.weights */
+  const float *lnf_g, *lnf_b; /* model.decoder.layer_norm */
+  const void* w_heads; /* [K*vocab][H]          lm_heads.{k}.weight stacked */
+  const PttsLayer* layers; /* HOST array of n_layers entries */
+} PttsModel;
+
+/* Generation state for a batch of B utterances (all device pointers; buffers sized for `rows` = max rows any call
+ * processes: B for decode, B*(P+T0) for prefill). */
+typedef struct {
+  int32_t B, S, P, T0;     /* batch, encoder length, prompt length, start columns (1 without audio prompt) */
+  int32_t c_max;           /* self-attention cache slots per sequence (>= P + max_len) */
+  int32_t max_len;         /* M: generation max_length (columns of ids / mask) */
+  int32_t impl;            /* PTTS_IMPL_* kernel family */
+  int32_t do_sample, top_k; float temperature; int32_t suppress_from; /* epilogue: sampling + optional vocab cut */
+  float guidance_scale;    /* >1: rows [B/2, B) are the unconditional half (classifier-free guidance) */
+  uint64_t seed; int64_t row_offset; /* seed: informational (the kernels read the key from PttsCtrl.reserved);
+                                        row_offset: global row index of local row 0 (batch sharding) */
+  PttsCtrl* ctrl;
+  void* kv_self;           /* [L][2][B][heads][c_max][d]  T */
+  void* kv_cross;          /* [L][2][B][heads][S][d]      T */
+  const int32_t* enc_mask; /* [B][S] or NULL */
+  const int32_t* prompt_mask; /* [B][P] or NULL */
+  float* h;                /* [rows][H] fp32 residual stream */
+  void* xn;                /* [rows][H] T   LayerNorm output */
+  void* q;                 /* [rows][H] T */
+  void* attn;              /* [rows][H] T */
+  void* ffn;               /* [rows][F] T */
+  float* logits;           /* [B*K][vocab] fp32 */
+  float* scratch;          /* fp32 scratch, >= ptts_scratch_floats(...) */
+  int64_t* ids;            /* [B*K][max_len] raw generated ids */
+  const int64_t* mask;     /* [B*K][max_len] delay-pattern mask */
+  int32_t* unfinished;     /* [B*K] */
+} PttsState;
+
+PTTS_API int32_t ptts_abi_version(void);
+PTTS_API const char* ptts_last_error_string(void);
+PTTS_API int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows);
+/* Cumulative number of kernel launches this library has enqueued from the calling process (one per PTTS launch
+ * site executed on the host; a CUDA-graph replay re-runs the launches recorded at capture time). */
+PTTS_API int64_t ptts_launch_count(void);
+
+/* ---- integer kernels -------------------------------------------------------------------------------------- */
+/* build_delay_pattern_mask, modeling_parler_tts.py:77-139.  first_start (device int32[1]) receives the number of
+ * leading columns that are already determined (the reference's `first_start_id`). */
+PTTS_API int ptts_build_delay_mask(const int64_t* start_ids, int32_t B, int32_t K, int32_t T0, int32_t max_len, int64_t bos,
+                          int64_t pad, int64_t* mask_out, int32_t* first_start, ptts_stream_t s);
+/* apply_delay_pattern_mask, modeling_parler_tts.py:68-74 */
+PTTS_API int ptts_apply_delay_mask(const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int32_t rows,
+                          int32_t len, int64_t* out, int64_t ld_out, ptts_stream_t s);
+/* de-delay of generate(), modeling_parler_tts.py:2633-2648 (no-prompt geometry): codes[b][k][f] = applied[b*K+k][f+k+1] */
+PTTS_API int ptts_dedelay(const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int32_t B, int32_t K,
+                 int32_t l_out, int64_t* codes, ptts_stream_t s);
+/* frame filter of the ragged DAC path, modeling_parler_tts.py:2668: valid[b][f] = all_k codes[b][k][f] < codebook_size;
+ * counts[b] = number of valid frames; packed[b][k][0..counts[b]) = surviving frames in order. */
+PTTS_API int ptts_filter_frames(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t codebook_size, int64_t* packed,
+                       int32_t* counts, ptts_stream_t s);
+
+/* ---- decoder building blocks (each replaces eager torch ops of modeling_parler_tts.py) ---------------------- */
+/* Sum_k embed_tokens[k](ids) + positions, modeling_parler_tts.py:836,884-886; prompt rows are gathered from
+ * embed_prompts (modeling_parler_tts.py:2243-2245) and prepended (839-840).  ids: applied ids [B*K][ld_ids], columns
+ * [0,T0).  h_out [B][P+T0][H]. */
+PTTS_API int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T0,
+                       const float* prompt_table, const int64_t* prompt_ids, const float* prompt_hidden, int32_t P,
+                       float* h_out, ptts_stream_t s);
+/* nn.LayerNorm (eps 1e-5), modeling_parler_tts.py:446,467,487,959.  x fp32 [rows][H] -> y T */
+PTTS_API int ptts_layernorm(const float* x, const float* g, const float* b, int32_t rows, int32_t H, float eps, void* y,
+                   int32_t ydtype, ptts_stream_t s);
+/* nn.Linear: Y = act(alpha * X W^T + bias) [* row_mask] [+ residual], modeling_parler_tts.py:282,301-302,380,488-490,
+ * 1143,2014-2017.  X [M][K] xdtype, W [N][K] wdtype, Y [M][N] ydtype (ld = N), residual fp32 [M][N] may alias Y. */
+PTTS_API int ptts_linear(const void* x, int32_t xdtype, const void* w, int32_t wdtype, const float* bias, int32_t M, int32_t N,
+                int32_t K, float alpha, int32_t act, const float* residual, const int32_t* row_mask, void* y,
+                int32_t ydtype, int32_t impl, ptts_stream_t s);
+/* Attention over a cache, modeling_parler_tts.py:326-378.  q [B][Tq][H] (already scaled), cache_k/v
+ * [B][heads][c_stride][d]; query t of batch b sees keys j < ctx_base + (*ctx_dyn) and, if causal, j <= ctx - Tq + t;
+ * key_mask [B][mask_len] (1 = keep) covers keys [0, mask_len), later keys are unmasked.  Masked scores are the
+ * dtype's finfo.min exactly as the reference's additive mask produces. */
+PTTS_API int ptts_attention(const void* q, const void* cache_k, const void* cache_v, int32_t dtype, int32_t B, int32_t heads,
+                   int32_t d, int32_t Tq, int32_t c_stride, int32_t ctx_base, const int32_t* ctx_dyn, int32_t causal,
+                   const int32_t* key_mask, int32_t mask_len, void* out, float* scratch, int32_t impl,
+                   ptts_stream_t s);
+
+/* ---- the hot path -------------------------------------------------------------------------------------------- */
+/* Cross-attention K/V of all layers from the projected encoder states (modeling_parler_tts.py:297-298), once per
+ * utterance.  enc [B][S][H] T. */
+PTTS_API int ptts_cross_kv(const PttsModel* m, const PttsState* st, const void* enc, ptts_stream_t s);
+/* First forward of generate(): prompt + start columns (modeling_parler_tts.py:794-978 with past=None), logits of the
+ * last position, then the step epilogue.  If all_logits != NULL, also writes logits of every position
+ * [B*K][P+T0][vocab] (ParlerTTSForCausalLM.forward, modeling_parler_tts.py:1096-1185). */
+PTTS_API int ptts_prefill(const PttsModel* m, const PttsState* st, const float* prompt_table, const int64_t* prompt_ids,
+                 const float* prompt_hidden, float* all_logits, int32_t run_epilogue, ptts_stream_t s);
+/* One cached decode step: 24 x (LN, QKV, self-attn, out_proj, LN, q, cross-attn, out_proj, LN, fc1+GELU, fc2), final
+ * LN, 9 lm_heads, epilogue.  Replaces prepare_inputs_for_generation + forward + greedy_search/sample body
+ * (modeling_parler_tts.py:2081-2148, 1927-2079, call sites 2582-2620).  Graph-capturable.  run_epilogue = 0 stops
+ * after the logits so that user logits_processors can run before ptts_step_epilogue. */
+PTTS_API int ptts_decode_step(const PttsModel* m, const PttsState* st, int32_t run_epilogue, ptts_stream_t s);
+/* The fused per-step epilogue alone: logits processing + argmax / top-k sample + EOS/PAD freeze + token write +
+ * delay-mask apply + next-step embedding gather-sum + position add. */
+PTTS_API int ptts_step_epilogue(const PttsModel* m, const PttsState* st, ptts_stream_t s);
+
+/* ---- DAC decode (dac_wrapper/modeling_dac.py:98-134; arithmetic of descript-audio-codec) ----------------------- */
+/* z[b][c][f] = sum_i (out_proj_i . codebook_i[codes[b][i][f]])[c] + bias; tables[i] = folded [codebook_size][latent]
+ * (codebook x weight-normalised out_proj, pre-multiplied at load).  z fp32 [B][latent][F]. */
+PTTS_API int ptts_dac_dequant(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
+                     const float* tables, const float* bias_sum, int32_t codebook_size, int32_t latent, float* z,
+                     ptts_stream_t s);
+/* y = [tanh]( conv1d( snake_alpha(x) or x, w, bias, dilation, same padding ) ) [+ residual]; w folded [Cout][Cin][k]. */
+PTTS_API int ptts_dac_conv1d(const float* x, int32_t B, int32_t Cin, int32_t T, const float* w, const float* bias,
+                    int32_t Cout, int32_t ksize, int32_t dilation, const float* snake_alpha, const float* residual,
+                    int32_t tanh_out, float* y, int32_t impl, ptts_stream_t s);
+/* y = conv_transpose1d(snake(x), w [Cin][Cout][2*stride], stride, padding ceil(stride/2)) */
+PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T, const float* w, const float* bias,
+                      int32_t Cout, int32_t stride, const float* snake_alpha, float* y, int32_t impl,
+                      ptts_stream_t s);
+
+#ifdef __cplusplus
+}
+#endif
+#endif /* PARLER_B200_H */

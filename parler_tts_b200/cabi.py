@@ -1,0 +1,131 @@
+"""ctypes binding of libparler_b200.so (the C ABI declared in include/parler_b200.h).
+
+There is NO CPU fallback: if the shared library is missing or cannot be loaded, importing the compute path raises.
+Struct layouts mirror include/parler_b200.h field by field.
+"""
+import ctypes as C
+import os
+
+_HERE = os.path.dirname(os.path.abspath(__file__))
+LIB_PATH = os.path.join(_HERE, "libparler_b200.so")
+
+PTTS_F32, PTTS_BF16 = 0, 1
+ACT = {"none": 0, "gelu": 1, "relu": 2, "silu": 3, "gelu_new": 4}
+IMPL_SIMPLE, IMPL_FAST = 0, 1
+MAX_CODEBOOKS = 16
+ABI_VERSION = 1
+
+c_i32, c_i64, c_f32, c_u64, c_vp = C.c_int32, C.c_int64, C.c_float, C.c_uint64, C.c_void_p
+
+
+class PttsCtrl(C.Structure):
+    _fields_ = [("len", c_i32), ("done", c_i32), ("stop_len", c_i32), ("n_unfinished", c_i32), ("ticket", c_i32),
+                ("steps", c_i32), ("reserved", c_i32 * 2)]
+
+
+class PttsLayer(C.Structure):
+    _fields_ = [(n, c_vp) for n in ("w_qkv", "w_o", "w_qc", "w_kvc", "w_oc", "w_fc1", "w_fc2", "ln1_g", "ln1_b",
+                                    "ln2_g", "ln2_b", "ln3_g", "ln3_b")]
+
+
+class PttsModel(C.Structure):
+    _fields_ = [(n, c_i32) for n in ("n_layers", "hidden", "n_heads", "head_dim", "ffn", "n_codebooks", "vocab",
+                                     "max_pos", "wdtype", "act_fn", "pad_id", "eos_id", "bos_id", "reserved0")] + [
+        ("embed", c_vp), ("pos", c_vp), ("lnf_g", c_vp), ("lnf_b", c_vp), ("w_heads", c_vp),
+        ("layers", C.POINTER(PttsLayer))]
+
+
+class PttsState(C.Structure):
+    _fields_ = [("B", c_i32), ("S", c_i32), ("P", c_i32), ("T0", c_i32), ("c_max", c_i32), ("max_len", c_i32),
+                ("impl", c_i32), ("do_sample", c_i32), ("top_k", c_i32), ("temperature", c_f32),
+                ("suppress_from", c_i32), ("guidance_scale", c_f32), ("seed", c_u64), ("row_offset", c_i64),
+                ("ctrl", c_vp), ("kv_self", c_vp), ("kv_cross", c_vp), ("enc_mask", c_vp), ("prompt_mask", c_vp),
+                ("h", c_vp), ("xn", c_vp), ("q", c_vp), ("attn", c_vp), ("ffn", c_vp), ("logits", c_vp),
+                ("scratch", c_vp), ("ids", c_vp), ("mask", c_vp), ("unfinished", c_vp)]
+
+
+_PM, _PS = C.POINTER(PttsModel), C.POINTER(PttsState)
+
+# name -> (restype, argtypes); must list every PTTS_API symbol of include/parler_b200.h
+PROTOTYPES = {
+    "ptts_abi_version": (c_i32, []),
+    "ptts_last_error_string": (C.c_char_p, []),
+    "ptts_scratch_floats": (c_i64, [_PM, c_i32]),
+    "ptts_launch_count": (c_i64, []),
+    "ptts_build_delay_mask": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_vp, c_vp]),
+    "ptts_apply_delay_mask": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
+    "ptts_dedelay": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp]),
+    "ptts_filter_frames": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp]),
+    "ptts_embed_prefill": (C.c_int, [_PM, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "ptts_layernorm": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_f32, c_vp, c_i32, c_vp]),
+    "ptts_linear": (C.c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_i32, c_i32, c_f32, c_i32, c_vp, c_vp, c_vp,
+                              c_i32, c_i32, c_vp]),
+    "ptts_attention": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i32,
+                                 c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "ptts_cross_kv": (C.c_int, [_PM, _PS, c_vp, c_vp]),
+    "ptts_prefill": (C.c_int, [_PM, _PS, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp]),
+    "ptts_decode_step": (C.c_int, [_PM, _PS, c_i32, c_vp]),
+    "ptts_step_epilogue": (C.c_int, [_PM, _PS, c_vp]),
+    "ptts_dac_dequant": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp]),
+    "ptts_dac_conv1d": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32,
+                                  c_vp, c_i32, c_vp]),
+    "ptts_dac_convtr1d": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
+}
+
+_lib = None
+
+
+class ParlerB200Error(RuntimeError):
+    pass
+
+
+def load():
+    """Loads the shared library (once).  Raises if it is missing: the product path never falls back to the CPU."""
+    global _lib
+    if _lib is not None:
+        return _lib
+    if not os.path.exists(LIB_PATH):
+        raise ParlerB200Error(
+            f"{LIB_PATH} not found: build it with `python -c 'import __graft_entry__ as g; g.build()'` "
+            "(make -C parler_tts_b200/csrc).  There is no CPU fallback.")
+    lib = C.CDLL(LIB_PATH)
+    for name, (res, args) in PROTOTYPES.items():
+        fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
+        fn.restype, fn.argtypes = res, args
+    v = lib.ptts_abi_version()
+    if v != ABI_VERSION:
+        raise ParlerB200Error(f"ABI mismatch: library {v}, binding {ABI_VERSION}")
+    _lib = lib
+    return lib
+
+
+def check(rc, what=""):
+    if rc != 0:
+        msg = load().ptts_last_error_string().decode("utf-8", "replace")
+        raise ParlerB200Error(f"{what} failed (code {rc}): {msg}")
+
+
+def call(name, *args):
+    check(getattr(load(), name)(*args), name)
+
+
+def ptr(t):
+    """Device (or host) pointer of a torch tensor, or None."""
+    return None if t is None else C.c_void_p(t.data_ptr())
+
+
+def stream_ptr(stream=None):
+    import torch
+
+    s = stream if stream is not None else torch.cuda.current_stream()
+    return C.c_void_p(s.cuda_stream)
+
+
+def dtype_enum(dt):
+    import torch
+
+    if dt == torch.float32:
+        return PTTS_F32
+    if dt == torch.bfloat16:
+        return PTTS_BF16
+    raise ParlerB200Error(f"unsupported dtype {dt}: the CUDA path stores fp32 or bf16")

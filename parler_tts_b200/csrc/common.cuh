@@ -1,0 +1,86 @@
+// Shared helpers for libparler_b200.so (sm_100a only).
+#pragma once
+#include <cuda_runtime.h>
+#include <cuda_bf16.h>
+#include <stdint.h>
+#include <stdio.h>
+#include <float.h>
+
+#include "../../include/parler_b200.h"
+
+namespace ptts {
+
+void set_error(const char* fmt, ...);
+void count_launch();  // host-side tally of kernel launches enqueued by this library (ptts_launch_count)
+
+#define PTTS_CHECK_ARG(cond, ...)                    \
+  do {                                               \
+    if (!(cond)) {                                   \
+      ::ptts::set_error(__VA_ARGS__);                \
+      return PTTS_E_ARG;                             \
+    }                                                \
+  } while (0)
+
+#define PTTS_CHECK_LAUNCH(what)                                              \
+  do {                                                                       \
+    ::ptts::count_launch();                                                  \
+    cudaError_t e__ = cudaPeekAtLastError();                                 \
+    if (e__ != cudaSuccess) {                                                \
+      ::ptts::set_error("%s: %s", what, cudaGetErrorString(e__));            \
+      (void)cudaGetLastError();                                              \
+      return PTTS_E_LAUNCH;                                                  \
+    }                                                                        \
+  } while (0)
+
+#define PTTS_TRY(expr)                 \
+  do {                                 \
+    int rc__ = (expr);                 \
+    if (rc__ != PTTS_OK) return rc__;  \
+  } while (0)
+
+inline cudaStream_t as_stream(ptts_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
+inline size_t dtype_size(int dt) { return dt == PTTS_BF16 ? 2 : 4; }
+
+template <typename T> struct DT;
+template <> struct DT<float> { static constexpr int id = PTTS_F32; };
+template <> struct DT<__nv_bfloat16> { static constexpr int id = PTTS_BF16; };
+
+__device__ __forceinline__ float to_f(float v) { return v; }
+__device__ __forceinline__ float to_f(__nv_bfloat16 v) { return __bfloat162float(v); }
+template <typename T> __device__ __forceinline__ T from_f(float v);
+template <> __device__ __forceinline__ float from_f<float>(float v) { return v; }
+template <> __device__ __forceinline__ __nv_bfloat16 from_f<__nv_bfloat16>(float v) { return __float2bfloat16_rn(v); }
+
+// finfo(dtype).min as a float: what the reference's additive attention masks hold (modeling_parler_tts.py:875-879)
+template <typename T> __device__ __forceinline__ float finfo_min();
+template <> __device__ __forceinline__ float finfo_min<float>() { return -FLT_MAX; }
+template <> __device__ __forceinline__ float finfo_min<__nv_bfloat16>() { return -3.3895313892515355e38f; }
+
+__device__ __forceinline__ float warp_sum(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v += __shfl_xor_sync(0xffffffffu, v, o);
+  return v;
+}
+__device__ __forceinline__ float warp_max(float v) {
+#pragma unroll
+  for (int o = 16; o > 0; o >>= 1) v = fmaxf(v, __shfl_xor_sync(0xffffffffu, v, o));
+  return v;
+}
+
+__device__ __forceinline__ float apply_act(float x, int act) {
+  switch (act) {
+    case PTTS_ACT_GELU: return 0.5f * x * (1.0f + erff(x * 0.70710678118654752440f));
+    case PTTS_ACT_RELU: return fmaxf(x, 0.0f);
+    case PTTS_ACT_SILU: return x / (1.0f + expf(-x));
+    case PTTS_ACT_GELU_TANH: {
+      float u = 0.79788456080286535588f * (x + 0.044715f * x * x * x);
+      return 0.5f * x * (1.0f + tanhf(u));
+    }
+    default: return x;
+  }
+}
+
+// value of a dynamic scalar: base + *dyn (dyn may be null)
+__device__ __forceinline__ int dyn_value(int base, const int* dyn) { return base + (dyn ? *dyn : 0); }
+
+}  // namespace ptts

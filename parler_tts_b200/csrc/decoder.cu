@@ -1,0 +1,207 @@
+// Orchestration of the decoder forward passes (prefill, one cached decode step) and the exported building blocks.
+// Every function only enqueues kernels on the caller's stream: no allocation, no synchronisation, graph-capturable.
+// Replaces /root/reference/parler_tts/modeling_parler_tts.py:794-978 (ParlerTTSDecoder.forward), 415-502 (layer),
+// 264-382 (attention), 1096-1185 (lm heads) for the generation path.
+#include "ops.cuh"
+
+namespace ptts {
+
+static int linear_dispatch(int impl, const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M,
+                           int N, int K, float alpha, int act, const float* residual, const int* row_mask, void* y,
+                           int ydtype, cudaStream_t st) {
+  if (impl == PTTS_IMPL_FAST && fast_linear_supported(xdtype, wdtype, M, N, K))
+    return linear_fast(x, xdtype, w, wdtype, bias, M, N, K, alpha, act, residual, row_mask, y, ydtype, st);
+  return linear_simple(x, xdtype, w, wdtype, bias, M, N, K, alpha, act, residual, row_mask, y, ydtype, st);
+}
+
+static int attention_dispatch(int impl, const void* q, const void* ck, const void* cv, int dtype, int B, int heads,
+                              int d, int Tq, int c_stride, int ctx_base, const int* ctx_dyn, int causal,
+                              const int* key_mask, int mask_len, void* out, float* scratch, cudaStream_t st) {
+  if (impl == PTTS_IMPL_FAST && fast_attention_supported(dtype, d, Tq))
+    return attention_fast(q, ck, cv, dtype, B, heads, d, Tq, c_stride, ctx_base, ctx_dyn, causal, key_mask, mask_len,
+                          out, scratch, st);
+  return attention_simple(q, ck, cv, dtype, B, heads, d, Tq, c_stride, ctx_base, ctx_dyn, causal, key_mask, mask_len,
+                          out, st);
+}
+
+static int check_model(const PttsModel* m) {
+  PTTS_CHECK_ARG(m && m->layers, "null model descriptor");
+  PTTS_CHECK_ARG(m->n_layers > 0 && m->hidden > 0 && m->n_heads > 0 && m->head_dim * m->n_heads == m->hidden,
+                 "bad model dims");
+  PTTS_CHECK_ARG(m->n_codebooks > 0 && m->n_codebooks <= PTTS_MAX_CODEBOOKS, "bad codebook count");
+  PTTS_CHECK_ARG(m->wdtype == PTTS_F32 || m->wdtype == PTTS_BF16, "bad wdtype");
+  PTTS_CHECK_ARG(m->embed && m->pos && m->w_heads && m->lnf_g && m->lnf_b, "null model tensor");
+  return PTTS_OK;
+}
+
+static int check_state(const PttsModel* m, const PttsState* s) {
+  PTTS_CHECK_ARG(s, "null state descriptor");
+  PTTS_CHECK_ARG(s->B > 0 && s->P >= 0 && s->T0 > 0 && s->S >= 0, "bad state dims");
+  PTTS_CHECK_ARG(s->c_max >= s->P + s->max_len, "c_max smaller than P + max_len");
+  PTTS_CHECK_ARG(s->P + s->max_len <= m->max_pos, "P + max_len exceeds max_position_embeddings");
+  PTTS_CHECK_ARG(s->ctrl && s->kv_self && s->h && s->xn && s->q && s->attn && s->ffn && s->logits && s->scratch &&
+                     s->ids && s->mask && s->unfinished,
+                 "null state tensor");
+  PTTS_CHECK_ARG(s->S == 0 || s->kv_cross, "null cross cache");
+  return PTTS_OK;
+}
+
+static inline size_t kv_layer_elems(const PttsModel* m, int B, int slots) {
+  return (size_t)B * m->n_heads * slots * m->head_dim;
+}
+
+// one decoder layer over `rows` = B*Tq tokens.  ctx_base/ctx_dyn give the self-attention context length AFTER the
+// new K/V have been written; the write slot of token t is ctx - Tq + t.
+static int run_layer(const PttsModel* m, const PttsState* s, int l, int Tq, int ctx_base, const int* ctx_dyn,
+                     cudaStream_t st) {
+  const PttsLayer& L = m->layers[l];
+  const int H = m->hidden, F = m->ffn, heads = m->n_heads, d = m->head_dim, B = s->B, dt = m->wdtype;
+  const int rows = B * Tq;
+  const size_t es = dtype_size(dt);
+  char* ks = (char*)s->kv_self + (size_t)(2 * l) * kv_layer_elems(m, B, s->c_max) * es;
+  char* vs = (char*)s->kv_self + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->c_max) * es;
+  const float scale = 1.0f / sqrtf((float)d);
+  void* qkv = (void*)s->scratch;
+  // self attention block
+  PTTS_TRY(layernorm(s->h, L.ln1_g, L.ln1_b, rows, H, 1e-5f, H, 0, s->xn, dt, st));
+  PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qkv, dt, nullptr, rows, 3 * H, H, 1.0f, PTTS_ACT_NONE, nullptr,
+                           nullptr, qkv, dt, st));
+  PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, s->c_max, ctx_base - Tq, ctx_dyn, scale, s->q, ks, vs, st));
+  PTTS_TRY(attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn, Tq > 1,
+                              s->prompt_mask, s->P, s->attn, s->scratch, st));
+  PTTS_TRY(linear_dispatch(s->impl, s->attn, dt, L.w_o, dt, nullptr, rows, H, H, 1.0f, PTTS_ACT_NONE, s->h, nullptr,
+                           s->h, PTTS_F32, st));
+  // cross attention block (modeling_parler_tts.py:465-483)
+  if (s->S > 0) {
+    char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
+    char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->S) * es;
+    PTTS_TRY(layernorm(s->h, L.ln2_g, L.ln2_b, rows, H, 1e-5f, H, 0, s->xn, dt, st));
+    PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale, PTTS_ACT_NONE, nullptr,
+                             nullptr, s->q, dt, st));
+    PTTS_TRY(attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0, s->enc_mask, s->S,
+                                s->attn, s->scratch, st));
+    PTTS_TRY(linear_dispatch(s->impl, s->attn, dt, L.w_oc, dt, nullptr, rows, H, H, 1.0f, PTTS_ACT_NONE, s->h,
+                             nullptr, s->h, PTTS_F32, st));
+  }
+  // feed forward block
+  PTTS_TRY(layernorm(s->h, L.ln3_g, L.ln3_b, rows, H, 1e-5f, H, 0, s->xn, dt, st));
+  PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn, nullptr, nullptr,
+                           s->ffn, dt, st));
+  PTTS_TRY(linear_dispatch(s->impl, s->ffn, dt, L.w_fc2, dt, nullptr, rows, H, F, 1.0f, PTTS_ACT_NONE, s->h, nullptr,
+                           s->h, PTTS_F32, st));
+  return PTTS_OK;
+}
+
+// [B][T][K][V] -> [B][K][T][V]
+__global__ void logits_bktv_kernel(const float* __restrict__ in, int T, int K, int V, float* __restrict__ out) {
+  const int row = blockIdx.x;  // (b, t, k)
+  const int k = row % K, t = (row / K) % T, b = row / (K * T);
+  const float* src = in + (int64_t)row * V;
+  float* dst = out + (((int64_t)b * K + k) * T + t) * V;
+  for (int i = threadIdx.x; i < V; i += blockDim.x) dst[i] = src[i];
+}
+
+}  // namespace ptts
+
+using namespace ptts;
+
+extern "C" int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows) {
+  if (!m || rows <= 0) return 0;
+  const int64_t a = (int64_t)rows * 3 * m->hidden;                   // fused qkv / cross kv staging
+  const int64_t b = (int64_t)rows * m->n_codebooks * m->vocab;       // all-position logits staging
+  return (a > b ? a : b) + 4096;
+}
+
+extern "C" int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T0,
+                                  const float* prompt_table, const int64_t* prompt_ids, const float* prompt_hidden,
+                                  int32_t P, float* h_out, ptts_stream_t s) {
+  PTTS_TRY(check_model(m));
+  PTTS_CHECK_ARG(ids && h_out && B > 0 && T0 > 0 && P >= 0, "embed_prefill: bad arguments");
+  PTTS_CHECK_ARG(P == 0 || prompt_hidden || (prompt_table && prompt_ids), "embed_prefill: no prompt source");
+  return embed_prefill(m, ids, ld_ids, nullptr, 0, B, B, T0, prompt_table, prompt_ids, prompt_hidden, P, h_out,
+                       as_stream(s));
+}
+
+extern "C" int ptts_layernorm(const float* x, const float* g, const float* b, int32_t rows, int32_t H, float eps,
+                              void* y, int32_t ydtype, ptts_stream_t s) {
+  PTTS_CHECK_ARG(x && g && b && y && rows >= 0 && H > 0, "layernorm: bad arguments");
+  return layernorm(x, g, b, rows, H, eps, H, 0, y, ydtype, as_stream(s));
+}
+
+extern "C" int ptts_linear(const void* x, int32_t xdtype, const void* w, int32_t wdtype, const float* bias, int32_t M,
+                           int32_t N, int32_t K, float alpha, int32_t act, const float* residual,
+                           const int32_t* row_mask, void* y, int32_t ydtype, int32_t impl, ptts_stream_t s) {
+  PTTS_CHECK_ARG(x && w && y && M >= 0 && N > 0 && K > 0, "linear: bad arguments");
+  return linear_dispatch(impl, x, xdtype, w, wdtype, bias, M, N, K, alpha, act, residual, row_mask, y, ydtype,
+                         as_stream(s));
+}
+
+extern "C" int ptts_attention(const void* q, const void* cache_k, const void* cache_v, int32_t dtype, int32_t B,
+                              int32_t heads, int32_t d, int32_t Tq, int32_t c_stride, int32_t ctx_base,
+                              const int32_t* ctx_dyn, int32_t causal, const int32_t* key_mask, int32_t mask_len,
+                              void* out, float* scratch, int32_t impl, ptts_stream_t s) {
+  PTTS_CHECK_ARG(q && cache_k && cache_v && out, "attention: null pointer");
+  PTTS_CHECK_ARG(B > 0 && heads > 0 && d > 0 && Tq > 0 && c_stride > 0, "attention: bad dims");
+  return attention_dispatch(impl, q, cache_k, cache_v, dtype, B, heads, d, Tq, c_stride, ctx_base, ctx_dyn, causal,
+                            key_mask, mask_len, out, scratch, as_stream(s));
+}
+
+extern "C" int ptts_cross_kv(const PttsModel* m, const PttsState* s, const void* enc, ptts_stream_t stream) {
+  PTTS_TRY(check_model(m));
+  PTTS_TRY(check_state(m, s));
+  PTTS_CHECK_ARG(enc && s->S > 0, "cross_kv: no encoder states");
+  cudaStream_t st = as_stream(stream);
+  const int H = m->hidden, dt = m->wdtype, rows = s->B * s->S;
+  const size_t es = dtype_size(dt);
+  for (int l = 0; l < m->n_layers; ++l) {
+    char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, s->B, s->S) * es;
+    char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, s->B, s->S) * es;
+    PTTS_TRY(linear_dispatch(s->impl, enc, dt, m->layers[l].w_kvc, dt, nullptr, rows, 2 * H, H, 1.0f, PTTS_ACT_NONE,
+                             nullptr, nullptr, s->scratch, dt, st));
+    PTTS_TRY(kv_scatter(s->scratch, dt, rows, H, m->n_heads, m->head_dim, s->S, kc, vc, st));
+  }
+  return PTTS_OK;
+}
+
+extern "C" int ptts_prefill(const PttsModel* m, const PttsState* s, const float* prompt_table,
+                            const int64_t* prompt_ids, const float* prompt_hidden, float* all_logits,
+                            int32_t run_epilogue, ptts_stream_t stream) {
+  PTTS_TRY(check_model(m));
+  PTTS_TRY(check_state(m, s));
+  PTTS_CHECK_ARG(s->P == 0 || prompt_hidden || (prompt_table && prompt_ids), "prefill: no prompt source");
+  cudaStream_t st = as_stream(stream);
+  const int T = s->P + s->T0, B = s->B, H = m->hidden, K = m->n_codebooks, V = m->vocab, dt = m->wdtype;
+  const int cfg = s->guidance_scale > 1.0f;
+  PTTS_CHECK_ARG(!cfg || B % 2 == 0, "prefill: guidance needs an even model batch");
+  // with classifier-free guidance rows [B/2, B) replay the ids of rows [0, B/2) (modeling_parler_tts.py:2109-2118)
+  PTTS_TRY(embed_prefill(m, s->ids, s->max_len, s->mask, s->max_len, B, cfg ? B / 2 : B, s->T0, prompt_table, prompt_ids, prompt_hidden,
+                         s->P, s->h, st));
+  for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, l, T, T, nullptr, st));
+  if (all_logits) {
+    PTTS_TRY(layernorm(s->h, m->lnf_g, m->lnf_b, B * T, H, 1e-5f, H, 0, s->xn, dt, st));
+    PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B * T, K * V, H, 1.0f, PTTS_ACT_NONE,
+                             nullptr, nullptr, s->scratch, PTTS_F32, st));
+    logits_bktv_kernel<<<B * T * K, 256, 0, st>>>(s->scratch, T, K, V, all_logits);
+    PTTS_CHECK_LAUNCH("logits_bktv");
+  }
+  // logits of the last position only (transformers takes outputs.logits[:, -1, :])
+  PTTS_TRY(layernorm(s->h, m->lnf_g, m->lnf_b, B, H, 1e-5f, (int64_t)T * H, (int64_t)(T - 1) * H, s->xn, dt, st));
+  PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
+                           nullptr, s->logits, PTTS_F32, st));
+  if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));
+  return PTTS_OK;
+}
+
+extern "C" int ptts_decode_step(const PttsModel* m, const PttsState* s, int32_t run_epilogue, ptts_stream_t stream) {
+  PTTS_TRY(check_model(m));
+  PTTS_TRY(check_state(m, s));
+  cudaStream_t st = as_stream(stream);
+  const int B = s->B, H = m->hidden, K = m->n_codebooks, V = m->vocab, dt = m->wdtype;
+  // context after this step's K/V write = P + len   (len = columns already in ids; input column = len-1)
+  for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, l, 1, s->P, &s->ctrl->len, st));
+  PTTS_TRY(layernorm(s->h, m->lnf_g, m->lnf_b, B, H, 1e-5f, H, 0, s->xn, dt, st));
+  PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
+                           nullptr, s->logits, PTTS_F32, st));
+  if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));
+  return PTTS_OK;
+}

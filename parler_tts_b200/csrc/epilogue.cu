@@ -1,0 +1,216 @@
+// The fused per-step epilogue: ONE kernel per decode step that replaces, for every row r = b*K + k,
+//   logits processors (classifier-free guidance, optional vocabulary cut)      transformers logits_process
+//   greedy argmax | temperature + top-k + softmax + draw                        transformers greedy_search / sample
+//   next = next*unfinished + pad*(1-unfinished); append; unfinished &= next!=eos     (same)
+//   apply_delay_pattern_mask on the new column                                  modeling_parler_tts.py:68-74, 2107
+//   sum_k embed_tokens[k](input) + position row                                 modeling_parler_tts.py:836, 884-886
+// (call sites /root/reference/parler_tts/modeling_parler_tts.py:2582-2620).  One block per utterance, one warp per
+// codebook row; all sequence-length state lives in the device control block so the launch is graph-replayable.
+#include "ops.cuh"
+
+namespace ptts {
+
+__device__ __forceinline__ void philox4x32_10(uint32_t c0, uint32_t c1, uint32_t c2, uint32_t c3, uint32_t k0,
+                                              uint32_t k1, uint32_t out[4]) {
+#pragma unroll
+  for (int r = 0; r < 10; ++r) {
+    const uint32_t hi0 = __umulhi(0xD2511F53u, c0), lo0 = 0xD2511F53u * c0;
+    const uint32_t hi1 = __umulhi(0xCD9E8D57u, c2), lo1 = 0xCD9E8D57u * c2;
+    const uint32_t n0 = hi1 ^ c1 ^ k0, n1 = lo1, n2 = hi0 ^ c3 ^ k1, n3 = lo0;
+    c0 = n0; c1 = n1; c2 = n2; c3 = n3;
+    k0 += 0x9E3779B9u; k1 += 0xBB67AE85u;
+  }
+  out[0] = c0; out[1] = c1; out[2] = c2; out[3] = c3;
+}
+
+__device__ __forceinline__ uint32_t order_key(float f) {
+  const uint32_t u = __float_as_uint(f);
+  return (u & 0x80000000u) ? ~u : (u | 0x80000000u);
+}
+
+// warp-wide log-sum-exp helpers over a row in shared memory
+__device__ __forceinline__ float row_max(const float* s, int V, int lane) {
+  float m = -INFINITY;
+  for (int i = lane; i < V; i += 32) m = fmaxf(m, s[i]);
+  return warp_max(m);
+}
+
+__global__ void __launch_bounds__(32 * PTTS_MAX_CODEBOOKS)
+step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ pos, int K, int V, int H, int Bu,
+                     int cfg, float guidance, int P, int T0, int M, int do_sample, int top_k, float temperature,
+                     int suppress_from, int64_t row_offset, int64_t pad_id, int64_t eos_id,
+                     PttsCtrl* __restrict__ ctrl, const float* __restrict__ logits, int64_t* __restrict__ ids,
+                     const int64_t* __restrict__ mask, int* __restrict__ unfinished, float* __restrict__ h,
+                     int h_rows_per_batch) {
+  extern __shared__ float smem[];
+  __shared__ int64_t next_in[PTTS_MAX_CODEBOOKS];
+  __shared__ int transitions;
+  if (ctrl->done) return;
+  const int len = ctrl->len;
+  if (len >= M) return;
+  const int b = blockIdx.x;
+  const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  if (threadIdx.x == 0) transitions = 0;
+  __syncthreads();
+  float* sc = smem + (size_t)k * V;        // this warp's score row
+  int* kept = (int*)(smem + (size_t)K * V) + (size_t)k * V;  // compacted kept indices (sampling only)
+  const int r = b * K + k;
+
+  // ---- logits processors
+  const float* lc = logits + (int64_t)r * V;
+  if (cfg) {
+    const float* lu = logits + ((int64_t)(b + Bu) * K + k) * V;
+    float mc = -INFINITY, mu = -INFINITY;
+    for (int i = lane; i < V; i += 32) { mc = fmaxf(mc, lc[i]); mu = fmaxf(mu, lu[i]); }
+    mc = warp_max(mc); mu = warp_max(mu);
+    float sc_ = 0.f, su = 0.f;
+    for (int i = lane; i < V; i += 32) { sc_ += expf(lc[i] - mc); su += expf(lu[i] - mu); }
+    sc_ = warp_sum(sc_); su = warp_sum(su);
+    const float lzc = mc + logf(sc_), lzu = mu + logf(su);
+    for (int i = lane; i < V; i += 32) {
+      const float c = lc[i] - lzc, u = lu[i] - lzu;
+      sc[i] = u + guidance * (c - u);
+    }
+  } else {
+    for (int i = lane; i < V; i += 32) sc[i] = lc[i];
+  }
+  if (suppress_from >= 0)
+    for (int i = suppress_from + lane; i < V; i += 32) sc[i] = -INFINITY;
+  __syncwarp();
+
+  // ---- token selection
+  int64_t tok;
+  if (!do_sample) {
+    float bv = -INFINITY; int bi = 0x7fffffff;
+    for (int i = lane; i < V; i += 32) {
+      const float v = sc[i];
+      if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }
+    }
+#pragma unroll
+    for (int o = 16; o > 0; o >>= 1) {
+      const float ov = __shfl_xor_sync(0xffffffffu, bv, o);
+      const int oi = __shfl_xor_sync(0xffffffffu, bi, o);
+      if (ov > bv || (ov == bv && oi < bi)) { bv = ov; bi = oi; }
+    }
+    tok = bi;
+  } else {
+    if (temperature != 1.0f) {
+      for (int i = lane; i < V; i += 32) sc[i] = sc[i] / temperature;
+      __syncwarp();
+    }
+    // k-th largest ordered key by MSB-first search: keep every score >= it (ties kept, TopKLogitsWarper)
+    uint32_t thr = 0u;
+    const int kk = top_k > 0 ? min(top_k, V) : V;
+    if (top_k > 0) {
+      for (int bit = 31; bit >= 0; --bit) {
+        const uint32_t cand = thr | (1u << bit);
+        int cnt = 0;
+        for (int i = lane; i < V; i += 32) cnt += order_key(sc[i]) >= cand;
+        cnt = __reduce_add_sync(0xffffffffu, cnt);
+        if (cnt >= kk) thr = cand;
+      }
+    }
+    // ordered compaction of the kept set
+    int nk = 0;
+    for (int i0 = 0; i0 < V; i0 += 32) {
+      const int i = i0 + lane;
+      const bool keep = i < V && order_key(sc[i]) >= thr;
+      const unsigned bal = __ballot_sync(0xffffffffu, keep);
+      if (keep) kept[nk + __popc(bal & ((1u << lane) - 1u))] = i;
+      nk += __popc(bal);
+    }
+    __syncwarp();
+    const float mx = row_max(sc, V, lane);
+    int choice = 0;
+    if (lane == 0) {
+      float total = 0.f;
+      for (int j = 0; j < nk; ++j) total += expf(sc[kept[j]] - mx);  // fixed ascending-index fp32 order
+      uint32_t rnd[4];
+      const uint64_t grow = (uint64_t)(row_offset + r);
+      // the Philox key lives in the control block so that a captured graph can be replayed with a new seed
+      philox4x32_10((uint32_t)grow, (uint32_t)(len - T0), 0u, 0u, (uint32_t)ctrl->reserved[0],
+                    (uint32_t)ctrl->reserved[1], rnd);
+      const float u = (float)(((double)rnd[0] + 0.5) * 2.3283064365386963e-10);
+      const float thresh = u * total;
+      float acc = 0.f;
+      choice = kept[nk - 1];
+      for (int j = 0; j < nk; ++j) {
+        acc += expf(sc[kept[j]] - mx);
+        if (acc > thresh) { choice = kept[j]; break; }
+      }
+    }
+    tok = __shfl_sync(0xffffffffu, choice, 0);
+  }
+
+  // ---- EOS / PAD bookkeeping, token write, delay mask for the next input
+  if (lane == 0) {
+    const int unf = unfinished[r];
+    tok = unf ? tok : pad_id;
+    ids[(int64_t)r * M + len] = tok;
+    const int unf2 = unf && (tok != eos_id);
+    unfinished[r] = unf2;
+    if (unf && !unf2) atomicAdd(&transitions, 1);
+    const int64_t mv = (len < M) ? mask[(int64_t)r * M + len] : -1;
+    next_in[k] = (mv == -1) ? tok : mv;
+  }
+  __syncthreads();
+
+  // ---- next-step hidden state: sum_k embed[k][input_k] + pos[P + len]   (written for both CFG halves)
+  if (len + 1 < M) {
+    const float* prow = pos + (int64_t)(P + len) * H;
+    for (int c = threadIdx.x; c < H; c += blockDim.x) {
+      float acc = 0.f;
+      for (int kk2 = 0; kk2 < K; ++kk2) acc += embed[((int64_t)kk2 * (V + 1) + next_in[kk2]) * H + c];
+      const float v = acc + prow[c];
+      h[(int64_t)b * h_rows_per_batch * H + c] = v;
+      if (cfg) h[(int64_t)(b + Bu) * h_rows_per_batch * H + c] = v;
+    }
+  }
+
+  // ---- global bookkeeping: the last block to arrive advances len and decides termination
+  if (threadIdx.x == 0) {
+    if (transitions) atomicSub(&ctrl->n_unfinished, transitions);
+    __threadfence();
+    const int t = atomicAdd(&ctrl->ticket, 1);
+    if (t == (int)gridDim.x - 1) {
+      __threadfence();
+      const int nl = len + 1;
+      const int nu = atomicAdd(&ctrl->n_unfinished, 0);
+      ctrl->ticket = 0;
+      ctrl->steps += 1;
+      if (nu == 0 || nl >= M) { ctrl->stop_len = nl; ctrl->done = 1; }
+      ctrl->len = nl;
+    }
+  }
+}
+
+int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st) {
+  const int K = m->n_codebooks, V = m->vocab;
+  const int cfg = s->guidance_scale > 1.0f;
+  PTTS_CHECK_ARG(!cfg || (s->B % 2 == 0), "step_epilogue: guidance needs an even model batch");
+  const int Bu = cfg ? s->B / 2 : s->B;
+  const size_t smem = (size_t)K * V * sizeof(float) * (s->do_sample ? 2 : 1);
+  if (smem > 48 * 1024) {
+    static size_t configured = 0;
+    if (smem > configured) {
+      cudaFuncSetAttribute(step_epilogue_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      configured = smem;
+    }
+  }
+  PTTS_CHECK_ARG(smem <= 200 * 1024, "step_epilogue: K*vocab too large");
+  // the hidden buffer holds one row per utterance during decode (rows_per_batch = 1)
+  step_epilogue_kernel<<<Bu, 32 * K, smem, st>>>(m->embed, m->pos, K, V, m->hidden, Bu, cfg, s->guidance_scale, s->P,
+                                                 s->T0, s->max_len, s->do_sample, s->top_k, s->temperature,
+                                                 s->suppress_from, s->row_offset, m->pad_id, m->eos_id,
+                                                 s->ctrl, s->logits, s->ids, s->mask, s->unfinished, s->h, 1);
+  PTTS_CHECK_LAUNCH("step_epilogue");
+  return PTTS_OK;
+}
+
+}  // namespace ptts
+
+extern "C" int ptts_step_epilogue(const PttsModel* m, const PttsState* st, ptts_stream_t s) {
+  PTTS_CHECK_ARG(m && st, "step_epilogue: null descriptor");
+  PTTS_CHECK_ARG(m->n_codebooks <= PTTS_MAX_CODEBOOKS, "step_epilogue: too many codebooks");
+  return ptts::step_epilogue(m, st, ptts::as_stream(s));
+}

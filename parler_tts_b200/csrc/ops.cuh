@@ -1,0 +1,39 @@
+// Internal (non-ABI) declarations shared by the translation units of libparler_b200.so.
+#pragma once
+#include "common.cuh"
+
+namespace ptts {
+
+int embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int B,
+                  int ids_batch, int T0, const float* prompt_table,
+                  const int64_t* prompt_ids, const float* prompt_hidden, int P, float* h, cudaStream_t st);
+int layernorm(const float* x, const float* g, const float* b, int rows, int H, float eps, int64_t in_stride,
+              int64_t in_offset, void* y, int ydtype, cudaStream_t st);
+int linear_simple(const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M, int N, int K,
+                  float alpha, int act, const float* residual, const int* row_mask, void* y, int ydtype,
+                  cudaStream_t st);
+int qkv_scatter(const void* qkv, int dtype, int rows, int H, int heads, int d, int Tq, int c_stride, int pos_base,
+                const int* pos_dyn, float scale, void* q, void* ck, void* cv, cudaStream_t st);
+int kv_scatter(const void* kv, int dtype, int rows, int H, int heads, int d, int S, void* ck, void* cv,
+               cudaStream_t st);
+int attention_simple(const void* q, const void* ck, const void* cv, int dtype, int B, int heads, int d, int Tq,
+                     int c_stride, int ctx_base, const int* ctx_dyn, int causal, const int* key_mask, int mask_len,
+                     void* out, cudaStream_t st);
+int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st);
+
+// fast (sm_100a tcgen05 / TMA) family -- fast_*.cu
+bool fast_linear_supported(int xdtype, int wdtype, int M, int N, int K);
+int linear_fast(const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M, int N, int K,
+                float alpha, int act, const float* residual, const int* row_mask, void* y, int ydtype,
+                cudaStream_t st);
+
+bool fast_attention_supported(int dtype, int d, int Tq);
+int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int B, int heads, int d, int Tq,
+                   int c_stride, int ctx_base, const int* ctx_dyn, int causal, const int* key_mask, int mask_len,
+                   void* out, float* scratch, cudaStream_t st);
+bool fast_conv_supported(int Cin, int Cout, int ksize);
+int dac_conv1d_fast(const float* x, int B, int Cin, int T, const float* w, const float* bias, int Cout, int ksize,
+                    int dilation, const float* snake_alpha, const float* residual, int tanh_out, float* y,
+                    cudaStream_t st);
+
+}  // namespace ptts

@@ -1,0 +1,127 @@
+"""DAC (Descript Audio Codec) decode on the CUDA path: codes -> waveform.
+
+Host side of /root/reference/parler_tts/dac_wrapper/modeling_dac.py:98-134 (`DACModel.decode` =
+`quantizer.from_codes` + `model.decode`, arithmetic in the un-vendored descript-audio-codec) and of the batched /
+ragged dispatch in /root/reference/parler_tts/modeling_parler_tts.py:2650-2680.  Weight-norm is folded once at load
+(w = g * v / ||v||) and every codebook is pre-multiplied with its out_proj into a [codebook_size][latent] table; all
+per-sample arithmetic runs in libparler_b200.so (ptts_dac_*).
+"""
+import math
+
+import torch
+
+from . import cabi
+
+
+def _fold(sd, prefix):
+    if prefix + ".weight" in sd:
+        w = sd[prefix + ".weight"].float()
+    else:
+        g, v = sd[prefix + ".weight_g"].float(), sd[prefix + ".weight_v"].float()
+        n = v.reshape(v.shape[0], -1).norm(dim=1).reshape(-1, *([1] * (v.dim() - 1)))
+        w = g * v / n
+    b = sd.get(prefix + ".bias")
+    return w.contiguous(), (None if b is None else b.float().contiguous())
+
+
+class DacDecoderEngine:
+    """Folded fp32 device weights + the launch sequence of the decoder stack."""
+
+    def __init__(self, sd, device, rates=(8, 8, 4, 2), impl=cabi.IMPL_FAST):
+        dev = torch.device(device)
+        sd = {k: v.detach().to(dev) for k, v in sd.items() if k.startswith(("quantizer.", "decoder."))}
+        self.device, self.impl, self.rates = dev, impl, tuple(rates)
+        self.hop = int(math.prod(rates))
+        n_q = 0
+        while f"quantizer.quantizers.{n_q}.codebook.weight" in sd:
+            n_q += 1
+        tabs = []
+        for i in range(n_q):
+            q = f"quantizer.quantizers.{i}"
+            w, b = _fold(sd, q + ".out_proj")  # [latent][dim][1]
+            t = sd[q + ".codebook.weight"].float() @ w[:, :, 0].t()
+            tabs.append(t if b is None else t + b)
+        self.tables = torch.stack(tabs).contiguous()  # [K][codebook_size][latent]
+        self.n_codebooks, self.codebook_size, self.latent = self.tables.shape
+        self.conv_in = _fold(sd, "decoder.model.0")
+        self.blocks = []
+        for bi, s in enumerate(self.rates):
+            p = f"decoder.model.{bi + 1}.block"
+            blk = dict(stride=s, alpha=sd[p + ".0.alpha"].float().reshape(-1).contiguous(), convt=_fold(sd, p + ".1"),
+                       res=[])
+            for ri, dil in enumerate((1, 3, 9)):
+                r = f"{p}.{ri + 2}.block"
+                blk["res"].append(dict(dil=dil, a1=sd[r + ".0.alpha"].float().reshape(-1).contiguous(),
+                                       c1=_fold(sd, r + ".1"), a2=sd[r + ".2.alpha"].float().reshape(-1).contiguous(),
+                                       c2=_fold(sd, r + ".3")))
+            self.blocks.append(blk)
+        n = len(self.rates)
+        self.alpha_out = sd[f"decoder.model.{n + 1}.alpha"].float().reshape(-1).contiguous()
+        self.conv_out = _fold(sd, f"decoder.model.{n + 2}")
+
+    # ---- single launches -------------------------------------------------------------------------------------
+    def _conv(self, x, wb, dil=1, alpha=None, residual=None, tanh=False):
+        w, b = wb
+        B, Cin, T = x.shape
+        Cout, _, k = w.shape
+        y = torch.empty(B, Cout, T, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_conv1d", cabi.ptr(x), B, Cin, T, cabi.ptr(w), cabi.ptr(b), Cout, k, dil, cabi.ptr(alpha),
+                  cabi.ptr(residual), int(tanh), cabi.ptr(y), self.impl, cabi.stream_ptr())
+        return y
+
+    def _convt(self, x, wb, stride, alpha):
+        w, b = wb  # [Cin][Cout][2*stride]
+        B, Cin, T = x.shape
+        Cout = w.shape[1]
+        y = torch.empty(B, Cout, T * stride, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_convtr1d", cabi.ptr(x), B, Cin, T, cabi.ptr(w), cabi.ptr(b), Cout, stride, cabi.ptr(alpha),
+                  cabi.ptr(y), self.impl, cabi.stream_ptr())
+        return y
+
+    def dequant(self, codes):
+        """codes (B, K, F) int64 -> z (B, latent, F) fp32  (quantizer.from_codes)."""
+        codes = codes.to(self.device, torch.int64).contiguous()
+        B, K, F = codes.shape
+        z = torch.empty(B, self.latent, F, device=self.device, dtype=torch.float32)
+        cabi.call("ptts_dac_dequant", cabi.ptr(codes), B, K, F, K * F, F, cabi.ptr(self.tables), None,
+                  self.codebook_size, self.latent, cabi.ptr(z), cabi.stream_ptr())
+        return z
+
+    def decode_latents(self, z):
+        x = self._conv(z, self.conv_in)
+        for blk in self.blocks:
+            x = self._convt(x, blk["convt"], blk["stride"], blk["alpha"])
+            for r in blk["res"]:
+                y = self._conv(x, r["c1"], dil=r["dil"], alpha=r["a1"])
+                x = self._conv(y, r["c2"], alpha=r["a2"], residual=x)
+        return self._conv(x, self.conv_out, alpha=self.alpha_out, tanh=True)  # (B, 1, hop*F)
+
+    def decode(self, codes, max_frames_per_call=16 * 1024):
+        """codes (B, K, F) -> audio (B, 1, hop*F); the batch is chunked to bound activation memory."""
+        B, K, F = codes.shape
+        if F == 0:
+            return torch.zeros(B, 1, 0, device=self.device)
+        per = max(1, max_frames_per_call // F)
+        outs = [self.decode_latents(self.dequant(codes[i : i + per])) for i in range(0, B, per)]
+        return torch.cat(outs, dim=0) if len(outs) > 1 else outs[0]
+
+    def decode_generated(self, codes, bos, pad, eos):
+        """modeling_parler_tts.py:2650-2680: batched decode when no special id survived the de-delay, else per sample
+        with invalid frames dropped (ptts_filter_frames) and zero right-padding.  Returns (B, T) fp32."""
+        codes = codes.to(self.device, torch.int64).contiguous()
+        B, K, F = codes.shape
+        special = bool(((codes == bos) | (codes == pad) | (codes == eos)).any().item())
+        if not special:
+            return self.decode(codes).squeeze(1)
+        packed = torch.empty_like(codes)
+        counts = torch.zeros(B, device=self.device, dtype=torch.int32)
+        cabi.call("ptts_filter_frames", cabi.ptr(codes), B, K, F, self.codebook_size, cabi.ptr(packed),
+                  cabi.ptr(counts), cabi.stream_ptr())
+        counts = counts.cpu().tolist()
+        outs = []
+        for b in range(B):
+            if counts[b] > 0:
+                outs.append(self.decode(packed[b : b + 1, :, : counts[b]].contiguous())[0, 0])
+            else:
+                outs.append(torch.zeros(1, device=self.device))
+        return torch.nn.utils.rnn.pad_sequence(outs, batch_first=True, padding_value=0.0)

@@ -1,0 +1,697 @@
+"""Public model API with the reference's names, arguments and checkpoint layout, driving the sm_100a CUDA path.
+
+Mirrors /root/reference/parler_tts/modeling_parler_tts.py:
+  build_delay_pattern_mask 77-139, apply_delay_pattern_mask 68-74, ParlerTTSForCausalLM 1062-1552,
+  ParlerTTSForConditionalGeneration 1560-2686, and /root/reference/parler_tts/dac_wrapper/modeling_dac.py (DACModel).
+Modules here only HOLD parameters under the reference's state-dict keys; no torch arithmetic runs on the hot path
+(the T5 text encoder - a third-party transformers module that runs once per call - is the exception).
+"""
+import copy
+import json
+import math
+import os
+from types import SimpleNamespace
+
+import torch
+import torch.nn as nn
+
+from . import cabi
+from .configuration import DACConfig, ParlerTTSConfig, ParlerTTSDecoderConfig
+from .dac import DacDecoderEngine
+from .engine import DecoderDims, DecoderEngine, DecoderWeights, GenState
+
+
+# --------------------------------------------------------------------------------------------- helpers
+def _cuda_device(t=None):
+    if not torch.cuda.is_available():
+        raise cabi.ParlerB200Error("parler_tts_b200 needs a CUDA device (sm_100a); there is no CPU fallback")
+    if t is not None and t.is_cuda:
+        return t.device
+    return torch.device("cuda", torch.cuda.current_device())
+
+
+def build_delay_pattern_mask(input_ids, bos_token_id, pad_token_id, max_length, num_codebooks):
+    """Same contract as the reference function (modeling_parler_tts.py:77-139): returns
+    (input_ids[:, :first_start], pattern_mask (B*K, max_length)); computed by ptts_build_delay_mask on the GPU."""
+    dev = _cuda_device(input_ids)
+    ids = input_ids.reshape(-1, input_ids.shape[-1]).to(dev, torch.int64).contiguous()
+    rows, T0 = ids.shape
+    B = rows // num_codebooks
+    mask = torch.empty(rows, max_length, device=dev, dtype=torch.int64)
+    first = torch.zeros(1, device=dev, dtype=torch.int32)
+    with torch.cuda.device(dev):
+        cabi.call("ptts_build_delay_mask", cabi.ptr(ids), B, num_codebooks, T0, max_length, int(bos_token_id),
+                  int(pad_token_id), cabi.ptr(mask), cabi.ptr(first), cabi.stream_ptr())
+    if max_length < 2 * num_codebooks - 1:
+        out_ids = ids
+    else:
+        out_ids = mask[:, : int(first.item())]
+    return out_ids.to(input_ids.device), mask.to(input_ids.device)
+
+
+def apply_delay_pattern_mask(input_ids, decoder_pad_token_mask):
+    """modeling_parler_tts.py:68-74 via ptts_apply_delay_mask."""
+    dev = _cuda_device(input_ids)
+    shape = input_ids.shape
+    ids = input_ids.reshape(-1, shape[-1]).to(dev, torch.int64).contiguous()
+    mask = decoder_pad_token_mask.reshape(-1, decoder_pad_token_mask.shape[-1]).to(dev, torch.int64).contiguous()
+    out = torch.empty_like(ids)
+    with torch.cuda.device(dev):
+        cabi.call("ptts_apply_delay_mask", cabi.ptr(ids), ids.shape[1], cabi.ptr(mask), mask.shape[1], ids.shape[0],
+                  ids.shape[1], cabi.ptr(out), out.shape[1], cabi.stream_ptr())
+    return out.reshape(shape).to(input_ids.device)
+
+
+class _Node(nn.Module):
+    """Anonymous container so that parameters can live under arbitrary dotted checkpoint keys."""
+
+
+def _add_param(root, dotted, tensor):
+    parts = dotted.split(".")
+    mod = root
+    for p in parts[:-1]:
+        if p not in mod._modules:
+            mod.add_module(p, _Node())
+        mod = mod._modules[p]
+    mod.register_parameter(parts[-1], nn.Parameter(tensor, requires_grad=False))
+
+
+def sinusoidal_table(num_positions, dim):
+    """Position table of the checkpoint (modeling_parler_tts.py:200-213): [cos | sin] halves."""
+    half = dim // 2
+    freq = torch.exp(torch.arange(half, dtype=torch.int64).float() * -(math.log(10000) / (half - 1)))
+    ang = torch.arange(num_positions, dtype=torch.int64).float().unsqueeze(1) * freq.unsqueeze(0)
+    tab = torch.cat([torch.cos(ang), torch.sin(ang)], dim=1).view(num_positions, -1)
+    if dim % 2 == 1:
+        tab = torch.cat([tab, torch.zeros(num_positions, 1)], dim=1)
+    return tab
+
+
+def _load_state_file(path):
+    st = os.path.join(path, "model.safetensors")
+    if os.path.exists(st):
+        from safetensors.torch import load_file
+
+        return load_file(st)
+    idx = os.path.join(path, "model.safetensors.index.json")
+    if os.path.exists(idx):
+        from safetensors.torch import load_file
+
+        out = {}
+        for shard in sorted(set(json.load(open(idx))["weight_map"].values())):
+            out.update(load_file(os.path.join(path, shard)))
+        return out
+    pt = os.path.join(path, "pytorch_model.bin")
+    if os.path.exists(pt):
+        return torch.load(pt, map_location="cpu", weights_only=True)
+    raise FileNotFoundError(f"no model.safetensors / pytorch_model.bin under {path}")
+
+
+def _save_state_file(sd, path):
+    from safetensors.torch import save_file
+
+    os.makedirs(path, exist_ok=True)
+    out, seen = {}, {}
+    for k, v in sd.items():  # tied tensors (T5 `shared` / `encoder.embed_tokens`) are stored once, like HF does
+        key = (v.data_ptr(), tuple(v.shape))
+        if key in seen and v.numel() > 0:
+            continue
+        seen[key] = k
+        out[k] = v.detach().cpu().contiguous().clone()
+    save_file(out, os.path.join(path, "model.safetensors"), metadata={"format": "pt"})
+
+
+# --------------------------------------------------------------------------------------------- DAC wrapper
+class DACModel(nn.Module):
+    """Holder of the descript `DAC.state_dict()` under `model.*` (dac_wrapper/modeling_dac.py:13-23) + CUDA decode."""
+
+    config_class = DACConfig
+
+    def __init__(self, config: DACConfig, state_dict=None, decoder_dim=1536, rates=(8, 8, 4, 2), codebook_dim=8):
+        super().__init__()
+        self.config = config
+        self.rates = tuple(rates)
+        self.model = _Node()
+        if state_dict is None:
+            state_dict = _random_dac_state(config, decoder_dim, self.rates, codebook_dim)
+        for k, v in state_dict.items():
+            _add_param(self.model, k, v.clone())
+        self._engine = None
+
+    def engine(self, impl=cabi.IMPL_FAST):
+        dev = next(self.parameters()).device
+        if self._engine is None or self._engine.device != dev or self._engine.impl != impl:
+            self._engine = DacDecoderEngine(dict(self.model.state_dict()), dev, self.rates, impl)
+        return self._engine
+
+    def decode(self, audio_codes, audio_scales=None, padding_mask=None, return_dict=None):
+        """audio_codes (1, B, K, F) -> audio_values (B, 1, T)   (dac_wrapper/modeling_dac.py:98-134)."""
+        if len(audio_codes) != 1:
+            raise ValueError(f"Expected one frame, got {len(audio_codes)}")
+        audio = self.engine().decode(audio_codes[0])
+        if return_dict is False:
+            return (audio,)
+        return SimpleNamespace(audio_values=audio)
+
+    def encode(self, *args, **kwargs):
+        raise NotImplementedError("DAC encode (audio-prompt continuation) is outside the generation hot path "
+                                  "(SURVEY.md section 8f rank 3)")
+
+    def forward(self, tensor):
+        raise ValueError("`DACModel.forward` not implemented yet")
+
+
+def _random_dac_state(config, decoder_dim, rates, codebook_dim, seed=0):
+    g = torch.Generator().manual_seed(seed)
+    sd = {}
+
+    def conv(prefix, cout, cin, k, transposed=False):
+        shape = (cin, cout, k) if transposed else (cout, cin, k)
+        v = torch.randn(*shape, generator=g) / math.sqrt((cout if transposed else cin) * k)
+        sd[prefix + ".weight_v"] = v
+        sd[prefix + ".weight_g"] = v.reshape(shape[0], -1).norm(dim=1).reshape(-1, 1, 1)
+        sd[prefix + ".bias"] = torch.zeros(cout)
+
+    for i in range(config.num_codebooks):
+        q = f"quantizer.quantizers.{i}"
+        sd[q + ".codebook.weight"] = torch.randn(config.codebook_size, codebook_dim, generator=g)
+        conv(q + ".out_proj", config.latent_dim, codebook_dim, 1)
+    ch = decoder_dim
+    conv("decoder.model.0", ch, config.latent_dim, 7)
+    for bi, s in enumerate(rates):
+        p = f"decoder.model.{bi + 1}.block"
+        cin, cout = ch // 2 ** bi, ch // 2 ** (bi + 1)
+        sd[p + ".0.alpha"] = torch.ones(1, cin, 1)
+        conv(p + ".1", cout, cin, 2 * s, transposed=True)
+        for ri in range(3):
+            r = f"{p}.{ri + 2}.block"
+            sd[r + ".0.alpha"] = torch.ones(1, cout, 1)
+            conv(r + ".1", cout, cout, 7)
+            sd[r + ".2.alpha"] = torch.ones(1, cout, 1)
+            conv(r + ".3", cout, cout, 1)
+    n = len(rates)
+    sd[f"decoder.model.{n + 1}.alpha"] = torch.ones(1, ch // 2 ** n, 1)
+    conv(f"decoder.model.{n + 2}", 1, ch // 2 ** n, 7)
+    return sd
+
+
+# --------------------------------------------------------------------------------------------- generation core
+def _default_generation_config(dec_cfg):
+    from transformers.generation.configuration_utils import GenerationConfig
+
+    return GenerationConfig(bos_token_id=dec_cfg.bos_token_id, pad_token_id=dec_cfg.pad_token_id,
+                            eos_token_id=dec_cfg.eos_token_id, decoder_start_token_id=dec_cfg.bos_token_id)
+
+
+def _resolve_generation(self_cfg, generation_config, kwargs, input_len_fn):
+    """Steps 1 and 6 of the reference generate (modeling_parler_tts.py:2416-2422, 2499-2527)."""
+    gc = copy.deepcopy(generation_config if generation_config is not None else self_cfg)
+    model_kwargs = gc.update(**kwargs)
+    if gc.pad_token_id is None and gc.eos_token_id is not None:
+        eos = gc.eos_token_id
+        gc.pad_token_id = eos[0] if isinstance(eos, (list, tuple)) else eos
+    if (gc.num_beams or 1) != 1 or (getattr(gc, "num_beam_groups", 1) or 1) != 1:
+        raise ValueError(
+            "Got incompatible mode for generation, should be one of greedy or sampling. "
+            "Ensure that beam search is de-activated by setting `num_beams=1` and `num_beam_groups=1`.")
+    return gc, model_kwargs
+
+
+def _final_max_length(gc, kwargs, input_len):
+    has_default = kwargs.get("max_length") is None and gc.max_length is not None
+    if gc.max_new_tokens is not None:
+        gc.max_length = gc.max_new_tokens + input_len
+    if gc.min_length is not None and gc.min_length > gc.max_length:
+        raise ValueError(f"Unfeasible length constraints: the minimum length ({gc.min_length}) is larger than"
+                         f" the maximum length ({gc.max_length})")
+    del has_default
+    return int(gc.max_length)
+
+
+def _draw_seed():
+    # follows torch's global generator so that `set_seed(s); model.generate(do_sample=True)` is reproducible
+    return int(torch.randint(0, 2 ** 62, (1,)).item())
+
+
+def _special_processors(logits_processor):
+    """Splits a user LogitsProcessorList into (suppress_from handled in-kernel, remaining python callables)."""
+    suppress, rest = -1, []
+    for p in (logits_processor or []):
+        if isinstance(p, SuppressTokensAtOrAbove):
+            suppress = p.first_banned if suppress < 0 else min(suppress, p.first_banned)
+        else:
+            rest.append(p)
+    return suppress, rest
+
+
+class SuppressTokensAtOrAbove:
+    """A logits processor the fused epilogue understands natively: scores[:, first_banned:] = -inf.
+    (Keeps random-init models away from EOS/BOS/unused ids)  Also callable like any HF
+    processor."""
+
+    def __init__(self, first_banned):
+        self.first_banned = int(first_banned)
+
+    def __call__(self, input_ids, scores):
+        scores = scores.clone()
+        scores[:, self.first_banned:] = -float("inf")
+        return scores
+
+
+def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hidden, prompt_mask, decoder_input_ids,
+                    gc, kwargs, logits_processor, stopping_criteria, streamer, impl, use_graph, seed, row_offset):
+    """The loop of transformers greedy_search / sample on the CUDA path.  Returns (codes (Bu,K,F), sequences, state)."""
+    w = decoder.packed_weights()
+    d = w.dims
+    K = d.num_codebooks
+    dev = w.device
+    cfg = gc.guidance_scale is not None and gc.guidance_scale > 1
+    B = enc.shape[0] if enc is not None else (prompt_ids if prompt_ids is not None else prompt_hidden).shape[0]
+    Bu = B // 2 if cfg else B
+    bos = gc.decoder_start_token_id if gc.decoder_start_token_id is not None else gc.bos_token_id
+    start = torch.full((Bu * K, 1), bos, dtype=torch.int64, device=dev)
+    if decoder_input_ids is not None:
+        user = decoder_input_ids.to(dev, torch.int64).reshape(Bu * K, -1)
+        if bool((user[..., 0] != bos).all().item()):  # modeling_parler_tts.py:2185-2186
+            user = torch.cat([start, user], dim=-1)
+        start = user
+    T0 = start.shape[1]
+    max_length = _final_max_length(gc, kwargs, T0)
+    if max_length < 2 * K - 1:
+        raise ValueError(f"max_length={max_length} is shorter than 2*num_codebooks-1: the delay pattern cannot be "
+                         "applied (modeling_parler_tts.py:105-106) and no frame would survive the de-delay")
+    if T0 >= max_length:
+        raise ValueError(f"Input length of decoder_input_ids is {T0}, but `max_length` is set to {max_length}")
+    P = 0 if (prompt_ids is None and prompt_hidden is None) else (prompt_ids if prompt_ids is not None
+                                                                    else prompt_hidden).shape[1]
+    if P + max_length > d.max_position_embeddings:
+        raise ValueError(f"prompt length {P} + max_length {max_length} exceeds max_position_embeddings "
+                         f"{d.max_position_embeddings}")
+    suppress, py_procs = _special_processors(logits_processor)
+    if cfg and py_procs:
+        raise NotImplementedError("python logits_processors together with guidance_scale > 1 are not supported")
+    do_sample = bool(gc.do_sample)
+    top_k = int(gc.top_k) if (do_sample and gc.top_k is not None) else 0
+    temperature = float(gc.temperature) if (do_sample and gc.temperature is not None) else 1.0
+    S = 0 if enc is None else enc.shape[1]
+    gscale = float(gc.guidance_scale) if cfg else 1.0
+    key = (id(w), B, S, P, T0, max_length, impl, do_sample, top_k, temperature, suppress, gscale, row_offset,
+           enc_mask is not None, prompt_mask is not None)
+    cached = getattr(decoder, "_state_cache", None)
+    if cached is not None and cached[0] == key:  # same shapes: reuse buffers and the captured CUDA graph
+        st = cached[1]
+        if enc_mask is not None:
+            st.enc_mask.copy_(enc_mask.to(dev, torch.int32))
+        if prompt_mask is not None:
+            st.prompt_mask.copy_(prompt_mask.to(dev, torch.int32))
+    else:
+        decoder._state_cache = None
+        st = GenState(w, B, S, P, T0, max_length, impl=impl, do_sample=do_sample, top_k=top_k,
+                      temperature=temperature, suppress_from=suppress, guidance_scale=gscale, seed=seed,
+                      row_offset=row_offset * K,
+                      enc_mask=None if enc_mask is None else enc_mask.to(dev, torch.int32).clone(),
+                      prompt_mask=None if prompt_mask is None else prompt_mask.to(dev, torch.int32).clone())
+        decoder._state_cache = (key, st)
+    eng = DecoderEngine(w)
+    st.reset(start, seed)
+    if streamer is not None:
+        streamer.put(start.cpu())
+    if enc is not None:
+        eng.cross_kv(st, enc)
+    slow = bool(py_procs) or streamer is not None or bool(stopping_criteria)
+    if not slow:
+        eng.prefill(st, prompt_table, prompt_ids, prompt_hidden)
+        ctrl = eng.run_loop(st, use_graph=use_graph)
+    else:
+        ctrl = _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, py_procs, stopping_criteria, streamer)
+    Lout = ctrl["stop_len"] if ctrl["done"] else ctrl["len"]
+    seq = st.ids[:, :Lout]
+    if T0 == 1:
+        codes = torch.empty(Bu, K, Lout - K, device=dev, dtype=torch.int64)
+        cabi.call("ptts_dedelay", cabi.ptr(st.ids), st.max_len, cabi.ptr(st.mask), st.max_len, Bu, K, Lout,
+                  cabi.ptr(codes), cabi.stream_ptr())
+    else:  # audio-prompt geometry: the general boolean-mask form of modeling_parler_tts.py:2637-2645
+        applied = apply_delay_pattern_mask(seq, st.mask)
+        _, m2 = build_delay_pattern_mask(start, bos, gc.pad_token_id, Lout, K)
+        keep = (m2 != bos) & (m2 != gc.pad_token_id)
+        codes = applied[keep].reshape(Bu, K, -1)
+    return codes, seq, st
+
+
+def _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, py_procs, stopping_criteria, streamer):
+    """Step-at-a-time variant used when python logits processors, stopping criteria or a streamer are supplied:
+    forward (kernels) -> python processors on the logits tensor -> fused epilogue kernel."""
+    first = True
+    while True:
+        if first:
+            eng.prefill(st, prompt_table, prompt_ids, prompt_hidden, run_epilogue=False)
+            first = False
+        else:
+            eng.step(st, run_epilogue=False)
+        c = st.read_ctrl()
+        hist = st.ids[:, : c["len"]]
+        for p in py_procs:
+            st.logits.copy_(p(hist, st.logits))
+        eng.epilogue(st)
+        c = st.read_ctrl()
+        hist = st.ids[:, : c["len"]]
+        if streamer is not None:
+            streamer.put(hist[:, -1].cpu())
+        stop = bool(c["done"])
+        for crit in (stopping_criteria or []):
+            r = crit(hist, st.logits)
+            stop = stop or bool(r.all() if hasattr(r, "all") else r)
+        if stop:
+            if streamer is not None:
+                streamer.end()
+            c["done"], c["stop_len"] = 1, c["len"]
+            return c
+
+
+# --------------------------------------------------------------------------------------------- decoder-only model
+class ParlerTTSForCausalLM(nn.Module):
+    """Decoder + 9 lm_heads (modeling_parler_tts.py:1062-1552).  State-dict keys: `model.decoder.*`, `lm_heads.{k}.*`."""
+
+    config_class = ParlerTTSDecoderConfig
+
+    def __init__(self, config: ParlerTTSDecoderConfig, state_dict=None, seed=0):
+        super().__init__()
+        self.config = config
+        self.num_codebooks = config.num_codebooks
+        self.generation_config = _default_generation_config(config)
+        dims = DecoderDims.from_config(config)
+        if state_dict is None:
+            state_dict = _random_decoder_state(dims, config.initializer_factor, seed)
+        self.model, self.lm_heads = _Node(), _Node()
+        for k, v in state_dict.items():
+            if k.startswith("model."):
+                _add_param(self.model, k[len("model."):], v.clone())
+            elif k.startswith("lm_heads."):
+                _add_param(self.lm_heads, k[len("lm_heads."):], v.clone())
+        self._packed = None
+        self._state_cache = None
+        self.impl = cabi.IMPL_FAST
+        self.use_cuda_graph = True
+
+    # ---- plumbing
+    @property
+    def device(self):
+        return next(self.parameters()).device
+
+    @property
+    def dtype(self):
+        return self.lm_heads._modules["0"].weight.dtype
+
+    def packed_weights(self):
+        dev, dt = self.device, self.dtype
+        if dev.type != "cuda":
+            raise cabi.ParlerB200Error("move the model to a CUDA device first: there is no CPU path")
+        if self._packed is None or self._packed.device != dev or self._packed.dtype != dt:
+            sd = {k: v for k, v in self.state_dict().items()}
+            self._packed = DecoderWeights(sd, DecoderDims.from_config(self.config), dev, dt)
+        return self._packed
+
+    def reset_engine(self):
+        self._packed, self._state_cache = None, None
+
+    def build_delay_pattern_mask(self, input_ids, bos_token_id, pad_token_id, max_length=None):
+        max_length = max_length if max_length is not None else self.generation_config.max_length
+        return build_delay_pattern_mask(input_ids, bos_token_id, pad_token_id, max_length, self.num_codebooks)
+
+    @staticmethod
+    def apply_delay_pattern_mask(input_ids, decoder_pad_token_mask):
+        return apply_delay_pattern_mask(input_ids, decoder_pad_token_mask)
+
+    # ---- forward: teacher-forced logits of every position (no cache returned)
+    @torch.no_grad()
+    def forward(self, input_ids=None, attention_mask=None, encoder_hidden_states=None, encoder_attention_mask=None,
+                prompt_hidden_states=None, prompt_attention_mask=None, past_key_values=None, **unused):
+        """logits (B*K, P+T, vocab) as ParlerTTSForCausalLM.forward without labels (modeling_parler_tts.py:1096-1185).
+        Only the cache-less call is provided; generation uses the static-cache kernels directly."""
+        if past_key_values is not None:
+            raise NotImplementedError("forward() with past_key_values: use generate(), which owns the static cache")
+        if attention_mask is not None:
+            raise NotImplementedError("decoder attention_mask is not supported; pass prompt_attention_mask")
+        w = self.packed_weights()
+        K = self.num_codebooks
+        ids = input_ids.to(w.device, torch.int64).reshape(-1, input_ids.shape[-1]).contiguous()
+        B, T = ids.shape[0] // K, ids.shape[1]
+        P = 0 if prompt_hidden_states is None else prompt_hidden_states.shape[1]
+        S = 0 if encoder_hidden_states is None else encoder_hidden_states.shape[1]
+        st = GenState(w, B, S, P, T, max(T + 1, 2), impl=self.impl, enc_mask=encoder_attention_mask,
+                      prompt_mask=prompt_attention_mask)
+        st.mask.fill_(-1)
+        st.ids[:, :T] = ids
+        st.ctrl.copy_(torch.tensor([T, 0, 0, B * K, 0, 0, 0, 0], dtype=torch.int32))
+        eng = DecoderEngine(w)
+        if S:
+            eng.cross_kv(st, encoder_hidden_states)
+        ph = None if prompt_hidden_states is None else prompt_hidden_states.to(w.device, torch.float32).contiguous()
+        logits = eng.prefill(st, prompt_hidden=ph, all_logits=True, run_epilogue=False)
+        return SimpleNamespace(logits=logits, past_key_values=None)
+
+    @torch.no_grad()
+    def generate(self, inputs=None, generation_config=None, logits_processor=None, stopping_criteria=None,
+                 synced_gpus=None, streamer=None, **kwargs):
+        """Decoder-only generation -> codes (B, K, F)   (modeling_parler_tts.py:1281-1552)."""
+        gc, mk = _resolve_generation(self.generation_config, generation_config, kwargs, None)
+        seed = mk.pop("seed", None)
+        enc = mk.pop("encoder_hidden_states", None)
+        enc_mask = mk.pop("encoder_attention_mask", None)
+        prm = mk.pop("prompt_hidden_states", None)
+        prm_mask = mk.pop("prompt_attention_mask", None)
+        dec_ids = inputs if inputs is not None else mk.pop("input_ids", None)
+        w = self.packed_weights()
+        if enc is None and prm is None and dec_ids is None:
+            raise ValueError("generate() needs encoder_hidden_states, prompt_hidden_states or input_ids")
+        cfg = gc.guidance_scale is not None and gc.guidance_scale > 1
+        if cfg:  # modeling_parler_tts.py:1214-1229: zero prompt for the unconditional half
+            if prm is not None:
+                prm = torch.cat([prm, torch.zeros_like(prm)], dim=0)
+            if prm_mask is not None:
+                prm_mask = torch.cat([prm_mask, torch.zeros_like(prm_mask)], dim=0)
+            # encoder_hidden_states / encoder_attention_mask must already hold both halves (as in the reference,
+            # where the composite model doubles them in _prepare_text_encoder_kwargs_for_generation)
+        if prm is not None:
+            prm = prm.to(w.device, torch.float32).contiguous()
+        if enc is None and prm is None:
+            B = dec_ids.shape[0] // self.num_codebooks
+            prm = torch.zeros(B, 0, self.config.hidden_size, device=w.device)
+        codes, seq, _ = _generate_codes(self, enc, enc_mask, None, None, prm, prm_mask, dec_ids, gc, kwargs,
+                                        logits_processor, stopping_criteria, streamer, self.impl, self.use_cuda_graph,
+                                        _draw_seed() if seed is None else seed, 0)
+        if gc.return_dict_in_generate:
+            return SimpleNamespace(sequences=codes)
+        return codes
+
+
+def _random_decoder_state(dims, std, seed):
+    """Random init as the reference's `_init_weights` (modeling_parler_tts.py:517-526): N(0, std), LayerNorm 1/0."""
+    g = torch.Generator().manual_seed(seed)
+    H, Fd, V, K = dims.hidden_size, dims.ffn_dim, dims.vocab_size, dims.num_codebooks
+    sd = {}
+    nrm = lambda *s: torch.randn(*s, generator=g) * std  # noqa: E731
+    for k in range(K):
+        sd[f"model.decoder.embed_tokens.{k}.weight"] = nrm(V + 1, H)
+    sd["model.decoder.embed_positions.weights"] = sinusoidal_table(dims.max_position_embeddings, H)
+    for i in range(dims.num_hidden_layers):
+        p = f"model.decoder.layers.{i}."
+        for att in ("self_attn", "encoder_attn"):
+            for proj in ("q_proj", "k_proj", "v_proj", "out_proj"):
+                sd[p + f"{att}.{proj}.weight"] = nrm(H, H)
+        for ln in ("self_attn_layer_norm", "encoder_attn_layer_norm", "final_layer_norm"):
+            sd[p + ln + ".weight"], sd[p + ln + ".bias"] = torch.ones(H), torch.zeros(H)
+        sd[p + "fc1.weight"], sd[p + "fc2.weight"] = nrm(Fd, H), nrm(H, Fd)
+    sd["model.decoder.layer_norm.weight"], sd["model.decoder.layer_norm.bias"] = torch.ones(H), torch.zeros(H)
+    for k in range(K):
+        sd[f"lm_heads.{k}.weight"] = nrm(V, H)
+    return sd
+
+
+# --------------------------------------------------------------------------------------------- composite model
+class ParlerTTSForConditionalGeneration(nn.Module):
+    """text encoder (T5) + DAC + decoder (modeling_parler_tts.py:1560-2686).  State-dict keys: `text_encoder.*`,
+    `audio_encoder.model.*`, `decoder.*`, `enc_to_dec_proj.{weight,bias}`, `embed_prompts.weight`."""
+
+    config_class = ParlerTTSConfig
+    main_input_name = "input_ids"
+
+    def __init__(self, config=None, text_encoder=None, audio_encoder=None, decoder=None, seed=0):
+        super().__init__()
+        if config is None and (text_encoder is None or audio_encoder is None or decoder is None):
+            raise ValueError("Either a configuration has to be provided, or all three of text encoder, audio encoder "
+                             "and Parler-TTS decoder.")
+        if config is None:
+            config = ParlerTTSConfig.from_sub_models_config(text_encoder.config, audio_encoder.config, decoder.config)
+        elif not isinstance(config, ParlerTTSConfig):
+            raise ValueError(f"Config: {config} has to be of type {ParlerTTSConfig}")
+        self.config = config
+        if text_encoder is None:
+            from transformers import AutoModelForTextEncoding
+
+            text_encoder = AutoModelForTextEncoding.from_config(config.text_encoder)
+        self.text_encoder = text_encoder.eval()
+        self.audio_encoder = audio_encoder if audio_encoder is not None else DACModel(config.audio_encoder)
+        self.decoder = decoder if decoder is not None else ParlerTTSForCausalLM(config.decoder, seed=seed)
+        g = torch.Generator().manual_seed(seed + 1)
+        std = config.decoder.initializer_factor
+        H, He = config.decoder.hidden_size, config.text_encoder.hidden_size
+        if He != H:
+            self.enc_to_dec_proj = _Node()
+            _add_param(self.enc_to_dec_proj, "weight", torch.randn(H, He, generator=g) * std)
+            _add_param(self.enc_to_dec_proj, "bias", torch.zeros(H))
+        self.embed_prompts = _Node()
+        _add_param(self.embed_prompts, "weight", torch.randn(config.vocab_size, H, generator=g) * std)
+        self.generation_config = _default_generation_config(config.decoder)
+        self._prompt_table = None
+
+    # ---- reference accessors
+    def get_audio_encoder(self):
+        return self.audio_encoder
+
+    def get_text_encoder(self):
+        return self.text_encoder
+
+    def get_encoder(self):
+        return self.text_encoder
+
+    def get_decoder(self):
+        return self.decoder
+
+    @property
+    def device(self):
+        return self.decoder.device
+
+    @property
+    def dtype(self):
+        return self.decoder.dtype
+
+    # ---- checkpoint I/O (config.json + generation_config.json + model.safetensors, reference key names)
+    @classmethod
+    def from_pretrained(cls, path, torch_dtype=None, **kwargs):
+        from transformers.generation.configuration_utils import GenerationConfig
+
+        config = ParlerTTSConfig.from_pretrained(path)
+        sd = _load_state_file(path)
+        dec_sd = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
+        dac_sd = {k[len("audio_encoder.model."):]: v for k, v in sd.items() if k.startswith("audio_encoder.model.")}
+        model = cls(config, decoder=ParlerTTSForCausalLM(config.decoder, state_dict=dec_sd),
+                    audio_encoder=DACModel(config.audio_encoder, state_dict=dac_sd))
+        rest = {k: v for k, v in sd.items() if not k.startswith(("decoder.", "audio_encoder."))}
+        missing, unexpected = model.load_state_dict(rest, strict=False)
+        missing = [k for k in missing if not k.startswith(("decoder.", "audio_encoder."))
+                   and not k.endswith("encoder.embed_tokens.weight")]  # tied to text_encoder.shared.weight
+        if missing or unexpected:
+            raise RuntimeError(f"checkpoint mismatch: missing {missing[:5]} unexpected {unexpected[:5]}")
+        if os.path.exists(os.path.join(path, "generation_config.json")):
+            model.generation_config = GenerationConfig.from_pretrained(path)
+        if torch_dtype is not None:
+            model = model.to(torch_dtype)
+        return model
+
+    def save_pretrained(self, path):
+        os.makedirs(path, exist_ok=True)
+        self.config.save_pretrained(path)
+        self.generation_config.save_pretrained(path)
+        _save_state_file(self.state_dict(), path)
+
+    def prompt_table(self):
+        t = self.embed_prompts.weight
+        if self._prompt_table is None or self._prompt_table.device != t.device:
+            self._prompt_table = t.detach().to(torch.float32).contiguous()
+        return self._prompt_table
+
+    # ---- pieces of generate
+    @torch.no_grad()
+    def encode_text(self, input_ids, attention_mask):
+        """T5 (third-party torch module, once per call) followed by enc_to_dec_proj + bias + attention-mask multiply on
+        the CUDA path (modeling_parler_tts.py:2010-2017, hoisted out of the per-step loop)."""
+        hs = self.text_encoder(input_ids=input_ids, attention_mask=attention_mask, return_dict=True).last_hidden_state
+        return hs
+
+    def project_encoder(self, hs, attention_mask):
+        w = self.decoder.packed_weights()
+        B, S, He = hs.shape
+        H = self.config.decoder.hidden_size
+        dt = w.dtype
+        rm = None if attention_mask is None else attention_mask.to(w.device, torch.int32).reshape(-1).contiguous()
+        if hasattr(self, "enc_to_dec_proj"):
+            x = hs.to(w.device, dt).contiguous()
+            wt = self.enc_to_dec_proj.weight.detach().to(w.device, dt).contiguous()
+            bias = self.enc_to_dec_proj.bias.detach().to(w.device, torch.float32).contiguous()
+            y = torch.empty(B, S, H, device=w.device, dtype=dt)
+            cabi.call("ptts_linear", cabi.ptr(x), cabi.dtype_enum(dt), cabi.ptr(wt), cabi.dtype_enum(dt),
+                      cabi.ptr(bias), B * S, H, He, 1.0, 0, None, cabi.ptr(rm), cabi.ptr(y), cabi.dtype_enum(dt),
+                      self.decoder.impl, cabi.stream_ptr())
+            return y
+        y = hs.to(w.device, dt)
+        return y if attention_mask is None else y * attention_mask[..., None].to(w.device, dt)
+
+    @torch.no_grad()
+    def generate(self, inputs=None, generation_config=None, logits_processor=None, stopping_criteria=None,
+                 synced_gpus=None, streamer=None, **kwargs):
+        """generate(input_ids=description ids, prompt_input_ids=transcript ids, ...) -> audio (B, T)
+        (modeling_parler_tts.py:2342-2686)."""
+        gc, mk = _resolve_generation(self.generation_config, generation_config, kwargs, None)
+        seed = mk.pop("seed", None)
+        row_offset = mk.pop("row_offset", 0)
+        return_codes = mk.pop("return_codes", False)
+        input_ids = inputs if inputs is not None else mk.pop("input_ids", None)
+        if "input_values" in mk:
+            raise NotImplementedError("audio-prompt continuation needs the DAC encoder (SURVEY.md 8f rank 3)")
+        dev = self.device
+        attention_mask = mk.pop("attention_mask", None)
+        enc_out = mk.pop("encoder_outputs", None)
+        if enc_out is not None:
+            hs = enc_out[0] if isinstance(enc_out, (tuple, list)) else enc_out.last_hidden_state
+        else:
+            if input_ids is None:
+                raise ValueError("generate() needs input_ids (description token ids) or encoder_outputs")
+            input_ids = input_ids.to(dev)
+            if attention_mask is None:  # _prepare_attention_mask_for_generation: mask only if pad is distinguishable
+                pad, eos = gc.pad_token_id, gc.eos_token_id
+                if pad is not None and pad != eos and bool((input_ids == pad).any()):
+                    attention_mask = (input_ids != pad).long()
+                else:
+                    attention_mask = torch.ones_like(input_ids)
+            attention_mask = attention_mask.to(dev)
+            hs = self.encode_text(input_ids, attention_mask)
+        B = hs.shape[0]
+        nret = gc.num_return_sequences or 1
+        if not gc.do_sample and nret > 1:
+            raise ValueError(f"num_return_sequences has to be 1 when doing greedy search, but is {nret}.")
+        cfg = gc.guidance_scale is not None and gc.guidance_scale > 1
+        prompt_ids = mk.pop("prompt_input_ids", None)
+        prompt_hidden = mk.pop("prompt_hidden_states", None)
+        prompt_mask = mk.pop("prompt_attention_mask", None)
+        dec_ids = mk.pop("decoder_input_ids", None)
+        if cfg:  # null conditioning for the second half (modeling_parler_tts.py:2231-2237, 2115-2118)
+            hs = torch.cat([hs, torch.zeros_like(hs)], dim=0)
+            if attention_mask is not None:
+                attention_mask = torch.cat([attention_mask, torch.zeros_like(attention_mask)], dim=0)
+            prompt_ids = None if prompt_ids is None else prompt_ids.repeat(2, 1)
+            prompt_hidden = None if prompt_hidden is None else prompt_hidden.repeat(2, 1, 1)
+            prompt_mask = None if prompt_mask is None else prompt_mask.repeat(2, 1)
+        if nret > 1:
+            rep = lambda t: None if t is None else t.repeat_interleave(nret, dim=0)  # noqa: E731
+            hs, attention_mask, prompt_ids, prompt_hidden, prompt_mask, dec_ids = map(
+                rep, (hs, attention_mask, prompt_ids, prompt_hidden, prompt_mask, dec_ids))
+        enc = self.project_encoder(hs, attention_mask)
+        prompt_table = None
+        if prompt_hidden is not None:
+            prompt_hidden, prompt_ids = prompt_hidden.to(dev, torch.float32).contiguous(), None
+        elif prompt_ids is not None:
+            prompt_ids = prompt_ids.to(dev, torch.int64).contiguous()
+            prompt_table = self.prompt_table()
+        codes, seq, st = _generate_codes(self.decoder, enc, attention_mask, prompt_table, prompt_ids, prompt_hidden,
+                                         prompt_mask, dec_ids, gc, kwargs, logits_processor, stopping_criteria,
+                                         streamer, self.decoder.impl, self.decoder.use_cuda_graph,
+                                         _draw_seed() if seed is None else seed, row_offset)
+        if return_codes:
+            return codes
+        audio = self.audio_encoder.engine(self.decoder.impl).decode_generated(
+            codes, gc.bos_token_id if gc.bos_token_id is not None else self.config.decoder.bos_token_id,
+            gc.pad_token_id, gc.eos_token_id if not isinstance(gc.eos_token_id, (list, tuple)) else gc.eos_token_id[0])
+        if gc.return_dict_in_generate:
+            return SimpleNamespace(sequences=audio, audio_codes=codes)
+        return audio

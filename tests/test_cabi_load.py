@@ -1,0 +1,58 @@
+"""CPU: the C-ABI shared library loads and exports every symbol that include/parler_b200.h declares."""
+import os
+import re
+
+import pytest
+
+from parler_tts_b200 import cabi
+
+ROOT = os.path.dirname(os.path.dirname(os.path.abspath(__file__)))
+
+
+def _declared():
+    text = open(os.path.join(ROOT, "include", "parler_b200.h")).read()
+    return sorted(set(re.findall(r"PTTS_API\s+[\w\s\*]+?\b(ptts_\w+)\s*\(", text)))
+
+
+def test_header_and_binding_agree():
+    names = _declared()
+    assert len(names) >= 18
+    assert sorted(cabi.PROTOTYPES) == names
+
+
+def test_library_exports_every_declared_symbol():
+    if not os.path.exists(cabi.LIB_PATH):
+        pytest.fail(f"{cabi.LIB_PATH} missing: run __graft_entry__.build()")
+    lib = cabi.load()
+    for name in _declared():
+        assert hasattr(lib, name), name
+    assert lib.ptts_abi_version() == cabi.ABI_VERSION
+    assert lib.ptts_last_error_string() is not None
+
+
+def test_struct_layout_matches_header():
+    import ctypes as C
+
+    assert C.sizeof(cabi.PttsCtrl) == 32
+    assert C.sizeof(cabi.PttsLayer) == 13 * 8
+    assert cabi.PttsModel.embed.offset == 56 and C.sizeof(cabi.PttsModel) == 56 + 6 * 8
+    assert cabi.PttsState.seed.offset == 48 and cabi.PttsState.ctrl.offset == 64
+    assert C.sizeof(cabi.PttsState) == 64 + 15 * 8
+
+
+def test_argument_errors_are_reported_without_a_gpu():
+    lib = cabi.load()
+    rc = lib.ptts_build_delay_mask(None, 1, 9, 1, 20, 1025, 1024, None, None, None)
+    assert rc == 1
+    assert b"null" in lib.ptts_last_error_string()
+
+
+def test_no_cpu_fallback_in_public_api():
+    import torch
+
+    import parler_tts_b200 as p
+
+    if torch.cuda.is_available():
+        pytest.skip("only meaningful on a CPU-only box")
+    with pytest.raises(cabi.ParlerB200Error):
+        p.build_delay_pattern_mask(torch.full((9, 1), 1025), 1025, 1024, 20, 9)

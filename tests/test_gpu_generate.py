@@ -1,0 +1,145 @@
+"""GPU parity of the public generate() API and of the DAC decoder against the oracle / reference fixtures."""
+import os
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+from oracle import dac_oracle, decoder_oracle, generate_oracle  # noqa: E402
+from oracle.gen_golden import TINY  # noqa: E402
+
+import parler_tts_b200 as ptts  # noqa: E402
+from parler_tts_b200 import cabi  # noqa: E402
+from parler_tts_b200.dac import DacDecoderEngine  # noqa: E402
+
+DEV = "cuda"
+DAC_TINY = dict(n_codebooks=4, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+
+
+def _composite(seed=0):
+    from transformers import T5Config
+
+    dims = decoder_oracle.DecoderDims(**TINY)
+    sd = decoder_oracle.random_decoder_state(dims, seed=11, ln_jitter=0.1)
+    dac_sd = dac_oracle.random_dac_state(DAC_TINY, seed=31)
+    dec_cfg = ptts.ParlerTTSDecoderConfig(**TINY)
+    t5 = T5Config(d_model=64, num_layers=2, d_ff=128, num_heads=2, d_kv=32, vocab_size=100)
+    dac_cfg = ptts.DACConfig(num_codebooks=4, codebook_size=32, latent_dim=128)
+    cfg = ptts.ParlerTTSConfig.from_sub_models_config(t5, dac_cfg, dec_cfg, vocab_size=100)
+    torch.manual_seed(seed)
+    model = ptts.ParlerTTSForConditionalGeneration(
+        cfg, decoder=ptts.ParlerTTSForCausalLM(dec_cfg, state_dict=sd),
+        audio_encoder=ptts.DACModel(dac_cfg, state_dict=dac_sd, decoder_dim=64, codebook_dim=4))
+    model.generation_config.max_length = 24
+    return model.to(DEV), dims, sd, dac_sd
+
+
+def _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, attention_mask=None, prompt_mask=None, **kw):
+    """The oracle's view of generate(): T5 (third-party, same module on the CPU) -> projection -> loop -> DAC."""
+    te = model.text_encoder.to("cpu").float()
+    am = torch.ones_like(input_ids) if attention_mask is None else attention_mask
+    with torch.no_grad():
+        hs = te(input_ids=input_ids, attention_mask=am).last_hidden_state
+    model.text_encoder.to(DEV)
+    w, b = model.enc_to_dec_proj.weight.detach().cpu().float(), model.enc_to_dec_proj.bias.detach().cpu().float()
+    guidance = kw.get("guidance_scale")
+    enc = decoder_oracle.project_encoder(hs, am, w, b)
+    if guidance is not None and guidance > 1:  # null conditioning is appended BEFORE the projection in the reference
+        hs2 = torch.cat([hs, torch.zeros_like(hs)])
+        am2 = torch.cat([am, torch.zeros_like(am)])
+        enc_full = decoder_oracle.project_encoder(hs2, am2, w, b)
+    prm = model.embed_prompts.weight.detach().cpu().float()[prompt_ids]
+    if guidance is not None and guidance > 1:
+        # generate_codes doubles enc itself with zeros; the projected null half equals bias*0-mask = 0 too
+        assert float(enc_full[enc.shape[0]:].abs().max()) == 0.0
+    res = generate_oracle.generate_codes(sd, dims, enc, encoder_attention_mask=am, prompt_hidden_states=prm,
+                                         prompt_attention_mask=prompt_mask, **kw)
+    codes = torch.from_numpy(res["codes"])
+    audio = dac_oracle.decode_generated(dac_sd, codes, dims.bos_token_id, dims.pad_token_id, dims.eos_token_id, 32,
+                                        DAC_TINY)
+    return res, audio
+
+
+def test_generate_end_to_end_greedy_vs_oracle():
+    model, dims, sd, dac_sd = _composite()
+    g = torch.Generator().manual_seed(2)
+    input_ids, prompt_ids = torch.randint(2, 100, (3, 7), generator=g), torch.randint(2, 100, (3, 4), generator=g)
+    res, want = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, max_length=24, do_sample=False)
+    audio = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV), do_sample=False)
+    codes = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV), do_sample=False,
+                           return_codes=True)
+    assert np.array_equal(codes.cpu().numpy(), res["codes"])
+    assert audio.shape == want.shape
+    np.testing.assert_allclose(audio.cpu().numpy(), want.numpy(), atol=1e-3)
+
+
+def test_generate_masks_sampling_and_guidance_vs_oracle():
+    model, dims, sd, dac_sd = _composite()
+    g = torch.Generator().manual_seed(3)
+    input_ids, prompt_ids = torch.randint(2, 100, (2, 6), generator=g), torch.randint(2, 100, (2, 5), generator=g)
+    am = torch.tensor([[1, 1, 1, 1, 1, 1], [1, 1, 1, 1, 0, 0]])
+    pm = torch.tensor([[1, 1, 1, 1, 1], [0, 0, 1, 1, 1]])
+    for kw in (dict(do_sample=False), dict(do_sample=True, top_k=10, temperature=0.8, seed=5),
+               dict(do_sample=False, guidance_scale=2.5)):
+        res, want = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, am, pm, max_length=20, **kw)
+        codes = model.generate(input_ids=input_ids.to(DEV), attention_mask=am.to(DEV),
+                               prompt_input_ids=prompt_ids.to(DEV), prompt_attention_mask=pm.to(DEV), max_length=20,
+                               return_codes=True, **kw)
+        assert np.array_equal(codes.cpu().numpy(), res["codes"]), kw
+
+
+def test_generate_argument_errors_match_reference():
+    model, *_ = _composite()
+    ids = torch.randint(2, 100, (1, 4)).to(DEV)
+    with pytest.raises(ValueError):
+        model.generate(input_ids=ids, prompt_input_ids=ids, num_beams=2)
+    with pytest.raises(ValueError):
+        model.generate(input_ids=ids, prompt_input_ids=ids, do_sample=False, num_return_sequences=2)
+    with pytest.raises(ValueError):
+        model.generate(input_ids=ids, prompt_input_ids=ids, max_length=30, min_length=40)
+
+
+# ------------------------------------------------------------------------------------------------ DAC
+def test_dac_decode_vs_transformers_fixture(golden_dir):
+    z = np.load(os.path.join(golden_dir, "dac_tiny.npz"))
+    c = z["cfg"]
+    cfg = dict(n_codebooks=int(c[0]), codebook_size=int(c[1]), codebook_dim=int(c[2]), latent_dim=int(c[3]),
+               decoder_dim=int(c[4]), rates=tuple(int(x) for x in c[5:]))
+    sd = dac_oracle.random_dac_state(cfg, seed=31)
+    for impl in (cabi.IMPL_SIMPLE, cabi.IMPL_FAST):
+        eng = DacDecoderEngine(sd, DEV, cfg["rates"], impl)
+        codes = torch.from_numpy(z["codes"]).to(DEV)
+        zlat = eng.dequant(codes)
+        np.testing.assert_allclose(zlat.cpu().numpy(), z["z"], atol=1e-4, rtol=1e-4)
+        wav = eng.decode(codes).squeeze(1)
+        assert wav.shape == z["wav"].shape
+        np.testing.assert_allclose(wav.cpu().numpy(), z["wav"], atol=1e-3)
+
+
+@pytest.mark.parametrize("impl", [cabi.IMPL_SIMPLE, cabi.IMPL_FAST])
+def test_dac_44k_architecture_vs_oracle_waveform_1e3(impl):
+    """Full 44.1 kHz decoder shape (1024 -> 1536 ... 96 -> 1, 9 codebooks): waveform within 1e-3 max-abs."""
+    sd = dac_oracle.random_dac_state(dac_oracle.DAC_44K, seed=2)
+    eng = DacDecoderEngine(sd, DEV, impl=impl)
+    g = torch.Generator().manual_seed(6)
+    codes = torch.randint(0, 1024, (2, 9, 11), generator=g)
+    want = dac_oracle.decode_codes(sd, codes).squeeze(1)
+    got = eng.decode(codes.to(DEV)).squeeze(1)
+    assert got.shape == (2, 512 * 11)
+    assert float((got.cpu() - want).abs().max()) < 1e-3
+
+
+def test_dac_ragged_path_vs_oracle():
+    sd = dac_oracle.random_dac_state(DAC_TINY, seed=31)
+    eng = DacDecoderEngine(sd, DEV, DAC_TINY["rates"], cabi.IMPL_SIMPLE)
+    g = torch.Generator().manual_seed(8)
+    codes = torch.randint(0, 32, (3, 4, 9), generator=g)
+    codes[0, 2, 3] = 33  # bos inside -> frame dropped
+    codes[1, :, 5:] = 32  # trailing pad frames
+    codes[2] = 32  # nothing valid
+    want = dac_oracle.decode_generated(sd, codes, 33, 32, 32, 32, DAC_TINY)
+    got = eng.decode_generated(codes.to(DEV), 33, 32, 32)
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), atol=1e-3)
