@@ -121,7 +121,8 @@ PTTS_API int ptts_build_delay_mask(const int64_t* start_ids, int32_t B, int32_t 
 /* apply_delay_pattern_mask, modeling_parler_tts.py:68-74 */
 PTTS_API int ptts_apply_delay_mask(const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int32_t rows,
                           int32_t len, int64_t* out, int64_t ld_out, ptts_stream_t s);
-/* de-delay of generate(), modeling_parler_tts.py:2633-2648 (no-prompt geometry): codes[b][k][f] = applied[b*K+k][f+k+1] */
+/* de-delay of generate(), modeling_parler_tts.py:2633-2648 (no-prompt geometry): codes[b][k][f] = applied[b*K+k][f+k+1],
+ * f < l_out-K; when l_out < 2K-1 the rebuilt mask is all -1 and codes[b][k][f] = applied[b*K+k][f], f < l_out. */
 PTTS_API int ptts_dedelay(const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int32_t B, int32_t K,
                  int32_t l_out, int64_t* codes, ptts_stream_t s);
 /* frame filter of the ragged DAC path, modeling_parler_tts.py:2668: valid[b][f] = all_k codes[b][k][f] < codebook_size;

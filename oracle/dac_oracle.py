@@ -59,13 +59,14 @@ def random_dac_state(cfg=DAC_44K, seed=0, dtype=torch.float32, alpha_jitter=0.2)
     g = torch.Generator().manual_seed(seed)
     sd = {}
 
-    def conv(prefix, cout, cin, k, transposed=False):
+    def conv(prefix, cout, cin, k, transposed=False, gain=1.0):
         shape = (cin, cout, k) if transposed else (cout, cin, k)
         fan_in = (cout if transposed else cin) * k
         v = torch.randn(*shape, generator=g) / math.sqrt(fan_in)
         sd[prefix + ".weight_v"] = v.to(dtype)
-        # g near ||v|| so activations keep unit scale through ~30 layers
-        n = v.reshape(shape[0], -1).norm(dim=1).reshape(-1, 1, 1)
+        # g near gain*||v||: activations stay O(1) through ~30 layers (like a trained codec), so that the comparison
+        # is well conditioned (snake's sin(alpha x) amplifies rounding noise when |x| grows)
+        n = gain * v.reshape(shape[0], -1).norm(dim=1).reshape(-1, 1, 1)
         sd[prefix + ".weight_g"] = (n * (1.0 + 0.1 * torch.randn(shape[0], 1, 1, generator=g))).to(dtype)
         sd[prefix + ".bias"] = (0.02 * torch.randn(cout, generator=g)).to(dtype)
 
@@ -75,24 +76,24 @@ def random_dac_state(cfg=DAC_44K, seed=0, dtype=torch.float32, alpha_jitter=0.2)
     for i in range(cfg["n_codebooks"]):
         q = f"quantizer.quantizers.{i}"
         sd[q + ".codebook.weight"] = torch.randn(cfg["codebook_size"], cfg["codebook_dim"], generator=g).to(dtype)
-        conv(q + ".out_proj", cfg["latent_dim"], cfg["codebook_dim"], 1)
+        conv(q + ".out_proj", cfg["latent_dim"], cfg["codebook_dim"], 1, gain=1.0 / 3.0)
     ch = cfg["decoder_dim"]
     conv("decoder.model.0", ch, cfg["latent_dim"], 7)
     for bi, s in enumerate(cfg["rates"]):
         p = f"decoder.model.{bi + 1}.block"
         cin, cout = ch // 2 ** bi, ch // 2 ** (bi + 1)
         alpha(p + ".0", cin)
-        conv(p + ".1", cout, cin, 2 * s, transposed=True)
+        conv(p + ".1", cout, cin, 2 * s, transposed=True, gain=1.0)
         for ri in range(3):
             r = f"{p}.{ri + 2}.block"
             alpha(r + ".0", cout)
             conv(r + ".1", cout, cout, 7)
             alpha(r + ".2", cout)
-            conv(r + ".3", cout, cout, 1)
+            conv(r + ".3", cout, cout, 1, gain=0.3)
     n = len(cfg["rates"])
     cl = ch // 2 ** n
     alpha(f"decoder.model.{n + 1}", cl)
-    conv(f"decoder.model.{n + 2}", 1, cl, 7)
+    conv(f"decoder.model.{n + 2}", 1, cl, 7, gain=1.0)
     return sd
 
 

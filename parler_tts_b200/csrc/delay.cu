@@ -39,13 +39,13 @@ __global__ void apply_delay_mask_kernel(const int64_t* __restrict__ ids, int64_t
 }
 
 __global__ void dedelay_kernel(const int64_t* __restrict__ ids, int64_t ld_ids, const int64_t* __restrict__ mask,
-                               int64_t ld_mask, int B, int K, int F, int64_t* __restrict__ codes) {
+                               int64_t ld_mask, int B, int K, int F, int shift, int64_t* __restrict__ codes) {
   const int64_t total = (int64_t)B * K * F;
   for (int64_t i = blockIdx.x * (int64_t)blockDim.x + threadIdx.x; i < total; i += (int64_t)gridDim.x * blockDim.x) {
     const int f = (int)(i % F);
     const int64_t r = i / F;
     const int k = (int)(r % K);
-    const int j = f + k + 1;
+    const int j = f + (shift ? k + 1 : 0);
     const int64_t m = mask[r * ld_mask + j];
     codes[i] = (m == -1) ? ids[r * ld_ids + j] : m;
   }
@@ -127,12 +127,14 @@ extern "C" int ptts_apply_delay_mask(const int64_t* ids, int64_t ld_ids, const i
 
 extern "C" int ptts_dedelay(const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int32_t B,
                             int32_t K, int32_t l_out, int64_t* codes, ptts_stream_t s) {
+  PTTS_CHECK_ARG(B > 0 && K > 0 && l_out >= 1 && ld_ids >= l_out && ld_mask >= l_out, "dedelay: bad dims");
+  // an output shorter than 2K-1 rebuilds an all -1 mask (modeling_parler_tts.py:105-106), so every column survives
+  const bool degenerate = l_out < 2 * K - 1;
+  const int F = degenerate ? l_out : l_out - K;
+  if (F == 0) return PTTS_OK;  // nothing survives the de-delay: empty (B, K, 0) result
   PTTS_CHECK_ARG(ids && mask && codes, "dedelay: null pointer");
-  PTTS_CHECK_ARG(B > 0 && K > 0 && l_out >= K && ld_ids >= l_out && ld_mask >= l_out, "dedelay: bad dims");
-  const int F = l_out - K;
-  if (F == 0) return PTTS_OK;
   dedelay_kernel<<<grid_for((int64_t)B * K * F, 256), 256, 0, as_stream(s)>>>(ids, ld_ids, mask, ld_mask, B, K, F,
-                                                                             codes);
+                                                                             degenerate ? 0 : 1, codes);
   PTTS_CHECK_LAUNCH("dedelay");
   return PTTS_OK;
 }

@@ -112,6 +112,9 @@ class DacDecoderEngine:
         B, K, F = codes.shape
         special = bool(((codes == bos) | (codes == pad) | (codes == eos)).any().item())
         if not special:
+            if int(codes.max().item()) >= self.codebook_size or int(codes.min().item()) < 0:
+                # the reference's codebook nn.Embedding raises here; fail just as loudly instead of decoding garbage
+                raise IndexError("audio code outside [0, codebook_size): index out of range in the DAC codebook")
             return self.decode(codes).squeeze(1)
         packed = torch.empty_like(codes)
         counts = torch.zeros(B, device=self.device, dtype=torch.int32)

@@ -327,7 +327,7 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
     Lout = ctrl["stop_len"] if ctrl["done"] else ctrl["len"]
     seq = st.ids[:, :Lout]
     if T0 == 1:
-        codes = torch.empty(Bu, K, Lout - K, device=dev, dtype=torch.int64)
+        codes = torch.empty(Bu, K, Lout if Lout < 2 * K - 1 else Lout - K, device=dev, dtype=torch.int64)
         cabi.call("ptts_dedelay", cabi.ptr(st.ids), st.max_len, cabi.ptr(st.mask), st.max_len, Bu, K, Lout,
                   cabi.ptr(codes), cabi.stream_ptr())
     else:  # audio-prompt geometry: the general boolean-mask form of modeling_parler_tts.py:2637-2645

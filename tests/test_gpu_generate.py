@@ -36,7 +36,8 @@ def _composite(seed=0):
     return model.to(DEV), dims, sd, dac_sd
 
 
-def _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, attention_mask=None, prompt_mask=None, **kw):
+def _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, attention_mask=None, prompt_mask=None,
+                     decode=True, **kw):
     """The oracle's view of generate(): T5 (third-party, same module on the CPU) -> projection -> loop -> DAC."""
     te = model.text_encoder.to("cpu").float()
     am = torch.ones_like(input_ids) if attention_mask is None else attention_mask
@@ -56,6 +57,8 @@ def _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, attention_m
         assert float(enc_full[enc.shape[0]:].abs().max()) == 0.0
     res = generate_oracle.generate_codes(sd, dims, enc, encoder_attention_mask=am, prompt_hidden_states=prm,
                                          prompt_attention_mask=prompt_mask, **kw)
+    if not decode:
+        return res, None
     codes = torch.from_numpy(res["codes"])
     audio = dac_oracle.decode_generated(dac_sd, codes, dims.bos_token_id, dims.pad_token_id, dims.eos_token_id, 32,
                                         DAC_TINY)
@@ -66,10 +69,14 @@ def test_generate_end_to_end_greedy_vs_oracle():
     model, dims, sd, dac_sd = _composite()
     g = torch.Generator().manual_seed(2)
     input_ids, prompt_ids = torch.randint(2, 100, (3, 7), generator=g), torch.randint(2, 100, (3, 4), generator=g)
-    res, want = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, max_length=24, do_sample=False)
-    audio = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV), do_sample=False)
+    # ids >= 32 are emittable but are not codebook entries (the reference's DAC would raise on them): cut them
+    res, want = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, max_length=24, do_sample=False,
+                                 suppress_from=32)
+    procs = [ptts.SuppressTokensAtOrAbove(32)]
+    audio = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV), do_sample=False,
+                           logits_processor=procs)
     codes = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV), do_sample=False,
-                           return_codes=True)
+                           logits_processor=procs, return_codes=True)
     assert np.array_equal(codes.cpu().numpy(), res["codes"])
     assert audio.shape == want.shape
     np.testing.assert_allclose(audio.cpu().numpy(), want.numpy(), atol=1e-3)
@@ -83,11 +90,47 @@ def test_generate_masks_sampling_and_guidance_vs_oracle():
     pm = torch.tensor([[1, 1, 1, 1, 1], [0, 0, 1, 1, 1]])
     for kw in (dict(do_sample=False), dict(do_sample=True, top_k=10, temperature=0.8, seed=5),
                dict(do_sample=False, guidance_scale=2.5)):
-        res, want = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, am, pm, max_length=20, **kw)
+        res, want = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, am, pm, decode=False,
+                                     max_length=20, **kw)
         codes = model.generate(input_ids=input_ids.to(DEV), attention_mask=am.to(DEV),
                                prompt_input_ids=prompt_ids.to(DEV), prompt_attention_mask=pm.to(DEV), max_length=20,
                                return_codes=True, **kw)
         assert np.array_equal(codes.cpu().numpy(), res["codes"]), kw
+
+
+def test_generate_ragged_audio_and_out_of_range_codes():
+    """Unsuppressed random-init generation emits EOS/unused ids: special ids route to the per-sample path with zero
+    right-padding (modeling_parler_tts.py:2664-2680); an id >= codebook_size without any special id raises like the
+    reference's codebook lookup would."""
+    model, dims, sd, dac_sd = _composite()
+    g = torch.Generator().manual_seed(12)
+    input_ids, prompt_ids = torch.randint(2, 100, (3, 7), generator=g), torch.randint(2, 100, (3, 4), generator=g)
+    res, _ = _oracle_generate_codes_only(model, dims, sd, input_ids, prompt_ids, max_length=24, do_sample=True,
+                                         top_k=0, seed=1)
+    codes = torch.from_numpy(res["codes"])
+    special = bool(((codes == 33) | (codes == 32)).any())
+    if special:
+        want = dac_oracle.decode_generated(dac_sd, codes, 33, 32, 32, 32, DAC_TINY)
+        audio = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV), do_sample=True,
+                               top_k=0, seed=1, max_length=24)
+        assert audio.shape == want.shape
+        np.testing.assert_allclose(audio.cpu().numpy(), want.numpy(), atol=1e-3)
+    eng = model.audio_encoder.engine()
+    bad = torch.full((1, 4, 5), 40, dtype=torch.int64, device=DEV)
+    with pytest.raises(IndexError):
+        eng.decode_generated(bad, 33, 32, 32)
+
+
+def _oracle_generate_codes_only(model, dims, sd, input_ids, prompt_ids, **kw):
+    te = model.text_encoder.to("cpu").float()
+    am = torch.ones_like(input_ids)
+    with torch.no_grad():
+        hs = te(input_ids=input_ids, attention_mask=am).last_hidden_state
+    model.text_encoder.to(DEV)
+    w, b = model.enc_to_dec_proj.weight.detach().cpu().float(), model.enc_to_dec_proj.bias.detach().cpu().float()
+    enc = decoder_oracle.project_encoder(hs, am, w, b)
+    prm = model.embed_prompts.weight.detach().cpu().float()[prompt_ids]
+    return generate_oracle.generate_codes(sd, dims, enc, encoder_attention_mask=am, prompt_hidden_states=prm, **kw), None
 
 
 def test_generate_argument_errors_match_reference():

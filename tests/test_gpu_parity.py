@@ -63,13 +63,13 @@ def test_dedelay_and_frame_filter_vs_oracle():
     B, K, M, bos, pad = 3, 9, 40, 1025, 1024
     start = np.full((B * K, 1), bos, dtype=np.int64)
     _, mask = delay_pattern.build_delay_pattern_mask(start, bos, pad, M, K)
-    for Lout in (M, 31, K):
+    for Lout in (M, 31, 17, 16, K):  # 16 and K are below 2K-1: the reference keeps every column there
         raw = rng.integers(0, 1088, size=(B * K, Lout)).astype(np.int64)
         want = delay_pattern.revert_delay_pattern(raw, start, mask, bos, pad, K)
         ids_d = torch.zeros(B * K, M, dtype=torch.int64, device=DEV)
         ids_d[:, :Lout] = torch.from_numpy(raw).to(DEV)
         mask_d = torch.from_numpy(mask).to(DEV)
-        codes = torch.empty(B, K, Lout - K, dtype=torch.int64, device=DEV)
+        codes = torch.empty(B, K, want.shape[-1], dtype=torch.int64, device=DEV)
         cabi.call("ptts_dedelay", cabi.ptr(ids_d), M, cabi.ptr(mask_d), M, B, K, Lout, cabi.ptr(codes),
                   cabi.stream_ptr())
         assert np.array_equal(codes.cpu().numpy(), want)
