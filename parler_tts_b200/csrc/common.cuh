@@ -38,6 +38,30 @@ void count_launch();  // host-side tally of kernel launches enqueued by this lib
     if (rc__ != PTTS_OK) return rc__;  \
   } while (0)
 
+bool pdl_enabled();  // PTTS_PDL=0 disables programmatic dependent launch (default on)
+
+// Launch helper of the fast family: cudaLaunchKernelEx, with the programmatic-stream-serialization attribute when
+// PDL is enabled (works eagerly and under stream capture into a CUDA graph).
+template <typename... KArgs, typename... Args>
+inline cudaError_t launch_k(void (*kernel)(KArgs...), dim3 grid, dim3 block, size_t smem, cudaStream_t st,
+                            Args... args) {
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = block;
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[1];
+  int n = 0;
+  if (pdl_enabled()) {
+    attr[0].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[0].val.programmaticStreamSerializationAllowed = 1;
+    n = 1;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  return cudaLaunchKernelEx(&cfg, kernel, KArgs(args)...);
+}
+
 inline cudaStream_t as_stream(ptts_stream_t s) { return reinterpret_cast<cudaStream_t>(s); }
 inline size_t dtype_size(int dt) { return dt == PTTS_BF16 ? 2 : 4; }
 
@@ -79,6 +103,12 @@ __device__ __forceinline__ float apply_act(float x, int act) {
     default: return x;
   }
 }
+
+// ---- programmatic dependent launch (PDL): every kernel of the fast family calls pdl_wait() before it touches data
+// written by an earlier kernel, and pdl_launch() as early as possible so that the next kernel's prologue (weight
+// prefetch, smem carve-up) overlaps this kernel's tail.  Both are no-ops for a launch without the attribute.
+__device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
+__device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
 // value of a dynamic scalar: base + *dyn (dyn may be null)
 __device__ __forceinline__ int dyn_value(int base, const int* dyn) { return base + (dyn ? *dyn : 0); }

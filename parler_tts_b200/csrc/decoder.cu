@@ -9,8 +9,8 @@ namespace ptts {
 static int linear_dispatch(int impl, const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M,
                            int N, int K, float alpha, int act, const float* residual, const int* row_mask, void* y,
                            int ydtype, cudaStream_t st) {
-  if (impl == PTTS_IMPL_FAST && fast_linear_supported(xdtype, wdtype, M, N, K))
-    return linear_fast(x, xdtype, w, wdtype, bias, M, N, K, alpha, act, residual, row_mask, y, ydtype, st);
+  if (impl == PTTS_IMPL_FAST && xdtype == PTTS_BF16 && wdtype == PTTS_BF16 && gemm_bf16_supported(M, N, K))
+    return gemm_bf16_store(x, w, M, N, K, alpha, act, bias, residual, row_mask, y, ydtype, st);
   return linear_simple(x, xdtype, w, wdtype, bias, M, N, K, alpha, act, residual, row_mask, y, ydtype, st);
 }
 
@@ -50,10 +50,71 @@ static inline size_t kv_layer_elems(const PttsModel* m, int B, int slots) {
   return (size_t)B * m->n_heads * slots * m->head_dim;
 }
 
+// Scratch layout: [0, attn_scratch_floats) split-KV attention partials | work area (qkv staging of the simple family,
+// all-position logits staging, split-K partial sums of the residual GEMMs).
+static inline float* work_area(const PttsModel* m, const PttsState* s) {
+  return s->scratch + attn_scratch_floats(s->B, m->n_heads);
+}
+
+// Split-K partial sums of a residual GEMM that the next LayerNorm still has to fold into the residual stream.
+struct Pending {
+  const float* part = nullptr;
+  int S = 0;
+  int64_t stride = 0;
+};
+
+struct Path {
+  bool gemm;  // bf16 tensor-core weight-streaming GEMMs with fused epilogues
+  bool ln;    // LayerNorm with the split-K reduction folded in
+};
+
+static Path pick_path(const PttsModel* m, const PttsState* s) {
+  Path p;
+  const bool fast = s->impl == PTTS_IMPL_FAST;
+  p.gemm = fast && m->wdtype == PTTS_BF16 && gemm_bf16_supported(1, m->hidden, m->hidden) &&
+           gemm_bf16_supported(1, m->hidden, m->ffn);
+  p.ln = fast && fast_layernorm_supported(m->hidden);
+  return p;
+}
+
+// y = LN(h [+ pending partial sums]) for rows_out rows; output row r reads residual row r*row_mul + row_add
+static int ln_step(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const float* g,
+                   const float* b, int rows_out, int row_mul, int row_add, cudaStream_t st) {
+  const int H = m->hidden;
+  if (path.ln) {
+    PTTS_TRY(layernorm_fast(s->h, pend.part, pend.S, pend.stride, g, b, rows_out, H, 1e-5f, row_mul, row_add, s->xn,
+                            m->wdtype, st));
+    pend = Pending();
+    return PTTS_OK;
+  }
+  PTTS_CHECK_ARG(pend.S == 0, "internal: pending split-K partials without the fast LayerNorm");
+  return layernorm(s->h, g, b, rows_out, H, 1e-5f, (int64_t)row_mul * H, (int64_t)row_add * H, s->xn, m->wdtype, st);
+}
+
+// h += x . w^T   (out_proj / fc2 with the residual add of modeling_parler_tts.py:460,483,492)
+static int residual_linear(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const void* x,
+                           const void* w, int rows, int K, cudaStream_t st) {
+  const int H = m->hidden, dt = m->wdtype;
+  if (path.gemm && path.ln && rows <= 256) {
+    int bn = 64;
+    const int S = gemm_bf16_plan_splits(rows, H, K, &bn);
+    if (S > 1) {
+      float* part = work_area(m, s);
+      PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st));
+      pend.part = part;
+      pend.S = S;
+      pend.stride = (int64_t)rows * H;
+      return PTTS_OK;
+    }
+  }
+  return linear_dispatch(s->impl, x, dt, w, dt, nullptr, rows, H, K, 1.0f, PTTS_ACT_NONE, s->h, nullptr, s->h,
+                         PTTS_F32, st);
+}
+
 // one decoder layer over `rows` = B*Tq tokens.  ctx_base/ctx_dyn give the self-attention context length AFTER the
 // new K/V have been written; the write slot of token t is ctx - Tq + t.
-static int run_layer(const PttsModel* m, const PttsState* s, int l, int Tq, int ctx_base, const int* ctx_dyn,
-                     cudaStream_t st) {
+static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, int l, int Tq,
+                     int ctx_base, const int* ctx_dyn, cudaStream_t st) {
   const PttsLayer& L = m->layers[l];
   const int H = m->hidden, F = m->ffn, heads = m->n_heads, d = m->head_dim, B = s->B, dt = m->wdtype;
   const int rows = B * Tq;
@@ -61,34 +122,36 @@ static int run_layer(const PttsModel* m, const PttsState* s, int l, int Tq, int 
   char* ks = (char*)s->kv_self + (size_t)(2 * l) * kv_layer_elems(m, B, s->c_max) * es;
   char* vs = (char*)s->kv_self + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->c_max) * es;
   const float scale = 1.0f / sqrtf((float)d);
-  void* qkv = (void*)s->scratch;
   // self attention block
-  PTTS_TRY(layernorm(s->h, L.ln1_g, L.ln1_b, rows, H, 1e-5f, H, 0, s->xn, dt, st));
-  PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qkv, dt, nullptr, rows, 3 * H, H, 1.0f, PTTS_ACT_NONE, nullptr,
-                           nullptr, qkv, dt, st));
-  PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, s->c_max, ctx_base - Tq, ctx_dyn, scale, s->q, ks, vs, st));
+  PTTS_TRY(ln_step(m, s, path, pend, L.ln1_g, L.ln1_b, rows, 1, 0, st));
+  if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
+    PTTS_TRY(gemm_bf16_scatter(s->xn, L.w_qkv, rows, 3 * H, H, 1, scale, s->q, ks, vs, H, heads, d, Tq, s->c_max,
+                               ctx_base - Tq, ctx_dyn, st));
+  } else {
+    void* qkv = (void*)work_area(m, s);
+    PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qkv, dt, nullptr, rows, 3 * H, H, 1.0f, PTTS_ACT_NONE, nullptr,
+                             nullptr, qkv, dt, st));
+    PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, s->c_max, ctx_base - Tq, ctx_dyn, scale, s->q, ks, vs, st));
+  }
   PTTS_TRY(attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn, Tq > 1,
                               s->prompt_mask, s->P, s->attn, s->scratch, st));
-  PTTS_TRY(linear_dispatch(s->impl, s->attn, dt, L.w_o, dt, nullptr, rows, H, H, 1.0f, PTTS_ACT_NONE, s->h, nullptr,
-                           s->h, PTTS_F32, st));
+  PTTS_TRY(residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
   // cross attention block (modeling_parler_tts.py:465-483)
   if (s->S > 0) {
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
     char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->S) * es;
-    PTTS_TRY(layernorm(s->h, L.ln2_g, L.ln2_b, rows, H, 1e-5f, H, 0, s->xn, dt, st));
+    PTTS_TRY(ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
     PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale, PTTS_ACT_NONE, nullptr,
                              nullptr, s->q, dt, st));
     PTTS_TRY(attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0, s->enc_mask, s->S,
                                 s->attn, s->scratch, st));
-    PTTS_TRY(linear_dispatch(s->impl, s->attn, dt, L.w_oc, dt, nullptr, rows, H, H, 1.0f, PTTS_ACT_NONE, s->h,
-                             nullptr, s->h, PTTS_F32, st));
+    PTTS_TRY(residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, st));
   }
   // feed forward block
-  PTTS_TRY(layernorm(s->h, L.ln3_g, L.ln3_b, rows, H, 1e-5f, H, 0, s->xn, dt, st));
+  PTTS_TRY(ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn, nullptr, nullptr,
                            s->ffn, dt, st));
-  PTTS_TRY(linear_dispatch(s->impl, s->ffn, dt, L.w_fc2, dt, nullptr, rows, H, F, 1.0f, PTTS_ACT_NONE, s->h, nullptr,
-                           s->h, PTTS_F32, st));
+  PTTS_TRY(residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, st));
   return PTTS_OK;
 }
 
@@ -107,9 +170,12 @@ using namespace ptts;
 
 extern "C" int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows) {
   if (!m || rows <= 0) return 0;
-  const int64_t a = (int64_t)rows * 3 * m->hidden;                   // fused qkv / cross kv staging
-  const int64_t b = (int64_t)rows * m->n_codebooks * m->vocab;       // all-position logits staging
-  return (a > b ? a : b) + 4096;
+  int64_t w = (int64_t)rows * 3 * m->hidden;                                  // fused qkv / cross kv staging
+  const int64_t b = (int64_t)rows * m->n_codebooks * m->vocab;                // all-position logits staging
+  const int64_t c = (int64_t)kMaxSplitK * (rows < 256 ? rows : 256) * m->hidden;  // split-K partial sums
+  if (b > w) w = b;
+  if (c > w) w = c;
+  return attn_scratch_floats(rows, m->n_heads) + w + 4096;  // rows >= B bounds the split-KV partial area
 }
 
 extern "C" int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T0,
@@ -125,6 +191,8 @@ extern "C" int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_
 extern "C" int ptts_layernorm(const float* x, const float* g, const float* b, int32_t rows, int32_t H, float eps,
                               void* y, int32_t ydtype, ptts_stream_t s) {
   PTTS_CHECK_ARG(x && g && b && y && rows >= 0 && H > 0, "layernorm: bad arguments");
+  if (fast_layernorm_supported(H))  // no pending split-K partials: the residual rows are only read
+    return layernorm_fast(const_cast<float*>(x), nullptr, 0, 0, g, b, rows, H, eps, 1, 0, y, ydtype, as_stream(s));
   return layernorm(x, g, b, rows, H, eps, H, 0, y, ydtype, as_stream(s));
 }
 
@@ -153,12 +221,19 @@ extern "C" int ptts_cross_kv(const PttsModel* m, const PttsState* s, const void*
   cudaStream_t st = as_stream(stream);
   const int H = m->hidden, dt = m->wdtype, rows = s->B * s->S;
   const size_t es = dtype_size(dt);
+  const Path path = pick_path(m, s);
   for (int l = 0; l < m->n_layers; ++l) {
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, s->B, s->S) * es;
     char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, s->B, s->S) * es;
-    PTTS_TRY(linear_dispatch(s->impl, enc, dt, m->layers[l].w_kvc, dt, nullptr, rows, 2 * H, H, 1.0f, PTTS_ACT_NONE,
-                             nullptr, nullptr, s->scratch, dt, st));
-    PTTS_TRY(kv_scatter(s->scratch, dt, rows, H, m->n_heads, m->head_dim, s->S, kc, vc, st));
+    if (path.gemm) {
+      PTTS_TRY(gemm_bf16_scatter(enc, m->layers[l].w_kvc, rows, 2 * H, H, 0, 1.0f, nullptr, kc, vc, H, m->n_heads,
+                                 m->head_dim, s->S, s->S, 0, nullptr, st));
+    } else {
+      float* stage = work_area(m, s);
+      PTTS_TRY(linear_dispatch(s->impl, enc, dt, m->layers[l].w_kvc, dt, nullptr, rows, 2 * H, H, 1.0f, PTTS_ACT_NONE,
+                               nullptr, nullptr, stage, dt, st));
+      PTTS_TRY(kv_scatter(stage, dt, rows, H, m->n_heads, m->head_dim, s->S, kc, vc, st));
+    }
   }
   return PTTS_OK;
 }
@@ -176,16 +251,19 @@ extern "C" int ptts_prefill(const PttsModel* m, const PttsState* s, const float*
   // with classifier-free guidance rows [B/2, B) replay the ids of rows [0, B/2) (modeling_parler_tts.py:2109-2118)
   PTTS_TRY(embed_prefill(m, s->ids, s->max_len, s->mask, s->max_len, B, cfg ? B / 2 : B, s->T0, prompt_table, prompt_ids, prompt_hidden,
                          s->P, s->h, st));
-  for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, l, T, T, nullptr, st));
+  const Path path = pick_path(m, s);
+  Pending pend;
+  for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, path, pend, l, T, T, nullptr, st));
   if (all_logits) {
-    PTTS_TRY(layernorm(s->h, m->lnf_g, m->lnf_b, B * T, H, 1e-5f, H, 0, s->xn, dt, st));
+    float* stage = work_area(m, s);
+    PTTS_TRY(ln_step(m, s, path, pend, m->lnf_g, m->lnf_b, B * T, 1, 0, st));
     PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B * T, K * V, H, 1.0f, PTTS_ACT_NONE,
-                             nullptr, nullptr, s->scratch, PTTS_F32, st));
-    logits_bktv_kernel<<<B * T * K, 256, 0, st>>>(s->scratch, T, K, V, all_logits);
+                             nullptr, nullptr, stage, PTTS_F32, st));
+    logits_bktv_kernel<<<B * T * K, 256, 0, st>>>(stage, T, K, V, all_logits);
     PTTS_CHECK_LAUNCH("logits_bktv");
   }
   // logits of the last position only (transformers takes outputs.logits[:, -1, :])
-  PTTS_TRY(layernorm(s->h, m->lnf_g, m->lnf_b, B, H, 1e-5f, (int64_t)T * H, (int64_t)(T - 1) * H, s->xn, dt, st));
+  PTTS_TRY(ln_step(m, s, path, pend, m->lnf_g, m->lnf_b, B, T, T - 1, st));
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
                            nullptr, s->logits, PTTS_F32, st));
   if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));
@@ -198,8 +276,10 @@ extern "C" int ptts_decode_step(const PttsModel* m, const PttsState* s, int32_t 
   cudaStream_t st = as_stream(stream);
   const int B = s->B, H = m->hidden, K = m->n_codebooks, V = m->vocab, dt = m->wdtype;
   // context after this step's K/V write = P + len   (len = columns already in ids; input column = len-1)
-  for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, l, 1, s->P, &s->ctrl->len, st));
-  PTTS_TRY(layernorm(s->h, m->lnf_g, m->lnf_b, B, H, 1e-5f, H, 0, s->xn, dt, st));
+  const Path path = pick_path(m, s);
+  Pending pend;
+  for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, path, pend, l, 1, s->P, &s->ctrl->len, st));
+  PTTS_TRY(ln_step(m, s, path, pend, m->lnf_g, m->lnf_b, B, 1, 0, st));
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
                            nullptr, s->logits, PTTS_F32, st));
   if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));

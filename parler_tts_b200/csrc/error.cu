@@ -1,4 +1,5 @@
 #include <stdarg.h>
+#include <stdlib.h>
 #include "common.cuh"
 
 namespace ptts {
@@ -11,6 +12,14 @@ void set_error(const char* fmt, ...) {
 }
 static int64_t g_launches = 0;
 void count_launch() { ++g_launches; }
+bool pdl_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_PDL");
+    v = (e && e[0] == '0') ? 0 : 1;
+  }
+  return v == 1;
+}
 }  // namespace ptts
 
 extern "C" int32_t ptts_abi_version(void) { return PTTS_ABI_VERSION; }

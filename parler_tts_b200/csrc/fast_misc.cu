@@ -1,0 +1,105 @@
+// LayerNorm of the residual stream with the split-K reduction of the preceding residual GEMM folded in:
+//   h[row] += sum_s part[s][row]   (out_proj / fc2 partial sums, fixed order => deterministic)
+//   y[row]  = LN(h[row]) * gamma + beta   (nn.LayerNorm eps 1e-5, /root/reference/parler_tts/modeling_parler_tts.py:446,467,487,959)
+// One CTA per row, the row stays in shared memory between the mean / variance / normalise passes (two-pass variance
+// like the simple family, so fp32 results agree to rounding).
+#include "ops.cuh"
+
+namespace ptts {
+
+namespace {
+
+template <typename TY>
+__global__ void __launch_bounds__(256)
+ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
+                 const float* __restrict__ g, const float* __restrict__ bta, int H, float eps, int row_mul, int row_add,
+                 TY* __restrict__ y) {
+  extern __shared__ float buf[];  // [H]
+  __shared__ float red[8];
+  __shared__ float stat[2];
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int64_t rin = (int64_t)blockIdx.x * row_mul + row_add;
+  float* hr = h + rin * H;
+  pdl_wait();
+  pdl_launch();
+  float s = 0.f;
+  for (int c = tid * 4; c < H; c += 256 * 4) {
+    float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
+    for (int i = 0; i < S; ++i) {
+      const float4 p = __ldcg(reinterpret_cast<const float4*>(part + i * part_stride + rin * H + c));
+      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    }
+    if (S > 0) *reinterpret_cast<float4*>(hr + c) = v;
+    *reinterpret_cast<float4*>(buf + c) = v;
+    s += (v.x + v.y) + (v.z + v.w);
+  }
+  s = warp_sum(s);
+  if (lane == 0) red[warp] = s;
+  __syncthreads();
+  if (warp == 0) {
+    float v = lane < 8 ? red[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) stat[0] = v / (float)H;
+  }
+  __syncthreads();
+  const float mean = stat[0];
+  float qq = 0.f;
+  for (int c = tid * 4; c < H; c += 256 * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(buf + c);
+    const float a = v.x - mean, b = v.y - mean, cc = v.z - mean, d = v.w - mean;
+    qq += (a * a + b * b) + (cc * cc + d * d);
+  }
+  qq = warp_sum(qq);
+  if (lane == 0) red[warp] = qq;
+  __syncthreads();
+  if (warp == 0) {
+    float v = lane < 8 ? red[lane] : 0.f;
+    v = warp_sum(v);
+    if (lane == 0) stat[1] = rsqrtf(v / (float)H + eps);
+  }
+  __syncthreads();
+  const float rstd = stat[1];
+  TY* yr = y + (int64_t)blockIdx.x * H;
+  for (int c = tid * 4; c < H; c += 256 * 4) {
+    const float4 v = *reinterpret_cast<const float4*>(buf + c);
+    const float4 gg = __ldg(reinterpret_cast<const float4*>(g + c));
+    const float4 bb = __ldg(reinterpret_cast<const float4*>(bta + c));
+    const float o0 = (v.x - mean) * rstd * gg.x + bb.x, o1 = (v.y - mean) * rstd * gg.y + bb.y;
+    const float o2 = (v.z - mean) * rstd * gg.z + bb.z, o3 = (v.w - mean) * rstd * gg.w + bb.w;
+    if constexpr (sizeof(TY) == 4) {
+      *reinterpret_cast<float4*>(yr + c) = make_float4(o0, o1, o2, o3);
+    } else {
+      __nv_bfloat162 lo = __floats2bfloat162_rn(o0, o1), hi = __floats2bfloat162_rn(o2, o3);
+      uint2 u;
+      u.x = *reinterpret_cast<uint32_t*>(&lo);
+      u.y = *reinterpret_cast<uint32_t*>(&hi);
+      *reinterpret_cast<uint2*>(yr + c) = u;
+    }
+  }
+}
+
+}  // namespace
+
+bool fast_layernorm_supported(int H) { return H % 4 == 0 && H <= 12288; }
+
+// rows output rows; output row r reads input row r*row_mul + row_add (of h and of every partial)
+int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, const float* g, const float* b, int rows,
+                   int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st) {
+  if (rows == 0) return PTTS_OK;
+  const size_t smem = sizeof(float) * (size_t)H;
+  cudaError_t e;
+  if (ydtype == PTTS_F32)
+    e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H, eps,
+                 row_mul, row_add, (float*)y);
+  else
+    e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H,
+                 eps, row_mul, row_add, (__nv_bfloat16*)y);
+  if (e != cudaSuccess) {
+    set_error("layernorm_fast launch: %s", cudaGetErrorString(e));
+    return PTTS_E_LAUNCH;
+  }
+  PTTS_CHECK_LAUNCH("layernorm_fast");
+  return PTTS_OK;
+}
+
+}  // namespace ptts

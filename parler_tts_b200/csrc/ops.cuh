@@ -21,11 +21,21 @@ int attention_simple(const void* q, const void* ck, const void* cv, int dtype, i
                      void* out, cudaStream_t st);
 int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st);
 
-// fast (sm_100a tcgen05 / TMA) family -- fast_*.cu
-bool fast_linear_supported(int xdtype, int wdtype, int M, int N, int K);
-int linear_fast(const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M, int N, int K,
-                float alpha, int act, const float* residual, const int* row_mask, void* y, int ydtype,
-                cudaStream_t st);
+// fast family -- fast_*.cu
+constexpr int kMaxSplitK = 16;
+bool gemm_bf16_supported(int M, int N, int K);
+int gemm_bf16_store(const void* x, const void* w, int M, int N, int K, float alpha, int act, const float* bias,
+                    const float* residual, const int* row_mask, void* y, int ydtype, cudaStream_t st);
+int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has_q, float q_scale, void* q, void* ck,
+                      void* cv, int H, int heads, int d, int Tq, int c_stride, int pos_base, const int* pos_dyn,
+                      cudaStream_t st);
+int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
+int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
+                      cudaStream_t st);
+bool fast_layernorm_supported(int H);
+int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, const float* g, const float* b, int rows,
+                   int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st);
+int64_t attn_scratch_floats(int B, int heads);
 
 bool fast_attention_supported(int dtype, int d, int Tq);
 int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int B, int heads, int d, int Tq,
