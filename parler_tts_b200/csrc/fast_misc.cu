@@ -25,9 +25,14 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   float s = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
-    for (int i = 0; i < S; ++i) {
-      const float4 p = __ldcg(reinterpret_cast<const float4*>(part + i * part_stride + rin * H + c));
-      v.x += p.x; v.y += p.y; v.z += p.z; v.w += p.w;
+    for (int i0 = 0; i0 < S; i0 += 8) {  // 8 independent loads in flight, summed in split order (deterministic)
+      float4 p[8];
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (i0 + u < S) p[u] = __ldcg(reinterpret_cast<const float4*>(part + (i0 + u) * part_stride + rin * H + c));
+#pragma unroll
+      for (int u = 0; u < 8; ++u)
+        if (i0 + u < S) { v.x += p[u].x; v.y += p[u].y; v.z += p[u].z; v.w += p[u].w; }
     }
     if (S > 0) *reinterpret_cast<float4*>(hr + c) = v;
     *reinterpret_cast<float4*>(buf + c) = v;
