@@ -113,6 +113,13 @@ PTTS_API int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows);
  * site executed on the host; a CUDA-graph replay re-runs the launches recorded at capture time). */
 PTTS_API int64_t ptts_launch_count(void);
 
+/* Diagnostic (not on the product path): enqueues a chain of n dependent trivial kernels (mode 0: empty, mode 1: one
+ * load + store per thread over buf[ctas*128]) so that the per-launch latency floor of a graph replay can be measured. */
+PTTS_API int ptts_diag_chain(int32_t n, int32_t mode, int32_t ctas, float* buf, ptts_stream_t s);
+
+/* Diagnostic: globaltimer stamps of the tcgen05 GEMM recorded under PTTS_GEMM_DBG=1 (8 x uint64 per launch). */
+PTTS_API int ptts_diag_gemm_stamps(uint64_t* host, int32_t n_launches);
+
 /* ---- integer kernels -------------------------------------------------------------------------------------- */
 /* build_delay_pattern_mask, modeling_parler_tts.py:77-139.  first_start (device int32[1]) receives the number of
  * leading columns that are already determined (the reference's `first_start_id`). */
@@ -186,6 +193,25 @@ PTTS_API int ptts_dac_conv1d(const float* x, int32_t B, int32_t Cin, int32_t T, 
 PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T, const float* w, const float* bias,
                       int32_t Cout, int32_t stride, const float* snake_alpha, float* y, int32_t impl,
                       ptts_stream_t s);
+
+
+/* ---- DAC decode, fast family: channels-last activations [B][T][C] fp32, tensor-core implicit GEMM ---------------- */
+/* weights are pre-split on the host into two bf16 planes (w = hi + mid) laid out [taps][N][Cin]; see
+ * parler_tts_b200/dac.py.  Same arithmetic as ptts_dac_conv1d / ptts_dac_convtr1d above. */
+PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
+                         const float* tables, int32_t codebook_size, int32_t latent, float* z, ptts_stream_t s);
+/* y[b][t][co] = bias + sum_k sum_ci snake(x)[b][t + (k - (ksize-1)/2)*dilation][ci] * w[k][co][ci] [+ residual] */
+PTTS_API int ptts_dac_conv1d_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const void* w_hi, const void* w_mid,
+                        const float* bias, int32_t Cout, int32_t ksize, int32_t dilation, const float* snake_alpha,
+                        const float* residual, float* y, ptts_stream_t s);
+/* conv_transpose1d(snake(x)), kernel 2*stride, padding ceil(stride/2); w planes [2][stride*Cout][Cin] with
+ * w2[tap][ph*Cout + co][ci] = w[ci][co][ph + tap*stride]; y [B][T*stride][Cout] */
+PTTS_API int ptts_dac_convtr1d_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const void* w_hi, const void* w_mid,
+                          const float* bias, int32_t Cout, int32_t stride, const float* snake_alpha, float* y,
+                          ptts_stream_t s);
+/* final conv (Cout = 1, k = 7) + tanh: w [7][Cin] fp32, y [B][T] */
+PTTS_API int ptts_dac_conv_out_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const float* w, const float* bias,
+                          const float* snake_alpha, float* y, ptts_stream_t s);
 
 #ifdef __cplusplus
 }

@@ -52,6 +52,8 @@ PROTOTYPES = {
     "ptts_last_error_string": (C.c_char_p, []),
     "ptts_scratch_floats": (c_i64, [_PM, c_i32]),
     "ptts_launch_count": (c_i64, []),
+    "ptts_diag_chain": (C.c_int, [c_i32, c_i32, c_i32, c_vp, c_vp]),
+    "ptts_diag_gemm_stamps": (C.c_int, [c_vp, c_i32]),
     "ptts_build_delay_mask": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "ptts_apply_delay_mask": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
     "ptts_dedelay": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp]),
@@ -70,6 +72,11 @@ PROTOTYPES = {
     "ptts_dac_conv1d": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32,
                                   c_vp, c_i32, c_vp]),
     "ptts_dac_convtr1d": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "ptts_dac_dequant_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32, c_vp, c_vp]),
+    "ptts_dac_conv1d_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp,
+                                      c_vp, c_vp]),
+    "ptts_dac_convtr1d_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
+    "ptts_dac_conv_out_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
 }
 
 _lib = None

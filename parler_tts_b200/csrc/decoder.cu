@@ -2,6 +2,8 @@
 // Every function only enqueues kernels on the caller's stream: no allocation, no synchronisation, graph-capturable.
 // Replaces /root/reference/parler_tts/modeling_parler_tts.py:794-978 (ParlerTTSDecoder.forward), 415-502 (layer),
 // 264-382 (attention), 1096-1185 (lm heads) for the generation path.
+#include <stdlib.h>
+
 #include "ops.cuh"
 
 namespace ptts {
@@ -91,11 +93,38 @@ static int ln_step(const PttsModel* m, const PttsState* s, const Path& path, Pen
   return layernorm(s->h, g, b, rows_out, H, 1e-5f, (int64_t)row_mul * H, (int64_t)row_add * H, s->xn, m->wdtype, st);
 }
 
+// Residual GEMMs (out_proj, fc2) write split-K partial sums that the next LayerNorm folds into the residual stream in
+// slice order (deterministic, no on-chip reduction); PTTS_GEMM=cluster selects the in-cluster DSMEM reduction instead.
+static bool split_k_partials_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_GEMM");
+    v = (e && e[0] == 'c') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+// PTTS_SKIP=<bitmask>: timing ablation ONLY (results are garbage): 1 LayerNorm, 2 QKV GEMM, 4 self-attention,
+// 8 residual GEMMs, 16 cross q GEMM, 32 cross-attention, 64 fc1, 128 heads.  Used by profiles/scripts/ablate.sh to get
+// the marginal cost of each kernel class inside the PDL-overlapped graph (ncu serialises launches and cannot).
+static int skip_mask() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_SKIP");
+    v = e ? atoi(e) : 0;
+  }
+  return v;
+}
+#define PTTS_UNLESS_SKIPPED(bit, expr) \
+  do {                                  \
+    if (!(skip_mask() & (bit))) PTTS_TRY(expr); \
+  } while (0)
+
 // h += x . w^T   (out_proj / fc2 with the residual add of modeling_parler_tts.py:460,483,492)
 static int residual_linear(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const void* x,
                            const void* w, int rows, int K, cudaStream_t st) {
   const int H = m->hidden, dt = m->wdtype;
-  if (path.gemm && path.ln && rows <= 256) {
+  if (path.gemm && path.ln && rows <= 256 && split_k_partials_enabled()) {
     int bn = 64;
     const int S = gemm_bf16_plan_splits(rows, H, K, &bn);
     if (S > 1) {
@@ -123,9 +152,9 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
   char* vs = (char*)s->kv_self + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->c_max) * es;
   const float scale = 1.0f / sqrtf((float)d);
   // self attention block
-  PTTS_TRY(ln_step(m, s, path, pend, L.ln1_g, L.ln1_b, rows, 1, 0, st));
+  PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln1_g, L.ln1_b, rows, 1, 0, st));
   if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
-    PTTS_TRY(gemm_bf16_scatter(s->xn, L.w_qkv, rows, 3 * H, H, 1, scale, s->q, ks, vs, H, heads, d, Tq, s->c_max,
+    PTTS_UNLESS_SKIPPED(2, gemm_bf16_scatter(s->xn, L.w_qkv, rows, 3 * H, H, 1, scale, s->q, ks, vs, H, heads, d, Tq, s->c_max,
                                ctx_base - Tq, ctx_dyn, st));
   } else {
     void* qkv = (void*)work_area(m, s);
@@ -133,25 +162,25 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
                              nullptr, qkv, dt, st));
     PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, s->c_max, ctx_base - Tq, ctx_dyn, scale, s->q, ks, vs, st));
   }
-  PTTS_TRY(attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn, Tq > 1,
-                              s->prompt_mask, s->P, s->attn, s->scratch, st));
-  PTTS_TRY(residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
+  PTTS_UNLESS_SKIPPED(4, attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn,
+                                            Tq > 1, s->prompt_mask, s->P, s->attn, s->scratch, st));
+  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
   // cross attention block (modeling_parler_tts.py:465-483)
   if (s->S > 0) {
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
     char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->S) * es;
-    PTTS_TRY(ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
-    PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale, PTTS_ACT_NONE, nullptr,
-                             nullptr, s->q, dt, st));
-    PTTS_TRY(attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0, s->enc_mask, s->S,
-                                s->attn, s->scratch, st));
-    PTTS_TRY(residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, st));
+    PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
+    PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale, PTTS_ACT_NONE,
+                                            nullptr, nullptr, s->q, dt, st));
+    PTTS_UNLESS_SKIPPED(32, attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0,
+                                               s->enc_mask, s->S, s->attn, s->scratch, st));
+    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, st));
   }
   // feed forward block
-  PTTS_TRY(ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
-  PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn, nullptr, nullptr,
-                           s->ffn, dt, st));
-  PTTS_TRY(residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, st));
+  PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
+  PTTS_UNLESS_SKIPPED(64, linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn,
+                                          nullptr, nullptr, s->ffn, dt, st));
+  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, st));
   return PTTS_OK;
 }
 

@@ -1,0 +1,44 @@
+// Diagnostics (not on the product path): dependent-launch chains used by profiles/ scripts to measure the per-kernel
+// latency floor of a CUDA-graph replay on the box (empty kernels, one-load kernels, with / without PDL).
+#include "gemm_common.cuh"
+
+namespace ptts {
+__global__ void diag_empty_kernel(float* buf) {
+  pdl_wait();
+  pdl_launch();
+  if (buf == nullptr && threadIdx.x == 9999) printf("x");
+}
+__global__ void diag_touch_kernel(float* buf, int n) {
+  pdl_wait();
+  pdl_launch();
+  const int i = blockIdx.x * blockDim.x + threadIdx.x;
+  if (i < n) buf[i] = __ldcg(buf + i) + 1.0f;
+}
+}  // namespace ptts
+
+using namespace ptts;
+
+// mode 0: n empty kernels (grid ctas x 128); mode 1: n kernels doing one dependent load+store per thread
+extern "C" int ptts_diag_chain(int32_t n, int32_t mode, int32_t ctas, float* buf, ptts_stream_t s) {
+  PTTS_CHECK_ARG(n >= 0 && ctas > 0 && buf, "diag_chain: bad arguments");
+  for (int i = 0; i < n; ++i) {
+    cudaError_t e;
+    if (mode == 0)
+      e = launch_k(diag_empty_kernel, dim3(ctas), dim3(128), 0, as_stream(s), buf);
+    else
+      e = launch_k(diag_touch_kernel, dim3(ctas), dim3(128), 0, as_stream(s), buf, ctas * 128);
+    if (e != cudaSuccess) {
+      set_error("diag_chain: %s", cudaGetErrorString(e));
+      return PTTS_E_LAUNCH;
+    }
+    PTTS_CHECK_LAUNCH("diag_chain");
+  }
+  return PTTS_OK;
+}
+
+// Copies the globaltimer stamps recorded by the tcgen05 GEMM under PTTS_GEMM_DBG=1 (8 x uint64 per launch, ring of 256)
+// to host memory; returns the number of launches recorded so far.  Synchronises the device (diagnostic only).
+extern "C" int ptts_diag_gemm_stamps(uint64_t* host, int32_t n_launches) {
+  cudaDeviceSynchronize();
+  return gemm::umma_read_stamps((unsigned long long*)host, n_launches);
+}

@@ -1,0 +1,362 @@
+// tcgen05 (UMMA) split-K GEMM for the decode step, "swap-AB": the weight tile is the 128-row A operand, the batch
+// rows are the 64-wide N operand, the fp32 accumulator [128 weight rows x 64 batch rows] lives in tensor memory.
+//   D[n][m] = sum_k W[n0 + n][k] * X[m][k]       (both operands K-major, SWIZZLE_128B shared-memory layout)
+// Why tcgen05 here although the step is HBM-bound: at M = 64 the decode step still needs ~46 GFLOP per 0.6 ms of
+// weight streaming (~75 TFLOP/s sustained, bursts of 400+ while a tile is resident); measured on B200 the legacy
+// mma.sync path with 4 warps per SM made every linear compute/latency-bound (5-17 us per launch, <= 1.2 TB/s of
+// weights, profiles/r01_gemm_sweep.txt).  One elected thread issues K/16 tcgen05.mma instructions per CTA instead.
+// Structure per CTA (128 threads): cp.async the whole W slab [128 x K/CS] (before griddepcontrol.wait: weights do
+// not depend on the previous kernel) and X slab [64 x K/CS] into 128-byte-swizzled rows -> fence.proxy.async ->
+// tcgen05.mma burst -> tcgen05.commit -> mbarrier -> tcgen05.ld (32x32b) -> transposed fp32 tile in shared memory ->
+// cluster barrier -> batched DSMEM loads of the CS K-slices, summed in rank order (deterministic) -> arrive at the
+// exit barrier -> fused epilogue (gemm_common.cuh) on 64/CS rows per CTA -> wait on the exit barrier.
+// (In-kernel stamps, profiles/scripts/gemm_stamps.py: pushing partials with 4-byte st.shared::cluster costs 7.9 us per
+// launch; unbatched DSMEM loads + a blocking exit barrier cost 3.2 us; hence batched pulls and a split barrier.)
+#include <stdlib.h>
+
+#include "gemm_common.cuh"
+
+namespace ptts {
+
+using namespace gemm;
+
+namespace {
+
+constexpr int UM = 128;            // weight rows per CTA (UMMA M)
+constexpr int UN = 64;             // batch rows per CTA (UMMA N)
+constexpr int KB64 = 64;           // K elements per 128-byte swizzled row block
+constexpr int PITCH3 = UM + 4;     // fp32 pitch of the transposed reduction tile [m][n]
+constexpr int WBLK = UM * 128;     // bytes of one W k-block (128 rows x 128 B)
+constexpr int XBLK = UN * 128;     // bytes of one X k-block
+constexpr uint32_t TMEM_COLS = 64;
+
+__device__ __forceinline__ uint32_t cluster_rank3() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_sync3() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ float2 ld_dsmem_f2_3(uint32_t local_addr, uint32_t rank) {
+  uint32_t ra;
+  float2 v;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(ra) : "r"(local_addr), "r"(rank));
+  asm volatile("ld.shared::cluster.v2.f32 {%0,%1}, [%2];\n" : "=f"(v.x), "=f"(v.y) : "r"(ra) : "memory");
+  return v;
+}
+
+// ROWS x 64 bf16 block: 128-byte rows, 16-byte chunk c of row r at chunk position c ^ (r & 7)  (= SWIZZLE_128B)
+template <int ROWS>
+__device__ __forceinline__ void load_block_sw128(uint32_t sbase, const __nv_bfloat16* g, int ld, int row0,
+                                                 int rows_total, int k0) {
+#pragma unroll
+  for (int i = threadIdx.x; i < ROWS * 8; i += NTH) {
+    const int r = i >> 3, c = i & 7;
+    const int gr = row0 + r;
+    const bool ok = gr < rows_total;
+    const __nv_bfloat16* src = ok ? g + (int64_t)gr * ld + k0 + c * 8 : g;
+    cp_async16(sbase + r * 128 + ((c ^ (r & 7)) << 4), src, ok);
+  }
+}
+
+// K-major, SWIZZLE_128B shared-memory matrix descriptor (cute::UMMA::SmemDescriptor): start >> 4 | LBO (unused for
+// swizzled K-major, 1) << 16 | SBO = 1024 B (8 rows x 128 B) >> 4 << 32 | version 1 << 46 | layout SWIZZLE_128B (2) << 61
+__device__ __forceinline__ uint64_t umma_desc_sw128(uint32_t saddr) {
+  return (uint64_t)((saddr >> 4) & 0x3FFF) | (1ull << 16) | (64ull << 32) | (1ull << 46) | (2ull << 61);
+}
+// kind::f16 instruction descriptor: D fp32, A/B bf16, both K-major, N = 64, M = 128
+constexpr uint32_t kIdesc = (1u << 4) | (1u << 7) | (1u << 10) | ((uint32_t)(UN >> 3) << 17) | ((uint32_t)(UM >> 4) << 24);
+
+__device__ __forceinline__ void umma_f16(uint32_t tmem_d, uint64_t adesc, uint64_t bdesc, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], %1, %2, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "l"(adesc), "l"(bdesc), "r"(kIdesc), "r"(accumulate)
+      : "memory");
+}
+
+__device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)[32]) {
+  asm volatile("tcgen05.ld.sync.aligned.32x32b.x32.b32 {%0, %1, %2, %3, %4, %5, %6, %7, %8, %9, %10, %11, %12, %13, %14, %15, %16, %17, %18, %19, %20, %21, %22, %23, %24, %25, %26, %27, %28, %29, %30, %31}, [%32];\n"
+               : "=r"(v[0]), "=r"(v[1]), "=r"(v[2]), "=r"(v[3]), "=r"(v[4]), "=r"(v[5]), "=r"(v[6]), "=r"(v[7]), "=r"(v[8]), "=r"(v[9]), "=r"(v[10]), "=r"(v[11]), "=r"(v[12]), "=r"(v[13]), "=r"(v[14]), "=r"(v[15]), "=r"(v[16]), "=r"(v[17]), "=r"(v[18]), "=r"(v[19]), "=r"(v[20]), "=r"(v[21]), "=r"(v[22]), "=r"(v[23]), "=r"(v[24]), "=r"(v[25]), "=r"(v[26]), "=r"(v[27]), "=r"(v[28]), "=r"(v[29]), "=r"(v[30]), "=r"(v[31])
+               : "r"(taddr)
+               : "memory");
+}
+// PTTS_GEMM_DBG=1: CTA (0,0,0) of every launch records SM-clock / globaltimer stamps (read back by
+// ptts_diag_gemm_stamps; profiles/scripts/gemm_stamps.py) - where inside the kernel does the time go?
+__device__ unsigned long long g_stamps[256 * 8];
+__device__ unsigned int g_stamp_idx;
+__device__ __forceinline__ unsigned long long gtime() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
+}
+#define STAMP(i)                                                    \
+  do {                                                              \
+    if (dbg_slot >= 0) g_stamps[dbg_slot * 8 + (i)] = gtime();      \
+  } while (0)
+
+// grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
+template <int EPI>
+__global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t mma_bar;
+  __shared__ uint32_t tmem_base_slot;
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
+  unsigned char* smem = smem_raw + (sbase - smem_u32(smem_raw));
+  const uint32_t sw = sbase, sx = sbase + KB * WBLK;
+  const int n0 = blockIdx.x * UM, m0 = blockIdx.y * UN;
+  const uint32_t rank = (EPI == EPI_PARTIAL) ? blockIdx.z : cluster_rank3();  // K slice of this CTA
+  const int kbeg = (int)rank * KB * KB64;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  int dbg_slot = -1;
+  if (dbg && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0)
+    dbg_slot = (int)(atomicAdd(&g_stamp_idx, 1u) & 255u);
+  STAMP(0);
+
+  for (int kb = 0; kb < KB; ++kb) load_block_sw128<UM>(sw + kb * WBLK, p.W, p.K, n0, p.N, kbeg + kb * KB64);
+  if (warp == 0) {  // tensor-memory allocation (one warp), barrier init (one thread)
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+  }
+  if (threadIdx.x == 32) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&mma_bar)), "r"(1) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  pdl_wait();
+  pdl_launch();
+  STAMP(1);
+  for (int kb = 0; kb < KB; ++kb) load_block_sw128<UN>(sx + kb * XBLK, p.X, p.K, m0, p.M, kbeg + kb * KB64);
+  cp_async_commit();
+  cp_async_wait<0>();
+  asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // cp.async (generic proxy) -> UMMA (async proxy)
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+  const uint32_t tmem_d = tmem_base_slot;
+  STAMP(2);
+
+  if (threadIdx.x == 0) {
+    for (int kb = 0; kb < KB; ++kb) {
+      const uint64_t ad = umma_desc_sw128(sw + kb * WBLK), bd = umma_desc_sw128(sx + kb * XBLK);
+#pragma unroll
+      for (int k = 0; k < KB64 / 16; ++k)  // +32 bytes (2 x 16 B) per UMMA_K = 16 inside the swizzle atom
+        umma_f16(tmem_d, ad + 2 * k, bd + 2 * k, (kb | k) ? 1u : 0u);
+    }
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(
+                     smem_u32(&mma_bar))
+                 : "memory");
+  }
+  {  // every thread waits for the MMA burst (bounded spin: a descriptor bug must trap, not hang the box)
+    uint32_t done = 0;
+    for (uint32_t spin = 0; !done; ++spin) {
+      asm volatile(
+          "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+          : "=r"(done)
+          : "r"(smem_u32(&mma_bar)), "r"(0)
+          : "memory");
+      if (spin > 4000000u) __trap();
+    }
+  }
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+  STAMP(3);
+
+  if constexpr (EPI == EPI_PARTIAL) {
+    // split-K partial sums straight to global memory [slice][m][n] (coalesced along n); the LayerNorm that consumes
+    // the residual stream next adds them up in slice order (deterministic) - no cluster, no on-chip reduction
+    const int n = n0 + warp * 32 + lane;
+#pragma unroll
+    for (int half = 0; half < 2; ++half) {
+      uint32_t v[32];
+      tmem_ld_32x32b_x32(tmem_d + ((uint32_t)(warp * 32) << 16) + half * 32, v);
+      asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+      for (int j = 0; j < 32; ++j) {
+        const int m = m0 + half * 32 + j;
+        if (m < p.M && n < p.N) p.part[((int64_t)rank * p.M + m) * p.N + n] = __uint_as_float(v[j]);
+      }
+    }
+    asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+    __syncthreads();
+    if (warp == 0) {
+      asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+    }
+    STAMP(6);
+    return;
+  }
+  // accumulator -> registers -> transposed fp32 tile red[m][n] in my own shared memory (the operand slabs are dead):
+  // thread (warp w, lane l) owns weight row n = 32 w + l and the 64 batch-row columns
+  const int rows_per = UN / CS;
+  float* red = reinterpret_cast<float*>(smem);
+#pragma unroll
+  for (int half = 0; half < 2; ++half) {
+    uint32_t v[32];
+    tmem_ld_32x32b_x32(tmem_d + ((uint32_t)(warp * 32) << 16) + half * 32, v);
+    asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+    for (int j = 0; j < 32; ++j) red[(half * 32 + j) * PITCH3 + warp * 32 + lane] = __uint_as_float(v[j]);
+  }
+  // residual pairs of my first 4 epilogue elements depend on earlier kernels only: fetch them now, the L2 round trip
+  // hides behind the cluster barrier
+  const int pairs = rows_per * (UM / 2);
+  float2 res[4];
+  auto fetch_res = [&](int e0) {
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      res[u] = make_float2(0.f, 0.f);
+      if constexpr (EPI == EPI_STORE) {
+        const int e = e0 + u * NTH;
+        const int row = m0 + (int)rank * rows_per + e / (UM / 2), col = n0 + (e % (UM / 2)) * 2;
+        if (p.residual && e < pairs && row < p.M && col < p.N)
+          res[u] = __ldcg(reinterpret_cast<const float2*>(p.residual + (int64_t)row * p.N + col));
+      }
+    }
+  };
+  fetch_res(threadIdx.x);
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  cluster_sync3();  // all CS partial tiles are visible cluster-wide
+  STAMP(4);
+  if (warp == 0) {
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+  }
+
+  // deterministic reduction over the CS K-slices (rank order): all DSMEM loads of up to 4 elements are issued
+  // back to back; after the last batch the CTA ARRIVES at the exit barrier (peers may release my tile as soon as they
+  // have read it) and only waits on it after its own global stores
+  for (int e0 = threadIdx.x; e0 < pairs; e0 += NTH * 4) {
+    if (e0 != (int)threadIdx.x) fetch_res(e0);
+    float2 part[4][8];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * NTH;
+      const int lr = (int)rank * rows_per + e / (UM / 2), lc = (e % (UM / 2)) * 2;
+      const uint32_t la = smem_u32(red + lr * PITCH3 + lc);
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < CS && e < pairs) part[u][r] = ld_dsmem_f2_3(la, (uint32_t)r);
+    }
+    if (e0 + NTH * 4 >= pairs + (int)threadIdx.x)  // uniform: the last batch of this CTA
+      asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * NTH;
+      if (e >= pairs) break;
+      float v0 = 0.f, v1 = 0.f;
+#pragma unroll
+      for (int r = 0; r < 8; ++r)
+        if (r < CS) {
+          v0 += part[u][r].x;
+          v1 += part[u][r].y;
+        }
+      const int row = m0 + (int)rank * rows_per + e / (UM / 2), col = n0 + (e % (UM / 2)) * 2;
+      if (row < p.M && col < p.N) epilogue_pair<EPI>(p, row, col, 0, v0, v1, &res[u]);
+    }
+  }
+  STAMP(5);
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");  // nobody exits while a peer reads its tile
+  STAMP(6);
+}
+
+constexpr int kMaxKB64 = 8;  // <= 512 K elements per CTA: (128 + 64) rows x 1 KB = 192 KB of operand slabs
+
+int plan_cluster3(int M, int N, int K) {
+  if (K % 128 != 0) return 0;
+  const int kblocks = K / KB64;
+  const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
+  static int forced = -1;
+  if (forced < 0) {
+    const char* e = getenv("PTTS_CS");
+    forced = e ? atoi(e) : 0;
+  }
+  if (forced > 0 && kblocks % forced == 0 && kblocks / forced <= kMaxKB64) return forced;
+  for (int cs = 1; cs <= 8; cs <<= 1) {
+    if (kblocks % cs) continue;
+    const int kb = kblocks / cs;
+    if (kb > kMaxKB64) continue;
+    const bool last = cs == 8 || (kblocks % (cs * 2)) != 0;
+    if ((nt * cs >= 120 && (kb <= 4 || nt * cs <= 148)) || last) return cs;
+  }
+  return 0;
+}
+
+template <int EPI>
+int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
+  const int cs = EPI == EPI_PARTIAL ? splits : plan_cluster3(p.M, p.N, p.K);
+  if (cs == 0) return PTTS_E_UNSUPPORTED;
+  const int kb = p.K / KB64 / cs;
+  size_t smem = (size_t)kb * (WBLK + XBLK);  // operand slabs, reused as the fp32 reduction tile
+  const size_t red = (size_t)UN * PITCH3 * sizeof(float);
+  if (smem < red) smem = red;
+  smem += 1024;  // alignment slack
+  static size_t configured = 0;
+  if (smem > configured) {
+    cudaFuncSetAttribute(umma_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    configured = smem;
+  }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = dim3((p.N + UM - 1) / UM, (p.M + UN - 1) / UN, cs);
+  cfg.blockDim = dim3(NTH);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int n = 0;
+  attr[n].id = cudaLaunchAttributeClusterDimension;
+  attr[n].val.clusterDim.x = 1;
+  attr[n].val.clusterDim.y = 1;
+  attr[n].val.clusterDim.z = EPI == EPI_PARTIAL ? 1 : cs;
+  ++n;
+  if (pdl_enabled()) {
+    attr[n].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[n].val.programmaticStreamSerializationAllowed = 1;
+    ++n;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = n;
+  static int dbg = -1;
+  if (dbg < 0) {
+    const char* ev = getenv("PTTS_GEMM_DBG");
+    dbg = (ev && ev[0] == '1') ? 1 : 0;
+  }
+  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg);
+  if (e != cudaSuccess) {
+    set_error("umma_gemm launch: %s", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return PTTS_E_LAUNCH;
+  }
+  PTTS_CHECK_LAUNCH("umma_gemm");
+  return PTTS_OK;
+}
+
+}  // namespace
+
+namespace gemm {
+int umma_read_stamps(unsigned long long* host, int n_launches) {
+  unsigned int idx = 0;
+  cudaMemcpyFromSymbol(&idx, g_stamp_idx, sizeof(idx));
+  cudaMemcpyFromSymbol(host, g_stamps, sizeof(unsigned long long) * 8 * (n_launches > 256 ? 256 : n_launches));
+  return (int)idx;
+}
+// split-K plan of the PARTIAL variant: smallest S in {2,4,8,16} that gives >= ~120 CTAs (else the largest that fits)
+int umma_plan_splits(int M, int N, int K) {
+  if (K % 128 != 0) return 0;
+  const int kblocks = K / KB64;
+  const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
+  int best = 0;
+  for (int s = 2; s <= kMaxSplitK; s <<= 1) {
+    if (kblocks % s || kblocks / s > kMaxKB64) continue;
+    best = s;
+    if (nt * s >= 120) break;
+  }
+  return best;
+}
+int umma_gemm_partial(const GemmParams& p, int splits, cudaStream_t st) {
+  return launch_umma<EPI_PARTIAL>(p, st, splits);
+}
+int umma_gemm_store(const GemmParams& p, cudaStream_t st) { return launch_umma<EPI_STORE>(p, st); }
+int umma_gemm_scatter(const GemmParams& p, cudaStream_t st) { return launch_umma<EPI_SCATTER>(p, st); }
+}  // namespace gemm
+
+}  // namespace ptts

@@ -58,6 +58,79 @@ class DacDecoderEngine:
         n = len(self.rates)
         self.alpha_out = sd[f"decoder.model.{n + 1}.alpha"].float().reshape(-1).contiguous()
         self.conv_out = _fold(sd, f"decoder.model.{n + 2}")
+        # fast family: channels-last activations + tensor-core implicit GEMM (needs channel counts that tile by 32)
+        chans = [self.latent, self.conv_in[0].shape[0]] + [b["convt"][0].shape[1] for b in self.blocks]
+        self.nwc = (impl == cabi.IMPL_FAST and all(c % 32 == 0 for c in chans) and self.conv_out[0].shape[0] == 1
+                    and self.latent % 4 == 0 and all(s >= 2 for s in self.rates))
+        if self.nwc:
+            self._prep_nwc()
+
+    # ---- fast family: pre-split bf16 weight planes (w = hi + mid), tap-major, channel-contiguous --------------
+    @staticmethod
+    def _split(w):
+        hi = w.to(torch.bfloat16)
+        mid = (w - hi.float()).to(torch.bfloat16)
+        return hi.contiguous(), mid.contiguous()
+
+    def _prep_nwc(self):
+        def conv(wb):  # [Cout][Cin][k] -> [k][Cout][Cin]
+            w, b = wb
+            return self._split(w.permute(2, 0, 1).contiguous()) + (b, w.shape[0], w.shape[2])
+
+        def convt(wb, s):  # [Cin][Cout][2s] -> [2][s*Cout][Cin], index (tap, ph*Cout + co, ci) = w[ci][co][ph + tap*s]
+            w, b = wb
+            cin, cout, _ = w.shape
+            w2 = w.permute(2, 1, 0).reshape(2, s * cout, cin).contiguous()
+            return self._split(w2) + (b, cout)
+
+        self.f_conv_in = conv(self.conv_in)
+        self.f_blocks = []
+        for blk in self.blocks:
+            fb = dict(stride=blk["stride"], alpha=blk["alpha"], convt=convt(blk["convt"], blk["stride"]), res=[])
+            for r in blk["res"]:
+                fb["res"].append(dict(dil=r["dil"], a1=r["a1"], c1=conv(r["c1"]), a2=r["a2"], c2=conv(r["c2"])))
+            self.f_blocks.append(fb)
+        w, b = self.conv_out
+        self.f_conv_out = (w[0].t().contiguous(), b)  # [7][Cin]
+
+    def _conv_nwc(self, x, wt, dil=1, alpha=None, residual=None):
+        hi, mid, bias, cout, k = wt
+        B, T, Cin = x.shape
+        y = torch.empty(B, T, cout, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_conv1d_nwc", cabi.ptr(x), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), cout, k,
+                  dil, cabi.ptr(alpha), cabi.ptr(residual), cabi.ptr(y), cabi.stream_ptr())
+        return y
+
+    def _convt_nwc(self, x, wt, stride, alpha):
+        hi, mid, bias, cout = wt
+        B, T, Cin = x.shape
+        y = torch.empty(B, T * stride, cout, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_convtr1d_nwc", cabi.ptr(x), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), cout,
+                  stride, cabi.ptr(alpha), cabi.ptr(y), cabi.stream_ptr())
+        return y
+
+    def dequant_nwc(self, codes):
+        """codes (B, K, F) int64 -> z (B, F, latent) fp32, channels-last."""
+        codes = codes.to(self.device, torch.int64).contiguous()
+        B, K, F = codes.shape
+        z = torch.empty(B, F, self.latent, device=self.device, dtype=torch.float32)
+        cabi.call("ptts_dac_dequant_nwc", cabi.ptr(codes), B, K, F, K * F, F, cabi.ptr(self.tables),
+                  self.codebook_size, self.latent, cabi.ptr(z), cabi.stream_ptr())
+        return z
+
+    def decode_latents_nwc(self, z):
+        x = self._conv_nwc(z, self.f_conv_in)
+        for blk in self.f_blocks:
+            x = self._convt_nwc(x, blk["convt"], blk["stride"], blk["alpha"])
+            for r in blk["res"]:
+                y = self._conv_nwc(x, r["c1"], dil=r["dil"], alpha=r["a1"])
+                x = self._conv_nwc(y, r["c2"], alpha=r["a2"], residual=x)
+        B, T, Cin = x.shape
+        w, b = self.f_conv_out
+        out = torch.empty(B, 1, T, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_conv_out_nwc", cabi.ptr(x), B, T, Cin, cabi.ptr(w), cabi.ptr(b), cabi.ptr(self.alpha_out),
+                  cabi.ptr(out), cabi.stream_ptr())
+        return out
 
     # ---- single launches -------------------------------------------------------------------------------------
     def _conv(self, x, wb, dil=1, alpha=None, residual=None, tanh=False):
@@ -102,7 +175,10 @@ class DacDecoderEngine:
         if F == 0:
             return torch.zeros(B, 1, 0, device=self.device)
         per = max(1, max_frames_per_call // F)
-        outs = [self.decode_latents(self.dequant(codes[i : i + per])) for i in range(0, B, per)]
+        if self.nwc:
+            outs = [self.decode_latents_nwc(self.dequant_nwc(codes[i : i + per])) for i in range(0, B, per)]
+        else:
+            outs = [self.decode_latents(self.dequant(codes[i : i + per])) for i in range(0, B, per)]
         return torch.cat(outs, dim=0) if len(outs) > 1 else outs[0]
 
     def decode_generated(self, codes, bos, pad, eos):

@@ -181,3 +181,70 @@ def test_fast_path_launches_its_own_kernels_and_graph_replays_match_eager():
     assert torch.equal(outs[0], outs[1])
     st = m._state_cache[1]
     assert st.graph is not None and st.graph_launches == 2 * 11 + 3, st.graph_launches
+
+
+# ------------------------------------------------------------------------------------------------ DAC fast family
+def _split(w):
+    hi = w.to(torch.bfloat16)
+    return hi.contiguous(), (w - hi.float()).to(torch.bfloat16).contiguous()
+
+
+@pytest.mark.parametrize("Cin,Cout,k,dil,T", [(96, 96, 7, 9, 700), (192, 192, 1, 1, 300), (1024, 1536, 7, 1, 37),
+                                              (384, 384, 7, 3, 129), (32, 26, 7, 1, 5)])
+def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T):
+    g = torch.Generator().manual_seed(Cin + k + dil)
+    B = 2
+    x = torch.randn(B, Cin, T, generator=g).to(DEV)
+    w = (torch.randn(Cout, Cin, k, generator=g) / (Cin * k) ** 0.5).to(DEV)
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    alpha = (1.0 + 0.2 * torch.randn(Cin, generator=g)).abs().add(0.05).to(DEV)
+    res = torch.randn(B, Cout, T, generator=g).to(DEV)
+    xs = x + (1.0 / (alpha[None, :, None] + 1e-9)) * torch.sin(alpha[None, :, None] * x) ** 2
+    want = torch.nn.functional.conv1d(xs.double(), w.double(), bias.double(), dilation=dil,
+                                      padding=dil * (k - 1) // 2).float() + res
+    hi, mid = _split(w.permute(2, 0, 1).contiguous())
+    x_nwc, res_nwc = x.transpose(1, 2).contiguous(), res.transpose(1, 2).contiguous()
+    y = torch.empty(B, T, Cout, device=DEV)
+    cabi.call("ptts_dac_conv1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, k,
+              dil, cabi.ptr(alpha), cabi.ptr(res_nwc), cabi.ptr(y), cabi.stream_ptr())
+    err = float((y.transpose(1, 2) - want).abs().max())
+    assert err < 2e-4 * max(1.0, float(want.abs().max())), err
+
+
+@pytest.mark.parametrize("Cin,Cout,s,T", [(1536, 768, 8, 11), (192, 96, 2, 300), (64, 32, 4, 130)])
+def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T):
+    g = torch.Generator().manual_seed(Cin + s)
+    B = 2
+    x = torch.randn(B, Cin, T, generator=g).to(DEV)
+    w = (torch.randn(Cin, Cout, 2 * s, generator=g) / (Cin * 2) ** 0.5).to(DEV)
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    alpha = (1.0 + 0.2 * torch.randn(Cin, generator=g)).abs().add(0.05).to(DEV)
+    xs = x + (1.0 / (alpha[None, :, None] + 1e-9)) * torch.sin(alpha[None, :, None] * x) ** 2
+    want = torch.nn.functional.conv_transpose1d(xs.double(), w.double(), bias.double(), stride=s,
+                                                padding=(s + 1) // 2).float()
+    assert want.shape[-1] == T * s
+    hi, mid = _split(w.permute(2, 1, 0).reshape(2, s * Cout, Cin).contiguous())
+    x_nwc = x.transpose(1, 2).contiguous()
+    y = torch.empty(B, T * s, Cout, device=DEV)
+    cabi.call("ptts_dac_convtr1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, s,
+              cabi.ptr(alpha), cabi.ptr(y), cabi.stream_ptr())
+    err = float((y.transpose(1, 2) - want).abs().max())
+    assert err < 2e-4 * max(1.0, float(want.abs().max())), err
+
+
+def test_dac_fast_equals_simple_on_ragged_batch():
+    """Channels-last tensor-core DAC == fp32 CUDA-core DAC (1e-3) through the batched and the per-sample path."""
+    from oracle import dac_oracle
+    from parler_tts_b200.dac import DacDecoderEngine
+
+    sd = dac_oracle.random_dac_state(dac_oracle.DAC_44K, seed=4)
+    fast, simple = DacDecoderEngine(sd, DEV, impl=cabi.IMPL_FAST), DacDecoderEngine(sd, DEV, impl=cabi.IMPL_SIMPLE)
+    assert fast.nwc and not simple.nwc
+    g = torch.Generator().manual_seed(1)
+    codes = torch.randint(0, 1024, (3, 9, 40), generator=g).to(DEV)
+    a, b = fast.decode(codes), simple.decode(codes)
+    assert a.shape == b.shape == (3, 1, 512 * 40)
+    assert float((a - b).abs().max()) < 1e-3
+    codes[1, :, 30:] = 1024
+    a, b = fast.decode_generated(codes, 1025, 1024, 1024), simple.decode_generated(codes, 1025, 1024, 1024)
+    assert a.shape == b.shape and float((a - b).abs().max()) < 1e-3
