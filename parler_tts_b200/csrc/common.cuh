@@ -110,6 +110,31 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 
+// ---- timeline diagnostics (PTTS_TIMELINE=1): every fast-family launch gets 4 uint64 slots {first CTA start, first /
+// last CTA past griddepcontrol.wait, last CTA end} filled with globaltimer by atomics; null pointer = disabled.
+struct TL {
+  unsigned long long* p;
+};
+TL tl_next(int kind);  // host: next timeline slot (null unless PTTS_TIMELINE=1); kind = tag of the launch site
+__device__ __forceinline__ unsigned long long gtimer_ns() {
+  unsigned long long t;
+  asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
+  return t;
+}
+__device__ __forceinline__ void tl_start(TL t) {
+  if (t.p && threadIdx.x == 0) atomicMin(t.p, gtimer_ns());
+}
+__device__ __forceinline__ void tl_dep(TL t) {
+  if (t.p && threadIdx.x == 0) {
+    const unsigned long long n = gtimer_ns();
+    atomicMin(t.p + 1, n);
+    atomicMax(t.p + 2, n);
+  }
+}
+__device__ __forceinline__ void tl_end(TL t) {
+  if (t.p && threadIdx.x == 0) atomicMax(t.p + 3, gtimer_ns());
+}
+
 // value of a dynamic scalar: base + *dyn (dyn may be null)
 __device__ __forceinline__ int dyn_value(int base, const int* dyn) { return base + (dyn ? *dyn : 0); }
 

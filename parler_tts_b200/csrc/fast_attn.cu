@@ -8,6 +8,8 @@
 // thread; scores live in shared memory between the two passes (K pass -> softmax -> V pass).  With fewer than ~600
 // (head, utterance) pairs the context is split across CTAs (split-KV) and merged by a tiny combine kernel.
 // Masked keys take finfo(dtype).min like the reference's additive mask (a fully masked row averages all keys).
+#include <stdlib.h>
+
 #include "ops.cuh"
 
 namespace ptts {
@@ -15,6 +17,8 @@ namespace ptts {
 namespace {
 
 constexpr int NT = 128;
+
+__device__ __forceinline__ uint32_t smem_addr(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
 
 template <typename T> struct Chunk;
 template <> struct Chunk<__nv_bfloat16> {
@@ -72,7 +76,7 @@ template <typename T, int D>
 __global__ void __launch_bounds__(NT)
 attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
                    int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask, int mask_len,
-                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap) {
+                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, TL tl) {
   constexpr int E = Chunk<T>::E;     // elements per 16-byte chunk
   constexpr int TPK = D / E;         // threads per key row
   constexpr int KPB = NT / TPK;      // key rows per CTA pass
@@ -85,8 +89,10 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* _
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = tid / TPK, c = tid % TPK;
   const int H = heads * D;
+  tl_start(tl);
   pdl_wait();
   pdl_launch();
+  tl_dep(tl);
   const int ctx = dyn_value(ctx_base, ctx_dyn);
   const int chunk = (ctx + splits - 1) / splits;
   const int j0 = sp * chunk;
@@ -98,22 +104,28 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* _
   const T* vb = cv + ((int64_t)b * heads + hd) * (int64_t)c_stride * D + c * E;
   const float neg = finfo_min<T>();
 
-  // ---- pass 1: scores = q . K^T (masked)
-  float lmax = -INFINITY;
-  for (int base = j0; base < j1; base += KPB * U) {
-    uint4 raw[U];
+  // Loads are software-pipelined: the next batch of U rows per thread is requested before the current one is
+  // consumed, and the first V batch is requested before the softmax reductions, so HBM never idles behind a barrier.
+  auto load_batch = [&](uint4 (&raw)[U], const T* base_ptr, int base) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int j = base + u * KPB + g;
-      if (j < j1) raw[u] = Chunk<T>::load_raw(kb + (int64_t)j * D);
+      if (j < j1) raw[u] = Chunk<T>::load_raw(base_ptr + (int64_t)j * D);
     }
+  };
+  // ---- pass 1: scores = q . K^T (masked)
+  float lmax = -INFINITY;
+  uint4 cur[U], nxt[U];
+  load_batch(cur, kb, j0);
+  for (int base = j0; base < j1; base += KPB * U) {
+    if (base + KPB * U < j1) load_batch(nxt, kb, base + KPB * U);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int j = base + u * KPB + g;
       float dot = 0.f;
       if (j < j1) {
         float kf[E];
-        Chunk<T>::unpack(raw[u], kf);
+        Chunk<T>::unpack(cur[u], kf);
 #pragma unroll
         for (int e = 0; e < E; ++e) dot = fmaf(qv[e], kf[e], dot);
       }
@@ -127,7 +139,10 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* _
         lmax = fmaxf(lmax, s);
       }
     }
+#pragma unroll
+    for (int u = 0; u < U; ++u) cur[u] = nxt[u];
   }
+  load_batch(cur, vb, j0);  // first V rows travel while the block reduces max / sum
   lmax = warp_max(lmax);
   if (lane == 0) red[warp] = lmax;
   __syncthreads();
@@ -149,23 +164,20 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* _
 #pragma unroll
   for (int e = 0; e < E; ++e) acc[e] = 0.f;
   for (int base = j0; base < j1; base += KPB * U) {
-    uint4 raw[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int j = base + u * KPB + g;
-      if (j < j1) raw[u] = Chunk<T>::load_raw(vb + (int64_t)j * D);
-    }
+    if (base + KPB * U < j1) load_batch(nxt, vb, base + KPB * U);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int j = base + u * KPB + g;
       if (j < j1) {
         float vf[E];
-        Chunk<T>::unpack(raw[u], vf);
+        Chunk<T>::unpack(cur[u], vf);
         const float pj = sc[j - j0] * inv;
 #pragma unroll
         for (int e = 0; e < E; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
       }
     }
+#pragma unroll
+    for (int u = 0; u < U; ++u) cur[u] = nxt[u];
   }
 #pragma unroll
   for (int e = 0; e < E; ++e) ored[g * D + c * E + e] = acc[e];
@@ -185,6 +197,177 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* _
       }
     }
   }
+  tl_end(tl);
+}
+
+// ---- bulk-copy (TMA engine, cp.async.bulk) variant: the K rows and then the V rows of this CTA's context stream
+// through a 4-stage shared-memory ring in 8 KB chunks; ONE thread issues the copies (no per-thread global loads, no
+// scoreboard stalls, 32 KB in flight per CTA and ~190 KB per SM), every thread waits on the stage's mbarrier and reads
+// its 16-byte pieces from shared memory.  K and V chunks form one sequence, so V is already travelling while the block
+// reduces the softmax statistics.
+constexpr int BULK_STAGES = 4;
+constexpr int BULK_BYTES = 8192;
+
+__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
+  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
+}
+__device__ __forceinline__ void mbar_wait_parity(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > 100000000u) __trap();  // a protocol bug must fail loudly, not hang the GPU
+  }
+}
+__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
+               "l"(src), "r"(bytes), "r"(bar)
+               : "memory");
+}
+
+template <typename T, int D>
+__global__ void __launch_bounds__(NT)
+attn_decode_bulk_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads,
+                        int c_stride, int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask,
+                        int mask_len, T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, TL tl) {
+  constexpr int E = Chunk<T>::E;
+  constexpr int TPK = D / E;                          // threads per key row
+  constexpr int KPB = NT / TPK;                       // key rows per pass of the CTA
+  constexpr int ROWB = D * (int)sizeof(T);            // bytes per key row
+  constexpr int KCH = BULK_BYTES / ROWB;              // key rows per chunk
+  extern __shared__ __align__(128) unsigned char smraw[];
+  __shared__ __align__(8) uint64_t full_bar[BULK_STAGES];
+  unsigned char* ring = smraw;                                            // [BULK_STAGES][BULK_BYTES]
+  float* sc = reinterpret_cast<float*>(smraw + BULK_STAGES * BULK_BYTES);  // [sc_cap]
+  float* red = sc + sc_cap;                                               // [8]
+  float* ored = red + 8;                                                  // [KPB][D]
+  const int hd = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
+  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
+  const int g = tid / TPK, c = tid % TPK;
+  const int H = heads * D;
+  tl_start(tl);
+  if (tid == 0) {
+#pragma unroll
+    for (int i = 0; i < BULK_STAGES; ++i) mbar_init(smem_addr(&full_bar[i]), 1);
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  __syncthreads();
+  pdl_wait();
+  pdl_launch();
+  tl_dep(tl);
+  const int ctx = dyn_value(ctx_base, ctx_dyn);
+  const int chunk = (ctx + splits - 1) / splits;
+  const int j0 = sp * chunk;
+  const int j1 = min(ctx, j0 + chunk);
+  const int n = max(j1 - j0, 0);
+  const int nk = (n + KCH - 1) / KCH;  // chunks per operand; sequence = K chunks 0..nk-1, then V chunks 0..nk-1
+  const T* kb = ck + (((int64_t)b * heads + hd) * (int64_t)c_stride + j0) * D;
+  const T* vb = cv + (((int64_t)b * heads + hd) * (int64_t)c_stride + j0) * D;
+  auto issue = [&](int i) {  // thread 0 only
+    const int op = i >= nk, ci = op ? i - nk : i;
+    const int rows = min(KCH, n - ci * KCH);
+    const T* src = (op ? vb : kb) + (int64_t)ci * KCH * D;
+    bulk_load(smem_addr(ring + (i % BULK_STAGES) * BULK_BYTES), src, (uint32_t)(rows * ROWB),
+              smem_addr(&full_bar[i % BULK_STAGES]));
+  };
+  if (tid == 0)
+    for (int i = 0; i < BULK_STAGES && i < 2 * nk; ++i) issue(i);
+  float qv[E];
+  Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
+  const float neg = finfo_min<T>();
+
+  // ---- pass 1: scores
+  float lmax = -INFINITY;
+  for (int i = 0; i < nk; ++i) {
+    mbar_wait_parity(smem_addr(&full_bar[i % BULK_STAGES]), (uint32_t)((i / BULK_STAGES) & 1));
+    const unsigned char* st = ring + (i % BULK_STAGES) * BULK_BYTES;
+    const int rows = min(KCH, n - i * KCH);
+#pragma unroll
+    for (int r0 = 0; r0 < KCH; r0 += KPB) {
+      const int r = r0 + g;
+      float dot = 0.f;
+      if (r < rows) {
+        float kf[E];
+        Chunk<T>::unpack(*reinterpret_cast<const uint4*>(st + r * ROWB + c * 16), kf);
+#pragma unroll
+        for (int e = 0; e < E; ++e) dot = fmaf(qv[e], kf[e], dot);
+      }
+#pragma unroll
+      for (int o = TPK / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+      if (c == 0 && r < rows) {
+        const int j = j0 + i * KCH + r;
+        bool keep = true;
+        if (key_mask && j < mask_len) keep = key_mask[(int64_t)b * mask_len + j] != 0;
+        const float s = keep ? dot : neg;
+        sc[i * KCH + r] = s;
+        lmax = fmaxf(lmax, s);
+      }
+    }
+    __syncthreads();  // everyone is done with this stage
+    if (tid == 0 && i + BULK_STAGES < 2 * nk) issue(i + BULK_STAGES);
+  }
+  lmax = warp_max(lmax);
+  if (lane == 0) red[warp] = lmax;
+  __syncthreads();
+  const float mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
+  float lsum = 0.f;
+  for (int i = tid; i < n; i += NT) {
+    const float e = expf(sc[i] - mx);
+    sc[i] = e;
+    lsum += e;
+  }
+  lsum = warp_sum(lsum);
+  if (lane == 0) red[4 + warp] = lsum;
+  __syncthreads();
+  const float total = red[4] + red[5] + red[6] + red[7];
+  const float inv = (splits == 1 && n > 0) ? 1.0f / total : 1.0f;
+
+  // ---- pass 3: out = sum_j p_j V_j
+  float acc[E];
+#pragma unroll
+  for (int e = 0; e < E; ++e) acc[e] = 0.f;
+  for (int i = nk; i < 2 * nk; ++i) {
+    mbar_wait_parity(smem_addr(&full_bar[i % BULK_STAGES]), (uint32_t)((i / BULK_STAGES) & 1));
+    const unsigned char* st = ring + (i % BULK_STAGES) * BULK_BYTES;
+    const int ci = i - nk;
+    const int rows = min(KCH, n - ci * KCH);
+#pragma unroll
+    for (int r0 = 0; r0 < KCH; r0 += KPB) {
+      const int r = r0 + g;
+      if (r < rows) {
+        float vf[E];
+        Chunk<T>::unpack(*reinterpret_cast<const uint4*>(st + r * ROWB + c * 16), vf);
+        const float pj = sc[ci * KCH + r] * inv;
+#pragma unroll
+        for (int e = 0; e < E; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
+      }
+    }
+    __syncthreads();
+    if (tid == 0 && i + BULK_STAGES < 2 * nk) issue(i + BULK_STAGES);
+  }
+#pragma unroll
+  for (int e = 0; e < E; ++e) ored[g * D + c * E + e] = acc[e];
+  __syncthreads();
+  if (tid < D) {
+    float o = 0.f;
+#pragma unroll
+    for (int gg = 0; gg < KPB; ++gg) o += ored[gg * D + tid];
+    if (splits == 1) {
+      out[(int64_t)b * H + hd * D + tid] = from_f<T>(o);
+    } else {
+      float* pp = part + (((int64_t)b * heads + hd) * splits + sp) * (D + 2);
+      pp[2 + tid] = o;
+      if (tid == 0) {
+        pp[0] = n > 0 ? mx : -INFINITY;
+        pp[1] = n > 0 ? total : 0.f;
+      }
+    }
+  }
+  tl_end(tl);
 }
 
 template <typename T, int D>
@@ -223,20 +406,42 @@ int launch_decode(const void* q, const void* ck, const void* cv, int B, int head
   constexpr int D = 64;
   constexpr int KPB = NT / (D / Chunk<T>::E);
   const int splits = plan_splits(B, heads, c_stride);
-  const int cap = (c_stride + splits - 1) / splits + 1;
-  const size_t smem = sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
-  if (smem > 48 * 1024) {
+  const int cap = ((c_stride + splits - 1) / splits + 1 + 63) / 64 * 64 + 64;
+  // PTTS_ATTN=bulk selects the cp.async.bulk (TMA engine) ring variant.  Measured on B200 at B=64, ctx 466 (bench.py
+  // roofline leg): software-pipelined ld.global.cg 23.2 us = 5.26 TB/s (80 % of the measured copy peak); bulk ring
+  // 28.3 us = 4.33 TB/s -> the per-thread vector loads are the default.
+  static int use_bulk = -1;
+  if (use_bulk < 0) {
+    const char* ev = getenv("PTTS_ATTN");
+    use_bulk = (ev && ev[0] == 'b') ? 1 : 0;
+  }
+  PTTS_CHECK_ARG(splits == 1 || scratch, "attention_fast: split-KV needs scratch");
+  cudaError_t e;
+  if (use_bulk) {
+    const size_t smem = (size_t)BULK_STAGES * BULK_BYTES + sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
     static size_t configured = 0;
-    if (smem > configured) {
-      cudaFuncSetAttribute(attn_decode_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (smem > 48 * 1024 && smem > configured) {
+      cudaFuncSetAttribute(attn_decode_bulk_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
+    PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
+    e = launch_k(attn_decode_bulk_kernel<T, D>, dim3(heads, B, splits), dim3(NT), smem, st, (const T*)q, (const T*)ck,
+                 (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch, splits, cap,
+                 tl_next(c_stride > 64 ? 2 : 3));
+  } else {
+    const size_t smem = sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
+    if (smem > 48 * 1024) {
+      static size_t configured = 0;
+      if (smem > configured) {
+        cudaFuncSetAttribute(attn_decode_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        configured = smem;
+      }
+    }
+    PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
+    e = launch_k(attn_decode_kernel<T, D>, dim3(heads, B, splits), dim3(NT), smem, st, (const T*)q, (const T*)ck,
+                 (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch, splits, cap,
+                 tl_next(c_stride > 64 ? 2 : 3));
   }
-  PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
-  PTTS_CHECK_ARG(splits == 1 || scratch, "attention_fast: split-KV needs scratch");
-  cudaError_t e = launch_k(attn_decode_kernel<T, D>, dim3(heads, B, splits), dim3(NT), smem, st, (const T*)q,
-                           (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out,
-                           scratch, splits, cap);
   if (e != cudaSuccess) {
     set_error("attn_decode launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;

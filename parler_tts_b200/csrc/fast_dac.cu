@@ -291,6 +291,10 @@ int launch_conv(const ConvParams& p, int B, cudaStream_t st) {
 }
 
 int launch_conv_any(const ConvParams& p, int B, cudaStream_t st) {
+  if (dac_umma_enabled()) {  // tcgen05 kernel (fast_dac2.cu); shapes it does not take fall through to mma.sync
+    const int rc = dac_conv_umma(&p, B, st);
+    if (rc != PTTS_E_UNSUPPORTED) return rc;
+  }
   if (p.N % 128 != 0 && p.N % 96 == 0) return launch_conv<96>(p, B, st);
   return launch_conv<128>(p, B, st);
 }

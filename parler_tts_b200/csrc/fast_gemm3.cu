@@ -99,7 +99,7 @@ __device__ __forceinline__ unsigned long long gtime() {
 
 // grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
 template <int EPI>
-__global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg) {
+__global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, TL tl) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mma_bar;
   __shared__ uint32_t tmem_base_slot;
@@ -114,6 +114,7 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   if (dbg && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0)
     dbg_slot = (int)(atomicAdd(&g_stamp_idx, 1u) & 255u);
   STAMP(0);
+  tl_start(tl);
 
   for (int kb = 0; kb < KB; ++kb) load_block_sw128<UM>(sw + kb * WBLK, p.W, p.K, n0, p.N, kbeg + kb * KB64);
   if (warp == 0) {  // tensor-memory allocation (one warp), barrier init (one thread)
@@ -129,6 +130,7 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   pdl_wait();
   pdl_launch();
   STAMP(1);
+  tl_dep(tl);
   for (int kb = 0; kb < KB; ++kb) load_block_sw128<UN>(sx + kb * XBLK, p.X, p.K, m0, p.M, kbeg + kb * KB64);
   cp_async_commit();
   cp_async_wait<0>();
@@ -154,11 +156,11 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
     uint32_t done = 0;
     for (uint32_t spin = 0; !done; ++spin) {
       asm volatile(
-          "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+          "{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
           : "=r"(done)
           : "r"(smem_u32(&mma_bar)), "r"(0)
           : "memory");
-      if (spin > 4000000u) __trap();
+      if (spin > 200000000u) __trap();
     }
   }
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
@@ -185,6 +187,7 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
       asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
     }
     STAMP(6);
+    tl_end(tl);
     return;
   }
   // accumulator -> registers -> transposed fp32 tile red[m][n] in my own shared memory (the operand slabs are dead):
@@ -258,6 +261,7 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   STAMP(5);
   asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");  // nobody exits while a peer reads its tile
   STAMP(6);
+  tl_end(tl);
 }
 
 constexpr int kMaxKB64 = 8;  // <= 512 K elements per CTA: (128 + 64) rows x 1 KB = 192 KB of operand slabs
@@ -320,7 +324,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     const char* ev = getenv("PTTS_GEMM_DBG");
     dbg = (ev && ev[0] == '1') ? 1 : 0;
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg, tl_next(10 + EPI));
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
     (void)cudaGetLastError();
@@ -344,11 +348,16 @@ int umma_plan_splits(int M, int N, int K) {
   if (K % 128 != 0) return 0;
   const int kblocks = K / KB64;
   const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
+  static int target = -1;  // PTTS_SPLIT_TARGET: CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold)
+  if (target < 0) {
+    const char* e = getenv("PTTS_SPLIT_TARGET");
+    target = e ? atoi(e) : 120;
+  }
   int best = 0;
   for (int s = 2; s <= kMaxSplitK; s <<= 1) {
     if (kblocks % s || kblocks / s > kMaxKB64) continue;
     best = s;
-    if (nt * s >= 120) break;
+    if (nt * s >= target) break;
   }
   return best;
 }

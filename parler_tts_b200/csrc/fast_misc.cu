@@ -13,15 +13,17 @@ template <typename TY>
 __global__ void __launch_bounds__(256)
 ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
                  const float* __restrict__ g, const float* __restrict__ bta, int H, float eps, int row_mul, int row_add,
-                 TY* __restrict__ y) {
+                 TY* __restrict__ y, TL tl) {
   extern __shared__ float buf[];  // [H]
   __shared__ float red[8];
   __shared__ float stat[2];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t rin = (int64_t)blockIdx.x * row_mul + row_add;
   float* hr = h + rin * H;
+  tl_start(tl);
   pdl_wait();
   pdl_launch();
+  tl_dep(tl);
   float s = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
@@ -81,6 +83,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
       *reinterpret_cast<uint2*>(yr + c) = u;
     }
   }
+  tl_end(tl);
 }
 
 }  // namespace
@@ -95,10 +98,10 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   cudaError_t e;
   if (ydtype == PTTS_F32)
     e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H, eps,
-                 row_mul, row_add, (float*)y);
+                 row_mul, row_add, (float*)y, tl_next(1));
   else
     e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H,
-                 eps, row_mul, row_add, (__nv_bfloat16*)y);
+                 eps, row_mul, row_add, (__nv_bfloat16*)y, tl_next(1));
   if (e != cudaSuccess) {
     set_error("layernorm_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
