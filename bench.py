@@ -192,7 +192,7 @@ def run_cuda(args):
     st = GenState(w, B, S, P, 1, M, impl=impl, suppress_from=1024, row_offset=rank * B * K)
     start = torch.full((B * K, 1), MINI["bos_token_id"], dtype=torch.int64, device=dev)
     codes = torch.empty(B, K, N, dtype=torch.int64, device=dev)
-    gathered = [torch.empty_like(codes) for _ in range(world)] if world > 1 else None
+    from parler_tts_b200 import sharding
     ev = lambda: torch.cuda.Event(enable_timing=True)  # noqa: E731
     loop_ms = []
 
@@ -207,7 +207,7 @@ def run_cuda(args):
         cabi.call("ptts_dedelay", cabi.ptr(st.ids), M, cabi.ptr(st.mask), M, B, K, M, cabi.ptr(codes),
                   cabi.stream_ptr())
         if world > 1:  # the only collective of the path: gather the finished codes
-            dist.all_gather(gathered, codes)
+            sharding.gather_padded(codes, MINI["pad_token_id"])
         return e0, e1
 
     def barrier():

@@ -104,6 +104,16 @@ static bool split_k_partials_enabled() {
   return v == 1;
 }
 
+// PTTS_QKV=scatter keeps the cluster GEMM with the scatter epilogue for the decode-step QKV / cross-q projections
+static bool qkv_fusion_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_QKV");
+    v = (e && e[0] == 's') ? 0 : 1;
+  }
+  return v == 1;
+}
+
 // PTTS_SKIP=<bitmask>: timing ablation ONLY (results are garbage): 1 LayerNorm, 2 QKV GEMM, 4 self-attention,
 // 8 residual GEMMs, 16 cross q GEMM, 32 cross-attention, 64 fc1, 128 heads.  Used by profiles/scripts/ablate.sh to get
 // the marginal cost of each kernel class inside the PDL-overlapped graph (ncu serialises launches and cannot).
@@ -153,6 +163,19 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
   const float scale = 1.0f / sqrtf((float)d);
   // self attention block
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln1_g, L.ln1_b, rows, 1, 0, st));
+  int bn_q = 64;
+  const bool fuse = path.gemm && Tq == 1 && d == 64 && qkv_fusion_enabled();
+  const int Sq = fuse ? gemm_bf16_plan_splits(rows, 3 * H, H, &bn_q) : 0;
+  if (fuse && Sq > 1 && bn_q == 0) {
+    // decode: QKV as split-K partial sums; the attention CTA of (b, head) folds them, scales q and writes the new
+    // K / V row into the cache itself
+    float* qpart = work_area(m, s);
+    PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
+    PTTS_UNLESS_SKIPPED(4, attention_fast_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, 1, scale, ctx_base - 1, ctx_dyn,
+                                                ks, vs, B, heads, s->c_max, ctx_base, ctx_dyn, s->prompt_mask, s->P,
+                                                s->attn, s->scratch, st));
+    goto self_attention_done;
+  }
   if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_scatter(s->xn, L.w_qkv, rows, 3 * H, H, 1, scale, s->q, ks, vs, H, heads, d, Tq, s->c_max,
                                ctx_base - Tq, ctx_dyn, st));
@@ -164,16 +187,27 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
   }
   PTTS_UNLESS_SKIPPED(4, attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn,
                                             Tq > 1, s->prompt_mask, s->P, s->attn, s->scratch, st));
+self_attention_done:
   PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
   // cross attention block (modeling_parler_tts.py:465-483)
   if (s->S > 0) {
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
     char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->S) * es;
     PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
-    PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale, PTTS_ACT_NONE,
-                                            nullptr, nullptr, s->q, dt, st));
-    PTTS_UNLESS_SKIPPED(32, attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0,
-                                               s->enc_mask, s->S, s->attn, s->scratch, st));
+    int bn_c = 64;
+    const int Sc = fuse ? gemm_bf16_plan_splits(rows, H, H, &bn_c) : 0;
+    if (fuse && Sc > 1 && bn_c == 0) {
+      float* qpart = work_area(m, s);
+      PTTS_UNLESS_SKIPPED(16, gemm_bf16_partial(s->xn, L.w_qc, rows, H, H, Sc, 0, qpart, st));
+      PTTS_UNLESS_SKIPPED(32, attention_fast_fused(qpart, Sc, (int64_t)rows * H, H, 0, scale, 0, nullptr, kc, vc, B,
+                                                   heads, s->S, s->S, nullptr, s->enc_mask, s->S, s->attn, s->scratch,
+                                                   st));
+    } else {
+      PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale,
+                                              PTTS_ACT_NONE, nullptr, nullptr, s->q, dt, st));
+      PTTS_UNLESS_SKIPPED(32, attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0,
+                                                 s->enc_mask, s->S, s->attn, s->scratch, st));
+    }
     PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, st));
   }
   // feed forward block
@@ -201,7 +235,7 @@ extern "C" int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows) {
   if (!m || rows <= 0) return 0;
   int64_t w = (int64_t)rows * 3 * m->hidden;                                  // fused qkv / cross kv staging
   const int64_t b = (int64_t)rows * m->n_codebooks * m->vocab;                // all-position logits staging
-  const int64_t c = (int64_t)kMaxSplitK * (rows < 256 ? rows : 256) * m->hidden;  // split-K partial sums
+  const int64_t c = (int64_t)kMaxSplitK * (rows < 256 ? rows : 256) * 3 * m->hidden;  // split-K partial sums (qkv)
   if (b > w) w = b;
   if (c > w) w = c;
   return attn_scratch_floats(rows, m->n_heads) + w + 4096;  // rows >= B bounds the split-KV partial area

@@ -71,16 +71,32 @@ template <> struct Chunk<float> {
   }
 };
 
+// Optional fused prologue: the q (and, for self-attention, the new k / v) projections arrive as split-K partial sums
+// [S][rows][ncols] of the tcgen05 GEMM; the CTA of (b, head) adds them up in slice order (deterministic), scales q,
+// writes the new K / V row into its static-cache slot (replaces torch.cat, modeling_parler_tts.py:303-304) and goes on -
+// no cluster reduction and no scatter epilogue in the GEMM, no extra launch.
+struct QFuse {
+  const float* part;   // null: q is read from the q buffer
+  int S;
+  int64_t stride;      // rows * ncols
+  int ncols;           // 3H (q | k | v) or H (q only)
+  int has_kv;
+  float scale;
+  int slot_base;
+  const int* slot_dyn;
+};
+
 // part layout: [(b*heads + h)*splits + s][D + 2] = { running max, sum of exp, unnormalised output[D] }
-template <typename T, int D>
-__global__ void __launch_bounds__(NT)
-attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
+template <typename T, int D, bool FUSED>
+__global__ void __launch_bounds__(NT, 8)
+attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
                    int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask, int mask_len,
                    T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, TL tl) {
   constexpr int E = Chunk<T>::E;     // elements per 16-byte chunk
   constexpr int TPK = D / E;         // threads per key row
   constexpr int KPB = NT / TPK;      // key rows per CTA pass
   constexpr int U = 4;               // independent loads in flight per thread
+  __shared__ __align__(16) T qs[D];
   extern __shared__ float sm[];
   float* sc = sm;                    // [sc_cap] scores -> probabilities
   float* red = sm + sc_cap;          // [8] block reductions
@@ -99,7 +115,45 @@ attn_decode_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* _
   const int j1 = min(ctx, j0 + chunk);
   const int n = max(j1 - j0, 0);
   float qv[E];
-  Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
+  if constexpr (FUSED) {
+    if (tid < D) {
+      const float* p0 = qf.part + (int64_t)b * qf.ncols + hd * D + tid;
+      float aq = 0.f, ak = 0.f, av = 0.f;
+      for (int s0 = 0; s0 < qf.S; s0 += 4) {  // 4 slices (12 loads) in flight, added in slice order
+        float tq[4], tk[4], tv[4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (s0 + u < qf.S) {
+            const float* ps = p0 + (s0 + u) * qf.stride;
+            tq[u] = __ldcg(ps);
+            if (qf.has_kv) {
+              tk[u] = __ldcg(ps + H);
+              tv[u] = __ldcg(ps + 2 * H);
+            }
+          }
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
+          if (s0 + u < qf.S) {
+            aq += tq[u];
+            if (qf.has_kv) {
+              ak += tk[u];
+              av += tv[u];
+            }
+          }
+      }
+      qs[tid] = from_f<T>(aq * qf.scale);
+      if (qf.has_kv) {
+        const int slot = dyn_value(qf.slot_base, qf.slot_dyn);
+        const int64_t o = (((int64_t)b * heads + hd) * c_stride + slot) * D + tid;
+        const_cast<T*>(ck)[o] = from_f<T>(ak);
+        const_cast<T*>(cv)[o] = from_f<T>(av);
+      }
+    }
+    __syncthreads();  // q in shared memory, the new cache row visible to the whole CTA
+    Chunk<T>::unpack(*reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(qs) + c * 16), qv);
+  } else {
+    Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
+  }
   const T* kb = ck + ((int64_t)b * heads + hd) * (int64_t)c_stride * D + c * E;
   const T* vb = cv + ((int64_t)b * heads + hd) * (int64_t)c_stride * D + c * E;
   const float neg = finfo_min<T>();
@@ -401,7 +455,7 @@ int plan_splits(int B, int heads, int c_stride) {
 }
 
 template <typename T>
-int launch_decode(const void* q, const void* ck, const void* cv, int B, int heads, int c_stride, int ctx_base,
+int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv, int B, int heads, int c_stride, int ctx_base,
                   const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch, cudaStream_t st) {
   constexpr int D = 64;
   constexpr int KPB = NT / (D / Chunk<T>::E);
@@ -417,7 +471,7 @@ int launch_decode(const void* q, const void* ck, const void* cv, int B, int head
   }
   PTTS_CHECK_ARG(splits == 1 || scratch, "attention_fast: split-KV needs scratch");
   cudaError_t e;
-  if (use_bulk) {
+  if (use_bulk && !qf.part) {
     const size_t smem = (size_t)BULK_STAGES * BULK_BYTES + sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
@@ -433,14 +487,20 @@ int launch_decode(const void* q, const void* ck, const void* cv, int B, int head
     if (smem > 48 * 1024) {
       static size_t configured = 0;
       if (smem > configured) {
-        cudaFuncSetAttribute(attn_decode_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(attn_decode_kernel<T, D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(attn_decode_kernel<T, D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
       }
     }
     PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
-    e = launch_k(attn_decode_kernel<T, D>, dim3(heads, B, splits), dim3(NT), smem, st, (const T*)q, (const T*)ck,
-                 (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch, splits, cap,
-                 tl_next(c_stride > 64 ? 2 : 3));
+    if (qf.part)
+      e = launch_k(attn_decode_kernel<T, D, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
+                   (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
+                   splits, cap, tl_next(c_stride > 64 ? 2 : 3));
+    else
+      e = launch_k(attn_decode_kernel<T, D, false>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
+                   (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
+                   splits, cap, tl_next(c_stride > 64 ? 2 : 3));
   }
   if (e != cudaSuccess) {
     set_error("attn_decode launch: %s", cudaGetErrorString(e));
@@ -473,11 +533,24 @@ int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int
   (void)causal;  // a single query at the end of the context sees every cached key
   (void)d;
   (void)Tq;
+  QFuse qf = {};
   if (dtype == PTTS_F32)
-    return launch_decode<float>(q, ck, cv, B, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, out, scratch,
+    return launch_decode<float>(qf, q, ck, cv, B, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, out, scratch,
                                 st);
-  return launch_decode<__nv_bfloat16>(q, ck, cv, B, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, out,
+  return launch_decode<__nv_bfloat16>(qf, q, ck, cv, B, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, out,
                                       scratch, st);
+}
+
+// bf16 decode attention whose q (and new k / v) come as split-K partial sums of the preceding tcgen05 GEMM
+int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, int has_kv, float scale,
+                         int slot_base, const int* slot_dyn, void* ck, void* cv, int B, int heads, int c_stride,
+                         int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch,
+                         cudaStream_t st) {
+  QFuse qf = {};
+  qf.part = qkv_part; qf.S = S; qf.stride = part_stride; qf.ncols = ncols; qf.has_kv = has_kv; qf.scale = scale;
+  qf.slot_base = slot_base; qf.slot_dyn = slot_dyn;
+  return launch_decode<__nv_bfloat16>(qf, nullptr, ck, cv, B, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len,
+                                      out, scratch, st);
 }
 
 }  // namespace ptts

@@ -43,6 +43,10 @@ int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int
                    void* out, float* scratch, cudaStream_t st);
 bool dac_umma_enabled();
 int dac_conv_umma(const void* conv_params, int B, cudaStream_t st);
+int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, int has_kv, float scale,
+                         int slot_base, const int* slot_dyn, void* ck, void* cv, int B, int heads, int c_stride,
+                         int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch,
+                         cudaStream_t st);
 bool fast_conv_supported(int Cin, int Cout, int ksize);
 int dac_conv1d_fast(const float* x, int B, int Cin, int T, const float* w, const float* bias, int Cout, int ksize,
                     int dilation, const float* snake_alpha, const float* residual, int tanh_out, float* y,
