@@ -201,7 +201,13 @@ PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T
 
 /* ---- DAC decode, fast family: channels-last activations [B][T][C] fp32, tensor-core implicit GEMM ---------------- */
 /* weights are pre-split on the host into two bf16 planes (w = hi + mid) laid out [taps][N][Cin]; see
- * parler_tts_b200/dac.py.  Same arithmetic as ptts_dac_conv1d / ptts_dac_convtr1d above. */
+ * parler_tts_b200/dac.py.  Same arithmetic as ptts_dac_conv1d / ptts_dac_convtr1d above.
+ * Pre-tiled form (default, feeds the warp-specialised tcgen05 kernel with one bulk copy per pipeline stage): pass
+ * w_mid = NULL and w_hi = ONE buffer [n_tile][Cin/32][taps][plane hi|mid][4][bn][8] bf16 with bn = ptts_dac_tile_n(N),
+ * N = Cout (conv1d) or stride*Cout (convtr1d), rows n >= N zero-filled.  ptts_dac_pretiled() tells the host which
+ * form the library wants (PTTS_DAC=umma|mma selects the older kernels, which take the two planes). */
+PTTS_API int ptts_dac_tile_n(int32_t N);
+PTTS_API int ptts_dac_pretiled(void);
 PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
                          const float* tables, int32_t codebook_size, int32_t latent, float* z, ptts_stream_t s);
 /* y[b][t][co] = bias + sum_k sum_ci snake(x)[b][t + (k - (ksize-1)/2)*dilation][ci] * w[k][co][ci] [+ residual] */

@@ -78,6 +78,8 @@ PROTOTYPES = {
                                       c_vp, c_vp]),
     "ptts_dac_convtr1d_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "ptts_dac_conv_out_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
+    "ptts_dac_tile_n": (C.c_int, [c_i32]),
+    "ptts_dac_pretiled": (C.c_int, []),
 }
 
 _lib = None

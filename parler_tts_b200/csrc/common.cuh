@@ -135,6 +135,26 @@ __device__ __forceinline__ void tl_end(TL t) {
   if (t.p && threadIdx.x == 0) atomicMax(t.p + 3, gtimer_ns());
 }
 
+// Asynchronous L2 prefetch of `bytes` (multiple of 16, 16-byte aligned) of global memory: fire and forget, holds no
+// registers and no shared memory; used to keep HBM busy while the SMs wait on a dependency.
+__device__ __forceinline__ void l2_prefetch_bulk(const void* p, uint32_t bytes) {
+  asm volatile("cp.async.bulk.prefetch.L2.global [%0], %1;\n" ::"l"(p), "r"(bytes) : "memory");
+}
+// the calling CTA prefetches [p, p + bytes) in 8 KB pieces, one per thread
+__device__ __forceinline__ void l2_prefetch_range(const void* p, int64_t bytes) {
+  constexpr int kPiece = 8192;
+  for (int64_t o = (int64_t)threadIdx.x * kPiece; o < bytes; o += (int64_t)blockDim.x * kPiece) {
+    const int64_t left = bytes - o;
+    l2_prefetch_bulk(reinterpret_cast<const char*>(p) + o, (uint32_t)(left < kPiece ? left : kPiece));
+  }
+}
+
+// same with one prefetch.global.L2 per 128-byte line (classic, LSU-issued)
+__device__ __forceinline__ void l2_prefetch_lines(const void* p, int64_t bytes) {
+  for (int64_t o = (int64_t)threadIdx.x * 128; o < bytes; o += (int64_t)blockDim.x * 128)
+    asm volatile("prefetch.global.L2 [%0];\n" ::"l"(reinterpret_cast<const char*>(p) + o) : "memory");
+}
+
 // value of a dynamic scalar: base + *dyn (dyn may be null)
 __device__ __forceinline__ int dyn_value(int base, const int* dyn) { return base + (dyn ? *dyn : 0); }
 

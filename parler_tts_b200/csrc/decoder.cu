@@ -58,6 +58,11 @@ static inline float* work_area(const PttsModel* m, const PttsState* s) {
   return s->scratch + attn_scratch_floats(s->B, m->n_heads);
 }
 
+// floats the caller-provided work area is guaranteed to hold for `rows` token rows (see ptts_scratch_floats)
+static inline int64_t work_area_floats(const PttsModel* m, int rows) {
+  return (int64_t)kMaxSplitK * (rows < 256 ? rows : 256) * 3 * m->hidden;
+}
+
 // Split-K partial sums of a residual GEMM that the next LayerNorm still has to fold into the residual stream.
 struct Pending {
   const float* part = nullptr;
@@ -110,6 +115,16 @@ static bool qkv_fusion_enabled() {
   if (v < 0) {
     const char* e = getenv("PTTS_QKV");
     v = (e && e[0] == 's') ? 0 : 1;
+  }
+  return v == 1;
+}
+
+// PTTS_FC1=cluster keeps the cluster GEMM with the fused activation epilogue for the decode-step fc1
+static bool fc1_partials_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_FC1");
+    v = (e && e[0] == 'c') ? 0 : 1;
   }
   return v == 1;
 }
@@ -173,7 +188,7 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
     PTTS_UNLESS_SKIPPED(4, attention_fast_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, 1, scale, ctx_base - 1, ctx_dyn,
                                                 ks, vs, B, heads, s->c_max, ctx_base, ctx_dyn, s->prompt_mask, s->P,
-                                                s->attn, s->scratch, st));
+                                                s->attn, s->scratch, nullptr, 0, 0, nullptr, st));
     goto self_attention_done;
   }
   if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
@@ -199,9 +214,14 @@ self_attention_done:
     if (fuse && Sc > 1 && bn_c == 0) {
       float* qpart = work_area(m, s);
       PTTS_UNLESS_SKIPPED(16, gemm_bf16_partial(s->xn, L.w_qc, rows, H, H, Sc, 0, qpart, st));
+      // the cross-attention CTAs also queue the L2 prefetch of the NEXT layer's self-attention K rows: HBM is
+      // otherwise idle during the six short kernels between here and that launch
+      const char* ks_next = l + 1 < m->n_layers
+                                ? (char*)s->kv_self + (size_t)(2 * (l + 1)) * kv_layer_elems(m, B, s->c_max) * es
+                                : nullptr;
       PTTS_UNLESS_SKIPPED(32, attention_fast_fused(qpart, Sc, (int64_t)rows * H, H, 0, scale, 0, nullptr, kc, vc, B,
                                                    heads, s->S, s->S, nullptr, s->enc_mask, s->S, s->attn, s->scratch,
-                                                   st));
+                                                   ks_next, s->c_max, ctx_base, ctx_dyn, st));
     } else {
       PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale,
                                               PTTS_ACT_NONE, nullptr, nullptr, s->q, dt, st));
@@ -212,8 +232,19 @@ self_attention_done:
   }
   // feed forward block
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
-  PTTS_UNLESS_SKIPPED(64, linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn,
-                                          nullptr, nullptr, s->ffn, dt, st));
+  {
+    int bn_f = 64;
+    const int Sf = (fuse && fc1_partials_enabled()) ? gemm_bf16_plan_splits(rows, F, H, &bn_f) : 0;
+    if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
+      // decode: fc1 as split-K partial sums + one small reduce / activation kernel (no cluster, no on-chip reduction)
+      float* fpart = work_area(m, s);
+      PTTS_UNLESS_SKIPPED(64, gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st));
+      PTTS_UNLESS_SKIPPED(64, partial_act_fast(fpart, Sf, (int64_t)rows * F, rows, F, m->act_fn, s->ffn, st));
+    } else {
+      PTTS_UNLESS_SKIPPED(64, linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn,
+                                              nullptr, nullptr, s->ffn, dt, st));
+    }
+  }
   PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, st));
   return PTTS_OK;
 }

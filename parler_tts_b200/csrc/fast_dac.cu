@@ -291,6 +291,11 @@ int launch_conv(const ConvParams& p, int B, cudaStream_t st) {
 }
 
 int launch_conv_any(const ConvParams& p, int B, cudaStream_t st) {
+  if (!p.w_mid) {  // pre-tiled weights: the warp-specialised persistent tcgen05 kernel (fast_dac3.cu)
+    const int rc = dac_conv_ws(&p, B, st);
+    if (rc == PTTS_E_UNSUPPORTED) set_error("dac conv: pre-tiled weights need Cin %% 32 == 0 and Cout %% 4 == 0");
+    return rc;
+  }
   if (dac_umma_enabled()) {  // tcgen05 kernel (fast_dac2.cu); shapes it does not take fall through to mma.sync
     const int rc = dac_conv_umma(&p, B, st);
     if (rc != PTTS_E_UNSUPPORTED) return rc;
@@ -303,6 +308,18 @@ int launch_conv_any(const ConvParams& p, int B, cudaStream_t st) {
 }  // namespace ptts
 
 using namespace ptts;
+
+extern "C" PTTS_API int ptts_dac_tile_n(int32_t N) { return dac_tile_n(N); }
+
+// 1: the host should pass pre-tiled weights (default); 0: PTTS_DAC=umma|mma selected a two-plane kernel
+extern "C" PTTS_API int ptts_dac_pretiled(void) {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_DAC");
+    v = (e && (e[0] == 'm' || e[0] == 'u')) ? 0 : 1;
+  }
+  return v;
+}
 
 extern "C" PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
                                     const float* tables, int32_t codebook_size, int32_t latent, float* z,
@@ -319,7 +336,7 @@ extern "C" PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, in
 extern "C" PTTS_API int ptts_dac_conv1d_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const void* w_hi,
                                    const void* w_mid, const float* bias, int32_t Cout, int32_t ksize, int32_t dilation,
                                    const float* snake_alpha, const float* residual, float* y, ptts_stream_t s) {
-  PTTS_CHECK_ARG(x && w_hi && w_mid && y, "dac_conv1d_nwc: null pointer");
+  PTTS_CHECK_ARG(x && w_hi && y, "dac_conv1d_nwc: null pointer");
   PTTS_CHECK_ARG(B > 0 && T > 0 && Cin > 0 && Cin % CIK == 0 && Cout > 0 && Cout % 2 == 0,
                  "dac_conv1d_nwc: Cin must be a multiple of 32 and Cout even");
   PTTS_CHECK_ARG((ksize == 1 || ksize == 7) && dilation >= 1 && (ksize - 1) * dilation <= MAX_SPAN,
@@ -336,7 +353,7 @@ extern "C" PTTS_API int ptts_dac_conv1d_nwc(const float* x, int32_t B, int32_t T
 extern "C" PTTS_API int ptts_dac_convtr1d_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const void* w_hi,
                                      const void* w_mid, const float* bias, int32_t Cout, int32_t stride,
                                      const float* snake_alpha, float* y, ptts_stream_t s) {
-  PTTS_CHECK_ARG(x && w_hi && w_mid && y, "dac_convtr1d_nwc: null pointer");
+  PTTS_CHECK_ARG(x && w_hi && y, "dac_convtr1d_nwc: null pointer");
   PTTS_CHECK_ARG(B > 0 && T > 0 && Cin > 0 && Cin % CIK == 0 && Cout > 0 && Cout % 2 == 0 && stride >= 2,
                  "dac_convtr1d_nwc: Cin must be a multiple of 32, Cout even, stride >= 2");
   ConvParams p = {};

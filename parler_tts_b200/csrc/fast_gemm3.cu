@@ -87,6 +87,11 @@ __device__ __forceinline__ void tmem_ld_32x32b_x32(uint32_t taddr, uint32_t (&v)
 // ptts_diag_gemm_stamps; profiles/scripts/gemm_stamps.py) - where inside the kernel does the time go?
 __device__ unsigned long long g_stamps[256 * 8];
 __device__ unsigned int g_stamp_idx;
+// PTTS_GEMM_DBG=3: per launch slot (dbg >> 8), sums over ALL CTAs (and replays) of SM-clock cycles since the CTA's
+// griddepcontrol.wait returned: [0] W slab landed, [1] X slab landed, [2] MMA done, [3] CTA end, [4] CTA count,
+// [5] max W, [6] max end, [7] max X
+__device__ unsigned long long g_agg[256 * 8];
+int g_agg_seq = 0;  // host: launch slot of the next launch
 __device__ __forceinline__ unsigned long long gtime() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
@@ -94,7 +99,7 @@ __device__ __forceinline__ unsigned long long gtime() {
 }
 #define STAMP(i)                                                    \
   do {                                                              \
-    if (dbg_slot >= 0) g_stamps[dbg_slot * 8 + (i)] = gtime();      \
+    if (dbg_slot >= 0) g_stamps[dbg_slot * 8 + (i)] = (dbg & 3) == 2 ? (unsigned long long)clock64() : gtime(); \
   } while (0)
 
 // grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
@@ -111,7 +116,7 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   const int kbeg = (int)rank * KB * KB64;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
   int dbg_slot = -1;
-  if (dbg && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0)
+  if ((dbg & 3) && (dbg & 3) != 3 && threadIdx.x == 0 && blockIdx.x == 0 && blockIdx.y == 0 && rank == 0)
     dbg_slot = (int)(atomicAdd(&g_stamp_idx, 1u) & 255u);
   STAMP(0);
   tl_start(tl);
@@ -127,13 +132,21 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&mma_bar)), "r"(1) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
+  cp_async_commit();  // group 0: the W slab
   pdl_wait();
   pdl_launch();
   STAMP(1);
   tl_dep(tl);
+  const long long c_dep = (dbg & 3) == 3 ? clock64() : 0;
+  long long c_w = 0, c_x = 0, c_mma = 0;
   for (int kb = 0; kb < KB; ++kb) load_block_sw128<UN>(sx + kb * XBLK, p.X, p.K, m0, p.M, kbeg + kb * KB64);
-  cp_async_commit();
+  cp_async_commit();  // group 1: the X slab
+  if ((dbg & 3) == 3) {
+    cp_async_wait<1>();
+    c_w = clock64();
+  }
   cp_async_wait<0>();
+  if ((dbg & 3) == 3) c_x = clock64();
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // cp.async (generic proxy) -> UMMA (async proxy)
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
@@ -165,28 +178,56 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   }
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
   STAMP(3);
+  if ((dbg & 3) == 3) c_mma = clock64();
+  auto agg = [&]() {
+    if ((dbg & 3) == 3 && threadIdx.x == 0) {
+      unsigned long long* a = g_agg + ((dbg >> 8) & 255) * 8;
+      const long long c_end = clock64();
+      atomicAdd(a + 0, (unsigned long long)(c_w - c_dep));
+      atomicAdd(a + 1, (unsigned long long)(c_x - c_dep));
+      atomicAdd(a + 2, (unsigned long long)(c_mma - c_dep));
+      atomicAdd(a + 3, (unsigned long long)(c_end - c_dep));
+      atomicAdd(a + 4, 1ull);
+      atomicMax(a + 5, (unsigned long long)(c_w - c_dep));
+      atomicMax(a + 6, (unsigned long long)(c_end - c_dep));
+      atomicMax(a + 7, (unsigned long long)(c_x - c_dep));
+    }
+  };
 
   if constexpr (EPI == EPI_PARTIAL) {
     // split-K partial sums straight to global memory [slice][m][n] (coalesced along n); the LayerNorm that consumes
     // the residual stream next adds them up in slice order (deterministic) - no cluster, no on-chip reduction
     const int n = n0 + warp * 32 + lane;
+    STAMP(4);
+    // one running pointer per thread and no per-element index arithmetic: this loop is the kernel's critical path
+    const size_t ldn = (size_t)p.N;
+    float* dst = p.part + ((size_t)rank * p.M + m0) * ldn + n;
+    const int rows = min(UN, p.M - m0);
 #pragma unroll
     for (int half = 0; half < 2; ++half) {
       uint32_t v[32];
       tmem_ld_32x32b_x32(tmem_d + ((uint32_t)(warp * 32) << 16) + half * 32, v);
       asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+      if (n < p.N) {
+        if (rows == UN) {
 #pragma unroll
-      for (int j = 0; j < 32; ++j) {
-        const int m = m0 + half * 32 + j;
-        if (m < p.M && n < p.N) p.part[((int64_t)rank * p.M + m) * p.N + n] = __uint_as_float(v[j]);
+          for (int j = 0; j < 32; ++j) dst[(size_t)j * ldn] = __uint_as_float(v[j]);
+        } else {
+#pragma unroll
+          for (int j = 0; j < 32; ++j)
+            if (half * 32 + j < rows) dst[(size_t)j * ldn] = __uint_as_float(v[j]);
+        }
       }
+      dst += 32 * ldn;
     }
+    STAMP(5);
     asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
     __syncthreads();
     if (warp == 0) {
       asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
     }
     STAMP(6);
+    agg();
     tl_end(tl);
     return;
   }
@@ -261,6 +302,7 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   STAMP(5);
   asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");  // nobody exits while a peer reads its tile
   STAMP(6);
+  agg();
   tl_end(tl);
 }
 
@@ -322,9 +364,10 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   static int dbg = -1;
   if (dbg < 0) {
     const char* ev = getenv("PTTS_GEMM_DBG");
-    dbg = (ev && ev[0] == '1') ? 1 : 0;
+    dbg = ev ? atoi(ev) : 0;  // 1: globaltimer stamps (256 ns ticks), 2: SM clock cycles (intra-kernel phases)
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg, tl_next(10 + EPI));
+  const int dbg_arg = dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg;
+  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg, tl_next(10 + EPI));
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
     (void)cudaGetLastError();
@@ -338,12 +381,21 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
 
 namespace gemm {
 int umma_read_stamps(unsigned long long* host, int n_launches) {
+  if (n_launches == -2) {  // reset the aggregate statistics
+    static unsigned long long zero[256 * 8];
+    cudaMemcpyToSymbol(g_agg, zero, sizeof(zero));
+    return 0;
+  }
+  if (n_launches < 0) {  // aggregate statistics of PTTS_GEMM_DBG=3 (256 x 8)
+    cudaMemcpyFromSymbol(host, g_agg, sizeof(unsigned long long) * 8 * 256);
+    return 256;
+  }
   unsigned int idx = 0;
   cudaMemcpyFromSymbol(&idx, g_stamp_idx, sizeof(idx));
   cudaMemcpyFromSymbol(host, g_stamps, sizeof(unsigned long long) * 8 * (n_launches > 256 ? 256 : n_launches));
   return (int)idx;
 }
-// split-K plan of the PARTIAL variant: smallest S in {2,4,8,16} that gives >= ~120 CTAs (else the largest that fits)
+// split-K plan of the PARTIAL variant: smallest S in {2,4,8,16} that gives >= ~30 CTAs (else the largest that fits)
 int umma_plan_splits(int M, int N, int K) {
   if (K % 128 != 0) return 0;
   const int kblocks = K / KB64;
@@ -351,7 +403,7 @@ int umma_plan_splits(int M, int N, int K) {
   static int target = -1;  // PTTS_SPLIT_TARGET: CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold)
   if (target < 0) {
     const char* e = getenv("PTTS_SPLIT_TARGET");
-    target = e ? atoi(e) : 120;
+    target = e ? atoi(e) : 30;
   }
   int best = 0;
   for (int s = 2; s <= kMaxSplitK; s <<= 1) {

@@ -21,8 +21,20 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   const int64_t rin = (int64_t)blockIdx.x * row_mul + row_add;
   float* hr = h + rin * H;
   tl_start(tl);
-  pdl_wait();
+  // Trigger BEFORE waiting: the consumer of a LayerNorm is always a GEMM whose pre-wait section only prefetches
+  // immutable weights, so it may become resident (and pull its W slab from HBM) while the kernel before this one is
+  // still running; its own griddepcontrol.wait still orders it after this grid.
   pdl_launch();
+  float4 gg4[4], bb4[4];  // gamma / beta are immutable too: fetch them while the producer finishes
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = tid * 4 + i * 1024;
+    if (c < H) {
+      gg4[i] = __ldg(reinterpret_cast<const float4*>(g + c));
+      bb4[i] = __ldg(reinterpret_cast<const float4*>(bta + c));
+    }
+  }
+  pdl_wait();
   tl_dep(tl);
   float s = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
@@ -67,10 +79,12 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   __syncthreads();
   const float rstd = stat[1];
   TY* yr = y + (int64_t)blockIdx.x * H;
-  for (int c = tid * 4; c < H; c += 256 * 4) {
+#pragma unroll
+  for (int i = 0; i < 4; ++i) {
+    const int c = tid * 4 + i * 1024;
+    if (c >= H) break;
     const float4 v = *reinterpret_cast<const float4*>(buf + c);
-    const float4 gg = __ldg(reinterpret_cast<const float4*>(g + c));
-    const float4 bb = __ldg(reinterpret_cast<const float4*>(bta + c));
+    const float4 gg = gg4[i], bb = bb4[i];
     const float o0 = (v.x - mean) * rstd * gg.x + bb.x, o1 = (v.y - mean) * rstd * gg.y + bb.y;
     const float o2 = (v.z - mean) * rstd * gg.z + bb.z, o3 = (v.w - mean) * rstd * gg.w + bb.w;
     if constexpr (sizeof(TY) == 4) {
@@ -88,7 +102,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
 
 }  // namespace
 
-bool fast_layernorm_supported(int H) { return H % 4 == 0 && H <= 12288; }
+bool fast_layernorm_supported(int H) { return H % 4 == 0 && H <= 4096; }  // gamma / beta live in registers
 
 // rows output rows; output row r reads input row r*row_mul + row_add (of h and of every partial)
 int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, const float* g, const float* b, int rows,
@@ -109,5 +123,54 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   PTTS_CHECK_LAUNCH("layernorm_fast");
   return PTTS_OK;
 }
+
+// y[r][c] = act(sum_s part[s][r][c]) as bf16: finishes the split-K fc1 of the decode step (partial sums are added in
+// slice order, deterministic).  One float4 column group per thread; all S loads of a thread are in flight together.
+__global__ void __launch_bounds__(256)
+partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, int64_t n4, int act,
+                   __nv_bfloat16* __restrict__ y, TL tl) {
+  tl_start(tl);
+  pdl_launch();  // before the wait: the consumer (fc2 GEMM) only prefetches immutable weights ahead of its own wait
+  pdl_wait();
+  tl_dep(tl);
+  const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
+  if (i < n4) {
+    const float4* p0 = reinterpret_cast<const float4*>(part) + i;
+    const int64_t st4 = part_stride / 4;
+    float4 v = __ldcg(p0);
+    for (int s0 = 1; s0 < S; s0 += 4) {
+      float4 t[4];
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < S) t[u] = __ldcg(p0 + (s0 + u) * st4);
+#pragma unroll
+      for (int u = 0; u < 4; ++u)
+        if (s0 + u < S) { v.x += t[u].x; v.y += t[u].y; v.z += t[u].z; v.w += t[u].w; }
+    }
+    __nv_bfloat162 lo = __floats2bfloat162_rn(apply_act(v.x, act), apply_act(v.y, act));
+    __nv_bfloat162 hi = __floats2bfloat162_rn(apply_act(v.z, act), apply_act(v.w, act));
+    uint2 u;
+    u.x = *reinterpret_cast<uint32_t*>(&lo);
+    u.y = *reinterpret_cast<uint32_t*>(&hi);
+    reinterpret_cast<uint2*>(y)[i] = u;
+  }
+  tl_end(tl);
+}
+
+int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, int N, int act, void* y,
+                     cudaStream_t st) {
+  PTTS_CHECK_ARG(part && y && S >= 1 && N % 4 == 0 && part_stride % 4 == 0, "partial_act_fast: bad arguments");
+  const int64_t n4 = (int64_t)rows * N / 4;
+  if (n4 == 0) return PTTS_OK;
+  cudaError_t e = launch_k(partial_act_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,
+                           part_stride, n4, act, (__nv_bfloat16*)y, tl_next(4));
+  if (e != cudaSuccess) {
+    set_error("partial_act_fast launch: %s", cudaGetErrorString(e));
+    return PTTS_E_LAUNCH;
+  }
+  PTTS_CHECK_LAUNCH("partial_act_fast");
+  return PTTS_OK;
+}
+
 
 }  // namespace ptts

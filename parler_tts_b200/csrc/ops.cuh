@@ -33,6 +33,9 @@ int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
                       cudaStream_t st);
 bool fast_layernorm_supported(int H);
+// y = act(sum of S split-K partial slices) as bf16 (fast_misc.cu)
+int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, int N, int act, void* y,
+                     cudaStream_t st);
 int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, const float* g, const float* b, int rows,
                    int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st);
 int64_t attn_scratch_floats(int B, int heads);
@@ -43,9 +46,13 @@ int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int
                    void* out, float* scratch, cudaStream_t st);
 bool dac_umma_enabled();
 int dac_conv_umma(const void* conv_params, int B, cudaStream_t st);
+// warp-specialised persistent tcgen05 conv over pre-tiled weights (fast_dac3.cu)
+int dac_tile_n(int N);
+int dac_conv_ws(const void* conv_params, int B, cudaStream_t st);
 int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, int has_kv, float scale,
                          int slot_base, const int* slot_dyn, void* ck, void* cv, int B, int heads, int c_stride,
                          int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch,
+                         const void* pf_next, int pf_stride, int pf_rows_base, const int* pf_rows_dyn,
                          cudaStream_t st);
 bool fast_conv_supported(int Cin, int Cout, int ksize);
 int dac_conv1d_fast(const float* x, int B, int Cin, int T, const float* w, const float* bias, int Cout, int ksize,

@@ -72,16 +72,35 @@ class DacDecoderEngine:
         mid = (w - hi.float()).to(torch.bfloat16)
         return hi.contiguous(), mid.contiguous()
 
+    @staticmethod
+    def _tile(hi, mid):
+        """[taps][N][Cin] hi / mid planes -> the pre-tiled stage image of the warp-specialised tcgen05 kernel:
+        [n_tile][Cin/32][taps][plane][4][bn][8] (one contiguous block per pipeline stage; include/parler_b200.h)."""
+        taps, n, cin = hi.shape
+        bn = int(cabi.load().ptts_dac_tile_n(n))
+        nt = (n + bn - 1) // bn
+        w = torch.stack([hi, mid])  # plane, tap, n, ci
+        if nt * bn != n:
+            w = torch.nn.functional.pad(w, (0, 0, 0, nt * bn - n))
+        w = w.view(2, taps, nt, bn, cin // 32, 4, 8).permute(2, 4, 1, 0, 5, 3, 6)  # nt, chunk, tap, plane, kc, n, e
+        return w.contiguous(), None
+
+    def _planes(self, w):
+        hi, mid = self._split(w)
+        return self._tile(hi, mid) if self.pretiled else (hi, mid)
+
     def _prep_nwc(self):
+        self.pretiled = bool(cabi.load().ptts_dac_pretiled())
+
         def conv(wb):  # [Cout][Cin][k] -> [k][Cout][Cin]
             w, b = wb
-            return self._split(w.permute(2, 0, 1).contiguous()) + (b, w.shape[0], w.shape[2])
+            return self._planes(w.permute(2, 0, 1).contiguous()) + (b, w.shape[0], w.shape[2])
 
         def convt(wb, s):  # [Cin][Cout][2s] -> [2][s*Cout][Cin], index (tap, ph*Cout + co, ci) = w[ci][co][ph + tap*s]
             w, b = wb
             cin, cout, _ = w.shape
             w2 = w.permute(2, 1, 0).reshape(2, s * cout, cin).contiguous()
-            return self._split(w2) + (b, cout)
+            return self._planes(w2) + (b, cout)
 
         self.f_conv_in = conv(self.conv_in)
         self.f_blocks = []

@@ -5,7 +5,7 @@ import ctypes as C
 import os
 import sys
 
-os.environ["PTTS_GEMM_DBG"] = "1"
+os.environ.setdefault("PTTS_GEMM_DBG", "1")  # 2 = SM clock cycles instead of globaltimer ns
 import numpy as np
 import torch
 

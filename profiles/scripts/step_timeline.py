@@ -44,10 +44,10 @@ t, kinds = t[ok], kinds[:n][ok]
 order = np.argsort(t[:, 1])
 t, kinds = t[order], kinds[order]
 t0 = t[0, 0]
-names = {1: "layernorm", 2: "self-attn", 3: "cross-attn", 10: "gemm partial", 11: "gemm store", 12: "gemm scatter"}
+names = {1: "layernorm", 2: "self-attn", 3: "cross-attn", 4: "reduce-act", 10: "gemm partial", 11: "gemm store", 12: "gemm scatter"}
 print(f"context ~{P + N}; {len(t)} instrumented launches in one replay; step span {(t[:, 3].max() - t0) / 1e3:.1f} us")
 print("  kernel          resident-before-dep  dep-spread  run(after dep)  handover(prev end -> dep)")
-for i in range(11, 22):
+for i in range(12, 24):
     r = t[i]
     print(f"  {names.get(int(kinds[i]), kinds[i]):14s} {(r[1] - r[0]) / 1e3:10.2f} us {(r[2] - r[1]) / 1e3:10.2f} us "
           f"{(r[3] - r[1]) / 1e3:10.2f} us {(r[1] - t[i - 1, 3]) / 1e3:12.2f} us")

@@ -165,7 +165,7 @@ def test_cached_decode_steps_teacher_forced_vs_oracle(impl, dtype):
 
 def test_fast_path_launches_its_own_kernels_and_graph_replays_match_eager():
     """bf16 fast path: a CUDA-graph replayed generation equals the eager launch sequence token for token, and the
-    library's launch counter shows the fused layer (11 launches per layer instead of the simple family's 15)."""
+    library's launch counter shows the fused layer (12 launches per layer instead of the simple family's 15)."""
     kw = dict(TINY, hidden_size=256, num_attention_heads=4, ffn_dim=1024, num_hidden_layers=2)
     dims = decoder_oracle.DecoderDims(**kw)
     sd = decoder_oracle.random_decoder_state(dims, seed=7, ln_jitter=0.05)
@@ -180,7 +180,7 @@ def test_fast_path_launches_its_own_kernels_and_graph_replays_match_eager():
                                logits_processor=[ptts.SuppressTokensAtOrAbove(32)]).cpu())
     assert torch.equal(outs[0], outs[1])
     st = m._state_cache[1]
-    assert st.graph is not None and st.graph_launches == 2 * 11 + 3, st.graph_launches
+    assert st.graph is not None and st.graph_launches == 2 * 12 + 3, st.graph_launches
 
 
 # ------------------------------------------------------------------------------------------------ DAC fast family
@@ -189,9 +189,22 @@ def _split(w):
     return hi.contiguous(), (w - hi.float()).to(torch.bfloat16).contiguous()
 
 
+def _weights(w_tnc, tiled):
+    """two bf16 planes [taps][N][Cin], or the pre-tiled single buffer of the warp-specialised tcgen05 kernel"""
+    hi, mid = _split(w_tnc)
+    if not tiled:
+        return hi, mid
+    from parler_tts_b200.dac import DacDecoderEngine
+    return DacDecoderEngine._tile(hi, mid)
+
+
+@pytest.mark.parametrize("tiled", [True, False])
 @pytest.mark.parametrize("Cin,Cout,k,dil,T", [(96, 96, 7, 9, 700), (192, 192, 1, 1, 300), (1024, 1536, 7, 1, 37),
-                                              (384, 384, 7, 3, 129), (32, 26, 7, 1, 5)])
-def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T):
+                                              (384, 384, 7, 3, 129), (32, 26, 7, 1, 5), (192, 192, 7, 9, 1000),
+                                              (96, 96, 1, 1, 257), (64, 40, 7, 3, 256)])
+def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T, tiled):
+    if tiled and Cout % 4:
+        pytest.skip("pre-tiled kernel stores 16-byte vectors")
     g = torch.Generator().manual_seed(Cin + k + dil)
     B = 2
     x = torch.randn(B, Cin, T, generator=g).to(DEV)
@@ -202,7 +215,7 @@ def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T):
     xs = x + (1.0 / (alpha[None, :, None] + 1e-9)) * torch.sin(alpha[None, :, None] * x) ** 2
     want = torch.nn.functional.conv1d(xs.double(), w.double(), bias.double(), dilation=dil,
                                       padding=dil * (k - 1) // 2).float() + res
-    hi, mid = _split(w.permute(2, 0, 1).contiguous())
+    hi, mid = _weights(w.permute(2, 0, 1).contiguous(), tiled)
     x_nwc, res_nwc = x.transpose(1, 2).contiguous(), res.transpose(1, 2).contiguous()
     y = torch.empty(B, T, Cout, device=DEV)
     cabi.call("ptts_dac_conv1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, k,
@@ -211,8 +224,9 @@ def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T):
     assert err < 2e-4 * max(1.0, float(want.abs().max())), err
 
 
-@pytest.mark.parametrize("Cin,Cout,s,T", [(1536, 768, 8, 11), (192, 96, 2, 300), (64, 32, 4, 130)])
-def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T):
+@pytest.mark.parametrize("tiled", [True, False])
+@pytest.mark.parametrize("Cin,Cout,s,T", [(1536, 768, 8, 11), (192, 96, 2, 300), (64, 32, 4, 130), (384, 192, 4, 515)])
+def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T, tiled):
     g = torch.Generator().manual_seed(Cin + s)
     B = 2
     x = torch.randn(B, Cin, T, generator=g).to(DEV)
@@ -223,7 +237,7 @@ def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T):
     want = torch.nn.functional.conv_transpose1d(xs.double(), w.double(), bias.double(), stride=s,
                                                 padding=(s + 1) // 2).float()
     assert want.shape[-1] == T * s
-    hi, mid = _split(w.permute(2, 1, 0).reshape(2, s * Cout, Cin).contiguous())
+    hi, mid = _weights(w.permute(2, 1, 0).reshape(2, s * Cout, Cin).contiguous(), tiled)
     x_nwc = x.transpose(1, 2).contiguous()
     y = torch.empty(B, T * s, Cout, device=DEV)
     cabi.call("ptts_dac_convtr1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, s,
