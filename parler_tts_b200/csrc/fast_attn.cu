@@ -93,7 +93,7 @@ struct QFuse {
 };
 
 // ---------------------------------------------------------------------------------------------------------------
-// One-pass (online softmax) flash-decode kernel - the default.  The K row and the V row of a cache slot travel
+// One-pass (online softmax) flash-decode kernel (PTTS_ATTN=online; NOT the default, see launch_decode).  The K row and the V row of a cache slot travel
 // together: no score buffer, no K pass / softmax / V pass phases in which every CTA of the single resident wave stops
 // loading at the same time (measured on B200: the three-pass kernel costs ~3.5 us of such bubbles per launch and tops
 // out at ~7 TB/s even when the cache is L2 resident).  Each group of TPK threads owns the rows j = j0 + g (mod KPB) and
@@ -693,10 +693,13 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
   }
   PTTS_CHECK_ARG(splits == 1 || scratch, "attention_fast: split-KV needs scratch");
   cudaError_t e;
-  static int three_pass = -1;  // PTTS_ATTN=threepass: the K pass / softmax / V pass kernel (kept for A/B timing)
+  // PTTS_ATTN=online selects the one-pass online-softmax kernel.  Measured on B200 (B=64, ctx 472, bf16): three-pass
+  // 24.7 us, one-pass 33.1 us per launch - the per-batch max / rescale chain costs more issue slots than the phase
+  // bubbles it removes, so the three-pass kernel stays the default.
+  static int three_pass = -1;
   if (three_pass < 0) {
     const char* ev = getenv("PTTS_ATTN");
-    three_pass = (ev && ev[0] == 't') ? 1 : 0;
+    three_pass = (ev && ev[0] == 'o') ? 0 : 1;
   }
   if (!use_bulk && !three_pass) {
     if (qf.part)
