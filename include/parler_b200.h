@@ -208,6 +208,22 @@ PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T
  * form the library wants (PTTS_DAC=umma|mma selects the older kernels, which take the two planes). */
 PTTS_API int ptts_dac_tile_n(int32_t N);
 PTTS_API int ptts_dac_pretiled(void);
+/* "Planes": an activation tensor stored the way the tensor core wants it - Snake already applied, split into two
+ * bf16 planes (x = hi + mid), 8-channel panels: [B][2 (hi, mid)][C/8][PAD_LO + T + PAD_HI][8] bf16 (4 bytes per
+ * element, like fp32).  Row PAD_LO - 1 and row PAD_LO + T must be zero (the caller zeroes the pads once), the other pad
+ * rows only need to exist.  A conv writes planes for its consumer (out_alpha = the consumer's Snake alpha, NULL = no
+ * activation) from its otherwise idle epilogue warps, and the consumer then streams them with bulk copies instead of
+ * activating its input again for every column tile (a k=1 conv, or a transposed conv with 6..48 column tiles).
+ * Exactly one of x / x_planes; y and/or y_planes; weights pre-tiled (see above); snake_alpha only with x. */
+#define PTTS_DAC_PLANE_PAD_LO 8
+#define PTTS_DAC_PLANE_PAD_HI 264
+PTTS_API int ptts_dac_conv1d_px(const float* x, const void* x_planes, int32_t B, int32_t T, int32_t Cin,
+                                const void* w_tiled, const float* bias, int32_t Cout, int32_t ksize, int32_t dilation,
+                                const float* snake_alpha, const float* residual, float* y, void* y_planes,
+                                const float* out_alpha, ptts_stream_t s);
+PTTS_API int ptts_dac_convtr1d_px(const float* x, const void* x_planes, int32_t B, int32_t T, int32_t Cin,
+                                  const void* w_tiled, const float* bias, int32_t Cout, int32_t stride,
+                                  const float* snake_alpha, float* y, ptts_stream_t s);
 PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
                          const float* tables, int32_t codebook_size, int32_t latent, float* z, ptts_stream_t s);
 /* y[b][t][co] = bias + sum_k sum_ci snake(x)[b][t + (k - (ksize-1)/2)*dilation][ci] * w[k][co][ci] [+ residual] */

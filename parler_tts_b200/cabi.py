@@ -79,6 +79,9 @@ PROTOTYPES = {
     "ptts_dac_convtr1d_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "ptts_dac_conv_out_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ptts_dac_tile_n": (C.c_int, [c_i32]),
+    "ptts_dac_conv1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp,
+                                     c_vp, c_vp, c_vp]),
+    "ptts_dac_convtr1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "ptts_dac_pretiled": (C.c_int, []),
 }
 

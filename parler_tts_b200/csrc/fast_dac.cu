@@ -292,8 +292,13 @@ int launch_conv(const ConvParams& p, int B, cudaStream_t st) {
 
 int launch_conv_any(const ConvParams& p, int B, cudaStream_t st) {
   if (!p.w_mid) {  // pre-tiled weights: the warp-specialised persistent tcgen05 kernel (fast_dac3.cu)
-    const int rc = dac_conv_ws(&p, B, st);
-    if (rc == PTTS_E_UNSUPPORTED) set_error("dac conv: pre-tiled weights need Cin %% 32 == 0 and Cout %% 4 == 0");
+    DacConv a = {};
+    a.x = p.x; a.w = p.w_hi; a.bias = p.bias; a.alpha = p.alpha; a.residual = p.residual; a.y = p.y;
+    a.T = p.T; a.Cin = p.Cin; a.N = p.N; a.Cout = p.Cout; a.taps = p.taps; a.tap_center = p.tap_center;
+    a.tap_step = p.tap_step; a.lo = p.lo; a.span = p.span; a.Mrows = p.Mrows; a.out_stride = p.out_stride;
+    a.out_pad = p.out_pad; a.Tout = p.Tout;
+    const int rc = dac_conv_ws(a, B, st);
+    if (rc == PTTS_E_UNSUPPORTED) set_error("dac conv: pre-tiled weights need Cin %% 32 == 0 and Cout %% 16 == 0");
     return rc;
   }
   if (dac_umma_enabled()) {  // tcgen05 kernel (fast_dac2.cu); shapes it does not take fall through to mma.sync
@@ -363,6 +368,47 @@ extern "C" PTTS_API int ptts_dac_convtr1d_nwc(const float* x, int32_t B, int32_t
   p.lo = -1; p.span = 1;
   p.Mrows = T + 1; p.out_stride = stride; p.out_pad = (stride + 1) / 2; p.Tout = T * stride;
   return launch_conv_any(p, B, as_stream(s));
+}
+
+// conv1d / transposed conv over pre-tiled weights with optional "planes" input and output (include/parler_b200.h)
+extern "C" PTTS_API int ptts_dac_conv1d_px(const float* x, const void* x_planes, int32_t B, int32_t T, int32_t Cin,
+                                           const void* w_tiled, const float* bias, int32_t Cout, int32_t ksize,
+                                           int32_t dilation, const float* snake_alpha, const float* residual, float* y,
+                                           void* y_planes, const float* out_alpha, ptts_stream_t s) {
+  PTTS_CHECK_ARG((x != nullptr) != (x_planes != nullptr) && w_tiled && (y || y_planes), "dac_conv1d_px: null pointer");
+  PTTS_CHECK_ARG(!(x_planes && snake_alpha), "dac_conv1d_px: planes are already activated");
+  PTTS_CHECK_ARG(B > 0 && T > 0 && Cin > 0 && Cin % CIK == 0 && Cout > 0 && Cout % 16 == 0,
+                 "dac_conv1d_px: Cin must be a multiple of 32 and Cout of 16");
+  PTTS_CHECK_ARG((ksize == 1 || ksize == 7) && dilation >= 1 && (ksize - 1) * dilation <= MAX_SPAN,
+                 "dac_conv1d_px: kernel size 1 or 7, (k-1)*dilation <= 54");
+  PTTS_CHECK_ARG(!x_planes || ((ksize - 1) / 2) * dilation <= PTTS_DAC_PLANE_PAD_LO, "dac_conv1d_px: planes halo");
+  DacConv a = {};
+  a.x = x; a.x_planes = (const __nv_bfloat16*)x_planes; a.w = (const __nv_bfloat16*)w_tiled; a.bias = bias;
+  a.alpha = snake_alpha; a.residual = residual; a.y = y; a.y_planes = (__nv_bfloat16*)y_planes; a.out_alpha = out_alpha;
+  a.T = T; a.Cin = Cin; a.N = Cout; a.Cout = Cout; a.taps = ksize; a.tap_center = (ksize - 1) / 2;
+  a.tap_step = dilation; a.lo = -((ksize - 1) / 2) * dilation; a.span = (ksize - 1) * dilation;
+  a.Mrows = T; a.out_stride = 1; a.out_pad = 0; a.Tout = T;
+  const int rc = dac_conv_ws(a, B, as_stream(s));
+  if (rc == PTTS_E_UNSUPPORTED) set_error("dac_conv1d_px: unsupported shape");
+  return rc;
+}
+
+extern "C" PTTS_API int ptts_dac_convtr1d_px(const float* x, const void* x_planes, int32_t B, int32_t T, int32_t Cin,
+                                             const void* w_tiled, const float* bias, int32_t Cout, int32_t stride,
+                                             const float* snake_alpha, float* y, ptts_stream_t s) {
+  PTTS_CHECK_ARG((x != nullptr) != (x_planes != nullptr) && w_tiled && y, "dac_convtr1d_px: null pointer");
+  PTTS_CHECK_ARG(!(x_planes && snake_alpha), "dac_convtr1d_px: planes are already activated");
+  PTTS_CHECK_ARG(B > 0 && T > 0 && Cin > 0 && Cin % CIK == 0 && Cout > 0 && Cout % 16 == 0 && stride >= 2,
+                 "dac_convtr1d_px: Cin must be a multiple of 32, Cout of 16, stride >= 2");
+  DacConv a = {};
+  a.x = x; a.x_planes = (const __nv_bfloat16*)x_planes; a.w = (const __nv_bfloat16*)w_tiled; a.bias = bias;
+  a.alpha = snake_alpha; a.y = y;
+  a.T = T; a.Cin = Cin; a.N = stride * Cout; a.Cout = Cout; a.taps = 2; a.tap_center = 0; a.tap_step = -1;
+  a.lo = -1; a.span = 1;
+  a.Mrows = T + 1; a.out_stride = stride; a.out_pad = (stride + 1) / 2; a.Tout = T * stride;
+  const int rc = dac_conv_ws(a, B, as_stream(s));
+  if (rc == PTTS_E_UNSUPPORTED) set_error("dac_convtr1d_px: unsupported shape");
+  return rc;
 }
 
 extern "C" PTTS_API int ptts_dac_conv_out_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const float* w,

@@ -47,8 +47,21 @@ int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int
 bool dac_umma_enabled();
 int dac_conv_umma(const void* conv_params, int B, cudaStream_t st);
 // warp-specialised persistent tcgen05 conv over pre-tiled weights (fast_dac3.cu)
+struct DacConv {
+  const float* x;                  // [B][T][Cin] fp32 (Snake `alpha` applied while staging), or null
+  const __nv_bfloat16* x_planes;   // or: activated hi/mid planes [B][2][Cin/8][T + pads][8]
+  const __nv_bfloat16* w;          // pre-tiled stages
+  const float* bias;
+  const float* alpha;
+  const float* residual;           // [B][Tout][Cout] or null
+  float* y;                        // [B][Tout][Cout] fp32, or null
+  __nv_bfloat16* y_planes;         // or: Snake(out_alpha) + hi/mid planes [B][2][Cout/8][Tout + pads][8]
+  const float* out_alpha;
+  int T, Cin, N, Cout, taps, tap_center, tap_step, lo, span;
+  int Mrows, out_stride, out_pad, Tout;
+};
 int dac_tile_n(int N);
-int dac_conv_ws(const void* conv_params, int B, cudaStream_t st);
+int dac_conv_ws(const DacConv& conv, int B, cudaStream_t st);
 int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, int has_kv, float scale,
                          int slot_base, const int* slot_dyn, void* ck, void* cv, int B, int heads, int c_stride,
                          int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch,

@@ -137,13 +137,70 @@ class DacDecoderEngine:
                   self.codebook_size, self.latent, cabi.ptr(z), cabi.stream_ptr())
         return z
 
+    PAD_LO, PAD_HI = 8, 264  # PTTS_DAC_PLANE_PAD_LO / _HI of include/parler_b200.h
+
+    def _new_planes(self, B, C, T):
+        """Uninitialised activation planes [B][2][C/8][PAD_LO + T + PAD_HI][8] bf16 with zeroed pad rows."""
+        p = torch.empty(B, 2, C // 8, self.PAD_LO + T + self.PAD_HI, 8, device=self.device, dtype=torch.bfloat16)
+        p[:, :, :, : self.PAD_LO].zero_()
+        p[:, :, :, self.PAD_LO + T :].zero_()
+        return p
+
+    def _conv_px(self, T, wt, dil=1, x=None, xp=None, alpha=None, residual=None, planes_alpha=None, to_planes=False):
+        """conv1d over pre-tiled weights: fp32 (x, Snake alpha) or planes (xp) in, fp32 or planes (activated with
+        planes_alpha for the consumer) out."""
+        w, _, bias, cout, k = wt
+        B = (x if x is not None else xp).shape[0]
+        cin = x.shape[2] if x is not None else xp.shape[2] * 8
+        y = yp = None
+        if to_planes:
+            yp = self._new_planes(B, cout, T)
+        else:
+            y = torch.empty(B, T, cout, device=self.device, dtype=torch.float32)
+        cabi.call("ptts_dac_conv1d_px", cabi.ptr(x), cabi.ptr(xp), B, T, cin, cabi.ptr(w), cabi.ptr(bias), cout, k, dil,
+                  cabi.ptr(alpha), cabi.ptr(residual), cabi.ptr(y), cabi.ptr(yp), cabi.ptr(planes_alpha),
+                  cabi.stream_ptr())
+        return yp if to_planes else y
+
+    def _convt_px(self, T, wt, stride, xp):
+        w, _, bias, cout = wt
+        B, cin = xp.shape[0], xp.shape[2] * 8
+        y = torch.empty(B, T * stride, cout, device=self.device, dtype=torch.float32)
+        cabi.call("ptts_dac_convtr1d_px", None, cabi.ptr(xp), B, T, cin, cabi.ptr(w), cabi.ptr(bias), cout, stride,
+                  None, cabi.ptr(y), cabi.stream_ptr())
+        return y
+
+    def _decode_latents_planes(self, z):
+        """Pre-tiled path: every Snake that feeds a k=1 conv or a transposed conv is applied by the producing conv's
+        epilogue, which writes hi/mid bf16 planes instead of fp32 (modeling_dac / dac.model.dac.Decoder order kept)."""
+        B, T, _ = z.shape
+        blocks = self.f_blocks
+        xp = self._conv_px(T, self.f_conv_in, x=z, planes_alpha=blocks[0]["alpha"], to_planes=True)
+        x = None
+        for i, blk in enumerate(blocks):
+            x = self._convt_px(T, blk["convt"], blk["stride"], xp)
+            T *= blk["stride"]
+            xp = None
+            for j, r in enumerate(blk["res"]):
+                yp = self._conv_px(T, r["c1"], dil=r["dil"], x=x, alpha=r["a1"], planes_alpha=r["a2"], to_planes=True)
+                if j == len(blk["res"]) - 1 and i + 1 < len(blocks):  # feeds the next block's transposed conv
+                    xp = self._conv_px(T, r["c2"], xp=yp, residual=x, planes_alpha=blocks[i + 1]["alpha"], to_planes=True)
+                    x = None
+                else:
+                    x = self._conv_px(T, r["c2"], xp=yp, residual=x)
+                del yp
+        return x
+
     def decode_latents_nwc(self, z):
-        x = self._conv_nwc(z, self.f_conv_in)
-        for blk in self.f_blocks:
-            x = self._convt_nwc(x, blk["convt"], blk["stride"], blk["alpha"])
-            for r in blk["res"]:
-                y = self._conv_nwc(x, r["c1"], dil=r["dil"], alpha=r["a1"])
-                x = self._conv_nwc(y, r["c2"], alpha=r["a2"], residual=x)
+        if self.pretiled:
+            x = self._decode_latents_planes(z)
+        else:
+            x = self._conv_nwc(z, self.f_conv_in)
+            for blk in self.f_blocks:
+                x = self._convt_nwc(x, blk["convt"], blk["stride"], blk["alpha"])
+                for r in blk["res"]:
+                    y = self._conv_nwc(x, r["c1"], dil=r["dil"], alpha=r["a1"])
+                    x = self._conv_nwc(y, r["c2"], alpha=r["a2"], residual=x)
         B, T, Cin = x.shape
         w, b = self.f_conv_out
         out = torch.empty(B, 1, T, device=x.device, dtype=torch.float32)

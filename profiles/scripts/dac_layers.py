@@ -29,6 +29,11 @@ def timed(name, *args):
         key, macs = (name, args[3], args[7], args[8], args[9]), args[1] * args[2] * args[3] * args[7] * args[8]
     elif name == "ptts_dac_convtr1d_nwc":
         key, macs = (name, args[3], args[7], args[8], 0), args[1] * args[2] * args[3] * args[7] * 2 * args[8]
+    elif name == "ptts_dac_conv1d_px":
+        mode = ("planes" if args[1] is not None else "fp32") + "->" + ("planes" if args[13] is not None else "fp32")
+        key, macs = (name + " " + mode, args[4], args[7], args[8], args[9]), args[2] * args[3] * args[4] * args[7] * args[8]
+    elif name == "ptts_dac_convtr1d_px":
+        key, macs = (name, args[4], args[7], args[8], 0), args[2] * args[3] * args[4] * args[7] * 2 * args[8]
     else:
         key, macs = (name, 0, 0, 0, 0), 0
     events.append((key, macs, e0, e1))
@@ -49,5 +54,5 @@ for key, macs, e0, e1 in events:
 tot = sum(a[1] for a in agg.values())
 print(f"B={B} F={F}: total {tot:.1f} ms")
 for key, (n, ms, macs) in agg.items():
-    print(f"{key[0][9:]:18s} Cin={key[1]:5d} Cout={key[2]:5d} k/s={key[3]:2d} dil={key[4]:2d} n={n:3d} {ms:8.2f} ms "
+    print(f"{key[0][9:]:32s} Cin={key[1]:5d} Cout={key[2]:5d} k/s={key[3]:2d} dil={key[4]:2d} n={n:3d} {ms:8.2f} ms "
           f"({100 * ms / tot:4.1f}%)  {2 * macs / ms / 1e9 if ms else 0:7.1f} TFLOP/s fp32-eq")

@@ -203,8 +203,8 @@ def _weights(w_tnc, tiled):
                                               (384, 384, 7, 3, 129), (32, 26, 7, 1, 5), (192, 192, 7, 9, 1000),
                                               (96, 96, 1, 1, 257), (64, 40, 7, 3, 256)])
 def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T, tiled):
-    if tiled and Cout % 4:
-        pytest.skip("pre-tiled kernel stores 16-byte vectors")
+    if tiled and Cout % 16:
+        pytest.skip("pre-tiled kernel works on 16-column groups")
     g = torch.Generator().manual_seed(Cin + k + dil)
     B = 2
     x = torch.randn(B, Cin, T, generator=g).to(DEV)
@@ -242,6 +242,67 @@ def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T, tiled):
     y = torch.empty(B, T * s, Cout, device=DEV)
     cabi.call("ptts_dac_convtr1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, s,
               cabi.ptr(alpha), cabi.ptr(y), cabi.stream_ptr())
+    err = float((y.transpose(1, 2) - want).abs().max())
+    assert err < 2e-4 * max(1.0, float(want.abs().max())), err
+
+
+def _to_planes(x_nct, alpha):
+    """reference construction of activated hi/mid planes [B][2][C/8][8 + T + 264][8] from (B, C, T) fp32"""
+    B, Cc, T = x_nct.shape
+    xs = x_nct if alpha is None else x_nct + (1.0 / (alpha[None, :, None] + 1e-9)) * torch.sin(alpha[None, :, None] * x_nct) ** 2
+    hi = xs.to(torch.bfloat16)
+    mid = (xs - hi.float()).to(torch.bfloat16)
+    p = torch.zeros(B, 2, Cc // 8, 8 + T + 264, 8, dtype=torch.bfloat16, device=x_nct.device)
+    for i, pl in enumerate((hi, mid)):
+        p[:, i, :, 8 : 8 + T] = pl.view(B, Cc // 8, 8, T).permute(0, 1, 3, 2)
+    return p.contiguous(), xs
+
+
+@pytest.mark.parametrize("Cin,Cout,k,dil,T", [(96, 96, 1, 1, 700), (192, 192, 1, 1, 513), (384, 384, 7, 1, 300)])
+def test_dac_conv1d_planes_in_and_out(Cin, Cout, k, dil, T):
+    """conv1d reading activated planes and writing planes for its consumer == torch fp64 on the same Snake'd input."""
+    from parler_tts_b200.dac import DacDecoderEngine
+    g = torch.Generator().manual_seed(Cin + k + T)
+    B = 2
+    x = torch.randn(B, Cin, T, generator=g).to(DEV)
+    w = (torch.randn(Cout, Cin, k, generator=g) / (Cin * k) ** 0.5).to(DEV)
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    a_in = (1.0 + 0.2 * torch.randn(Cin, generator=g)).abs().add(0.05).to(DEV)
+    a_out = (1.0 + 0.2 * torch.randn(Cout, generator=g)).abs().add(0.05).to(DEV)
+    res = torch.randn(B, Cout, T, generator=g).to(DEV)
+    xp, xs = _to_planes(x, a_in)
+    want = torch.nn.functional.conv1d(xs.double(), w.double(), bias.double(), dilation=dil,
+                                      padding=dil * (k - 1) // 2).float() + res
+    wt, _ = DacDecoderEngine._tile(*_split(w.permute(2, 0, 1).contiguous()))
+    res_nwc = res.transpose(1, 2).contiguous()
+    y = torch.empty(B, T, Cout, device=DEV)
+    yp = torch.zeros(B, 2, Cout // 8, 8 + T + 264, 8, dtype=torch.bfloat16, device=DEV)
+    cabi.call("ptts_dac_conv1d_px", None, cabi.ptr(xp), B, T, Cin, cabi.ptr(wt), cabi.ptr(bias), Cout, k, dil, None,
+              cabi.ptr(res_nwc), cabi.ptr(y), cabi.ptr(yp), cabi.ptr(a_out), cabi.stream_ptr())
+    tol = 2e-4 * max(1.0, float(want.abs().max()))
+    assert float((y.transpose(1, 2) - want).abs().max()) < tol
+    want_p, want_s = _to_planes(want, a_out)
+    got = (yp[:, 0].float() + yp[:, 1].float())[:, :, 8 : 8 + T].permute(0, 1, 3, 2).reshape(B, Cout, T)
+    assert float((got - want_s).abs().max()) < 2 * tol
+    assert float(yp[:, :, :, :8].float().abs().max()) == 0 and float(yp[:, :, :, 8 + T :].float().abs().max()) == 0
+
+
+@pytest.mark.parametrize("Cin,Cout,s,T", [(384, 192, 4, 515), (1536, 768, 8, 11)])
+def test_dac_convtr1d_planes_in(Cin, Cout, s, T):
+    from parler_tts_b200.dac import DacDecoderEngine
+    g = torch.Generator().manual_seed(Cin + s + T)
+    B = 2
+    x = torch.randn(B, Cin, T, generator=g).to(DEV)
+    w = (torch.randn(Cin, Cout, 2 * s, generator=g) / (Cin * 2) ** 0.5).to(DEV)
+    bias = torch.randn(Cout, generator=g).to(DEV)
+    alpha = (1.0 + 0.2 * torch.randn(Cin, generator=g)).abs().add(0.05).to(DEV)
+    xp, xs = _to_planes(x, alpha)
+    want = torch.nn.functional.conv_transpose1d(xs.double(), w.double(), bias.double(), stride=s,
+                                                padding=(s + 1) // 2).float()
+    wt, _ = DacDecoderEngine._tile(*_split(w.permute(2, 1, 0).reshape(2, s * Cout, Cin).contiguous()))
+    y = torch.empty(B, T * s, Cout, device=DEV)
+    cabi.call("ptts_dac_convtr1d_px", None, cabi.ptr(xp), B, T, Cin, cabi.ptr(wt), cabi.ptr(bias), Cout, s, None,
+              cabi.ptr(y), cabi.stream_ptr())
     err = float((y.transpose(1, 2) - want).abs().max())
     assert err < 2e-4 * max(1.0, float(want.abs().max())), err
 
