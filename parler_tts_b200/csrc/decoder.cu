@@ -4,6 +4,7 @@
 // 264-382 (attention), 1096-1185 (lm heads) for the generation path.
 #include <stdlib.h>
 
+#include "gemm_common.cuh"
 #include "ops.cuh"
 
 namespace ptts {
@@ -52,10 +53,13 @@ static inline size_t kv_layer_elems(const PttsModel* m, int B, int slots) {
   return (size_t)B * m->n_heads * slots * m->head_dim;
 }
 
-// Scratch layout: [0, attn_scratch_floats) split-KV attention partials | work area (qkv staging of the simple family,
+// Scratch layout: [0, 64) grid-barrier counters of the fused GEMM finisher (zero between launches; the caller hands
+// over zero-initialised scratch) | split-KV attention partials | work area (qkv staging of the simple family,
 // all-position logits staging, split-K partial sums of the residual GEMMs).
+constexpr int kScratchHeader = 64;
+static inline float* attn_area(const PttsState* s) { return s->scratch + kScratchHeader; }
 static inline float* work_area(const PttsModel* m, const PttsState* s) {
-  return s->scratch + attn_scratch_floats(s->B, m->n_heads);
+  return attn_area(s) + attn_scratch_floats(s->B, m->n_heads);
 }
 
 // floats the caller-provided work area is guaranteed to hold for `rows` token rows (see ptts_scratch_floats)
@@ -68,6 +72,7 @@ struct Pending {
   const float* part = nullptr;
   int S = 0;
   int64_t stride = 0;
+  const float* ln_done = nullptr;  // gamma of the LayerNorm the producing GEMM's finisher has already applied
 };
 
 struct Path {
@@ -88,6 +93,11 @@ static Path pick_path(const PttsModel* m, const PttsState* s) {
 static int ln_step(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const float* g,
                    const float* b, int rows_out, int row_mul, int row_add, cudaStream_t st) {
   const int H = m->hidden;
+  if (pend.ln_done) {  // the residual GEMM folded its partial sums and wrote this LayerNorm itself
+    PTTS_CHECK_ARG(pend.ln_done == g && row_mul == 1 && row_add == 0, "internal: fused LayerNorm mismatch");
+    pend = Pending();
+    return PTTS_OK;
+  }
   if (path.ln) {
     PTTS_TRY(layernorm_fast(s->h, pend.part, pend.S, pend.stride, g, b, rows_out, H, 1e-5f, row_mul, row_add, s->xn,
                             m->wdtype, st));
@@ -146,14 +156,38 @@ static int skip_mask() {
   } while (0)
 
 // h += x . w^T   (out_proj / fc2 with the residual add of modeling_parler_tts.py:460,483,492)
+// PTTS_LNFUSE=1: let the residual GEMM fold its partial sums and apply the next LayerNorm itself behind a grid-wide
+// arrival counter (no separate launch).  Measured on B200 (B=64): 1.99 ms per decode step against 1.78 ms with the
+// separate fold + LayerNorm launch - the fence + atomic + poll of the barrier and two rows per CTA cost more than the
+// 0.8 us kernel hand-over they replace - so it is OFF by default.
+static bool ln_fusion_enabled() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_LNFUSE");
+    v = (e && e[0] == '1') ? 1 : 0;
+  }
+  return v == 1;
+}
+
+// next_g / next_b: the LayerNorm that consumes the residual stream next over the SAME rows (or null): with the
+// tcgen05 split-K kernel and a grid small enough to be co-resident, the GEMM finishes it itself (grid barrier).
 static int residual_linear(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const void* x,
-                           const void* w, int rows, int K, cudaStream_t st) {
+                           const void* w, int rows, int K, const float* next_g, const float* next_b,
+                           cudaStream_t st) {
   const int H = m->hidden, dt = m->wdtype;
   if (path.gemm && path.ln && rows <= 256 && split_k_partials_enabled()) {
     int bn = 64;
     const int S = gemm_bf16_plan_splits(rows, H, K, &bn);
     if (S > 1) {
       float* part = work_area(m, s);
+      const int ctas = ((H + 127) / 128) * ((rows + 63) / 64) * S;
+      if (bn == 0 && next_g && next_b && ctas <= 96 && H % 4 == 0 && ln_fusion_enabled()) {
+        gemm::GemmFinish fin = {s->h, next_g, next_b, s->xn, reinterpret_cast<unsigned int*>(s->scratch), 1e-5f};
+        PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st, &fin));
+        pend = Pending();
+        pend.ln_done = next_g;
+        return PTTS_OK;
+      }
       PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st));
       pend.part = part;
       pend.S = S;
@@ -188,7 +222,7 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
     PTTS_UNLESS_SKIPPED(4, attention_fast_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, 1, scale, ctx_base - 1, ctx_dyn,
                                                 ks, vs, B, heads, s->c_max, ctx_base, ctx_dyn, s->prompt_mask, s->P,
-                                                s->attn, s->scratch, nullptr, 0, 0, nullptr, st));
+                                                s->attn, attn_area(s), nullptr, 0, 0, nullptr, st));
     goto self_attention_done;
   }
   if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
@@ -201,9 +235,13 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, s->c_max, ctx_base - Tq, ctx_dyn, scale, s->q, ks, vs, st));
   }
   PTTS_UNLESS_SKIPPED(4, attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn,
-                                            Tq > 1, s->prompt_mask, s->P, s->attn, s->scratch, st));
+                                            Tq > 1, s->prompt_mask, s->P, s->attn, attn_area(s), st));
 self_attention_done:
-  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
+  {
+    const bool cross = s->S > 0;
+    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, fuse ? (cross ? L.ln2_g : L.ln3_g) : nullptr,
+                                           fuse ? (cross ? L.ln2_b : L.ln3_b) : nullptr, st));
+  }
   // cross attention block (modeling_parler_tts.py:465-483)
   if (s->S > 0) {
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
@@ -220,15 +258,16 @@ self_attention_done:
                                 ? (char*)s->kv_self + (size_t)(2 * (l + 1)) * kv_layer_elems(m, B, s->c_max) * es
                                 : nullptr;
       PTTS_UNLESS_SKIPPED(32, attention_fast_fused(qpart, Sc, (int64_t)rows * H, H, 0, scale, 0, nullptr, kc, vc, B,
-                                                   heads, s->S, s->S, nullptr, s->enc_mask, s->S, s->attn, s->scratch,
+                                                   heads, s->S, s->S, nullptr, s->enc_mask, s->S, s->attn, attn_area(s),
                                                    ks_next, s->c_max, ctx_base, ctx_dyn, st));
     } else {
       PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale,
                                               PTTS_ACT_NONE, nullptr, nullptr, s->q, dt, st));
       PTTS_UNLESS_SKIPPED(32, attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0,
-                                                 s->enc_mask, s->S, s->attn, s->scratch, st));
+                                                 s->enc_mask, s->S, s->attn, attn_area(s), st));
     }
-    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, st));
+    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, fuse ? L.ln3_g : nullptr,
+                                           fuse ? L.ln3_b : nullptr, st));
   }
   // feed forward block
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
@@ -245,7 +284,14 @@ self_attention_done:
                                               nullptr, nullptr, s->ffn, dt, st));
     }
   }
-  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, st));
+  {
+    // decode: the LayerNorm after fc2 is the next layer's first one, or the final one in front of the LM heads
+    const bool last = l + 1 == m->n_layers;
+    const float* ng = last ? m->lnf_g : m->layers[l + 1].ln1_g;
+    const float* nb = last ? m->lnf_b : m->layers[l + 1].ln1_b;
+    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, fuse ? ng : nullptr,
+                                           fuse ? nb : nullptr, st));
+  }
   return PTTS_OK;
 }
 
@@ -269,7 +315,7 @@ extern "C" int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows) {
   const int64_t c = (int64_t)kMaxSplitK * (rows < 256 ? rows : 256) * 3 * m->hidden;  // split-K partial sums (qkv)
   if (b > w) w = b;
   if (c > w) w = c;
-  return attn_scratch_floats(rows, m->n_heads) + w + 4096;  // rows >= B bounds the split-KV partial area
+  return kScratchHeader + attn_scratch_floats(rows, m->n_heads) + w + 4096;  // rows >= B bounds the split-KV partial area
 }
 
 extern "C" int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T0,

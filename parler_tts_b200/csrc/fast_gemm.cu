@@ -230,12 +230,17 @@ int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out) {
 }
 
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st) {
+                      cudaStream_t st, const GemmFinish* fin) {
   GemmParams p = {};
   p.X = (const __nv_bfloat16*)x;
   p.W = (const __nv_bfloat16*)w;
   p.M = M; p.N = N; p.K = K; p.k_per_split = K / splits;
   p.part = part;
+  PTTS_CHECK_ARG(!fin || bn == 0, "gemm_bf16_partial: the fused fold + LayerNorm finisher needs the tcgen05 kernel");
+  if (fin) {
+    p.fin_h = fin->h; p.fin_g = fin->g; p.fin_b = fin->b; p.fin_y = (__nv_bfloat16*)fin->y; p.fin_ctr = fin->ctr;
+    p.fin_eps = fin->eps;
+  }
   if (bn == 0) return umma_gemm_partial(p, splits, st);
   return launch_bn<EPI_PARTIAL>(bn, p, splits, st);
 }

@@ -228,6 +228,85 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
     }
     STAMP(6);
     agg();
+    if (p.fin_h) {
+      // ---- finisher: grid-wide arrival, then this CTA folds + LayerNorms its share of the rows.  Every CTA of the
+      // grid is resident (grid <= #SMs, and a dependent grid is only launched once all of them have started), so
+      // the wait cannot deadlock; it is bounded anyway.
+      const unsigned total = gridDim.x * gridDim.y * gridDim.z;
+      __threadfence();  // my partial tile is visible device-wide before I announce it
+      __syncthreads();
+      if (threadIdx.x == 0) {
+        atomicAdd(p.fin_ctr, 1u);
+        const long long t0 = clock64();
+        unsigned seen;
+        do {
+          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(seen) : "l"(p.fin_ctr) : "memory");
+          if (clock64() - t0 > 2000000000ll) __trap();
+        } while (seen < total);
+      }
+      __syncthreads();
+      const unsigned cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
+      float* rowbuf = reinterpret_cast<float*>(smem);  // operand slabs are dead: N floats
+      float* redbuf = rowbuf + p.N;                    // 8 floats
+      const int S = (int)gridDim.z;
+      for (int row = (int)cta; row < p.M; row += (int)total) {
+        float* hr = p.fin_h + (size_t)row * p.N;
+        float sum = 0.f;
+        for (int c = threadIdx.x * 4; c < p.N; c += NTH * 4) {
+          float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
+          for (int s0 = 0; s0 < S; s0 += 4) {  // 4 slices in flight, added in slice order (deterministic)
+            float4 t[4];
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (s0 + u < S)
+                t[u] = __ldcg(reinterpret_cast<const float4*>(p.part + ((size_t)(s0 + u) * p.M + row) * p.N + c));
+#pragma unroll
+            for (int u = 0; u < 4; ++u)
+              if (s0 + u < S) { v.x += t[u].x; v.y += t[u].y; v.z += t[u].z; v.w += t[u].w; }
+          }
+          *reinterpret_cast<float4*>(hr + c) = v;
+          *reinterpret_cast<float4*>(rowbuf + c) = v;
+          sum += (v.x + v.y) + (v.z + v.w);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
+        if (lane == 0) redbuf[warp] = sum;
+        __syncthreads();
+        const float mean = ((redbuf[0] + redbuf[1]) + (redbuf[2] + redbuf[3])) / (float)p.N;
+        float qq = 0.f;
+        for (int c = threadIdx.x * 4; c < p.N; c += NTH * 4) {
+          const float4 v = *reinterpret_cast<const float4*>(rowbuf + c);
+          const float a = v.x - mean, b = v.y - mean, cc = v.z - mean, d = v.w - mean;
+          qq += (a * a + b * b) + (cc * cc + d * d);
+        }
+#pragma unroll
+        for (int o = 16; o > 0; o >>= 1) qq += __shfl_xor_sync(0xffffffffu, qq, o);
+        if (lane == 0) redbuf[4 + warp] = qq;
+        __syncthreads();
+        const float rstd = rsqrtf(((redbuf[4] + redbuf[5]) + (redbuf[6] + redbuf[7])) / (float)p.N + p.fin_eps);
+        for (int c = threadIdx.x * 4; c < p.N; c += NTH * 4) {
+          const float4 v = *reinterpret_cast<const float4*>(rowbuf + c);
+          const float4 gg = __ldg(reinterpret_cast<const float4*>(p.fin_g + c));
+          const float4 bb = __ldg(reinterpret_cast<const float4*>(p.fin_b + c));
+          const __nv_bfloat162 lo = __floats2bfloat162_rn((v.x - mean) * rstd * gg.x + bb.x, (v.y - mean) * rstd * gg.y + bb.y);
+          const __nv_bfloat162 hi = __floats2bfloat162_rn((v.z - mean) * rstd * gg.z + bb.z, (v.w - mean) * rstd * gg.w + bb.w);
+          uint2 u;
+          u.x = *reinterpret_cast<const uint32_t*>(&lo);
+          u.y = *reinterpret_cast<const uint32_t*>(&hi);
+          *reinterpret_cast<uint2*>(p.fin_y + (size_t)row * p.N + c) = u;
+        }
+        __syncthreads();  // rowbuf / redbuf are reused by the next row
+      }
+      // departure: the last CTA to leave restores both counters to zero for the next launch
+      if (threadIdx.x == 0) {
+        const unsigned d = atomicAdd(p.fin_ctr + 1, 1u);
+        if (d == total - 1) {
+          p.fin_ctr[0] = 0u;
+          p.fin_ctr[1] = 0u;
+          __threadfence();
+        }
+      }
+    }
     tl_end(tl);
     return;
   }

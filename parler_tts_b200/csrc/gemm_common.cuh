@@ -28,6 +28,26 @@ struct GemmParams {
   float q_scale;
   // PARTIAL
   float* part;
+  // PARTIAL + finisher (tcgen05 kernel only, fin_h != null): once every CTA of the grid has stored its partial tile
+  // (arrival counter fin_ctr[0], departure counter fin_ctr[1]; both zero between launches), CTA i folds the split-K
+  // slices of rows i, i + #CTAs, ... into the residual stream fin_h (N = hidden) in slice order and writes their
+  // LayerNorm (fin_g, fin_b, eps) as bf16 to fin_y - the separate fold + LayerNorm launch disappears
+  float* fin_h;
+  const float* fin_g;
+  const float* fin_b;
+  __nv_bfloat16* fin_y;
+  unsigned int* fin_ctr;
+  float fin_eps;
+};
+
+// optional finisher of gemm_bf16_partial (see GemmParams)
+struct GemmFinish {
+  float* h;
+  const float* g;
+  const float* b;
+  void* y;  // bf16 [M][N]
+  unsigned int* ctr;
+  float eps;
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }

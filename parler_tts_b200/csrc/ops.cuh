@@ -30,8 +30,9 @@ int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has
                       void* cv, int H, int heads, int d, int Tq, int c_stride, int pos_base, const int* pos_dyn,
                       cudaStream_t st);
 int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
+namespace gemm { struct GemmFinish; }
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st);
+                      cudaStream_t st, const gemm::GemmFinish* fin = nullptr);
 bool fast_layernorm_supported(int H);
 // y = act(sum of S split-K partial slices) as bf16 (fast_misc.cu)
 int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, int N, int act, void* y,
