@@ -92,195 +92,6 @@ struct QFuse {
   int pf_pct;
 };
 
-// ---------------------------------------------------------------------------------------------------------------
-// One-pass (online softmax) flash-decode kernel (PTTS_ATTN=online; NOT the default, see launch_decode).  The K row and the V row of a cache slot travel
-// together: no score buffer, no K pass / softmax / V pass phases in which every CTA of the single resident wave stops
-// loading at the same time (measured on B200: the three-pass kernel costs ~3.5 us of such bubbles per launch and tops
-// out at ~7 TB/s even when the cache is L2 resident).  Each group of TPK threads owns the rows j = j0 + g (mod KPB) and
-// keeps its own running (max, sum, acc[D]); the KPB groups are merged through shared memory at the end, in fixed
-// order (deterministic).  A register slot is re-requested as soon as it has been consumed, so 2U 16-byte loads per
-// thread stay in flight.
-template <typename T, int D, bool FUSED>
-__global__ void __launch_bounds__(NT, 7)  // 7 x 148 = 1036 CTA slots >= 64 x 16 (b, head) pairs: one wave
-attn_online_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads,
-                   int c_stride, int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask,
-                   int mask_len, T* __restrict__ out, float* __restrict__ part, int splits, TL tl) {
-  constexpr int E = Chunk<T>::E;     // elements per 16-byte chunk
-  constexpr int TPK = D / E;         // threads per cache row
-  constexpr int KPB = NT / TPK;      // rows per CTA pass
-  constexpr int U = 4;               // rows per thread group and batch
-  constexpr float kLog2e = 1.4426950408889634f;
-  __shared__ __align__(16) T qs[D];
-  __shared__ float gm[KPB], gl[KPB];
-  __shared__ __align__(16) float ored[KPB * D];
-  const int hd = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
-  const int tid = threadIdx.x;
-  const int g = tid / TPK, c = tid % TPK;
-  const int H = heads * D;
-  tl_start(tl);
-  const T* kb = ck + ((int64_t)b * heads + hd) * (int64_t)c_stride * D + c * E;
-  const T* vb = cv + ((int64_t)b * heads + hd) * (int64_t)c_stride * D + c * E;
-  int ctx = 0, j0 = 0, j1 = 0, n = 0;
-  auto plan = [&]() {
-    ctx = dyn_value(ctx_base, ctx_dyn);
-    const int chunk = (ctx + splits - 1) / splits;
-    j0 = sp * chunk;
-    j1 = min(ctx, j0 + chunk);
-    n = max(j1 - j0, 0);
-  };
-  uint4 kc[U], vc[U];
-  auto load_first = [&]() {
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int j = j0 + u * KPB + g;
-      if (j < j1) {
-        kc[u] = Chunk<T>::load_raw(kb + (int64_t)j * D);
-        vc[u] = Chunk<T>::load_raw(vb + (int64_t)j * D);
-      }
-    }
-  };
-  bool pre = false;
-  if constexpr (FUSED) {
-    // Decode-step contract of the fused entry point: cache rows below the slot this launch appends (self-attention) or
-    // the whole cross-attention cache, and the position counter (written by the previous step's epilogue), are at
-    // least two launches old - they may be read BEFORE griddepcontrol.wait, while the producer GEMM still runs.
-    plan();
-    const int old_end = qf.has_kv ? dyn_value(qf.slot_base, qf.slot_dyn) : ctx;
-    pre = n > 0 && min(j1, j0 + KPB * U) <= old_end;
-    if (pre) load_first();
-    // HBM is idle during the short kernels between two attention launches: queue the L2 prefetch of the rows the
-    // NEXT attention launch streams first
-    if (qf.pf_next && sp == 0) {
-      const int rows = dyn_value(qf.pf_rows_base, qf.pf_rows_dyn) * qf.pf_pct / 100;
-      l2_prefetch_range(reinterpret_cast<const T*>(qf.pf_next) + ((int64_t)b * heads + hd) * qf.pf_stride * D,
-                        (int64_t)rows * D * sizeof(T));
-    }
-  }
-  pdl_wait();
-  pdl_launch();
-  tl_dep(tl);
-  if constexpr (!FUSED) plan();
-  float qv[E];
-  if constexpr (FUSED) {
-    if (tid < D) {
-      const float* p0 = qf.part + (int64_t)b * qf.ncols + hd * D + tid;
-      float aq = 0.f, ak = 0.f, av = 0.f;
-      for (int s0 = 0; s0 < qf.S; s0 += 4) {  // 4 slices (12 loads) in flight, added in slice order
-        float tq[4], tk[4], tv[4];
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (s0 + u < qf.S) {
-            const float* ps = p0 + (s0 + u) * qf.stride;
-            tq[u] = __ldcg(ps);
-            if (qf.has_kv) {
-              tk[u] = __ldcg(ps + H);
-              tv[u] = __ldcg(ps + 2 * H);
-            }
-          }
-#pragma unroll
-        for (int u = 0; u < 4; ++u)
-          if (s0 + u < qf.S) {
-            aq += tq[u];
-            if (qf.has_kv) {
-              ak += tk[u];
-              av += tv[u];
-            }
-          }
-      }
-      qs[tid] = from_f<T>(aq * qf.scale);
-      if (qf.has_kv) {
-        const int slot = dyn_value(qf.slot_base, qf.slot_dyn);
-        const int64_t o = (((int64_t)b * heads + hd) * c_stride + slot) * D + tid;
-        const_cast<T*>(ck)[o] = from_f<T>(ak);
-        const_cast<T*>(cv)[o] = from_f<T>(av);
-      }
-    }
-    __syncthreads();  // q in shared memory, the new cache row visible to the whole CTA
-    Chunk<T>::unpack(*reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(qs) + c * 16), qv);
-  } else {
-    Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
-  }
-  if (!pre) load_first();
-  const float neg = finfo_min<T>();
-  const int* mrow = key_mask ? key_mask + (int64_t)b * mask_len : nullptr;
-  float m = -INFINITY, l = 0.f, acc[E];
-#pragma unroll
-  for (int e = 0; e < E; ++e) acc[e] = 0.f;
-  for (int base = j0; base < j1; base += KPB * U) {
-    float s[U];
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int j = base + u * KPB + g;
-      float dot = 0.f;
-      if (j < j1) {
-        float kf[E];
-        Chunk<T>::unpack(kc[u], kf);
-#pragma unroll
-        for (int e = 0; e < E; ++e) dot = fmaf(qv[e], kf[e], dot);
-      }
-      const int jn = j + KPB * U;  // this register slot is free again: request the row it serves in the next batch
-      if (jn < j1) kc[u] = Chunk<T>::load_raw(kb + (int64_t)jn * D);
-#pragma unroll
-      for (int o = TPK / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-      bool keep = true;
-      if (mrow && j < mask_len && j < j1) keep = mrow[j] != 0;
-      s[u] = j < j1 ? (keep ? dot : neg) : -INFINITY;
-    }
-    float m_new = m;
-#pragma unroll
-    for (int u = 0; u < U; ++u) m_new = fmaxf(m_new, s[u]);
-    const float rescale = m == -INFINITY ? 0.f : exp2f((m - m_new) * kLog2e);
-    l *= rescale;
-#pragma unroll
-    for (int e = 0; e < E; ++e) acc[e] *= rescale;
-#pragma unroll
-    for (int u = 0; u < U; ++u) {
-      const int j = base + u * KPB + g;
-      if (j < j1) {
-        const float pj = exp2f((s[u] - m_new) * kLog2e);
-        l += pj;
-        float vf[E];
-        Chunk<T>::unpack(vc[u], vf);
-#pragma unroll
-        for (int e = 0; e < E; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
-      }
-      const int jn = j + KPB * U;
-      if (jn < j1) vc[u] = Chunk<T>::load_raw(vb + (int64_t)jn * D);
-    }
-    m = m_new;
-  }
-  if (c == 0) {
-    gm[g] = m;
-    gl[g] = l;
-  }
-#pragma unroll
-  for (int e = 0; e < E; ++e) ored[g * D + c * E + e] = acc[e];
-  __syncthreads();
-  if (tid < D) {
-    float M = -INFINITY;
-#pragma unroll
-    for (int gg = 0; gg < KPB; ++gg) M = fmaxf(M, gm[gg]);
-    float total = 0.f, o = 0.f;
-#pragma unroll
-    for (int gg = 0; gg < KPB; ++gg) {
-      const float w = gm[gg] == -INFINITY ? 0.f : exp2f((gm[gg] - M) * kLog2e);
-      total = fmaf(gl[gg], w, total);
-      o = fmaf(ored[gg * D + tid], w, o);
-    }
-    if (splits == 1) {
-      out[(int64_t)b * H + hd * D + tid] = from_f<T>(n > 0 ? o / total : 0.f);
-    } else {
-      float* pp = part + (((int64_t)b * heads + hd) * splits + sp) * (D + 2);
-      pp[2 + tid] = o;
-      if (tid == 0) {
-        pp[0] = n > 0 ? M : -INFINITY;
-        pp[1] = n > 0 ? total : 0.f;
-      }
-    }
-  }
-  tl_end(tl);
-}
-
 // part layout: [(b*heads + h)*splits + s][D + 2] = { running max, sum of exp, unnormalised output[D] }
 template <typename T, int D, bool FUSED>
 __global__ void __launch_bounds__(NT, FUSED ? 7 : 8)  // 7 x 148 = 1036 CTA slots >= 64 x 16 (b, head) pairs
@@ -693,24 +504,11 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
   }
   PTTS_CHECK_ARG(splits == 1 || scratch, "attention_fast: split-KV needs scratch");
   cudaError_t e;
-  // PTTS_ATTN=online selects the one-pass online-softmax kernel.  Measured on B200 (B=64, ctx 472, bf16): three-pass
-  // 24.7 us, one-pass 33.1 us per launch - the per-batch max / rescale chain costs more issue slots than the phase
-  // bubbles it removes, so the three-pass kernel stays the default.
-  static int three_pass = -1;
-  if (three_pass < 0) {
-    const char* ev = getenv("PTTS_ATTN");
-    three_pass = (ev && ev[0] == 'o') ? 0 : 1;
-  }
-  if (!use_bulk && !three_pass) {
-    if (qf.part)
-      e = launch_k(attn_online_kernel<T, D, true>, dim3(heads, B, splits), dim3(NT), 0, st, qf, (const T*)q,
-                   (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
-                   splits, tl_next(c_stride > 64 ? 2 : 3));
-    else
-      e = launch_k(attn_online_kernel<T, D, false>, dim3(heads, B, splits), dim3(NT), 0, st, qf, (const T*)q,
-                   (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
-                   splits, tl_next(c_stride > 64 ? 2 : 3));
-  } else if (use_bulk && !qf.part) {
+  // Two one-pass (online softmax) variants were tried and removed: a scalar one (33.1 us per launch at B=64, ctx 472
+  // against 24.7 us for this three-pass kernel) and a tensor-core one (mma.sync for q.K^T and P.V, 26.8 us).  Even on an
+  // L2-resident cache all three top out at 6..7 TB/s (profiles/scripts/attn_l2.py), i.e. the limit is the 16-byte
+  // load path per SM, not the arithmetic and not the pass structure.
+  if (use_bulk && !qf.part) {
     const size_t smem = (size_t)BULK_STAGES * BULK_BYTES + sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
     static size_t configured = 0;
     if (smem > 48 * 1024 && smem > configured) {
