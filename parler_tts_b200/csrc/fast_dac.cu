@@ -210,47 +210,92 @@ __global__ void __launch_bounds__(NT2, 1) dac_conv_mma_kernel(const ConvParams p
     }
 }
 
-// Final conv (Cout = 1, k = 7) + tanh: y[b][t] = tanh(bias + sum_k sum_ci snake(x)[t + k - 3][ci] * w[k][ci]).
-// HBM-bound (reads x once): one CTA per 128 samples, snake(x) tile staged in shared memory (odd pitch: conflict-free).
+// Output conv (Cout = 1, k = 7) + tanh over channels-last fp32 input: y[t] = tanh(b + sum_k sum_c snake(x)[t+k-3][c] w[k][c]).
+// HBM-bound (one read of x).  Phase 1: z[r][k] = sum_c snake(x[r][c]) w[k][c] for the 134 input rows of a 128-row tile:
+// 8 threads per row (fully coalesced 128-byte reads), every element is activated once and used for all 7 taps; the 8
+// partial vectors are combined by a 7-shuffle butterfly that leaves tap k in lane k.  Phase 2: y[t] = sum_k z[t+k][k].
+constexpr int CO_ROWS = 128, CO_HALO = 6, CO_MAXC = 256;
+__device__ __forceinline__ float snake_fast(float x, float a, float inv) {  // range-reduced SFU sine (see fast_dac2.cu)
+  const float ax = a * x;
+  const float k = rintf(ax * 0.15915494309189535f);
+  float r = fmaf(k, -6.2831854820251465f, ax);
+  r = fmaf(k, 1.7484556000744883e-7f, r);
+  const float sn = __sinf(r);
+  return fmaf(inv * sn, sn, x);
+}
 __global__ void __launch_bounds__(256)
 dac_conv_out_kernel(const float* __restrict__ x, int T, int Cin, const float* __restrict__ w /*[7][Cin]*/,
                     const float* __restrict__ bias, const float* __restrict__ alpha, float* __restrict__ y) {
-  extern __shared__ float sm[];
-  const int pitch = Cin + 1;
-  float* xs = sm;                      // [134][pitch]
-  float* ws = sm + 134 * pitch;        // [7][Cin]
-  float* red = ws + 7 * Cin;           // [128]
-  const int b = blockIdx.y, t0 = blockIdx.x * 128, tid = threadIdx.x;
+  __shared__ __align__(16) float ws[8 * CO_MAXC];                    // [tap 0..6, zero tap 7][Cin]
+  __shared__ float zs[(CO_ROWS + CO_HALO) * 8];                      // [row][tap]
+  const int b = blockIdx.y, t0 = blockIdx.x * CO_ROWS, tid = threadIdx.x, lane = tid & 31;
+  const int sub = tid & 7, rg = tid >> 3;                            // 8 threads per row, 32 rows per pass
   const float* xb = x + (int64_t)b * T * Cin;
-  for (int i = tid; i < 134 * Cin; i += 256) {
-    const int r = i / Cin, c = i - r * Cin;
-    const int t = t0 - 3 + r;
-    float v = 0.f;
+  for (int i = tid; i < 8 * Cin; i += 256) ws[i] = i < 7 * Cin ? w[i] : 0.f;
+  const int nj = Cin / 32;                                           // float4 chunks per thread and row (<= 8)
+  __syncthreads();
+  for (int r0 = 0; r0 < CO_ROWS + CO_HALO; r0 += 32) {  // uniform trip count: the shuffles below need whole warps
+    const int r = r0 + rg;
+    const int t = r < CO_ROWS + CO_HALO ? t0 - 3 + r : -1;
+    float acc[8];
+#pragma unroll
+    for (int k = 0; k < 8; ++k) acc[k] = 0.f;
     if (t >= 0 && t < T) {
-      v = __ldg(xb + (int64_t)t * Cin + c);
-      if (alpha) {
-        const float a = alpha[c];
-        v = snake_f(v, a, 1.0f / (a + 1e-9f));
+      const float* xr = xb + (int64_t)t * Cin + sub * 4;
+      for (int j = 0; j < nj; ++j) {
+        float4 v = __ldg(reinterpret_cast<const float4*>(xr + j * 32));
+        if (alpha) {
+          const float4 al = __ldg(reinterpret_cast<const float4*>(alpha + j * 32 + sub * 4));
+          v.x = snake_fast(v.x, al.x, __frcp_rn(al.x + 1e-9f));
+          v.y = snake_fast(v.y, al.y, __frcp_rn(al.y + 1e-9f));
+          v.z = snake_fast(v.z, al.z, __frcp_rn(al.z + 1e-9f));
+          v.w = snake_fast(v.w, al.w, __frcp_rn(al.w + 1e-9f));
+        }
+#pragma unroll
+        for (int k = 0; k < 7; ++k) {
+          const float4 wk = *reinterpret_cast<const float4*>(ws + k * Cin + j * 32 + sub * 4);
+          acc[k] = fmaf(v.x, wk.x, fmaf(v.y, wk.y, fmaf(v.z, wk.z, fmaf(v.w, wk.w, acc[k]))));
+        }
       }
     }
-    xs[r * pitch + c] = v;
-  }
-  for (int i = tid; i < 7 * Cin; i += 256) ws[i] = w[i];
-  __syncthreads();
-  const int tl = tid & 127, half = tid >> 7;
-  const int c0 = half * (Cin / 2), c1 = half ? Cin : Cin / 2;
-  float acc = 0.f;
+    // butterfly over the 8 lanes of the row: after step s every lane keeps the half of its vector selected by its
+    // own bit; lane `sub` ends with the full sum of tap `sub`
+    {
+      const bool up = sub & 4;
 #pragma unroll
-  for (int k = 0; k < 7; ++k) {
-    const float* xr = xs + (tl + k) * pitch;
-    const float* wr = ws + k * Cin;
-    for (int c = c0; c < c1; ++c) acc = fmaf(xr[c], wr[c], acc);
+      for (int k = 0; k < 4; ++k) {
+        const float send = up ? acc[k] : acc[k + 4];
+        const float keep = up ? acc[k + 4] : acc[k];
+        acc[k] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
+      }
+    }
+    {
+      const bool up = sub & 2;
+#pragma unroll
+      for (int k = 0; k < 2; ++k) {
+        const float send = up ? acc[k] : acc[k + 2];
+        const float keep = up ? acc[k + 2] : acc[k];
+        acc[k] = keep + __shfl_xor_sync(0xffffffffu, send, 2);
+      }
+    }
+    {
+      const bool up = sub & 1;
+      const float send = up ? acc[0] : acc[1];
+      const float keep = up ? acc[1] : acc[0];
+      acc[0] = keep + __shfl_xor_sync(0xffffffffu, send, 1);
+    }
+    if (r < CO_ROWS + CO_HALO) zs[r * 8 + sub] = acc[0];
   }
-  if (half) red[tl] = acc;
+  (void)lane;
   __syncthreads();
-  if (!half) {
-    const int t = t0 + tl;
-    if (t < T) y[(int64_t)b * T + t] = tanhf(acc + red[tl] + (bias ? bias[0] : 0.f));
+  if (tid < CO_ROWS) {
+    const int t = t0 + tid;
+    if (t < T) {
+      float o = bias ? bias[0] : 0.f;
+#pragma unroll
+      for (int k = 0; k < 7; ++k) o += zs[(tid + k) * 8 + k];
+      y[(int64_t)b * T + t] = tanhf(o);
+    }
   }
 }
 
@@ -414,14 +459,9 @@ extern "C" PTTS_API int ptts_dac_convtr1d_px(const float* x, const void* x_plane
 extern "C" PTTS_API int ptts_dac_conv_out_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const float* w,
                                      const float* bias, const float* snake_alpha, float* y, ptts_stream_t s) {
   PTTS_CHECK_ARG(x && w && y, "dac_conv_out_nwc: null pointer");
-  PTTS_CHECK_ARG(B > 0 && T > 0 && Cin > 0 && Cin % 2 == 0 && Cin <= 256, "dac_conv_out_nwc: bad dims");
-  const size_t smem = sizeof(float) * ((size_t)134 * (Cin + 1) + 7 * Cin + 128);
-  static size_t configured = 0;
-  if (smem > 48 * 1024 && smem > configured) {
-    cudaFuncSetAttribute(dac_conv_out_kernel, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    configured = smem;
-  }
-  dac_conv_out_kernel<<<dim3((T + 127) / 128, B), 256, smem, as_stream(s)>>>(x, T, Cin, w, bias, snake_alpha, y);
+  PTTS_CHECK_ARG(B > 0 && T > 0 && Cin > 0 && Cin % 32 == 0 && Cin <= CO_MAXC,
+                 "dac_conv_out_nwc: Cin must be a multiple of 32, <= 256");
+  dac_conv_out_kernel<<<dim3((T + CO_ROWS - 1) / CO_ROWS, B), 256, 0, as_stream(s)>>>(x, T, Cin, w, bias, snake_alpha, y);
   PTTS_CHECK_LAUNCH("dac_conv_out_nwc");
   return PTTS_OK;
 }

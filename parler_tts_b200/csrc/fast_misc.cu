@@ -15,8 +15,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
                  const float* __restrict__ g, const float* __restrict__ bta, int H, float eps, int row_mul, int row_add,
                  TY* __restrict__ y, TL tl) {
   extern __shared__ float buf[];  // [H]
-  __shared__ float red[8];
-  __shared__ float stat[2];
+  __shared__ float red[8], red2[8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t rin = (int64_t)blockIdx.x * row_mul + row_add;
   float* hr = h + rin * H;
@@ -52,16 +51,11 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
     *reinterpret_cast<float4*>(buf + c) = v;
     s += (v.x + v.y) + (v.z + v.w);
   }
+  // block reductions: one barrier each - every thread adds the 8 warp sums itself, in fixed order (deterministic)
   s = warp_sum(s);
   if (lane == 0) red[warp] = s;
   __syncthreads();
-  if (warp == 0) {
-    float v = lane < 8 ? red[lane] : 0.f;
-    v = warp_sum(v);
-    if (lane == 0) stat[0] = v / (float)H;
-  }
-  __syncthreads();
-  const float mean = stat[0];
+  const float mean = (((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]))) / (float)H;
   float qq = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
     const float4 v = *reinterpret_cast<const float4*>(buf + c);
@@ -69,15 +63,10 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
     qq += (a * a + b * b) + (cc * cc + d * d);
   }
   qq = warp_sum(qq);
-  if (lane == 0) red[warp] = qq;
+  if (lane == 0) red2[warp] = qq;
   __syncthreads();
-  if (warp == 0) {
-    float v = lane < 8 ? red[lane] : 0.f;
-    v = warp_sum(v);
-    if (lane == 0) stat[1] = rsqrtf(v / (float)H + eps);
-  }
-  __syncthreads();
-  const float rstd = stat[1];
+  const float rstd =
+      rsqrtf((((red2[0] + red2[1]) + (red2[2] + red2[3])) + ((red2[4] + red2[5]) + (red2[6] + red2[7]))) / (float)H + eps);
   TY* yr = y + (int64_t)blockIdx.x * H;
 #pragma unroll
   for (int i = 0; i < 4; ++i) {

@@ -245,12 +245,13 @@ class DacDecoderEngine:
                 x = self._conv(y, r["c2"], alpha=r["a2"], residual=x)
         return self._conv(x, self.conv_out, alpha=self.alpha_out, tanh=True)  # (B, 1, hop*F)
 
-    def decode(self, codes, max_frames_per_call=16 * 1024):
+    def decode(self, codes, max_frames_per_call=32 * 1024):
         """codes (B, K, F) -> audio (B, 1, hop*F); the batch is chunked to bound activation memory."""
         B, K, F = codes.shape
         if F == 0:
             return torch.zeros(B, 1, 0, device=self.device)
         per = max(1, max_frames_per_call // F)
+        per = -(-B // -(-B // per))  # equal-sized chunks (64 utterances -> 32 + 32, not 38 + 26)
         if self.nwc:
             outs = [self.decode_latents_nwc(self.dequant_nwc(codes[i : i + per])) for i in range(0, B, per)]
         else:
