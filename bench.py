@@ -112,8 +112,8 @@ def run_reference(args):
     rank = int(os.environ.get("RANK", "0"))
     if rank != 0:
         return
-    n = 4
-    for _ in range(args.warmup):
+    n = 32
+    for _ in range(min(args.warmup, 2)):
         cpu_oracle_sample(1)
     t0 = time.perf_counter()
     vals = [cpu_oracle_sample(n) for _ in range(args.steps)]
@@ -261,8 +261,13 @@ def run_cuda(args):
     avg_ctx = P + 1 + (M - 1) / 2.0
     step_bytes = W * es + B * kvb * (avg_ctx + S) + B * kvb + B * K * H * 4
     step_gbs = step_bytes / (ms_decode * 1e-3) / 1e9
+    # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel at exactly these arguments, from the
+    # committed `ncu --set full` capture profiles/r01_ncu_attn_full_v6.csv (122.31 MB read + 3.68 MB written)
+    traffic = 125996117 if (B, N, es) == (64, 860, 2) and impl == cabi.IMPL_FAST else None
     roofline = {"bound": "hbm", "kernel": "self-attention decode (ptts_attention, ctx=%d)" % ctx, "achieved": achieved,
-                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": None, "peak_source": peak_src,
+                "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
+                "traffic_source": "profiles/r01_ncu_attn_full_v6.csv (ncu --set full, mean of 3 launches)",
+                "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms,
                 "whole_step": {"algorithmic_bytes": step_bytes, "ms": ms_decode, "achieved": step_gbs,
                                "frac": step_gbs / peak}}
@@ -338,7 +343,7 @@ def main():
     ap.add_argument("--batch", type=int, default=WORK["B"])
     ap.add_argument("--frames", type=int, default=WORK["frames"])
     ap.add_argument("--e2e-steps", type=int, default=2)
-    ap.add_argument("--cpu-steps", type=int, default=8)
+    ap.add_argument("--cpu-steps", type=int, default=128)
     ap.add_argument("--no-graph", action="store_true")
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
