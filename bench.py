@@ -25,6 +25,11 @@ sys.path.insert(0, ROOT)
 MINI = dict(vocab_size=1088, hidden_size=1024, num_hidden_layers=24, num_attention_heads=16, ffn_dim=4096,
             num_codebooks=9, max_position_embeddings=4096, pad_token_id=1024, eos_token_id=1024, bos_token_id=1025)
 WORK = dict(B=64, S=48, P=32, frames=860)  # configs[1] shape, greedy (the metric's own wording)
+T5 = dict(d_model=768, d_ff=2048, num_layers=12, num_heads=12)  # flan-t5-base shape
+# BASELINE.json configs[3]: 36 layers x 1536 hidden (heads / ffn by the Mini rule d=64, ffn=4H), flan-t5-large-shaped
+# encoder (--arch scaled; not the headline workload)
+SCALED = dict(hidden_size=1536, num_hidden_layers=36, num_attention_heads=24, ffn_dim=6144)
+T5_LARGE = dict(d_model=1024, d_ff=2816, num_layers=24, num_heads=16)
 
 
 def _peaks():
@@ -141,8 +146,7 @@ def build_models(device, dtype, seed=0):
     import parler_tts_b200 as ptts
 
     dec_cfg = ptts.ParlerTTSDecoderConfig(**MINI)
-    t5 = T5Config(vocab_size=32128, d_model=768, d_kv=64, d_ff=2048, num_layers=12, num_heads=12,
-                  feed_forward_proj="gated-gelu", tie_word_embeddings=False)  # flan-t5-base shape
+    t5 = T5Config(vocab_size=32128, d_kv=64, feed_forward_proj="gated-gelu", tie_word_embeddings=False, **T5)
     cfg = ptts.ParlerTTSConfig.from_sub_models_config(t5, ptts.DACConfig(), dec_cfg, vocab_size=32128)
     torch.manual_seed(seed)
     model = ptts.ParlerTTSForConditionalGeneration(cfg, seed=seed)
@@ -189,7 +193,8 @@ def run_cuda(args):
         enc = model.project_encoder(hs, torch.ones_like(ids_d))
     prompt_ids = prompt_ids_h.to(dev)
     table = model.prompt_table()
-    st = GenState(w, B, S, P, 1, M, impl=impl, suppress_from=1024, row_offset=rank * B * K)
+    st = GenState(w, B, S, P, 1, M, impl=impl, suppress_from=1024, row_offset=rank * B * K,
+                  do_sample=args.do_sample, top_k=50 if args.do_sample else 0)
     start = torch.full((B * K, 1), MINI["bos_token_id"], dtype=torch.int64, device=dev)
     codes = torch.empty(B, K, N, dtype=torch.int64, device=dev)
     from parler_tts_b200 import sharding
@@ -263,7 +268,7 @@ def run_cuda(args):
     step_gbs = step_bytes / (ms_decode * 1e-3) / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel at exactly these arguments, from the
     # committed `ncu --set full` capture profiles/r01_ncu_attn_full_v6.csv (122.31 MB read + 3.68 MB written)
-    traffic = 125996117 if (B, N, es) == (64, 860, 2) and impl == cabi.IMPL_FAST else None
+    traffic = 125996117 if (B, N, es, heads) == (64, 860, 2, 16) and impl == cabi.IMPL_FAST else None
     roofline = {"bound": "hbm", "kernel": "self-attention decode (ptts_attention, ctx=%d)" % ctx, "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
                 "traffic_source": "profiles/r01_ncu_attn_full_v6.csv (ncu --set full, mean of 3 launches)",
@@ -281,7 +286,7 @@ def run_cuda(args):
         nonlocal audio_h
         i_d = input_ids_h.to(dev, non_blocking=True)
         p_d = prompt_ids_h.to(dev, non_blocking=True)
-        out = model.generate(input_ids=i_d, prompt_input_ids=p_d, do_sample=False, logits_processor=procs, seed=0,
+        out = model.generate(input_ids=i_d, prompt_input_ids=p_d, do_sample=args.do_sample, logits_processor=procs, seed=0,
                              row_offset=rank * B)
         if audio_h is None:
             audio_h = torch.empty(out.shape, dtype=out.dtype).pin_memory()
@@ -319,11 +324,13 @@ def run_cuda(args):
                 "n_gpus": world, "steps": args.steps, "warmup": args.warmup, "ms_per_step": total_ms / args.steps,
                 "ms_per_decode_step": ms_decode, "higher_is_better": True, "scaling": "weak", "vs_baseline": None,
                 "dtype": "bf16" if dtype == torch.bfloat16 else "f32", "data": "synthetic",
-                "config": {"workload": f"Mini v0.1 architecture random-init (24x1024, 9 codebooks), B={B} per GPU, "
-                                       f"S={S}, P={P}, {N} frames (max_length {M}), greedy, ids>=1024 suppressed, "
+                "config": {"workload": f"{'Mini v0.1' if args.arch == 'mini' else 'scaled'} architecture random-init "
+                                       f"({L}x{H}, 9 codebooks), B={B} per GPU, "
+                                       f"S={S}, P={P}, {N} frames (max_length {M}), "
+                                       f"{'top-k 50 sampling' if args.do_sample else 'greedy'}, ids>=1024 suppressed, "
                                        "static KV cache + CUDA graph",
                            "kernels": args.kernels, "kv_dtype": "bf16" if dtype == torch.bfloat16 else "f32",
-                           "l2": "per-step working set (weights 725 MB + KV) exceeds the 126 MB L2; no flush needed",
+                           "l2": f"per-step working set (weights {W * es / 1e6:.0f} MB + KV) exceeds the 126 MB L2; no flush needed",
                            "parallelism": f"batch-sharded replicas x{world}, NCCL all_gather of codes only"},
                 "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
                 "cpu_baseline": cpu}
@@ -345,9 +352,14 @@ def main():
     ap.add_argument("--e2e-steps", type=int, default=2)
     ap.add_argument("--cpu-steps", type=int, default=128)
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--do-sample", action="store_true", help="top-k 50 sampling instead of greedy (configs[1] wording)")
+    ap.add_argument("--arch", default="mini", choices=["mini", "scaled"])
     ap.add_argument("--skip-e2e", action="store_true")
     ap.add_argument("--skip-cpu", action="store_true")
     args = ap.parse_args()
+    if args.arch == "scaled":
+        MINI.update(SCALED)
+        T5.update(T5_LARGE)
     if args.impl == "reference":
         run_reference(args)
     else:

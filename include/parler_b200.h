@@ -239,6 +239,38 @@ PTTS_API int ptts_dac_convtr1d_nwc(const float* x, int32_t B, int32_t T, int32_t
 PTTS_API int ptts_dac_conv_out_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const float* w, const float* bias,
                           const float* snake_alpha, float* y, ptts_stream_t s);
 
+/* ---- T5 text encoder: the description encoder generate() runs once per call --------------- */
+/* Replaces the third-party transformers T5EncoderModel called at modeling_parler_tts.py:2229
+ * (_prepare_text_encoder_kwargs_for_generation, 2197-2241).  Weight layout = HF T5 state-dict keys
+ * text_encoder.encoder.block.{i}.layer.0.SelfAttention.{q,k,v,o}.weight, ...layer.0.layer_norm.weight,
+ * ...layer.1.DenseReluDense.{wi_0,wi_1,wo | wi,wo}.weight, ...layer.1.layer_norm.weight,
+ * text_encoder.encoder.final_layer_norm.weight, text_encoder.shared.weight and block 0's
+ * relative_attention_bias.weight. */
+typedef struct {
+  const void* w_qkv;   /* [3*inner][D]  q | k | v stacked, inner = n_heads * d_kv */
+  const void* w_o;     /* [D][inner] */
+  const void* w_wi;    /* gated: [2*d_ff][D] wi_0 | wi_1 stacked; else [d_ff][D] */
+  const void* w_wo;    /* [D][d_ff] */
+  const float *ln0, *ln1; /* RMS-norm weights in front of attention / feed-forward */
+} PttsT5Layer;
+
+typedef struct {
+  int32_t n_layers, d_model, n_heads, d_kv, d_ff, gated, act_fn, wdtype;
+  int32_t vocab, n_buckets, max_rel, reserved0;
+  float eps, reserved1;
+  const float* embed;       /* [vocab][D] fp32 */
+  const float* rel_bias;    /* [n_buckets][n_heads] fp32 */
+  const int32_t* bucket_of; /* [2*max_rel+1]: bucket of relative position (key - query) + max_rel, clamped outside */
+  const float* ln_f;        /* final_layer_norm */
+  const PttsT5Layer* layers; /* HOST array of n_layers entries */
+} PttsT5;
+
+PTTS_API int64_t ptts_t5_workspace_bytes(const PttsT5* m, int32_t rows);
+/* ids [B][S] int64, mask [B][S] int32 (1 = keep) or NULL, out [B][S][D] T (last_hidden_state); workspace device
+ * bytes >= ptts_t5_workspace_bytes(m, B*S). */
+PTTS_API int ptts_t5_encode(const PttsT5* m, const int64_t* ids, const int32_t* mask, int32_t B, int32_t S, void* workspace,
+                            void* out, int32_t impl, ptts_stream_t s);
+
 #ifdef __cplusplus
 }
 #endif

@@ -193,6 +193,43 @@ def gen_dac():
     print("dac_tiny.npz:", wav.shape)
 
 
+T5_TINY = dict(vocab_size=120, d_model=64, d_kv=16, d_ff=96, num_layers=2, num_heads=4,
+               relative_attention_num_buckets=32, relative_attention_max_distance=128, layer_norm_epsilon=1e-6)
+T5_CASES = {"gated": dict(T5_TINY, gated=True, dense_act_fn="gelu_new", feed_forward_proj="gated-gelu"),
+            "relu": dict(T5_TINY, gated=False, dense_act_fn="relu", feed_forward_proj="relu", d_kv=32, num_heads=2)}
+
+
+def hf_t5(cfg, sd):
+    """transformers' own T5EncoderModel (what the reference's AutoModelForTextEncoding builds) with our seeded state."""
+    from transformers import T5Config, T5EncoderModel
+
+    keys = ("vocab_size", "d_model", "d_kv", "d_ff", "num_layers", "num_heads", "relative_attention_num_buckets",
+            "relative_attention_max_distance", "layer_norm_epsilon", "feed_forward_proj")
+    m = T5EncoderModel(T5Config(**{k: cfg[k] for k in keys}, tie_word_embeddings=False)).eval()
+    missing, unexpected = m.load_state_dict(sd, strict=False)
+    assert not unexpected and all("embed_tokens" in k for k in missing), (missing, unexpected)
+    return m
+
+
+def gen_t5():
+    from oracle import t5_oracle
+
+    out = {}
+    for name, cfg in T5_CASES.items():
+        sd = t5_oracle.random_t5_state(cfg, seed=5)
+        g = torch.Generator().manual_seed(17)
+        ids = torch.randint(0, cfg["vocab_size"], (3, 150), generator=g)  # 150 > max_distance: clamped buckets too
+        mask = torch.ones(3, 150, dtype=torch.long)
+        mask[1, 97:] = 0
+        mask[2, 5:] = 0
+        with torch.no_grad():
+            want = hf_t5(cfg, sd)(input_ids=ids, attention_mask=mask).last_hidden_state
+        out[name + "_ids"], out[name + "_mask"], out[name + "_out"] = ids.numpy(), mask.numpy(), want.numpy()
+        got = t5_oracle.t5_encode(sd, cfg, ids, mask)
+        print(f"t5 {name}: oracle vs transformers max abs {float((got - want).abs().max()):.2e}")
+    np.savez_compressed(os.path.join(GOLD, "t5_tiny.npz"), **out)
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = import_reference()
@@ -200,7 +237,10 @@ def main():
     dims, sd, model = gen_decoder(ref)
     gen_loop(ref, dims, sd, model)
     gen_dac()
+    gen_t5()
 
 
-if __name__ == "__main__":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "t5":
+    gen_t5()  # transformers only: does not need /root/reference
+elif __name__ == "__main__":
     main()

@@ -44,7 +44,18 @@ class PttsState(C.Structure):
                 ("scratch", c_vp), ("ids", c_vp), ("mask", c_vp), ("unfinished", c_vp)]
 
 
-_PM, _PS = C.POINTER(PttsModel), C.POINTER(PttsState)
+class PttsT5Layer(C.Structure):
+    _fields_ = [(n, c_vp) for n in ("w_qkv", "w_o", "w_wi", "w_wo", "ln0", "ln1")]
+
+
+class PttsT5(C.Structure):
+    _fields_ = [(n, c_i32) for n in ("n_layers", "d_model", "n_heads", "d_kv", "d_ff", "gated", "act_fn", "wdtype",
+                                     "vocab", "n_buckets", "max_rel", "reserved0")] + [
+        ("eps", c_f32), ("reserved1", c_f32), ("embed", c_vp), ("rel_bias", c_vp), ("bucket_of", c_vp),
+        ("ln_f", c_vp), ("layers", C.POINTER(PttsT5Layer))]
+
+
+_PM, _PS, _PT5 = C.POINTER(PttsModel), C.POINTER(PttsState), C.POINTER(PttsT5)
 
 # name -> (restype, argtypes); must list every PTTS_API symbol of include/parler_b200.h
 PROTOTYPES = {
@@ -83,6 +94,8 @@ PROTOTYPES = {
                                      c_vp, c_vp, c_vp]),
     "ptts_dac_convtr1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "ptts_dac_pretiled": (C.c_int, []),
+    "ptts_t5_workspace_bytes": (c_i64, [_PT5, c_i32]),
+    "ptts_t5_encode": (C.c_int, [_PT5, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
 }
 
 _lib = None

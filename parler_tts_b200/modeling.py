@@ -544,6 +544,8 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         _add_param(self.embed_prompts, "weight", torch.randn(config.vocab_size, H, generator=g) * std)
         self.generation_config = _default_generation_config(config.decoder)
         self._prompt_table = None
+        self.text_encoder_impl = "native"  # CUDA T5 encoder (ptts_t5_encode); "torch" = the third-party module
+        self._t5_engine = None
 
     # ---- reference accessors
     def get_audio_encoder(self):
@@ -604,10 +606,30 @@ class ParlerTTSForConditionalGeneration(nn.Module):
     # ---- pieces of generate
     @torch.no_grad()
     def encode_text(self, input_ids, attention_mask):
-        """T5 (third-party torch module, once per call) followed by enc_to_dec_proj + bias + attention-mask multiply on
-        the CUDA path (modeling_parler_tts.py:2010-2017, hoisted out of the per-step loop)."""
+        """T5 description encoder, once per call (modeling_parler_tts.py:2229): the CUDA encoder for a T5 text_encoder,
+        else the third-party torch module.  enc_to_dec_proj + bias + attention-mask multiply follow in
+        project_encoder (modeling_parler_tts.py:2010-2017, hoisted out of the per-step loop)."""
+        eng = self.text_encoder_engine()
+        if eng is not None:
+            return eng.encode(input_ids, attention_mask, impl=self.decoder.impl)
         hs = self.text_encoder(input_ids=input_ids, attention_mask=attention_mask, return_dict=True).last_hidden_state
         return hs
+
+    def text_encoder_engine(self):
+        """CUDA T5 encoder over the text_encoder module's own parameters (HF key names), rebuilt when they move or
+        change dtype.  `text_encoder_impl = "torch"` keeps the third-party module (any non-T5 encoder does too)."""
+        te = self.text_encoder
+        if self.text_encoder_impl != "native" or getattr(te.config, "model_type", None) != "t5":
+            return None
+        p = next(te.parameters())
+        if p.device.type != "cuda" or p.dtype not in (torch.float32, torch.bfloat16):
+            return None
+        key = (p.device, p.dtype, p.data_ptr())
+        if self._t5_engine is None or self._t5_engine[0] != key:
+            from .text_encoder import T5EncoderEngine
+
+            self._t5_engine = (key, T5EncoderEngine(te.config, te.state_dict(), p.device, p.dtype))
+        return self._t5_engine[1]
 
     def project_encoder(self, hs, attention_mask):
         w = self.decoder.packed_weights()

@@ -163,6 +163,30 @@ def test_cached_decode_steps_teacher_forced_vs_oracle(impl, dtype):
         assert err / float(want.abs().max()) < 1e-2, err
 
 
+@pytest.mark.parametrize("H,heads,F,B", [(1536, 24, 6144, 32), (1024, 16, 4096, 64)])
+def test_scaled_and_mini_layer_shapes_bf16_vs_oracle(H, heads, F, B):
+    """BASELINE.json configs[3] (36 x 1536 decoder, 24 heads, ffn 6144, bs=32) and configs[1] (Mini, bs=64) layer
+    shapes on the tcgen05 split-K path, two layers deep: bf16 logits within 1e-2 of the logit scale of the fp32
+    oracle on bf16-rounded weights."""
+    kw = dict(TINY, hidden_size=H, num_attention_heads=heads, ffn_dim=F, num_hidden_layers=2, vocab_size=1088,
+              num_codebooks=9, pad_token_id=1024, eos_token_id=1024, bos_token_id=1025, max_position_embeddings=128)
+    dims = decoder_oracle.DecoderDims(**kw)
+    sd = decoder_oracle.random_decoder_state(dims, seed=6, ln_jitter=0.05)
+    m = ptts.ParlerTTSForCausalLM(ptts.ParlerTTSDecoderConfig(**kw), state_dict=sd).to(DEV).to(torch.bfloat16)
+    m.impl = cabi.IMPL_FAST
+    g = torch.Generator().manual_seed(4)
+    S, P, T = 48, 32, 4
+    enc, prm = torch.randn(B, S, H, generator=g) * 0.3, torch.randn(B, P, H, generator=g) * 0.1
+    ids = torch.randint(0, 1024, (B * 9, T), generator=g)
+    sd_bf = {k: (v.to(torch.bfloat16).float() if v.dim() == 2 and "embed" not in k else v) for k, v in sd.items()}
+    want, _ = decoder_oracle.decoder_forward(sd_bf, dims, ids, enc.to(torch.bfloat16).float(), None, prm, None, None)
+    n0 = cabi.load().ptts_launch_count()
+    got = _teacher_forced_decode(m, dims, ids, enc.to(torch.bfloat16), prm).cpu()
+    assert cabi.load().ptts_launch_count() - n0 >= (T - 1) * (2 * 12 + 2)
+    want = want[:, P:, :]
+    assert float((got - want).abs().max()) / float(want.abs().max()) < 1e-2
+
+
 def test_fast_path_launches_its_own_kernels_and_graph_replays_match_eager():
     """bf16 fast path: a CUDA-graph replayed generation equals the eager launch sequence token for token, and the
     library's launch counter shows the fused layer (12 launches per layer instead of the simple family's 15)."""

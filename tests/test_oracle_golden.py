@@ -104,3 +104,27 @@ def test_sampling_candidates_and_distribution():
     draws = [generate_oracle.sample_row(s, generate_oracle.uniform_for(5, 0, i), 1.0, 50) for i in range(400)]
     assert all(keep[d] for d in draws)
     assert len(set(draws)) > 20
+
+
+def test_t5_encoder_vs_transformers(golden_dir):
+    """oracle/t5_oracle.py against transformers' T5EncoderModel outputs (tests/golden/t5_tiny.npz: gated-gelu and
+    relu stacks, 150 tokens > max_distance, padded and almost-empty rows)."""
+    from oracle import t5_oracle
+    from oracle.gen_golden import T5_CASES
+
+    z = np.load(os.path.join(golden_dir, "t5_tiny.npz"))
+    for name, cfg in T5_CASES.items():
+        sd = t5_oracle.random_t5_state(cfg, seed=5)
+        got = t5_oracle.t5_encode(sd, cfg, torch.from_numpy(z[name + "_ids"]), torch.from_numpy(z[name + "_mask"]))
+        assert float((got - torch.from_numpy(z[name + "_out"])).abs().max()) < 1e-5, name
+
+
+def test_t5_bucket_table_matches_transformers():
+    from transformers.models.t5.modeling_t5 import T5Attention
+
+    from parler_tts_b200.text_encoder import MAX_REL, relative_position_buckets
+
+    rel = torch.arange(-MAX_REL, MAX_REL + 1)
+    for nb, md in ((32, 128), (16, 64)):
+        want = T5Attention._relative_position_bucket(rel, bidirectional=True, num_buckets=nb, max_distance=md)
+        assert torch.equal(relative_position_buckets(nb, md).long(), want)
