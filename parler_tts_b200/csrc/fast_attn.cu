@@ -91,6 +91,7 @@ struct QFuse {
   const int* pf_rows_dyn;
   int pf_pct;
   int pf_late;         // queue that prefetch after griddepcontrol.wait instead of before it
+  int64_t pf_v_off;    // elements from pf_next to the V cache of the same launch (pf_pct > 100 also pulls V rows)
 };
 
 // part layout: [(b*heads + h)*splits + s][D + 2] = { running max, sum of exp, unnormalised output[D] }
@@ -98,16 +99,18 @@ template <typename T, int D, bool FUSED>
 __global__ void __launch_bounds__(NT, FUSED ? 7 : 8)  // 7 x 148 = 1036 CTA slots >= 64 x 16 (b, head) pairs
 attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
                    int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask, int mask_len,
-                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, TL tl) {
+                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, int stage_cap, TL tl) {
   constexpr int E = Chunk<T>::E;     // elements per 16-byte chunk
   constexpr int TPK = D / E;         // threads per key row
   constexpr int KPB = NT / TPK;      // key rows per CTA pass
   constexpr int U = 4;               // independent loads in flight per thread
+  constexpr int ROWB = D * (int)sizeof(T);  // bytes per cache row
   __shared__ __align__(16) T qs[D];
   extern __shared__ float sm[];
   float* sc = sm;                    // [sc_cap] scores -> probabilities
   float* red = sm + sc_cap;          // [8] block reductions
   float* ored = red + 8;             // [KPB][D] output partials
+  unsigned char* ksm = reinterpret_cast<unsigned char*>(ored + KPB * D);  // [stage_cap] K rows staged before the wait
   const int hd = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int g = tid / TPK, c = tid % TPK;
@@ -134,13 +137,17 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   };
   uint4 cur[U], nxt[U];
   bool pre_k = false, pre_v = false;
+  int staged = 0;
   auto prefetch_next = [&]() {
-    const int rows = dyn_value(qf.pf_rows_base, qf.pf_rows_dyn) * qf.pf_pct / 100;
+    const int all = dyn_value(qf.pf_rows_base, qf.pf_rows_dyn);
+    const int rows = all * (qf.pf_pct > 100 ? 100 : qf.pf_pct) / 100;
     const T* src = reinterpret_cast<const T*>(qf.pf_next) + ((int64_t)b * heads + hd) * qf.pf_stride * D;
     if (qf.pf_pct < 0)
       l2_prefetch_lines(src, (int64_t)(rows * -1) * D * sizeof(T));
     else
       l2_prefetch_range(src, (int64_t)rows * D * sizeof(T));
+    if (qf.pf_pct > 100 && qf.pf_v_off > 0)  // and the first (pct - 100) % of the V rows of that launch
+      l2_prefetch_range(src + qf.pf_v_off, (int64_t)(all * (qf.pf_pct - 100) / 100) * D * sizeof(T));
   };
   if constexpr (FUSED) {
     // Decode-step contract of the fused entry point: cache rows below the slot this launch appends (self-attention) or
@@ -148,8 +155,19 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
     // least two launches old - they may be read BEFORE griddepcontrol.wait, while the producer GEMM still runs.
     plan();
     const int old_end = qf.has_kv ? dyn_value(qf.slot_base, qf.slot_dyn) : ctx;
-    pre_k = n > 0 && min(j1, j0 + KPB * U) <= old_end;
-    if (pre_k) load_batch(cur, kb, j0);
+    // Self-attention: while the QKV GEMM still runs, the first `staged` (immutable) K rows of this CTA travel into
+    // shared memory with cp.async - that share of the stream no longer sits behind the dependency.
+    if (stage_cap > 0 && qf.has_kv) {
+      staged = min(stage_cap, max(min(j1, old_end) - j0, 0) / (KPB * U) * (KPB * U));
+      const uint32_t dst0 = smem_addr(ksm) + c * 16;
+      for (int r = g; r < staged; r += KPB)
+        asm volatile("cp.async.cg.shared.global [%0], [%1], 16;\n" ::"r"(dst0 + r * ROWB), "l"(kb + (int64_t)(j0 + r) * D)
+                     : "memory");
+      asm volatile("cp.async.commit_group;\n" ::: "memory");
+    }
+    const int jg = j0 + staged;  // first row of the register-pipelined (global) part of the K pass
+    pre_k = jg < j1 && min(j1, jg + KPB * U) <= old_end;
+    if (pre_k) load_batch(cur, kb, jg);
     pre_v = pre_k && !qf.has_kv && n <= KPB * U;
     if (pre_v) load_batch(nxt, vb, j0);
     // HBM would idle between the K pass and the V pass of the wave, and during the short kernels between two
@@ -200,7 +218,8 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
         const_cast<T*>(cv)[o] = from_f<T>(av);
       }
     }
-    __syncthreads();  // q in shared memory, the new cache row visible to the whole CTA
+    asm volatile("cp.async.wait_group 0;\n" ::: "memory");  // my share of the staged K rows has landed
+    __syncthreads();  // q in shared memory, the new cache row and the staged K rows visible to the whole CTA
     Chunk<T>::unpack(*reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(qs) + c * 16), qv);
   } else {
     Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
@@ -208,8 +227,28 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   const float neg = finfo_min<T>();
   // ---- pass 1: scores = q . K^T (masked)
   float lmax = -INFINITY;
-  if (!pre_k) load_batch(cur, kb, j0);
-  for (int base = j0; base < j1; base += KPB * U) {
+  if (!pre_k) load_batch(cur, kb, j0 + staged);
+  if constexpr (FUSED) {
+    for (int r0 = 0; r0 < staged; r0 += KPB) {  // staged rows: all below j1 and below the append slot
+      const int r = r0 + g;
+      float kf[E];
+      Chunk<T>::unpack(*reinterpret_cast<const uint4*>(ksm + r * ROWB + c * 16), kf);
+      float dot = 0.f;
+#pragma unroll
+      for (int e = 0; e < E; ++e) dot = fmaf(qv[e], kf[e], dot);
+#pragma unroll
+      for (int o = TPK / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
+      if (c == 0) {
+        const int j = j0 + r;
+        bool keep = true;
+        if (key_mask && j < mask_len) keep = key_mask[(int64_t)b * mask_len + j] != 0;
+        const float s = keep ? dot : neg;
+        sc[r] = s;
+        lmax = fmaxf(lmax, s);
+      }
+    }
+  }
+  for (int base = j0 + staged; base < j1; base += KPB * U) {
     if (base + KPB * U < j1) load_batch(nxt, kb, base + KPB * U);
 #pragma unroll
     for (int u = 0; u < U; ++u) {
@@ -525,7 +564,23 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
                  (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch, splits, cap,
                  tl_next(c_stride > 64 ? 2 : 3));
   } else {
-    const size_t smem = sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
+    size_t smem = sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
+    // K rows staged in shared memory before the dependency wait (fused self-attention only): what fits next to the
+    // score buffer with 7 CTAs per SM, in units of one K-pass batch (64 rows = 8 KB).  PTTS_ATTN_STAGE=<rows>.
+    // Measured on B200 (B=64, 860 frames): 0 rows 1.686, 64 rows 1.698, 128 rows 1.707 ms per decode step - the rows
+    // are L2-resident anyway and the extra shared memory / barrier costs more than the earlier start saves: OFF.
+    static int stage_req = -1;
+    if (stage_req < 0) {
+      const char* ev = getenv("PTTS_ATTN_STAGE");
+      stage_req = ev ? atoi(ev) : 0;
+    }
+    int stage_cap = 0;
+    if (qf.part && qf.has_kv && sizeof(T) == 2) {
+      const int unit = KPB * 4, budget = 31 * 1024;
+      stage_cap = smem < (size_t)budget ? (int)((budget - smem) / (D * sizeof(T))) / unit * unit : 0;
+      if (stage_cap > stage_req / unit * unit) stage_cap = stage_req / unit * unit;
+      smem += (size_t)stage_cap * D * sizeof(T);
+    }
     if (smem > 48 * 1024) {
       static size_t configured = 0;
       if (smem > configured) {
@@ -538,11 +593,11 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
     if (qf.part)
       e = launch_k(attn_decode_kernel<T, D, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
                    (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
-                   splits, cap, tl_next(c_stride > 64 ? 2 : 3));
+                   splits, cap, stage_cap, tl_next(c_stride > 64 ? 2 : 3));
     else
       e = launch_k(attn_decode_kernel<T, D, false>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
                    (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
-                   splits, cap, tl_next(c_stride > 64 ? 2 : 3));
+                   splits, cap, 0, tl_next(c_stride > 64 ? 2 : 3));
   }
   if (e != cudaSuccess) {
     set_error("attn_decode launch: %s", cudaGetErrorString(e));
@@ -592,15 +647,18 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
   QFuse qf = {};
   qf.part = qkv_part; qf.S = S; qf.stride = part_stride; qf.ncols = ncols; qf.has_kv = has_kv; qf.scale = scale;
   qf.slot_base = slot_base; qf.slot_dyn = slot_dyn;
-  static int pf = -1;  // PTTS_L2PF: bit 0 = own V rows (self-attention), bit 1 = next launch's K rows; default both
+  // PTTS_L2PF: bit 0 = own V rows (self-attention), bit 1 = next launch's K rows.  Measured on B200 (B=64, 860
+  // frames): 3 -> 1.748 ms per decode step, 2 -> 1.708 ms (the own-V prefetch competes with the K pass) - default 2.
+  static int pf = -1;
   if (pf < 0) {
     const char* e = getenv("PTTS_L2PF");
-    pf = e ? atoi(e) : 3;
+    pf = e ? atoi(e) : 2;
   }
   static int pf_pct = -1;  // PTTS_L2PF_PCT: share of the next launch's K rows to pull (L2 capacity is finite)
   if (pf_pct < 0) {
     const char* e = getenv("PTTS_L2PF_PCT");
-    pf_pct = e ? atoi(e) : 100;
+    pf_pct = e ? atoi(e) : 50;  // measured (early release on, own-V prefetch off): 0 % 1.677, 50 % 1.673, 100 % 1.690,
+                                // 160 % 1.711, 200 % (K and V) 1.724 ms per decode step
   }
   // PTTS_L2PF_LATE=1 queues the next-launch prefetch after the dependency wait, so that the producer GEMM's epilogue
   // stores do not queue behind it.  Measured on B200 (B=64, 860 frames): 1.838 ms per decode step against 1.745 ms
@@ -615,6 +673,7 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
   if (pf & 2) {
     qf.pf_next = pf_next; qf.pf_stride = pf_stride; qf.pf_rows_base = pf_rows_base; qf.pf_rows_dyn = pf_rows_dyn;
     qf.pf_pct = pf_pct;
+    qf.pf_v_off = (int64_t)B * heads * pf_stride * 64;  // [L][2][B][heads][c_max][64]: V follows K
   }
   return launch_decode<__nv_bfloat16>(qf, nullptr, ck, cv, B, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len,
                                       out, scratch, st);

@@ -133,8 +133,16 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   cp_async_commit();  // group 0: the W slab
+  // dbg bit 4 (split-K partial GEMMs, PTTS_PDL_EARLY=0 to disable): release the dependent kernel BEFORE waiting on
+  // the own producer, so that its CTAs are resident and its pre-wait prologue (gamma / beta, first K batch, L2
+  // prefetches) has run by the time this grid completes.  Safe because every consumer touches producer data only
+  // after its own griddepcontrol.wait (which waits for THIS grid to complete and flush), and what the consumers read
+  // before their wait is immutable for the whole step: weights, cache rows below the append slot, and the position
+  // counter, which only the step epilogue writes - the epilogue never triggers early and a graph's first node has a
+  // full dependency on the previous replay, so no early-resident kernel can see a stale counter.
+  if (dbg & 16) pdl_launch();
   pdl_wait();
-  pdl_launch();
+  if (!(dbg & 16)) pdl_launch();
   STAMP(1);
   tl_dep(tl);
   const long long c_dep = (dbg & 3) == 3 ? clock64() : 0;
@@ -445,7 +453,12 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     const char* ev = getenv("PTTS_GEMM_DBG");
     dbg = ev ? atoi(ev) : 0;  // 1: globaltimer stamps (256 ns ticks), 2: SM clock cycles (intra-kernel phases)
   }
-  const int dbg_arg = dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg;
+  static int early = -1;
+  if (early < 0) {
+    const char* ev = getenv("PTTS_PDL_EARLY");  // measured: 1.727 ms per decode step against 1.748 ms -> default on
+    early = (ev && ev[0] == '0') ? 0 : 16;
+  }
+  const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early : 0);
   cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg, tl_next(10 + EPI));
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
@@ -484,9 +497,15 @@ int umma_plan_splits(int M, int N, int K) {
     const char* e = getenv("PTTS_SPLIT_TARGET");
     target = e ? atoi(e) : 30;
   }
+  static int kbmax = -1;  // PTTS_KBMAX: 64-element k-blocks per CTA (8 = 128 KB of W per CTA, 4 = 64 KB)
+  if (kbmax < 0) {
+    const char* e = getenv("PTTS_KBMAX");
+    kbmax = e ? atoi(e) : kMaxKB64;
+    if (kbmax < 1 || kbmax > kMaxKB64) kbmax = kMaxKB64;
+  }
   int best = 0;
   for (int s = 2; s <= kMaxSplitK; s <<= 1) {
-    if (kblocks % s || kblocks / s > kMaxKB64) continue;
+    if (kblocks % s || kblocks / s > kbmax) continue;
     best = s;
     if (nt * s >= target) break;
   }

@@ -163,6 +163,30 @@ def test_cached_decode_steps_teacher_forced_vs_oracle(impl, dtype):
         assert err / float(want.abs().max()) < 1e-2, err
 
 
+@pytest.mark.parametrize("B,H,heads,L,P,T", [(3, 256, 4, 2, 70, 340), (32, 1024, 16, 1, 40, 150)])
+def test_fused_attention_prologue_long_context_vs_oracle(B, H, heads, L, P, T):
+    """The fused flash-decode path (split-K q/k/v partials folded in the attention prologue, in-place cache append,
+    pre-wait K staging) over a context of several hundred tokens: every step's bf16 logits stay within 1e-2 of the
+    logit scale of the fp32 oracle's full-sequence forward."""
+    # (3, 4 heads): split-KV + combine kernel; (32, 16 heads) = 512 (utterance, head) pairs: one CTA per pair
+    kw = dict(TINY, hidden_size=H, num_attention_heads=heads, ffn_dim=1024, num_hidden_layers=L, vocab_size=1088,
+              num_codebooks=9, pad_token_id=1024, eos_token_id=1024, bos_token_id=1025, max_position_embeddings=512)
+    dims = decoder_oracle.DecoderDims(**kw)
+    sd = decoder_oracle.random_decoder_state(dims, seed=8, ln_jitter=0.05)
+    m = ptts.ParlerTTSForCausalLM(ptts.ParlerTTSDecoderConfig(**kw), state_dict=sd).to(DEV).to(torch.bfloat16)
+    m.impl = cabi.IMPL_FAST
+    g = torch.Generator().manual_seed(9)
+    S = 11
+    enc, prm = torch.randn(B, S, H, generator=g), torch.randn(B, P, H, generator=g) * 0.5
+    ids = torch.randint(0, 1024, (B * 9, T), generator=g)
+    sd_bf = {k: (v.to(torch.bfloat16).float() if v.dim() == 2 and "embed" not in k else v) for k, v in sd.items()}
+    want, _ = decoder_oracle.decoder_forward(sd_bf, dims, ids, enc.to(torch.bfloat16).float(), None, prm, None, None)
+    got = _teacher_forced_decode(m, dims, ids, enc.to(torch.bfloat16), prm).cpu()
+    want = want[:, P:, :]
+    err = (got - want).abs().amax(dim=(0, 2)) / float(want.abs().max())
+    assert float(err.max()) < 1e-2, (int(err.argmax()), float(err.max()))
+
+
 @pytest.mark.parametrize("H,heads,F,B", [(1536, 24, 6144, 32), (1024, 16, 4096, 64)])
 def test_scaled_and_mini_layer_shapes_bf16_vs_oracle(H, heads, F, B):
     """BASELINE.json configs[3] (36 x 1536 decoder, 24 heads, ffn 6144, bs=32) and configs[1] (Mini, bs=64) layer
