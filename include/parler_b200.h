@@ -239,6 +239,23 @@ PTTS_API int ptts_dac_convtr1d_nwc(const float* x, int32_t B, int32_t T, int32_t
 PTTS_API int ptts_dac_conv_out_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const float* w, const float* bias,
                           const float* snake_alpha, float* y, ptts_stream_t s);
 
+/* ---- DAC encode for audio-prompt continuation ------------------------------------------------ */
+/* dac_wrapper/modeling_dac.py:25-96 (DACModel.encode -> descript DAC.encode), called by modeling_parler_tts.py:2247-2292.
+ * The encoder's residual units run on ptts_dac_conv1d; these are the two remaining pieces. */
+/* y[b][co][to] = bias + sum_ci,k w[co][ci][k] * snake_alpha(x)[b][ci][to*stride - pad + k];  x [B][Cin][T] fp32,
+ * w folded [Cout][Cin][ksize], y [B][Cout][(T + 2 pad - ksize)/stride + 1]. */
+PTTS_API int ptts_dac_conv1d_strided(const float* x, int32_t B, int32_t Cin, int32_t T, const float* w, const float* bias,
+                                     int32_t Cout, int32_t ksize, int32_t stride, int32_t pad, const float* snake_alpha,
+                                     float* y, ptts_stream_t s);
+/* Residual vector quantisation of latents z [B][C][F]: for codebook i: e = in_proj_i(residual); code = nearest
+ * l2-normalised codebook row (first index on ties); residual -= out_proj_i(codebook_i[code]).  w_in [K][D][C],
+ * b_in [K][D], codebook / codebook_normalized [K][codebook_size][D], w_out [K][C][D], b_out [K][C] (weight norm folded);
+ * codes [B][K][F] int64. */
+PTTS_API int ptts_dac_vq_encode(const float* z, int32_t B, int32_t C, int32_t F, int32_t K, int32_t D, int32_t codebook_size,
+                                const float* w_in, const float* b_in, const float* codebook,
+                                const float* codebook_normalized, const float* w_out, const float* b_out, int64_t* codes,
+                                ptts_stream_t s);
+
 /* ---- T5 text encoder: the description encoder generate() runs once per call --------------- */
 /* Replaces the third-party transformers T5EncoderModel called at modeling_parler_tts.py:2229
  * (_prepare_text_encoder_kwargs_for_generation, 2197-2241).  Weight layout = HF T5 state-dict keys

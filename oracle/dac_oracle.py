@@ -157,3 +157,119 @@ def decode_generated(sd, codes, bos, pad, eos, codebook_size, cfg=DAC_44K, dtype
         else:
             outs.append(torch.zeros(1, dtype=dtype))
     return torch.nn.utils.rnn.pad_sequence(outs, batch_first=True, padding_value=0.0)
+
+
+# ------------------------------------------------------------------------------------------------------ encode
+# Audio-prompt continuation: /root/reference/parler_tts/modeling_parler_tts.py:2247-2292 calls
+# DACModel.encode (dac_wrapper/modeling_dac.py:25-96) = descript `DAC.preprocess` (right-pad to a multiple of the hop)
+# + `DAC.encode` (encoder conv stack, then residual vector quantisation).  Arithmetic as mirrored by transformers
+# models/dac/modeling_dac.py: DacEncoder :442-473, DacEncoderBlock :210-231, DacVectorQuantize :122-170 (factorised,
+# l2-normalised nearest neighbour), DacResidualVectorQuantizer.forward :281-343.  Descript key names:
+# `encoder.block.0` (conv k7), `encoder.block.{1..4}.block.{0,1,2}.block.{0 alpha,1 conv7,2 alpha,3 conv1}`,
+# `encoder.block.{i}.block.3.alpha`, `encoder.block.{i}.block.4` (strided conv k=2s), `encoder.block.5.alpha`,
+# `encoder.block.6` (conv k3), `quantizer.quantizers.{i}.in_proj`.
+def random_dac_encoder_state(cfg=DAC_44K, seed=0, dtype=torch.float32, alpha_jitter=0.2, encoder_dim=64):
+    """Random descript-layout encoder + in_proj weights.  Separate generator: random_dac_state's stream (and every
+    fixture regenerated from it) stays as it is."""
+    g = torch.Generator().manual_seed(seed + 1000)
+    sd = {}
+
+    def conv(prefix, cout, cin, k, gain=1.0):
+        v = torch.randn(cout, cin, k, generator=g) / math.sqrt(cin * k)
+        sd[prefix + ".weight_v"] = v.to(dtype)
+        n = gain * v.reshape(cout, -1).norm(dim=1).reshape(-1, 1, 1)
+        sd[prefix + ".weight_g"] = (n * (1.0 + 0.1 * torch.randn(cout, 1, 1, generator=g))).to(dtype)
+        sd[prefix + ".bias"] = (0.02 * torch.randn(cout, generator=g)).to(dtype)
+
+    def alpha(prefix, c):
+        sd[prefix + ".alpha"] = (1.0 + alpha_jitter * torch.randn(1, c, 1, generator=g)).abs().add(0.05).to(dtype)
+
+    d = encoder_dim
+    conv("encoder.block.0", d, 1, 7, gain=2.0)
+    strides = tuple(reversed(cfg["rates"]))
+    for bi, s in enumerate(strides):
+        p = f"encoder.block.{bi + 1}.block"
+        for ri in range(3):
+            r = f"{p}.{ri}.block"
+            alpha(r + ".0", d)
+            conv(r + ".1", d, d, 7)
+            alpha(r + ".2", d)
+            conv(r + ".3", d, d, 1, gain=0.3)
+        alpha(p + ".3", d)
+        conv(p + ".4", 2 * d, d, 2 * s)
+        d *= 2
+    n = len(strides)
+    alpha(f"encoder.block.{n + 1}", d)
+    conv(f"encoder.block.{n + 2}", cfg["latent_dim"], d, 3)
+    for i in range(cfg["n_codebooks"]):
+        conv(f"quantizer.quantizers.{i}.in_proj", cfg["codebook_dim"], cfg["latent_dim"], 1, gain=1.0)
+    return sd
+
+
+def hop_length(cfg=DAC_44K):
+    h = 1
+    for s in cfg["rates"]:
+        h *= s
+    return h
+
+
+def preprocess(audio, cfg=DAC_44K):
+    """descript DAC.preprocess: zero right-pad (B, 1, T) to a multiple of the hop length."""
+    hop = hop_length(cfg)
+    T = audio.shape[-1]
+    return F.pad(audio, (0, math.ceil(T / hop) * hop - T))
+
+
+def encode_latents(sd, audio, cfg=DAC_44K, dtype=torch.float32):
+    """(B, 1, T) -> z (B, latent, T / hop): the encoder conv stack."""
+    w, b = wn(sd, "encoder.block.0", dtype)
+    x = F.conv1d(audio.to(dtype), w, b, padding=3)
+    strides = tuple(reversed(cfg["rates"]))
+    for bi, s in enumerate(strides):
+        p = f"encoder.block.{bi + 1}.block"
+        for ri, dil in enumerate((1, 3, 9)):
+            r = f"{p}.{ri}.block"
+            y = snake(x, sd[r + ".0.alpha"].to(dtype))
+            w, b = wn(sd, r + ".1", dtype)
+            y = F.conv1d(y, w, b, dilation=dil, padding=3 * dil)
+            y = snake(y, sd[r + ".2.alpha"].to(dtype))
+            w, b = wn(sd, r + ".3", dtype)
+            x = x + F.conv1d(y, w, b)
+        x = snake(x, sd[p + ".3.alpha"].to(dtype))
+        w, b = wn(sd, p + ".4", dtype)
+        x = F.conv1d(x, w, b, stride=s, padding=math.ceil(s / 2))
+    n = len(strides)
+    x = snake(x, sd[f"encoder.block.{n + 1}.alpha"].to(dtype))
+    w, b = wn(sd, f"encoder.block.{n + 2}", dtype)
+    return F.conv1d(x, w, b, padding=1)
+
+
+def rvq_encode(sd, z, cfg=DAC_44K, dtype=torch.float32, n_quantizers=None, return_margins=False):
+    """z (B, latent, F) -> codes (B, K, F) int64: per codebook in_proj -> nearest l2-normalised codebook row (first
+    index on ties) -> residual -= out_proj(codebook[code]).  margins = best minus second-best similarity."""
+    residual = z.to(dtype)
+    codes, margins = [], []
+    K = cfg["n_codebooks"] if n_quantizers is None else n_quantizers
+    for i in range(K):
+        q = f"quantizer.quantizers.{i}"
+        w, b = wn(sd, q + ".in_proj", dtype)
+        e = F.conv1d(residual, w, b)  # (B, D, F)
+        B_, D, Fr = e.shape
+        enc = F.normalize(e.permute(0, 2, 1).reshape(B_ * Fr, D))
+        cb = F.normalize(sd[q + ".codebook.weight"].to(dtype))
+        dist = -(enc.pow(2).sum(1, keepdim=True) - 2 * enc @ cb.t()) + cb.pow(2).sum(1, keepdim=True).t()
+        top2 = dist.topk(2, dim=1).values
+        margins.append((top2[:, 0] - top2[:, 1]).reshape(B_, Fr))
+        idx = dist.max(1)[1].reshape(B_, Fr)
+        codes.append(idx)
+        zq = F.embedding(idx, sd[q + ".codebook.weight"].to(dtype)).transpose(1, 2)
+        zq = e + (zq - e)  # the straight-through expression the reference evaluates in the forward pass (:149)
+        w, b = wn(sd, q + ".out_proj", dtype)
+        residual = residual - F.conv1d(zq, w, b)
+    codes = torch.stack(codes, dim=1)
+    return (codes, torch.stack(margins, dim=1)) if return_margins else codes
+
+
+def encode_audio(sd, audio, cfg=DAC_44K, dtype=torch.float32):
+    """DACModel.encode: (B, 1, T) waveform -> codes (B, K, ceil(T / hop))."""
+    return rvq_encode(sd, encode_latents(sd, preprocess(audio, cfg), cfg, dtype), cfg, dtype)

@@ -193,6 +193,54 @@ def gen_dac():
     print("dac_tiny.npz:", wav.shape)
 
 
+def gen_dac_encode():
+    """transformers' DacModel.encode (encoder + residual VQ) on the oracle's random weights -> tests/golden/dac_enc_tiny.npz."""
+    from transformers import DacConfig, DacModel
+
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+    sd = dict(dac_oracle.random_dac_state(cfg, seed=31))
+    sd.update(dac_oracle.random_dac_encoder_state(cfg, seed=31, encoder_dim=8))
+    hf_cfg = DacConfig(encoder_hidden_size=8, downsampling_ratios=[2, 4, 8, 8], decoder_hidden_size=64,
+                       n_codebooks=3, codebook_size=32, codebook_dim=4, sampling_rate=44100)
+    hf = DacModel(hf_cfg).eval()
+    new = {}
+
+    def put(dst, src):
+        new[dst + ".weight"], new[dst + ".bias"] = dac_oracle.wn(sd, src)
+
+    for i in range(3):
+        q = f"quantizer.quantizers.{i}"
+        new[q + ".codebook.weight"] = sd[q + ".codebook.weight"]
+        put(q + ".out_proj", q + ".out_proj")
+        put(q + ".in_proj", q + ".in_proj")
+    put("encoder.conv1", "encoder.block.0")
+    for bi in range(4):
+        p, h = f"encoder.block.{bi + 1}.block", f"encoder.block.{bi}"
+        for ri in range(3):
+            r, hr = f"{p}.{ri}.block", f"{h}.res_unit{ri + 1}"
+            new[hr + ".snake1.alpha"], new[hr + ".snake2.alpha"] = sd[r + ".0.alpha"], sd[r + ".2.alpha"]
+            put(hr + ".conv1", r + ".1")
+            put(hr + ".conv2", r + ".3")
+        new[h + ".snake1.alpha"] = sd[p + ".3.alpha"]
+        put(h + ".conv1", p + ".4")
+    new["encoder.snake1.alpha"] = sd["encoder.block.5.alpha"]
+    put("encoder.conv2", "encoder.block.6")
+    res = hf.load_state_dict(new, strict=False)
+    assert not res.unexpected_keys and all(k.startswith("decoder.") for k in res.missing_keys), res
+    g = torch.Generator().manual_seed(33)
+    audio = torch.randn(2, 1, 512 * 9, generator=g) * 0.5
+    with torch.no_grad():
+        out = hf.encode(audio)
+        z = hf.encoder(audio)
+    codes = out.audio_codes
+    got_z = dac_oracle.encode_latents(sd, audio, cfg)
+    got, margins = dac_oracle.rvq_encode(sd, got_z, cfg, return_margins=True)
+    print(f"dac encode: latents max abs {float((got_z - z).abs().max()):.2e}, codes equal "
+          f"{bool(torch.equal(got, codes))}, min margin {float(margins.min()):.2e}")
+    np.savez_compressed(os.path.join(GOLD, "dac_enc_tiny.npz"), audio=audio.numpy(), z=z.numpy(), codes=codes.numpy(),
+                        margins=margins.numpy())
+
+
 T5_TINY = dict(vocab_size=120, d_model=64, d_kv=16, d_ff=96, num_layers=2, num_heads=4,
                relative_attention_num_buckets=32, relative_attention_max_distance=128, layer_norm_epsilon=1e-6)
 T5_CASES = {"gated": dict(T5_TINY, gated=True, dense_act_fn="gelu_new", feed_forward_proj="gated-gelu"),
@@ -237,10 +285,13 @@ def main():
     dims, sd, model = gen_decoder(ref)
     gen_loop(ref, dims, sd, model)
     gen_dac()
+    gen_dac_encode()
     gen_t5()
 
 
 if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "t5":
     gen_t5()  # transformers only: does not need /root/reference
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "dac_encode":
+    gen_dac_encode()
 elif __name__ == "__main__":
     main()

@@ -94,6 +94,10 @@ PROTOTYPES = {
                                      c_vp, c_vp, c_vp]),
     "ptts_dac_convtr1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "ptts_dac_pretiled": (C.c_int, []),
+    "ptts_dac_conv1d_strided": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp,
+                                          c_vp]),
+    "ptts_dac_vq_encode": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
+                                     c_vp, c_vp]),
     "ptts_t5_workspace_bytes": (c_i64, [_PT5, c_i32]),
     "ptts_t5_encode": (C.c_int, [_PT5, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
 }

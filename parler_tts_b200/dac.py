@@ -281,3 +281,105 @@ class DacDecoderEngine:
             else:
                 outs.append(torch.zeros(1, device=self.device))
         return torch.nn.utils.rnn.pad_sequence(outs, batch_first=True, padding_value=0.0)
+
+
+class DacEncoderEngine:
+    """Waveform -> codes on the CUDA path (audio-prompt continuation): host side of
+    /root/reference/parler_tts/dac_wrapper/modeling_dac.py:25-96 (`DACModel.encode` = descript `DAC.preprocess` +
+    `DAC.encode`).  Descript key names: `encoder.block.0` (conv k7), `encoder.block.{1..n}.block.{0,1,2}` (residual
+    units), `.block.3.alpha`, `.block.4` (strided conv), `encoder.block.{n+1}.alpha`, `encoder.block.{n+2}` (conv k3),
+    `quantizer.quantizers.{i}.{in_proj,out_proj,codebook}`.  Weight norm is folded once at load."""
+
+    def __init__(self, sd, device, rates=(8, 8, 4, 2), impl=cabi.IMPL_FAST):
+        dev = torch.device(device)
+        sd = {k: v.detach().to(dev) for k, v in sd.items() if k.startswith(("quantizer.", "encoder."))}
+        if "encoder.block.0.weight_v" not in sd and "encoder.block.0.weight" not in sd:
+            raise cabi.ParlerB200Error("this DAC checkpoint holds no encoder weights (encoder.block.*): audio prompts "
+                                       "cannot be encoded")
+        self.device, self.impl = dev, impl
+        self.strides = tuple(reversed(tuple(rates)))  # the encoder mirrors the decoder's up-sampling rates
+        self.hop = int(math.prod(rates))
+        alpha = lambda k: sd[k].float().reshape(-1).contiguous()  # noqa: E731
+        self.conv_in = _fold(sd, "encoder.block.0")
+        self.blocks = []
+        for bi, s in enumerate(self.strides):
+            p = f"encoder.block.{bi + 1}.block"
+            blk = dict(stride=s, res=[], alpha=alpha(p + ".3.alpha"), down=_fold(sd, p + ".4"))
+            for ri, dil in enumerate((1, 3, 9)):
+                r = f"{p}.{ri}.block"
+                blk["res"].append(dict(dil=dil, a1=alpha(r + ".0.alpha"), c1=_fold(sd, r + ".1"),
+                                       a2=alpha(r + ".2.alpha"), c2=_fold(sd, r + ".3")))
+            self.blocks.append(blk)
+        n = len(self.strides)
+        self.alpha_out = alpha(f"encoder.block.{n + 1}.alpha")
+        self.conv_out = _fold(sd, f"encoder.block.{n + 2}")
+        K = 0
+        while f"quantizer.quantizers.{K}.codebook.weight" in sd:
+            K += 1
+        w_in, b_in, w_out, b_out, cb = [], [], [], [], []
+        for i in range(K):
+            q = f"quantizer.quantizers.{i}"
+            w, b = _fold(sd, q + ".in_proj")   # [D][C][1]
+            w_in.append(w[:, :, 0])
+            b_in.append(b if b is not None else torch.zeros(w.shape[0], device=dev))
+            w, b = _fold(sd, q + ".out_proj")  # [C][D][1]
+            w_out.append(w[:, :, 0])
+            b_out.append(b if b is not None else torch.zeros(w.shape[0], device=dev))
+            cb.append(sd[q + ".codebook.weight"].float())
+        self.n_codebooks = K
+        self.w_in, self.b_in = torch.stack(w_in).contiguous(), torch.stack(b_in).contiguous()
+        self.w_out, self.b_out = torch.stack(w_out).contiguous(), torch.stack(b_out).contiguous()
+        self.codebook = torch.stack(cb).contiguous()
+        self.codebook_n = torch.nn.functional.normalize(self.codebook, dim=-1).contiguous()  # F.normalize(codebook)
+        self.codebook_size, self.codebook_dim = self.codebook.shape[1:]
+        self.latent = self.w_in.shape[2]
+
+    def _strided(self, x, wb, stride, pad, alpha=None):
+        w, b = wb
+        B, Cin, T = x.shape
+        Cout, _, k = w.shape
+        Tout = (T + 2 * pad - k) // stride + 1
+        y = torch.empty(B, Cout, Tout, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_conv1d_strided", cabi.ptr(x), B, Cin, T, cabi.ptr(w), cabi.ptr(b), Cout, k, stride, pad,
+                  cabi.ptr(alpha), cabi.ptr(y), cabi.stream_ptr())
+        return y
+
+    def _conv(self, x, wb, dil=1, alpha=None, residual=None):
+        w, b = wb
+        B, Cin, T = x.shape
+        Cout, _, k = w.shape
+        y = torch.empty(B, Cout, T, device=x.device, dtype=torch.float32)
+        cabi.call("ptts_dac_conv1d", cabi.ptr(x), B, Cin, T, cabi.ptr(w), cabi.ptr(b), Cout, k, dil, cabi.ptr(alpha),
+                  cabi.ptr(residual), 0, cabi.ptr(y), self.impl, cabi.stream_ptr())
+        return y
+
+    def encode_latents(self, audio):
+        """audio (B, 1, T) fp32, T a multiple of the hop -> z (B, latent, T / hop)."""
+        x = self._strided(audio, self.conv_in, 1, 3)
+        for blk in self.blocks:
+            for r in blk["res"]:
+                y = self._conv(x, r["c1"], dil=r["dil"], alpha=r["a1"])
+                x = self._conv(y, r["c2"], alpha=r["a2"], residual=x)
+            s = blk["stride"]
+            x = self._strided(x, blk["down"], s, math.ceil(s / 2), alpha=blk["alpha"])
+        return self._strided(x, self.conv_out, 1, 1, alpha=self.alpha_out)
+
+    def quantize(self, z, n_quantizers=None):
+        """z (B, latent, F) -> codes (B, K, F) int64."""
+        z = z.contiguous()
+        B, C, F = z.shape
+        K = self.n_codebooks if n_quantizers is None else min(int(n_quantizers), self.n_codebooks)
+        codes = torch.empty(B, K, F, device=z.device, dtype=torch.int64)
+        cabi.call("ptts_dac_vq_encode", cabi.ptr(z), B, C, F, K, self.codebook_dim, self.codebook_size,
+                  cabi.ptr(self.w_in), cabi.ptr(self.b_in), cabi.ptr(self.codebook), cabi.ptr(self.codebook_n),
+                  cabi.ptr(self.w_out), cabi.ptr(self.b_out), cabi.ptr(codes), cabi.stream_ptr())
+        return codes
+
+    def encode(self, audio, n_quantizers=None):
+        """audio (B, 1, T) -> codes (B, K, ceil(T / hop)); zero right-padding to a hop multiple like DAC.preprocess."""
+        if self.device.type != "cuda":
+            raise cabi.ParlerB200Error("the DAC encoder runs on the CUDA path only (no CPU fallback)")
+        a = audio.to(self.device, torch.float32)
+        T = a.shape[-1]
+        a = torch.nn.functional.pad(a, (0, -(-T // self.hop) * self.hop - T)).contiguous()
+        return self.quantize(self.encode_latents(a), n_quantizers)

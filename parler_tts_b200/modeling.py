@@ -17,7 +17,7 @@ import torch.nn as nn
 
 from . import cabi
 from .configuration import DACConfig, ParlerTTSConfig, ParlerTTSDecoderConfig
-from .dac import DacDecoderEngine
+from .dac import DacDecoderEngine, DacEncoderEngine
 from .engine import DecoderDims, DecoderEngine, DecoderWeights, GenState
 
 
@@ -137,6 +137,7 @@ class DACModel(nn.Module):
         for k, v in state_dict.items():
             _add_param(self.model, k, v.clone())
         self._engine = None
+        self._enc_engine = None
 
     def engine(self, impl=cabi.IMPL_FAST):
         dev = next(self.parameters()).device
@@ -153,9 +154,27 @@ class DACModel(nn.Module):
             return (audio,)
         return SimpleNamespace(audio_values=audio)
 
-    def encode(self, *args, **kwargs):
-        raise NotImplementedError("DAC encode (audio-prompt continuation) is outside the generation hot path "
-                                  "(SURVEY.md section 8f rank 3)")
+    def encoder_engine(self, impl=cabi.IMPL_FAST):
+        dev = next(self.parameters()).device
+        if self._enc_engine is None or self._enc_engine.device != dev or self._enc_engine.impl != impl:
+            self._enc_engine = DacEncoderEngine(dict(self.model.state_dict()), dev, self.rates, impl)
+        return self._enc_engine
+
+    def encode(self, input_values, padding_mask=None, bandwidth=None, return_dict=None, n_quantizers=None,
+               sample_rate=None):
+        """input_values (B, channels, T) -> audio_codes (1, B, K, ceil(T / hop)), audio_scales [None]
+        (dac_wrapper/modeling_dac.py:25-96; one chunk, like the reference's `chunk_length = None`)."""
+        if input_values.dim() != 3:
+            raise ValueError(f"input_values must be (batch, channels, length), got {tuple(input_values.shape)}")
+        channels = input_values.shape[1]
+        if channels < 1 or channels > 2:
+            raise ValueError(f"Number of audio channels must be 1 or 2, but got {channels}")
+        if channels != 1:
+            raise ValueError("the DAC encoder takes mono audio (its first conv has one input channel)")
+        codes = self.encoder_engine().encode(input_values, n_quantizers)[None]
+        if return_dict is False:
+            return (codes, [None])
+        return SimpleNamespace(audio_codes=codes, audio_scales=[None])
 
     def forward(self, tensor):
         raise ValueError("`DACModel.forward` not implemented yet")
@@ -192,6 +211,24 @@ def _random_dac_state(config, decoder_dim, rates, codebook_dim, seed=0):
     n = len(rates)
     sd[f"decoder.model.{n + 1}.alpha"] = torch.ones(1, ch // 2 ** n, 1)
     conv(f"decoder.model.{n + 2}", 1, ch // 2 ** n, 7)
+    # encoder + in_proj (audio-prompt path): descript Encoder(d_model=64, strides = reversed decoder rates)
+    d = max(decoder_dim // 24, 1)
+    conv("encoder.block.0", d, 1, 7)
+    for bi, s in enumerate(reversed(rates)):
+        p = f"encoder.block.{bi + 1}.block"
+        for ri in range(3):
+            r = f"{p}.{ri}.block"
+            sd[r + ".0.alpha"] = torch.ones(1, d, 1)
+            conv(r + ".1", d, d, 7)
+            sd[r + ".2.alpha"] = torch.ones(1, d, 1)
+            conv(r + ".3", d, d, 1)
+        sd[p + ".3.alpha"] = torch.ones(1, d, 1)
+        conv(p + ".4", 2 * d, d, 2 * s)
+        d *= 2
+    sd[f"encoder.block.{n + 1}.alpha"] = torch.ones(1, d, 1)
+    conv(f"encoder.block.{n + 2}", config.latent_dim, d, 3)
+    for i in range(config.num_codebooks):
+        conv(f"quantizer.quantizers.{i}.in_proj", codebook_dim, config.latent_dim, 1)
     return sd
 
 
@@ -659,8 +696,7 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         row_offset = mk.pop("row_offset", 0)
         return_codes = mk.pop("return_codes", False)
         input_ids = inputs if inputs is not None else mk.pop("input_ids", None)
-        if "input_values" in mk:
-            raise NotImplementedError("audio-prompt continuation needs the DAC encoder (SURVEY.md 8f rank 3)")
+        input_values = mk.pop("input_values", None)
         dev = self.device
         attention_mask = mk.pop("attention_mask", None)
         enc_out = mk.pop("encoder_outputs", None)
@@ -687,6 +723,14 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         prompt_hidden = mk.pop("prompt_hidden_states", None)
         prompt_mask = mk.pop("prompt_attention_mask", None)
         dec_ids = mk.pop("decoder_input_ids", None)
+        if input_values is not None:
+            # audio-prompt continuation (modeling_parler_tts.py:2247-2292): the prompt's codes become decoder_input_ids
+            enc_codes = self.audio_encoder.encode(input_values.to(dev)).audio_codes
+            frames, bsz, codebooks, seq_len = enc_codes.shape
+            if frames != 1:
+                raise ValueError(f"Expected 1 frame in the audio code outputs, got {frames} frames. Ensure chunking is "
+                                 "disabled by setting `chunk_length=None` in the audio encoder.")
+            dec_ids = enc_codes[0].reshape(bsz * self.config.decoder.num_codebooks, seq_len)
         if cfg:  # null conditioning for the second half (modeling_parler_tts.py:2231-2237, 2115-2118)
             hs = torch.cat([hs, torch.zeros_like(hs)], dim=0)
             if attention_mask is not None:

@@ -186,3 +186,73 @@ def test_dac_ragged_path_vs_oracle():
     got = eng.decode_generated(codes.to(DEV), 33, 32, 32)
     assert got.shape == want.shape
     np.testing.assert_allclose(got.cpu().numpy(), want.numpy(), atol=1e-3)
+
+
+# ------------------------------------------------------------------------------------ audio-prompt continuation
+def _enc_state(cfg, encoder_dim):
+    sd = dict(dac_oracle.random_dac_state(cfg, seed=31))
+    sd.update(dac_oracle.random_dac_encoder_state(cfg, seed=31, encoder_dim=encoder_dim))
+    return sd
+
+
+def test_dac_encode_vs_transformers_fixture(golden_dir):
+    """ptts_dac_conv1d_strided + ptts_dac_vq_encode against transformers' DacModel.encode: latents within 1e-4,
+    codes identical wherever the reference's own best-vs-second margin exceeds 1e-4 (all of them here)."""
+    from parler_tts_b200.dac import DacEncoderEngine
+
+    z = np.load(os.path.join(golden_dir, "dac_enc_tiny.npz"))
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+    for impl in (cabi.IMPL_SIMPLE, cabi.IMPL_FAST):
+        eng = DacEncoderEngine(_enc_state(cfg, 8), DEV, cfg["rates"], impl)
+        audio = torch.from_numpy(z["audio"]).to(DEV)
+        lat = eng.encode_latents(audio)
+        assert float((lat.cpu() - torch.from_numpy(z["z"])).abs().max()) < 1e-4
+        codes = eng.quantize(lat).cpu().numpy()
+        sure = z["margins"] > 1e-4
+        assert sure.all() and np.array_equal(codes[sure], z["codes"][sure])
+        # ragged length: zero right-padding to a hop multiple (DAC.preprocess)
+        want = dac_oracle.encode_audio(_enc_state(cfg, 8), torch.from_numpy(z["audio"])[..., :4200], cfg)
+        assert np.array_equal(eng.encode(audio[..., :4200]).cpu().numpy(), want.numpy())
+
+
+def test_dac_encode_44k_architecture_vs_oracle():
+    """Full 44.1 kHz encoder shape (1 -> 64 -> ... -> 1024, strides 2,4,8,8, 9 codebooks x 1024 x 8): latents within
+    1e-3 of the fp32 oracle, codes identical wherever the oracle's margin exceeds 1e-3."""
+    from parler_tts_b200.dac import DacEncoderEngine
+
+    cfg = dac_oracle.DAC_44K
+    sd = _enc_state(cfg, 64)
+    audio = torch.randn(2, 1, 512 * 12, generator=torch.Generator().manual_seed(5)) * 0.3
+    want_z = dac_oracle.encode_latents(sd, audio, cfg)
+    want, margins = dac_oracle.rvq_encode(sd, want_z, cfg, return_margins=True)
+    eng = DacEncoderEngine(sd, DEV, cfg["rates"])
+    lat = eng.encode_latents(audio.to(DEV))
+    assert float((lat.cpu() - want_z).abs().max()) < 1e-3 * max(1.0, float(want_z.abs().max()))
+    # quantise the ORACLE's latents so that every codebook sees the same residual: index-exact up to near ties
+    codes = eng.quantize(want_z.to(DEV)).cpu()
+    sure = margins > 1e-3
+    assert float(sure.float().mean()) > 0.95 and torch.equal(codes[sure], want[sure])
+
+
+def test_generate_with_audio_prompt_vs_oracle():
+    """generate(input_values=...) (modeling_parler_tts.py:2247-2292): the prompt is DAC-encoded on the CUDA path, its
+    codes seed the delay pattern, and the continuation equals the oracle's greedy loop on the same codes."""
+    model, dims, sd, dac_sd = _composite()
+    enc_sd = dac_oracle.random_dac_encoder_state(DAC_TINY, seed=31, encoder_dim=8)
+    full = dict(dac_sd)
+    full.update(enc_sd)
+    model.audio_encoder = ptts.DACModel(model.config.audio_encoder, state_dict=full, decoder_dim=64,
+                                        codebook_dim=4).to(DEV)
+    g = torch.Generator().manual_seed(21)
+    input_ids, prompt_ids = torch.randint(2, 100, (2, 6), generator=g), torch.randint(2, 100, (2, 4), generator=g)
+    audio = torch.randn(2, 1, 512 * 3, generator=g) * 0.4
+    prompt_codes = dac_oracle.encode_audio(full, audio, DAC_TINY)  # (2, 4, 3)
+    got_codes = model.audio_encoder.encode(audio.to(DEV)).audio_codes[0].cpu()
+    assert torch.equal(got_codes, prompt_codes)
+    kw = dict(max_length=24, do_sample=False, suppress_from=32)
+    res, _ = _oracle_generate(model, dims, sd, dac_sd, input_ids, prompt_ids, decode=False,
+                              decoder_input_ids=prompt_codes.reshape(2 * 4, 3).numpy(), **kw)
+    codes = model.generate(input_ids=input_ids.to(DEV), prompt_input_ids=prompt_ids.to(DEV),
+                           input_values=audio.to(DEV), max_length=24, do_sample=False, return_codes=True,
+                           logits_processor=[ptts.SuppressTokensAtOrAbove(32)])
+    assert np.array_equal(codes.cpu().numpy(), res["codes"])

@@ -128,3 +128,17 @@ def test_t5_bucket_table_matches_transformers():
     for nb, md in ((32, 128), (16, 64)):
         want = T5Attention._relative_position_bucket(rel, bidirectional=True, num_buckets=nb, max_distance=md)
         assert torch.equal(relative_position_buckets(nb, md).long(), want)
+
+
+def test_dac_encode_vs_transformers(golden_dir):
+    """oracle/dac_oracle.py encode path (encoder conv stack + residual VQ) against transformers' DacModel.encode
+    (tests/golden/dac_enc_tiny.npz); also the right-padding of a ragged length."""
+    z = np.load(os.path.join(golden_dir, "dac_enc_tiny.npz"))
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+    sd = dict(dac_oracle.random_dac_state(cfg, seed=31))
+    sd.update(dac_oracle.random_dac_encoder_state(cfg, seed=31, encoder_dim=8))
+    audio = torch.from_numpy(z["audio"])
+    lat = dac_oracle.encode_latents(sd, audio, cfg)
+    assert float((lat - torch.from_numpy(z["z"])).abs().max()) < 1e-5
+    assert np.array_equal(dac_oracle.rvq_encode(sd, lat, cfg).numpy(), z["codes"])
+    assert dac_oracle.encode_audio(sd, audio[..., : 512 * 8 + 100], cfg).shape == (2, 3, 9)
