@@ -155,6 +155,30 @@ __device__ __forceinline__ void l2_prefetch_lines(const void* p, int64_t bytes) 
     asm volatile("prefetch.global.L2 [%0];\n" ::"l"(reinterpret_cast<const char*>(p) + o) : "memory");
 }
 
+// ---- weight prefetch hints: the decode step is a chain of short dependent kernels, and a GEMM's weight slab only
+// starts to travel from HBM when its CTAs become resident (~4 us before their dependency resolves, 6 us of stream at
+// 128 KB per SM).  The orchestrator (decoder.cu) therefore hands the matrix a LATER launch will stream to a kernel a
+// few launches ahead of it (set_l2_hint, consumed by the next launch site that supports hints); that grid queues
+// cp.async.bulk.prefetch.L2 over the matrix, one contiguous share per CTA, so the later slab loads hit L2.
+struct L2Hint {
+  const void* ptr;
+  long long bytes;
+};
+void set_l2_hint(const void* ptr, long long bytes);  // host; PTTS_WPF bit mask selects which sites call it
+L2Hint take_l2_hint();                               // host: the pending hint (or {null, 0}); clears it
+int wpf_mask();                                      // PTTS_WPF (default: all sites on)
+__device__ __forceinline__ void l2_hint_prefetch(const L2Hint& hint, int cta, int n_ctas) {
+  if (!hint.ptr) return;
+  constexpr long long kPiece = 8192;
+  const long long share = ((hint.bytes + n_ctas - 1) / n_ctas + 127) / 128 * 128;
+  const long long lo = (long long)cta * share;
+  const long long hi = lo + share < hint.bytes ? lo + share : hint.bytes;
+  for (long long o = lo + (long long)threadIdx.x * kPiece; o < hi; o += (long long)blockDim.x * kPiece) {
+    const long long left = hi - o;
+    l2_prefetch_bulk(reinterpret_cast<const char*>(hint.ptr) + o, (uint32_t)(left < kPiece ? left : kPiece));
+  }
+}
+
 // value of a dynamic scalar: base + *dyn (dyn may be null)
 __device__ __forceinline__ int dyn_value(int base, const int* dyn) { return base + (dyn ? *dyn : 0); }
 

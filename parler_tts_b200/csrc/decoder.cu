@@ -220,6 +220,8 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     // K / V row into the cache itself
     float* qpart = work_area(m, s);
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
+    // weight prefetch hints (common.cuh): the attention CTAs pull out_proj's matrix into L2 as they finish
+    if (wpf_mask() & 2) set_l2_hint(L.w_o, (long long)H * H * es);
     PTTS_UNLESS_SKIPPED(4, attention_fast_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, 1, scale, ctx_base - 1, ctx_dyn,
                                                 ks, vs, B, heads, s->c_max, ctx_base, ctx_dyn, s->prompt_mask, s->P,
                                                 s->attn, attn_area(s), nullptr, 0, 0, nullptr, st));
@@ -246,11 +248,28 @@ self_attention_done:
   if (s->S > 0) {
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
     char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->S) * es;
+    // decode: the whole block (fold + LayerNorm, q projection, attention over the cached T5 K/V, out projection as
+    // per-head partial sums) is ONE launch (fast_xblock.cu); the next LayerNorm folds the self-attention out_proj
+    // slices and the per-head slices, stored back to back, into the residual stream
+    if (fuse && path.ln && dt == PTTS_BF16 && pend.part && !pend.ln_done && pend.part == work_area(m, s) &&
+        pend.stride == (int64_t)rows * H && xblock_supported(H, heads, d, s->S) &&
+        (int64_t)(pend.S + heads) * rows * H <= work_area_floats(m, rows) && !(skip_mask() & (1 | 16 | 32))) {
+      const char* ks_next = l + 1 < m->n_layers
+                                ? (char*)s->kv_self + (size_t)(2 * (l + 1)) * kv_layer_elems(m, B, s->c_max) * es
+                                : nullptr;
+      float* xout = work_area(m, s) + (int64_t)pend.S * pend.stride;
+      if (wpf_mask() & 4) set_l2_hint(L.w_fc1, (long long)F * H * es);  // fc1 is two launches ahead
+      PTTS_TRY(xblock_fast(s->h, pend.part, pend.S, pend.stride, L.ln2_g, L.ln2_b, 1e-5f, L.w_qc, L.w_oc, kc, vc,
+                           s->enc_mask, B, heads, H, s->S, scale, xout, ks_next, s->c_max, ctx_base, ctx_dyn, st));
+      pend.S += heads;
+      goto cross_attention_done;
+    }
     PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
     int bn_c = 64;
     const int Sc = fuse ? gemm_bf16_plan_splits(rows, H, H, &bn_c) : 0;
     if (fuse && Sc > 1 && bn_c == 0) {
       float* qpart = work_area(m, s);
+      if (wpf_mask() & 4) set_l2_hint(L.w_fc1, (long long)F * H * es);
       PTTS_UNLESS_SKIPPED(16, gemm_bf16_partial(s->xn, L.w_qc, rows, H, H, Sc, 0, qpart, st));
       // the cross-attention CTAs also queue the L2 prefetch of the NEXT layer's self-attention K rows: HBM is
       // otherwise idle during the six short kernels between here and that launch
@@ -269,7 +288,9 @@ self_attention_done:
     PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, fuse ? L.ln3_g : nullptr,
                                            fuse ? L.ln3_b : nullptr, st));
   }
+cross_attention_done:
   // feed forward block
+  if (fuse && (wpf_mask() & 8)) set_l2_hint(L.w_fc2, (long long)F * H * es);  // fc2 is three launches ahead
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
   {
     int bn_f = 64;
@@ -278,6 +299,12 @@ self_attention_done:
       // decode: fc1 as split-K partial sums + one small reduce / activation kernel (no cluster, no on-chip reduction)
       float* fpart = work_area(m, s);
       PTTS_UNLESS_SKIPPED(64, gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st));
+      if (wpf_mask() & 1) {  // the next layer's QKV matrix (or the LM heads) is three launches ahead
+        if (l + 1 < m->n_layers)
+          set_l2_hint(m->layers[l + 1].w_qkv, (long long)3 * H * H * es);
+        else
+          set_l2_hint(m->w_heads, (long long)m->n_codebooks * m->vocab * H * es);
+      }
       PTTS_UNLESS_SKIPPED(64, partial_act_fast(fpart, Sf, (int64_t)rows * F, rows, F, m->act_fn, s->ffn, st));
     } else {
       PTTS_UNLESS_SKIPPED(64, linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn,
@@ -407,6 +434,7 @@ extern "C" int ptts_prefill(const PttsModel* m, const PttsState* s, const float*
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
                            nullptr, s->logits, PTTS_F32, st));
   if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));
+  (void)take_l2_hint();  // a hint never outlives the call that set it (its matrix may be freed afterwards)
   return PTTS_OK;
 }
 
@@ -423,5 +451,6 @@ extern "C" int ptts_decode_step(const PttsModel* m, const PttsState* s, int32_t 
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
                            nullptr, s->logits, PTTS_F32, st));
   if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));
+  (void)take_l2_hint();  // a hint never outlives the call that set it (its matrix may be freed afterwards)
   return PTTS_OK;
 }

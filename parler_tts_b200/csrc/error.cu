@@ -20,6 +20,24 @@ bool pdl_enabled() {
   }
   return v == 1;
 }
+static thread_local L2Hint g_hint = {nullptr, 0};
+int wpf_mask() {
+  static int v = -1;
+  if (v < 0) {
+    const char* e = getenv("PTTS_WPF");
+    v = e ? atoi(e) : 15;
+  }
+  return v;
+}
+void set_l2_hint(const void* ptr, long long bytes) {
+  g_hint.ptr = ptr;
+  g_hint.bytes = ptr ? bytes : 0;
+}
+L2Hint take_l2_hint() {
+  const L2Hint h = g_hint;
+  g_hint = {nullptr, 0};
+  return h;
+}
 }  // namespace ptts
 
 extern "C" int32_t ptts_abi_version(void) { return PTTS_ABI_VERSION; }

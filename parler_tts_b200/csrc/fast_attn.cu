@@ -92,6 +92,8 @@ struct QFuse {
   int pf_pct;
   int pf_late;         // queue that prefetch after griddepcontrol.wait instead of before it
   int64_t pf_v_off;    // elements from pf_next to the V cache of the same launch (pf_pct > 100 also pulls V rows)
+  L2Hint tail;         // matrix of the GEMM that consumes this launch (out_proj): each CTA pulls its share into L2 when
+                       // its own stream is done - issued earlier it would be evicted by the K/V stream
 };
 
 // part layout: [(b*heads + h)*splits + s][D + 2] = { running max, sum of exp, unnormalised output[D] }
@@ -328,6 +330,9 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
       }
     }
   }
+  if constexpr (FUSED)
+    l2_hint_prefetch(qf.tail, (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z,
+                     gridDim.x * gridDim.y * gridDim.z);
   tl_end(tl);
 }
 
@@ -647,6 +652,7 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
   QFuse qf = {};
   qf.part = qkv_part; qf.S = S; qf.stride = part_stride; qf.ncols = ncols; qf.has_kv = has_kv; qf.scale = scale;
   qf.slot_base = slot_base; qf.slot_dyn = slot_dyn;
+  qf.tail = take_l2_hint();
   // PTTS_L2PF: bit 0 = own V rows (self-attention), bit 1 = next launch's K rows.  Measured on B200 (B=64, 860
   // frames): 3 -> 1.748 ms per decode step, 2 -> 1.708 ms (the own-V prefetch competes with the K pass) - default 2.
   static int pf = -1;

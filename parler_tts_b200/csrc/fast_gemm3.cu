@@ -104,7 +104,7 @@ __device__ __forceinline__ unsigned long long gtime() {
 
 // grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
 template <int EPI>
-__global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, TL tl) {
+__global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint, TL tl) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mma_bar;
   __shared__ uint32_t tmem_base_slot;
@@ -133,6 +133,8 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   cp_async_commit();  // group 0: the W slab
+  l2_hint_prefetch(hint, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                   gridDim.x * gridDim.y * gridDim.z);
   // dbg bit 4 (split-K partial GEMMs, PTTS_PDL_EARLY=0 to disable): release the dependent kernel BEFORE waiting on
   // the own producer, so that its CTAs are resident and its pre-wait prologue (gamma / beta, first K batch, L2
   // prefetches) has run by the time this grid completes.  Safe because every consumer touches producer data only
@@ -459,7 +461,8 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     early = (ev && ev[0] == '0') ? 0 : 16;
   }
   const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early : 0);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg, tl_next(10 + EPI));
+  const L2Hint hint = EPI == EPI_PARTIAL ? take_l2_hint() : L2Hint{nullptr, 0};
+  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg, hint, tl_next(10 + EPI));
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
     (void)cudaGetLastError();

@@ -13,7 +13,7 @@ template <typename TY>
 __global__ void __launch_bounds__(256)
 ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
                  const float* __restrict__ g, const float* __restrict__ bta, int H, float eps, int row_mul, int row_add,
-                 TY* __restrict__ y, TL tl) {
+                 TY* __restrict__ y, const L2Hint hint, TL tl) {
   extern __shared__ float buf[];  // [H]
   __shared__ float red[8], red2[8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -33,6 +33,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
       bb4[i] = __ldg(reinterpret_cast<const float4*>(bta + c));
     }
   }
+  l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
   pdl_wait();
   tl_dep(tl);
   float s = 0.f;
@@ -98,13 +99,14 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
                    int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st) {
   if (rows == 0) return PTTS_OK;
   const size_t smem = sizeof(float) * (size_t)H;
+  const L2Hint hint = take_l2_hint();
   cudaError_t e;
   if (ydtype == PTTS_F32)
     e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H, eps,
-                 row_mul, row_add, (float*)y, tl_next(1));
+                 row_mul, row_add, (float*)y, hint, tl_next(1));
   else
     e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H,
-                 eps, row_mul, row_add, (__nv_bfloat16*)y, tl_next(1));
+                 eps, row_mul, row_add, (__nv_bfloat16*)y, hint, tl_next(1));
   if (e != cudaSuccess) {
     set_error("layernorm_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
@@ -117,9 +119,10 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
 // slice order, deterministic).  One float4 column group per thread; all S loads of a thread are in flight together.
 __global__ void __launch_bounds__(256)
 partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, int64_t n4, int act,
-                   __nv_bfloat16* __restrict__ y, TL tl) {
+                   __nv_bfloat16* __restrict__ y, const L2Hint hint, TL tl) {
   tl_start(tl);
   pdl_launch();  // before the wait: the consumer (fc2 GEMM) only prefetches immutable weights ahead of its own wait
+  l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
   pdl_wait();
   tl_dep(tl);
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
@@ -152,7 +155,7 @@ int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, in
   const int64_t n4 = (int64_t)rows * N / 4;
   if (n4 == 0) return PTTS_OK;
   cudaError_t e = launch_k(partial_act_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,
-                           part_stride, n4, act, (__nv_bfloat16*)y, tl_next(4));
+                           part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), tl_next(4));
   if (e != cudaSuccess) {
     set_error("partial_act_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;

@@ -68,6 +68,12 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
                          int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch,
                          const void* pf_next, int pf_stride, int pf_rows_base, const int* pf_rows_dyn,
                          cudaStream_t st);
+// the cross-attention block of a decode step in one launch (fast_xblock.cu)
+bool xblock_supported(int H, int heads, int d, int S);
+int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, const float* gamma, const float* beta,
+                float eps, const void* wq, const void* wo, const void* kc, const void* vc, const int* key_mask, int B,
+                int heads, int H, int S, float scale, float* part_out, const void* pf_next, int pf_stride,
+                int pf_rows_base, const int* pf_rows_dyn, cudaStream_t st);
 bool fast_conv_supported(int Cin, int Cout, int ksize);
 int dac_conv1d_fast(const float* x, int B, int Cin, int T, const float* w, const float* bias, int Cout, int ksize,
                     int dilation, const float* snake_alpha, const float* residual, int tanh_out, float* y,

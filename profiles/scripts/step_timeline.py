@@ -44,7 +44,7 @@ t, kinds = t[ok], kinds[:n][ok]
 order = np.argsort(t[:, 1])
 t, kinds = t[order], kinds[order]
 t0 = t[0, 0]
-names = {1: "layernorm", 2: "self-attn", 3: "cross-attn", 4: "reduce-act", 10: "gemm partial", 11: "gemm store", 12: "gemm scatter"}
+names = {1: "layernorm", 2: "self-attn", 3: "cross-attn", 4: "reduce-act", 5: "cross-block", 10: "gemm partial", 11: "gemm store", 12: "gemm scatter"}
 print(f"context ~{P + N}; {len(t)} instrumented launches in one replay; step span {(t[:, 3].max() - t0) / 1e3:.1f} us")
 print("  kernel          resident-before-dep  dep-spread  run(after dep)  handover(prev end -> dep)")
 for i in range(12, 24):
