@@ -120,6 +120,10 @@ PTTS_API int ptts_diag_chain(int32_t n, int32_t mode, int32_t ctas, float* buf, 
 /* Diagnostic: globaltimer stamps of the tcgen05 GEMM recorded under PTTS_GEMM_DBG=1 (8 x uint64 per launch). */
 PTTS_API int ptts_diag_gemm_stamps(uint64_t* host, int32_t n_launches);
 
+/* Diagnostic (PTTS_XB_DBG=1): 8 x uint64 per-phase SM-clock sums of the fused cross-attention block; reset != 0
+ * clears them. */
+PTTS_API int ptts_diag_xblock(uint64_t* host, int32_t reset);
+
 /* Diagnostic (PTTS_TIMELINE=1): per-launch globaltimer slots {first start, first/last dependency resolved, last end}
  * of the fast-family kernels.  cmd 0 = reset, cmd 1 = read (4 x uint64 per slot + launch-site tag); returns #slots. */
 PTTS_API int ptts_diag_timeline(int32_t cmd, uint64_t* host, int32_t* kinds, int32_t max_slots);

@@ -166,7 +166,7 @@ struct L2Hint {
 };
 void set_l2_hint(const void* ptr, long long bytes);  // host; PTTS_WPF bit mask selects which sites call it
 L2Hint take_l2_hint();                               // host: the pending hint (or {null, 0}); clears it
-int wpf_mask();                                      // PTTS_WPF (default: all sites on)
+int wpf_mask();                                      // PTTS_WPF bit mask of hint sites (default 0, see error.cu)
 __device__ __forceinline__ void l2_hint_prefetch(const L2Hint& hint, int cta, int n_ctas) {
   if (!hint.ptr) return;
   constexpr long long kPiece = 8192;

@@ -89,6 +89,13 @@ extern "C" int ptts_diag_chain(int32_t n, int32_t mode, int32_t ctas, float* buf
   return PTTS_OK;
 }
 
+// PTTS_XB_DBG=1: per-phase SM-clock sums of the fused cross-attention block (fast_xblock.cu); reset != 0 clears them
+namespace ptts { int xblock_read_stamps(unsigned long long* host, int reset); }
+extern "C" int ptts_diag_xblock(uint64_t* host, int32_t reset) {
+  cudaDeviceSynchronize();
+  return xblock_read_stamps((unsigned long long*)host, reset);
+}
+
 // Copies the globaltimer stamps recorded by the tcgen05 GEMM under PTTS_GEMM_DBG=1 (8 x uint64 per launch, ring of 256)
 // to host memory; returns the number of launches recorded so far.  Synchronises the device (diagnostic only).
 extern "C" int ptts_diag_gemm_stamps(uint64_t* host, int32_t n_launches) {

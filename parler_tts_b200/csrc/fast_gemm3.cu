@@ -417,6 +417,8 @@ int plan_cluster3(int M, int N, int K) {
   return 0;
 }
 
+thread_local int g_late_once = 0;
+
 template <int EPI>
 int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const int cs = EPI == EPI_PARTIAL ? splits : plan_cluster3(p.M, p.N, p.K);
@@ -460,7 +462,12 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     const char* ev = getenv("PTTS_PDL_EARLY");  // measured: 1.727 ms per decode step against 1.748 ms -> default on
     early = (ev && ev[0] == '0') ? 0 : 16;
   }
-  const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early : 0);
+  int early_now = early;
+  if (EPI == EPI_PARTIAL && g_late_once) {
+    early_now = 0;
+    g_late_once = 0;
+  }
+  const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early_now : 0);
   const L2Hint hint = EPI == EPI_PARTIAL ? take_l2_hint() : L2Hint{nullptr, 0};
   cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg, hint, tl_next(10 + EPI));
   if (e != cudaSuccess) {
@@ -473,6 +480,8 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
 }
 
 }  // namespace
+
+void gemm_next_trigger_late() { g_late_once = 1; }
 
 namespace gemm {
 int umma_read_stamps(unsigned long long* host, int n_launches) {

@@ -62,8 +62,13 @@ __device__ __forceinline__ uint32_t swz(int r, int c, int row_bytes) {
   return (uint32_t)(r * row_bytes + ((c ^ (r & 7)) << 4));
 }
 
+// PTTS_XB_DBG=1: sums over all CTAs (and launches) of SM-clock cycles since the CTA's griddepcontrol.wait returned:
+// [0] LayerNorm done, [1] Wq slab landed (barrier), [2] q done (barrier), [3] attention done, [4] Wo slab landed
+// (barrier), [5] end, [6] CTA count, [7] max end; read by ptts_diag_xblock
+__device__ unsigned long long g_xb_agg[8];
+
 template <int HT>  // H = 128 * HT
-__global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int sc_cap, TL tl) {
+__global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int sc_cap, int dbg, TL tl) {
   constexpr int H = 128 * HT;
   constexpr int ROWB = 2 * H;  // bytes per bf16 row of H
   extern __shared__ __align__(128) unsigned char smraw[];
@@ -114,6 +119,8 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
   }
   pdl_wait();
   tl_dep(tl);
+  const long long c_dep = dbg ? clock64() : 0;
+  long long c_st[5] = {0, 0, 0, 0, 0};
 
   // ---- phase 1: fold + LayerNorm of row b0 + warp -> xn (bf16, shared memory)
   {
@@ -121,27 +128,26 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     float4 v[HT];
     if (warp < nrows) {
       const float* hr = p.h + (int64_t)b * H;
+      constexpr int SB = HT <= 8 ? 4 : 2;  // partial slices in flight next to the residual row (register budget)
 #pragma unroll
       for (int i = 0; i < HT; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(hr) + i * 32 + lane);
-      for (int s0 = 0; s0 < p.S_in; s0 += 2) {  // two slices (2 x HT loads) in flight, added in slice order
-        float4 t0[HT], t1[HT];
-        const float* p0 = p.part_in + (int64_t)s0 * p.stride + (int64_t)b * H;
-        const bool two = s0 + 1 < p.S_in;
+      for (int s0 = 0; s0 < p.S_in; s0 += SB) {  // SB slices (SB x HT loads) in flight, added in slice order
+        float4 t[SB][HT];
 #pragma unroll
-        for (int i = 0; i < HT; ++i) {
-          t0[i] = __ldcg(reinterpret_cast<const float4*>(p0) + i * 32 + lane);
-          if (two) t1[i] = __ldcg(reinterpret_cast<const float4*>(p0 + p.stride) + i * 32 + lane);
-        }
+        for (int u = 0; u < SB; ++u)
+          if (s0 + u < p.S_in) {
+            const float4* ps = reinterpret_cast<const float4*>(p.part_in + (int64_t)(s0 + u) * p.stride + (int64_t)b * H);
 #pragma unroll
-        for (int i = 0; i < HT; ++i) {
-          v[i].x += t0[i].x; v[i].y += t0[i].y; v[i].z += t0[i].z; v[i].w += t0[i].w;
-        }
-        if (two) {
-#pragma unroll
-          for (int i = 0; i < HT; ++i) {
-            v[i].x += t1[i].x; v[i].y += t1[i].y; v[i].z += t1[i].z; v[i].w += t1[i].w;
+            for (int i = 0; i < HT; ++i) t[u][i] = __ldcg(ps + i * 32 + lane);
           }
-        }
+#pragma unroll
+        for (int u = 0; u < SB; ++u)
+          if (s0 + u < p.S_in) {
+#pragma unroll
+            for (int i = 0; i < HT; ++i) {
+              v[i].x += t[u][i].x; v[i].y += t[u][i].y; v[i].z += t[u][i].z; v[i].w += t[u][i].w;
+            }
+          }
       }
       float s = 0.f;
 #pragma unroll
@@ -174,8 +180,10 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
       }
     }
   }
+  if (dbg) c_st[0] = clock64();
   cp_async_wait<0>();
   __syncthreads();  // xn complete, the Wq slab has landed
+  if (dbg) c_st[1] = clock64();
 
   // ---- phase 2: q[8][64] = xn . Wq_head^T; warp w owns output features [8w, 8w + 8)
   {
@@ -204,6 +212,7 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     qd[1] = __bfloat162float(__float2bfloat16_rn(q1 * p.scale));
   }
   __syncthreads();  // q visible; every warp is done with the Wq slab
+  if (dbg) c_st[2] = clock64();
 
   // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs
   {
@@ -328,8 +337,10 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
   } else if (lane < 8) {
     *reinterpret_cast<uint4*>(at + swz(warp, lane, 128)) = make_uint4(0u, 0u, 0u, 0u);
   }
+  if (dbg) c_st[3] = clock64();
   cp_async_wait<0>();
   __syncthreads();  // attention tile complete, the Wo slab has landed
+  if (dbg) c_st[4] = clock64();
 
   // ---- phase 4: part_out[head][b][n] = a[b][0:64] . Wo[n][head*64 : head*64+64]; warp w owns n in [w*H/8, (w+1)*H/8)
   {
@@ -357,10 +368,28 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
       if (g < nrows) *reinterpret_cast<float2*>(orow + n0) = make_float2(c[0] + d[0], c[1] + d[1]);
     }
   }
+  if (dbg && tid == 0) {
+    const long long c_end = clock64();
+#pragma unroll
+    for (int i = 0; i < 5; ++i) atomicAdd(g_xb_agg + i, (unsigned long long)(c_st[i] - c_dep));
+    atomicAdd(g_xb_agg + 5, (unsigned long long)(c_end - c_dep));
+    atomicAdd(g_xb_agg + 6, 1ull);
+    atomicMax(g_xb_agg + 7, (unsigned long long)(c_end - c_dep));
+  }
   tl_end(tl);
 }
 
 }  // namespace
+
+int xblock_read_stamps(unsigned long long* host, int reset) {
+  if (reset) {
+    static unsigned long long zero[8];
+    cudaMemcpyToSymbol(g_xb_agg, zero, sizeof(zero));
+    return 0;
+  }
+  cudaMemcpyFromSymbol(host, g_xb_agg, sizeof(unsigned long long) * 8);
+  return 8;
+}
 
 // PTTS_XBLOCK=0 keeps the four separate launches (LayerNorm, q GEMM, cross flash-decode, out_proj GEMM)
 bool xblock_enabled() {
@@ -407,6 +436,11 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   const size_t smem = xblock_smem(H, S);
   const int sc_cap = (S + 7) / 8 * 8;
   const dim3 grid(heads, (B + XG - 1) / XG);
+  static int dbg = -1;
+  if (dbg < 0) {
+    const char* ev = getenv("PTTS_XB_DBG");
+    dbg = ev ? atoi(ev) : 0;
+  }
   cudaError_t e;
   if (H == 1024) {
     static size_t configured = 0;
@@ -414,14 +448,14 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
       cudaFuncSetAttribute(xblock_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
-    e = launch_k(xblock_kernel<8>, grid, dim3(XT), smem, st, p, sc_cap, tl_next(5));
+    e = launch_k(xblock_kernel<8>, grid, dim3(XT), smem, st, p, sc_cap, dbg, tl_next(5));
   } else {
     static size_t configured = 0;
     if (smem > configured) {
       cudaFuncSetAttribute(xblock_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
-    e = launch_k(xblock_kernel<12>, grid, dim3(XT), smem, st, p, sc_cap, tl_next(5));
+    e = launch_k(xblock_kernel<12>, grid, dim3(XT), smem, st, p, sc_cap, dbg, tl_next(5));
   }
   if (e != cudaSuccess) {
     set_error("xblock_fast launch: %s", cudaGetErrorString(e));
