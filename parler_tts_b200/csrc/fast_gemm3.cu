@@ -12,7 +12,12 @@
 // exit barrier -> fused epilogue (gemm_common.cuh) on 64/CS rows per CTA -> wait on the exit barrier.
 // (In-kernel stamps, profiles/scripts/gemm_stamps.py: pushing partials with 4-byte st.shared::cluster costs 7.9 us per
 // launch; unbatched DSMEM loads + a blocking exit barrier cost 3.2 us; hence batched pulls and a split barrier.)
+#include <cuda.h>
 #include <stdlib.h>
+#include <string.h>
+
+#include <mutex>
+#include <unordered_map>
 
 #include "gemm_common.cuh"
 
@@ -102,11 +107,41 @@ __device__ __forceinline__ unsigned long long gtime() {
     if (dbg_slot >= 0) g_stamps[dbg_slot * 8 + (i)] = (dbg & 3) == 2 ? (unsigned long long)clock64() : gtime(); \
   } while (0)
 
+// ---- TMA operand loads (dbg bit 32, PTTS_GEMM_TMA=0 to disable): the W slab [128 x KB*64] and the X slab [64 x KB*64]
+// arrive as KB box copies each (cp.async.bulk.tensor.2d, box = 64 elements x 128 / 64 rows, SWIZZLE_128B = the very
+// shared-memory image load_block_sw128 builds), issued by ONE thread and tracked by an mbarrier.  With 16-byte
+// cp.async the 8192 requests of a 128 KB slab trickle through the LSU (measured: slab landed 1.6 us AFTER the
+// dependency resolved although it was requested 4+ us before); the TMA engine keeps the whole slab in flight.
+__device__ __forceinline__ void tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void mbar_expect_tx3(uint32_t bar, uint32_t bytes) {
+  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+}
+__device__ __forceinline__ void mbar_wait3(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > 200000000u) __trap();  // a protocol bug must fail loudly, not hang the box
+  }
+}
+
 // grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
 template <int EPI>
-__global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint, TL tl) {
+__global__ void __launch_bounds__(NTH)
+umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint, const __grid_constant__ CUtensorMap tm_w,
+                 const __grid_constant__ CUtensorMap tm_x, TL tl) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mma_bar;
+  __shared__ __align__(8) uint64_t w_bar, x_bar;
+  const bool tma = (dbg & 32) != 0;
   __shared__ uint32_t tmem_base_slot;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
   unsigned char* smem = smem_raw + (sbase - smem_u32(smem_raw));
@@ -121,7 +156,8 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   STAMP(0);
   tl_start(tl);
 
-  for (int kb = 0; kb < KB; ++kb) load_block_sw128<UM>(sw + kb * WBLK, p.W, p.K, n0, p.N, kbeg + kb * KB64);
+  if (!tma)
+    for (int kb = 0; kb < KB; ++kb) load_block_sw128<UM>(sw + kb * WBLK, p.W, p.K, n0, p.N, kbeg + kb * KB64);
   if (warp == 0) {  // tensor-memory allocation (one warp), barrier init (one thread)
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tmem_base_slot)),
                  "r"(TMEM_COLS)
@@ -130,7 +166,16 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   }
   if (threadIdx.x == 32) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&mma_bar)), "r"(1) : "memory");
+    if (tma) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&w_bar)), "r"(1) : "memory");
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&x_bar)), "r"(1) : "memory");
+    }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    if (tma) {  // the whole W slab of this CTA, before the dependency resolves (weights are immutable)
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+      mbar_expect_tx3(smem_u32(&w_bar), (uint32_t)(KB * WBLK));
+      for (int kb = 0; kb < KB; ++kb) tma_load_2d(sw + kb * WBLK, &tm_w, smem_u32(&w_bar), kbeg + kb * KB64, n0);
+    }
   }
   cp_async_commit();  // group 0: the W slab
   l2_hint_prefetch(hint, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
@@ -149,14 +194,21 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   tl_dep(tl);
   const long long c_dep = (dbg & 3) == 3 ? clock64() : 0;
   long long c_w = 0, c_x = 0, c_mma = 0;
-  for (int kb = 0; kb < KB; ++kb) load_block_sw128<UN>(sx + kb * XBLK, p.X, p.K, m0, p.M, kbeg + kb * KB64);
-  cp_async_commit();  // group 1: the X slab
-  if ((dbg & 3) == 3) {
-    cp_async_wait<1>();
-    c_w = clock64();
+  if (tma) {
+    if (threadIdx.x == 32) {
+      mbar_expect_tx3(smem_u32(&x_bar), (uint32_t)(KB * XBLK));
+      for (int kb = 0; kb < KB; ++kb) tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar), kbeg + kb * KB64, m0);
+    }
+  } else {
+    for (int kb = 0; kb < KB; ++kb) load_block_sw128<UN>(sx + kb * XBLK, p.X, p.K, m0, p.M, kbeg + kb * KB64);
+    cp_async_commit();  // group 1: the X slab
+    if ((dbg & 3) == 3) {
+      cp_async_wait<1>();
+      c_w = clock64();
+    }
+    cp_async_wait<0>();
+    if ((dbg & 3) == 3) c_x = clock64();
   }
-  cp_async_wait<0>();
-  if ((dbg & 3) == 3) c_x = clock64();
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // cp.async (generic proxy) -> UMMA (async proxy)
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();
@@ -165,6 +217,13 @@ __global__ void __launch_bounds__(NTH) umma_gemm_kernel(const GemmParams p, int 
   STAMP(2);
 
   if (threadIdx.x == 0) {
+    if (tma) {  // barrier inits are visible since the __syncthreads above; the slabs arrive through the async proxy
+      mbar_wait3(smem_u32(&w_bar), 0);
+      if ((dbg & 3) == 3) c_w = clock64();
+      mbar_wait3(smem_u32(&x_bar), 0);
+      if ((dbg & 3) == 3) c_x = clock64();
+      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+    }
     for (int kb = 0; kb < KB; ++kb) {
       const uint64_t ad = umma_desc_sw128(sw + kb * WBLK), bd = umma_desc_sw128(sx + kb * XBLK);
 #pragma unroll
@@ -419,6 +478,64 @@ int plan_cluster3(int M, int N, int K) {
 
 thread_local int g_late_once = 0;
 
+// ---- tensor maps (host): one per (matrix, shape, box rows), created on first use through the driver entry point (no
+// link-time dependency on libcuda) and cached; the map is passed to the kernel by value (__grid_constant__)
+typedef CUresult (*EncodeTiledFn)(CUtensorMap*, CUtensorMapDataType, cuuint32_t, void*, const cuuint64_t*,
+                                  const cuuint64_t*, const cuuint32_t*, const cuuint32_t*, CUtensorMapInterleave,
+                                  CUtensorMapSwizzle, CUtensorMapL2promotion, CUtensorMapFloatOOBfill);
+EncodeTiledFn encode_tiled_fn() {
+  static EncodeTiledFn fn = nullptr;
+  static bool tried = false;
+  if (!tried) {
+    tried = true;
+    void* ptr = nullptr;
+    cudaDriverEntryPointQueryResult q;
+    if (cudaGetDriverEntryPoint("cuTensorMapEncodeTiled", &ptr, cudaEnableDefault, &q) == cudaSuccess &&
+        q == cudaDriverEntryPointSuccess)
+      fn = reinterpret_cast<EncodeTiledFn>(ptr);
+    (void)cudaGetLastError();
+  }
+  return fn;
+}
+struct MapKey {
+  const void* ptr;
+  int rows, cols, box_rows;
+  bool operator==(const MapKey& o) const { return ptr == o.ptr && rows == o.rows && cols == o.cols && box_rows == o.box_rows; }
+};
+struct MapKeyHash {
+  size_t operator()(const MapKey& k) const {
+    return std::hash<const void*>()(k.ptr) ^ (size_t)k.rows * 0x9E3779B97F4A7C15ull ^ (size_t)k.cols * 0xC2B2AE3D27D4EB4Full ^
+           (size_t)k.box_rows;
+  }
+};
+// bf16 row-major [rows][cols]; box = 64 columns (128 bytes, SWIZZLE_128B) x box_rows rows; out-of-range rows read as 0
+bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  static std::mutex mu;
+  static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
+  EncodeTiledFn fn = encode_tiled_fn();
+  if (!fn || (reinterpret_cast<uintptr_t>(ptr) & 15) || cols % 8) return false;
+  std::lock_guard<std::mutex> lock(mu);
+  const MapKey key = {ptr, rows, cols, box_rows};
+  auto it = cache.find(key);
+  if (it != cache.end()) {
+    *out = it->second;
+    return true;
+  }
+  CUtensorMap m;
+  const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
+  const cuuint32_t box[2] = {(cuuint32_t)KB64, (cuuint32_t)box_rows};
+  const cuuint32_t estr[2] = {1, 1};
+  const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
+                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  if (r != CUDA_SUCCESS) return false;
+  if (cache.size() > 4096) cache.clear();
+  cache.emplace(key, m);
+  *out = m;
+  return true;
+}
+
 template <int EPI>
 int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const int cs = EPI == EPI_PARTIAL ? splits : plan_cluster3(p.M, p.N, p.K);
@@ -469,7 +586,17 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   }
   const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early_now : 0);
   const L2Hint hint = EPI == EPI_PARTIAL ? take_l2_hint() : L2Hint{nullptr, 0};
-  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg, hint, tl_next(10 + EPI));
+  static int use_tma = -1;
+  if (use_tma < 0) {
+    const char* ev = getenv("PTTS_GEMM_TMA");
+    use_tma = (ev && ev[0] == '0') ? 0 : 1;
+  }
+  CUtensorMap tm_w, tm_x;
+  memset(&tm_w, 0, sizeof(tm_w));
+  memset(&tm_x, 0, sizeof(tm_x));
+  const bool tma = use_tma && tensor_map_2d(p.W, p.N, p.K, UM, &tm_w) && tensor_map_2d(p.X, p.M, p.K, UN, &tm_x);
+  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg | (tma ? 32 : 0), hint, tm_w, tm_x,
+                                     tl_next(10 + EPI));
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
     (void)cudaGetLastError();

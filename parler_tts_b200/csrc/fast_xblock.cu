@@ -67,21 +67,46 @@ __device__ __forceinline__ uint32_t swz(int r, int c, int row_bytes) {
 // (barrier), [5] end, [6] CTA count, [7] max end; read by ptts_diag_xblock
 __device__ unsigned long long g_xb_agg[8];
 
+__device__ __forceinline__ uint32_t cluster_rank_x() {
+  uint32_t r;
+  asm volatile("mov.u32 %0, %%cluster_ctarank;\n" : "=r"(r));
+  return r;
+}
+__device__ __forceinline__ void cluster_arrive() {
+  asm volatile("barrier.cluster.arrive.release.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void cluster_wait() {
+  asm volatile("barrier.cluster.wait.acquire.aligned;\n" ::: "memory");
+}
+__device__ __forceinline__ void st_dsmem_v2(uint32_t local_addr, uint32_t rank, uint32_t x, uint32_t y) {
+  uint32_t ra;
+  asm volatile("mapa.shared::cluster.u32 %0, %1, %2;\n" : "=r"(ra) : "r"(local_addr), "r"(rank));
+  asm volatile("st.shared::cluster.v2.b32 [%0], {%1, %2};\n" ::"r"(ra), "r"(x), "r"(y) : "memory");
+}
+
+// grid (heads, ceil(B / 8)), cluster (8, 1, 1): the 8 CTAs of a cluster are 8 heads of the SAME group of 8 utterances.
+// The fold + LayerNorm of the group's 8 rows is shared: cluster rank r normalises row r and pushes it into the xn tile
+// of all 8 CTAs through distributed shared memory (every head needs every row; computed per CTA it cost 2.3 us of
+// L2 bandwidth: 128 CTAs x 160 KB).
 template <int HT>  // H = 128 * HT
 __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int sc_cap, int dbg, TL tl) {
   constexpr int H = 128 * HT;
   constexpr int ROWB = 2 * H;  // bytes per bf16 row of H
+  constexpr int UP = 6;        // key passes (8 keys each) whose K and V rows a warp keeps in registers: 48 keys
   extern __shared__ __align__(128) unsigned char smraw[];
   unsigned char* wbuf = smraw;                         // Wq head slab [64][H] bf16, later Wo head slab [H][64] bf16
-  unsigned char* xn = wbuf + XD * ROWB;                // [8][H] bf16 (swizzled)
+  unsigned char* xn = wbuf + XD * ROWB;                // [8][H] bf16 (swizzled); later the q split-K reduction tile
   float* qs = reinterpret_cast<float*>(xn + XG * ROWB);  // [8][64] scaled q (rounded to bf16 like the q buffer)
   unsigned char* at = reinterpret_cast<unsigned char*>(qs + XG * XD);  // [8][64] bf16 attention output (swizzled)
   float* sc = reinterpret_cast<float*>(at + XG * XD * 2);              // [8][sc_cap] scores -> probabilities
+  __shared__ float red[16];
   const int hd = blockIdx.x, b0 = blockIdx.y * XG;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nrows = min(XG, p.B - b0);
   const uint32_t wbuf_s = smem_u32(wbuf), xn_s = smem_u32(xn), at_s = smem_u32(at);
+  const uint32_t crank = cluster_rank_x();
   tl_start(tl);
+  cluster_arrive();  // "my shared memory is live": peers wait for this before they push rows into it
 
   // ---- before the dependency: everything below only touches immutable data (weights, the cross cache, cache rows of
   // the next self-attention launch that are older than this step)
@@ -95,125 +120,172 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     cp_async_commit();
   }
   pdl_launch();
+  // K and V rows of utterance b0 + warp for this head travel into registers now (4 lanes per 128-byte row, 8 rows per
+  // pass): by the time q exists they have long landed, and the attention phase is pure arithmetic
+  const int kg = lane >> 2, c4 = lane & 3;
+  const int bw = b0 + warp;
+  const bool live = warp < nrows;
+  const __nv_bfloat16* kb = p.kc + ((int64_t)(live ? bw : b0) * p.heads + hd) * p.S * XD + c4 * 16;
+  const __nv_bfloat16* vb = p.vc + ((int64_t)(live ? bw : b0) * p.heads + hd) * p.S * XD + c4 * 16;
+  uint4 rk[UP][2], rv[UP][2];
+  if (live) {
+#pragma unroll
+    for (int u = 0; u < UP; ++u) {
+      const int j = u * 8 + kg;
+      if (j < p.S) {
+        rk[u][0] = __ldcg(reinterpret_cast<const uint4*>(kb + (int64_t)j * XD));
+        rk[u][1] = __ldcg(reinterpret_cast<const uint4*>(kb + (int64_t)j * XD + 8));
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < UP; ++u) {
+      const int j = u * 8 + kg;
+      if (j < p.S) {
+        rv[u][0] = __ldcg(reinterpret_cast<const uint4*>(vb + (int64_t)j * XD));
+        rv[u][1] = __ldcg(reinterpret_cast<const uint4*>(vb + (int64_t)j * XD + 8));
+      }
+    }
+  }
   l2_hint_prefetch(p.hint, blockIdx.y * gridDim.x + blockIdx.x, gridDim.x * gridDim.y);
   for (int n = tid; n < H; n += XT)  // Wo[:, head]: one 128-byte line per output feature
     asm volatile("prefetch.global.L2 [%0];\n" ::"l"(p.wo + (int64_t)n * H + hd * XD) : "memory");
-  {
-    const int64_t kv_bytes = (int64_t)p.S * XD * 2;
-    for (int i = tid; i < nrows * 2; i += XT) {  // K and V of the group's utterances for this head
-      const int b = b0 + (i >> 1);
-      const __nv_bfloat16* base = ((i & 1) ? p.vc : p.kc) + ((int64_t)b * p.heads + hd) * p.S * XD;
-      for (int64_t o = 0; o < kv_bytes; o += 8192)
-        l2_prefetch_bulk(reinterpret_cast<const char*>(base) + o, (uint32_t)min((int64_t)8192, kv_bytes - o));
-    }
-    if (p.pf_next && p.pf_pct > 0) {
-      const int rows = dyn_value(p.pf_rows_base, p.pf_rows_dyn) * min(p.pf_pct, 100) / 100;
-      const int64_t bytes = (int64_t)rows * XD * 2;
-      const int pair = tid >> 5;  // warp w pulls the rows of utterance b0 + w
-      if (pair < nrows) {
-        const char* src = reinterpret_cast<const char*>(p.pf_next + ((int64_t)(b0 + pair) * p.heads + hd) * p.pf_stride * XD);
-        for (int64_t o = (int64_t)lane * 8192; o < bytes; o += 32 * 8192)
-          l2_prefetch_bulk(src + o, (uint32_t)min((int64_t)8192, bytes - o));
-      }
-    }
+  if (p.S > 8 * UP && live && lane < 2) {  // keys beyond the register-held ones: L2 prefetch of K (lane 0) / V (lane 1)
+    const char* base = reinterpret_cast<const char*>((lane ? p.vc : p.kc) + (((int64_t)bw * p.heads + hd) * p.S + 8 * UP) * XD);
+    const int64_t bytes = (int64_t)(p.S - 8 * UP) * XD * 2;
+    for (int64_t o = 0; o < bytes; o += 8192) l2_prefetch_bulk(base + o, (uint32_t)min((int64_t)8192, bytes - o));
+  }
+  if (p.pf_next && p.pf_pct > 0 && live) {
+    const int rows = dyn_value(p.pf_rows_base, p.pf_rows_dyn) * min(p.pf_pct, 100) / 100;
+    const int64_t bytes = (int64_t)rows * XD * 2;
+    const char* src = reinterpret_cast<const char*>(p.pf_next + ((int64_t)bw * p.heads + hd) * p.pf_stride * XD);
+    for (int64_t o = (int64_t)lane * 8192; o < bytes; o += 32 * 8192)
+      l2_prefetch_bulk(src + o, (uint32_t)min((int64_t)8192, bytes - o));
   }
   pdl_wait();
   tl_dep(tl);
   const long long c_dep = dbg ? clock64() : 0;
   long long c_st[5] = {0, 0, 0, 0, 0};
 
-  // ---- phase 1: fold + LayerNorm of row b0 + warp -> xn (bf16, shared memory)
+  // ---- phase 1: this CTA folds + normalises row b0 + crank (all 256 threads on one row) and pushes it to the cluster
   {
-    const int b = b0 + warp;
-    float4 v[HT];
-    if (warp < nrows) {
-      const float* hr = p.h + (int64_t)b * H;
-      constexpr int SB = HT <= 8 ? 4 : 2;  // partial slices in flight next to the residual row (register budget)
+    constexpr int V4 = (H / 4 + XT - 1) / XT;  // float4 per thread (1 at H = 1024, 2 at H = 1536)
+    const bool mine = (int)crank < nrows;
+    const int b = b0 + (int)crank;
+    float4 v[V4];
 #pragma unroll
-      for (int i = 0; i < HT; ++i) v[i] = __ldcg(reinterpret_cast<const float4*>(hr) + i * 32 + lane);
-      for (int s0 = 0; s0 < p.S_in; s0 += SB) {  // SB slices (SB x HT loads) in flight, added in slice order
-        float4 t[SB][HT];
+    for (int i = 0; i < V4; ++i) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+    if (mine) {
+      const float4* hr = reinterpret_cast<const float4*>(p.h + (int64_t)b * H);
 #pragma unroll
-        for (int u = 0; u < SB; ++u)
+      for (int i = 0; i < V4; ++i)
+        if (tid + i * XT < H / 4) v[i] = __ldcg(hr + tid + i * XT);
+      for (int s0 = 0; s0 < p.S_in; s0 += 4) {  // 4 slices in flight, added in slice order (deterministic)
+        float4 t[4][V4];
+#pragma unroll
+        for (int u = 0; u < 4; ++u)
           if (s0 + u < p.S_in) {
             const float4* ps = reinterpret_cast<const float4*>(p.part_in + (int64_t)(s0 + u) * p.stride + (int64_t)b * H);
 #pragma unroll
-            for (int i = 0; i < HT; ++i) t[u][i] = __ldcg(ps + i * 32 + lane);
+            for (int i = 0; i < V4; ++i)
+              if (tid + i * XT < H / 4) t[u][i] = __ldcg(ps + tid + i * XT);
           }
 #pragma unroll
-        for (int u = 0; u < SB; ++u)
+        for (int u = 0; u < 4; ++u)
           if (s0 + u < p.S_in) {
 #pragma unroll
-            for (int i = 0; i < HT; ++i) {
-              v[i].x += t[u][i].x; v[i].y += t[u][i].y; v[i].z += t[u][i].z; v[i].w += t[u][i].w;
-            }
+            for (int i = 0; i < V4; ++i)
+              if (tid + i * XT < H / 4) {
+                v[i].x += t[u][i].x; v[i].y += t[u][i].y; v[i].z += t[u][i].z; v[i].w += t[u][i].w;
+              }
           }
       }
-      float s = 0.f;
+    }
+    float s = 0.f;
 #pragma unroll
-      for (int i = 0; i < HT; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);
-      const float mean = warp_sum(s) / (float)H;
-      float qq = 0.f;
+    for (int i = 0; i < V4; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);  // lanes past H / 4 hold zeros
+    s = warp_sum(s);
+    if (lane == 0) red[warp] = s;
+    __syncthreads();
+    const float mean = (((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]))) / (float)H;
+    float qq = 0.f;
 #pragma unroll
-      for (int i = 0; i < HT; ++i) {
+    for (int i = 0; i < V4; ++i)
+      if (tid + i * XT < H / 4) {
         const float a = v[i].x - mean, bb = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
         qq += (a * a + bb * bb) + (c * c + d * d);
       }
-      const float rstd = rsqrtf(warp_sum(qq) / (float)H + p.eps);
+    qq = warp_sum(qq);
+    if (lane == 0) red[8 + warp] = qq;
+    __syncthreads();
+    const float rstd =
+        rsqrtf((((red[8] + red[9]) + (red[10] + red[11])) + ((red[12] + red[13]) + (red[14] + red[15]))) / (float)H + p.eps);
+    cluster_wait();  // every CTA of the cluster is running: its shared memory may be written
 #pragma unroll
-      for (int i = 0; i < HT; ++i) {
-        const int col = (i * 32 + lane) * 4;
-        const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
-        const float4 be = __ldg(reinterpret_cast<const float4*>(p.beta + col));
-        const __nv_bfloat162 lo = __floats2bfloat162_rn((v[i].x - mean) * rstd * g.x + be.x, (v[i].y - mean) * rstd * g.y + be.y);
-        const __nv_bfloat162 hi = __floats2bfloat162_rn((v[i].z - mean) * rstd * g.z + be.z, (v[i].w - mean) * rstd * g.w + be.w);
-        uint2 u;
-        u.x = *reinterpret_cast<const uint32_t*>(&lo);
-        u.y = *reinterpret_cast<const uint32_t*>(&hi);
-        *reinterpret_cast<uint2*>(xn + swz(warp, col >> 3, ROWB) + (col & 7) * 2) = u;
-      }
-    } else {  // rows past the batch: zeros (their results are never stored)
+    for (int i = 0; i < V4; ++i) {
+      const int c4i = tid + i * XT;
+      if (c4i < H / 4) {
+        const int col = c4i * 4;
+        uint32_t lo = 0u, hi = 0u;
+        if (mine) {
+          const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
+          const float4 be = __ldg(reinterpret_cast<const float4*>(p.beta + col));
+          const __nv_bfloat162 l2 = __floats2bfloat162_rn((v[i].x - mean) * rstd * g.x + be.x, (v[i].y - mean) * rstd * g.y + be.y);
+          const __nv_bfloat162 h2 = __floats2bfloat162_rn((v[i].z - mean) * rstd * g.z + be.z, (v[i].w - mean) * rstd * g.w + be.w);
+          lo = *reinterpret_cast<const uint32_t*>(&l2);
+          hi = *reinterpret_cast<const uint32_t*>(&h2);
+        }
+        const uint32_t dst = xn_s + swz((int)crank, col >> 3, ROWB) + (col & 7) * 2;
 #pragma unroll
-      for (int i = 0; i < HT; ++i) {
-        const int col = (i * 32 + lane) * 4;
-        *reinterpret_cast<uint2*>(xn + swz(warp, col >> 3, ROWB) + (col & 7) * 2) = make_uint2(0u, 0u);
+        for (uint32_t r = 0; r < XG; ++r) st_dsmem_v2(dst, r, lo, hi);
       }
     }
   }
   if (dbg) c_st[0] = clock64();
   cp_async_wait<0>();
-  __syncthreads();  // xn complete, the Wq slab has landed
+  cluster_arrive();
+  cluster_wait();  // all 8 rows of xn are here (pushed by the 8 CTAs), and this CTA's Wq slab has landed
   if (dbg) c_st[1] = clock64();
 
-  // ---- phase 2: q[8][64] = xn . Wq_head^T; warp w owns output features [8w, 8w + 8)
+  // ---- phase 2: q[8][64] = xn . Wq_head^T, split over K: warp w multiplies k in [w*H/8, (w+1)*H/8) for all 64 features
+  // (every shared-memory operand byte is read exactly once), the 8 partial tiles are summed through the dead xn tile
   {
-    float acc[4][4];
+    float acc[8][4];
 #pragma unroll
-    for (int i = 0; i < 4; ++i)
+    for (int i = 0; i < 8; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
     const int mi = lane >> 3, ri = lane & 7;  // ldmatrix: lane supplies row ri of 8x8 matrix mi (= k chunk kc + mi)
-    const uint32_t a_base = xn_s + ri * ROWB, b_base = wbuf_s + (warp * 8 + ri) * ROWB;
-#pragma unroll 4
-    for (int kc = 0; kc < ROWB / 16; kc += 4) {  // 32 k per iteration = two k16 steps
-      uint32_t a[4], bq[4];
+    constexpr int CPW = ROWB / 16 / 8;        // 16-byte k chunks per warp
+    const uint32_t a_base = xn_s + ri * ROWB, b_base = wbuf_s + ri * ROWB;
+#pragma unroll
+    for (int it = 0; it < CPW / 4; ++it) {  // 32 k per iteration = two k16 steps
+      const int kc = warp * CPW + it * 4;
       const uint32_t off = (uint32_t)(((kc + mi) ^ ri) << 4);
+      uint32_t a[4];
       ldmatrix_x4(a, a_base + off);
-      ldmatrix_x4(bq, b_base + off);
       const uint32_t a0[4] = {a[0], 0u, a[1], 0u}, a1[4] = {a[2], 0u, a[3], 0u};
-      mma_bf16(acc[(kc >> 2) & 1 ? 2 : 0], a0, bq[0], bq[1]);
-      mma_bf16(acc[(kc >> 2) & 1 ? 3 : 1], a1, bq[2], bq[3]);
+#pragma unroll
+      for (int nt = 0; nt < 8; ++nt) {
+        uint32_t bq[4];
+        ldmatrix_x4(bq, b_base + nt * 8 * ROWB + off);
+        mma_bf16(acc[nt], a0, bq[0], bq[1]);
+        mma_bf16(acc[nt], a1, bq[2], bq[3]);
+      }
     }
+    __syncthreads();  // every warp is done reading xn (and the Wq slab)
+    float* redq = reinterpret_cast<float*>(xn);  // [8 warps][8 rows][64] fp32 = 16 KB <= 8 * ROWB
     const int g = lane >> 2, t = lane & 3;
-    const float q0 = (acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]);
-    const float q1 = (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]);
-    float* qd = qs + g * XD + warp * 8 + 2 * t;
-    qd[0] = __bfloat162float(__float2bfloat16_rn(q0 * p.scale));
-    qd[1] = __bfloat162float(__float2bfloat16_rn(q1 * p.scale));
+#pragma unroll
+    for (int nt = 0; nt < 8; ++nt)
+      *reinterpret_cast<float2*>(redq + (warp * XG + g) * XD + nt * 8 + 2 * t) = make_float2(acc[nt][0], acc[nt][1]);
+    __syncthreads();
+    for (int i = tid; i < XG * XD; i += XT) {
+      float q = 0.f;
+#pragma unroll
+      for (int w = 0; w < 8; ++w) q += redq[w * XG * XD + i];
+      qs[i] = __bfloat162float(__float2bfloat16_rn(q * p.scale));
+    }
   }
-  __syncthreads();  // q visible; every warp is done with the Wq slab
-  if (dbg) c_st[2] = clock64();
-
   // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs
   {
     const __nv_bfloat16* src = p.wo + hd * XD;
@@ -223,30 +295,18 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     }
     cp_async_commit();
   }
+  __syncthreads();  // q visible
+  if (dbg) c_st[2] = clock64();
 
   // ---- phase 3: cross-attention of utterance b0 + warp over its S cached keys (4 lanes per key row, 8 rows per pass)
-  if (warp < nrows) {
-    const int b = b0 + warp;
-    const int kg = lane >> 2, c4 = lane & 3;
-    const __nv_bfloat16* kb = p.kc + ((int64_t)b * p.heads + hd) * p.S * XD + c4 * 16;
-    const __nv_bfloat16* vb = p.vc + ((int64_t)b * p.heads + hd) * p.S * XD + c4 * 16;
+  if (live) {
     float* scw = sc + warp * sc_cap;
     float qv[16];
 #pragma unroll
     for (int e = 0; e < 16; ++e) qv[e] = qs[warp * XD + c4 * 16 + e];
     const float neg = finfo_min<__nv_bfloat16>();
-    constexpr int UP = 6;  // passes (of 8 keys) in flight per batch
     float lmax = -INFINITY;
-    for (int j0 = 0; j0 < p.S; j0 += 8 * UP) {
-      uint4 raw[UP][2];
-#pragma unroll
-      for (int u = 0; u < UP; ++u) {
-        const int j = j0 + u * 8 + kg;
-        if (j < p.S) {
-          raw[u][0] = __ldcg(reinterpret_cast<const uint4*>(kb + (int64_t)j * XD));
-          raw[u][1] = __ldcg(reinterpret_cast<const uint4*>(kb + (int64_t)j * XD + 8));
-        }
-      }
+    auto score_batch = [&](const uint4 (&raw)[UP][2], int j0) {
 #pragma unroll
       for (int u = 0; u < UP; ++u) {
         const int j = j0 + u * 8 + kg;
@@ -267,12 +327,28 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
         dot += __shfl_xor_sync(0xffffffffu, dot, 2);
         if (j < p.S && c4 == 0) {
           bool keep = true;
-          if (p.key_mask) keep = p.key_mask[(int64_t)b * p.S + j] != 0;
-          const float s = keep ? dot : neg;
-          scw[j] = s;
-          lmax = fmaxf(lmax, s);
+          if (p.key_mask) keep = p.key_mask[(int64_t)bw * p.S + j] != 0;
+          const float sj = keep ? dot : neg;
+          scw[j] = sj;
+          lmax = fmaxf(lmax, sj);
         }
       }
+    };
+    auto load_batch = [&](uint4 (&raw)[UP][2], const __nv_bfloat16* base, int j0) {
+#pragma unroll
+      for (int u = 0; u < UP; ++u) {
+        const int j = j0 + u * 8 + kg;
+        if (j < p.S) {
+          raw[u][0] = __ldcg(reinterpret_cast<const uint4*>(base + (int64_t)j * XD));
+          raw[u][1] = __ldcg(reinterpret_cast<const uint4*>(base + (int64_t)j * XD + 8));
+        }
+      }
+    };
+    score_batch(rk, 0);
+    for (int j0 = 8 * UP; j0 < p.S; j0 += 8 * UP) {  // descriptions longer than 48 tokens
+      uint4 raw[UP][2];
+      load_batch(raw, kb, j0);
+      score_batch(raw, j0);
     }
     const float mx = warp_max(lmax);
     __syncwarp();
@@ -287,16 +363,7 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     float acc[16];
 #pragma unroll
     for (int e = 0; e < 16; ++e) acc[e] = 0.f;
-    for (int j0 = 0; j0 < p.S; j0 += 8 * UP) {
-      uint4 raw[UP][2];
-#pragma unroll
-      for (int u = 0; u < UP; ++u) {
-        const int j = j0 + u * 8 + kg;
-        if (j < p.S) {
-          raw[u][0] = __ldcg(reinterpret_cast<const uint4*>(vb + (int64_t)j * XD));
-          raw[u][1] = __ldcg(reinterpret_cast<const uint4*>(vb + (int64_t)j * XD + 8));
-        }
-      }
+    auto accum_batch = [&](const uint4 (&raw)[UP][2], int j0) {
 #pragma unroll
       for (int u = 0; u < UP; ++u) {
         const int j = j0 + u * 8 + kg;
@@ -314,6 +381,12 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
           }
         }
       }
+    };
+    accum_batch(rv, 0);
+    for (int j0 = 8 * UP; j0 < p.S; j0 += 8 * UP) {
+      uint4 raw[UP][2];
+      load_batch(raw, vb, j0);
+      accum_batch(raw, j0);
     }
 #pragma unroll
     for (int e = 0; e < 16; ++e) {  // sum over the 8 key groups of the warp (fixed order)
@@ -409,7 +482,7 @@ static size_t xblock_smem(int H, int S) {
 
 bool xblock_supported(int H, int heads, int d, int S) {
   if (!xblock_enabled()) return false;
-  if (d != XD || heads * d != H || (H != 1024 && H != 1536) || S < 1) return false;
+  if (d != XD || heads * d != H || (H != 1024 && H != 1536) || heads % XG != 0 || S < 1) return false;
   return xblock_smem(H, S) <= 227 * 1024;
 }
 
@@ -423,12 +496,12 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   p.wq = (const __nv_bfloat16*)wq; p.wo = (const __nv_bfloat16*)wo;
   p.kc = (const __nv_bfloat16*)kc; p.vc = (const __nv_bfloat16*)vc; p.key_mask = key_mask;
   p.B = B; p.heads = heads; p.S = S; p.scale = scale; p.part_out = part_out;
-  static int pf_pct = -1;  // same knob as the cross flash-decode kernel (fast_attn.cu)
+  static int pf_pct = -1;  // share of the next self-attention launch's K rows to pull into L2 from here
   if (pf_pct < 0) {
-    const char* e = getenv("PTTS_L2PF_PCT");
-    pf_pct = e ? atoi(e) : 50;
-    const char* m = getenv("PTTS_L2PF");
-    if (m && !(atoi(m) & 2)) pf_pct = 0;
+    // measured on B200 with this kernel (B=64, 860 frames): 50 % 1.694, 25 % 1.674, 0 % 1.652 ms per decode step - the
+    // prefetch queues in front of the block's own slab loads, so it is off unless PTTS_XB_L2PF_PCT asks for it
+    const char* x = getenv("PTTS_XB_L2PF_PCT");
+    pf_pct = x ? atoi(x) : 0;
   }
   p.pf_next = (const __nv_bfloat16*)pf_next; p.pf_stride = pf_stride; p.pf_rows_base = pf_rows_base;
   p.pf_rows_dyn = pf_rows_dyn; p.pf_pct = pf_pct;
@@ -441,6 +514,25 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
     const char* ev = getenv("PTTS_XB_DBG");
     dbg = ev ? atoi(ev) : 0;
   }
+  cudaLaunchConfig_t cfg = {};
+  cfg.gridDim = grid;
+  cfg.blockDim = dim3(XT);
+  cfg.dynamicSmemBytes = smem;
+  cfg.stream = st;
+  cudaLaunchAttribute attr[2];
+  int na = 0;
+  attr[na].id = cudaLaunchAttributeClusterDimension;
+  attr[na].val.clusterDim.x = XG;
+  attr[na].val.clusterDim.y = 1;
+  attr[na].val.clusterDim.z = 1;
+  ++na;
+  if (pdl_enabled()) {
+    attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
+    attr[na].val.programmaticStreamSerializationAllowed = 1;
+    ++na;
+  }
+  cfg.attrs = attr;
+  cfg.numAttrs = na;
   cudaError_t e;
   if (H == 1024) {
     static size_t configured = 0;
@@ -448,14 +540,14 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
       cudaFuncSetAttribute(xblock_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
-    e = launch_k(xblock_kernel<8>, grid, dim3(XT), smem, st, p, sc_cap, dbg, tl_next(5));
+    e = cudaLaunchKernelEx(&cfg, xblock_kernel<8>, p, sc_cap, dbg, tl_next(5));
   } else {
     static size_t configured = 0;
     if (smem > configured) {
       cudaFuncSetAttribute(xblock_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
-    e = launch_k(xblock_kernel<12>, grid, dim3(XT), smem, st, p, sc_cap, dbg, tl_next(5));
+    e = cudaLaunchKernelEx(&cfg, xblock_kernel<12>, p, sc_cap, dbg, tl_next(5));
   }
   if (e != cudaSuccess) {
     set_error("xblock_fast launch: %s", cudaGetErrorString(e));
