@@ -34,6 +34,7 @@ constexpr int PITCH3 = UM + 4;     // fp32 pitch of the transposed reduction til
 constexpr int WBLK = UM * 128;     // bytes of one W k-block (128 rows x 128 B)
 constexpr int XBLK = UN * 128;     // bytes of one X k-block
 constexpr uint32_t TMEM_COLS = 64;
+constexpr int kMaxKB64 = 8;  // <= 512 K elements per CTA: (128 + 64) rows x 1 KB = 192 KB of operand slabs
 
 __device__ __forceinline__ uint32_t cluster_rank3() {
   uint32_t r;
@@ -140,7 +141,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
                  const __grid_constant__ CUtensorMap tm_x, TL tl) {
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mma_bar;
-  __shared__ __align__(8) uint64_t w_bar, x_bar;
+  __shared__ __align__(8) uint64_t w_bar, x_bar[kMaxKB64];  // one barrier per X k-block: MMAs start as blocks land
   const bool tma = (dbg & 32) != 0;
   __shared__ uint32_t tmem_base_slot;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
@@ -168,7 +169,8 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&mma_bar)), "r"(1) : "memory");
     if (tma) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&w_bar)), "r"(1) : "memory");
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&x_bar)), "r"(1) : "memory");
+      for (int kb = 0; kb < KB; ++kb)
+        asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&x_bar[kb])), "r"(1) : "memory");
     }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
     if (tma) {  // the whole W slab of this CTA, before the dependency resolves (weights are immutable)
@@ -196,8 +198,10 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
   long long c_w = 0, c_x = 0, c_mma = 0;
   if (tma) {
     if (threadIdx.x == 32) {
-      mbar_expect_tx3(smem_u32(&x_bar), (uint32_t)(KB * XBLK));
-      for (int kb = 0; kb < KB; ++kb) tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar), kbeg + kb * KB64, m0);
+      for (int kb = 0; kb < KB; ++kb) {
+        mbar_expect_tx3(smem_u32(&x_bar[kb]), (uint32_t)XBLK);
+        tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar[kb]), kbeg + kb * KB64, m0);
+      }
     }
   } else {
     for (int kb = 0; kb < KB; ++kb) load_block_sw128<UN>(sx + kb * XBLK, p.X, p.K, m0, p.M, kbeg + kb * KB64);
@@ -220,11 +224,13 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
     if (tma) {  // barrier inits are visible since the __syncthreads above; the slabs arrive through the async proxy
       mbar_wait3(smem_u32(&w_bar), 0);
       if ((dbg & 3) == 3) c_w = clock64();
-      mbar_wait3(smem_u32(&x_bar), 0);
-      if ((dbg & 3) == 3) c_x = clock64();
-      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
     }
     for (int kb = 0; kb < KB; ++kb) {
+      if (tma) {
+        mbar_wait3(smem_u32(&x_bar[kb]), 0);
+        if ((dbg & 3) == 3 && kb == KB - 1) c_x = clock64();
+        asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+      }
       const uint64_t ad = umma_desc_sw128(sw + kb * WBLK), bd = umma_desc_sw128(sx + kb * XBLK);
 #pragma unroll
       for (int k = 0; k < KB64 / 16; ++k)  // +32 bytes (2 x 16 B) per UMMA_K = 16 inside the swizzle atom
@@ -454,7 +460,6 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
   tl_end(tl);
 }
 
-constexpr int kMaxKB64 = 8;  // <= 512 K elements per CTA: (128 + 64) rows x 1 KB = 192 KB of operand slabs
 
 int plan_cluster3(int M, int N, int K) {
   if (K % 128 != 0) return 0;

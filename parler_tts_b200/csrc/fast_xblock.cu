@@ -84,11 +84,13 @@ __device__ __forceinline__ void st_dsmem_v2(uint32_t local_addr, uint32_t rank, 
   asm volatile("st.shared::cluster.v2.b32 [%0], {%1, %2};\n" ::"r"(ra), "r"(x), "r"(y) : "memory");
 }
 
-// grid (heads, ceil(B / 8)), cluster (8, 1, 1): the 8 CTAs of a cluster are 8 heads of the SAME group of 8 utterances.
-// The fold + LayerNorm of the group's 8 rows is shared: cluster rank r normalises row r and pushes it into the xn tile
-// of all 8 CTAs through distributed shared memory (every head needs every row; computed per CTA it cost 2.3 us of
-// L2 bandwidth: 128 CTAs x 160 KB).
-template <int HT>  // H = 128 * HT
+// grid (heads, ceil(B / 8)), cluster (CS, 1, 1), CS in {1, 2, 4}: the CTAs of a cluster are CS heads of the SAME group
+// of 8 utterances and share the fold + LayerNorm of the group's rows: cluster rank r normalises rows [r*8/CS, (r+1)*8/CS)
+// (32*CS threads per row) and pushes them into the xn tile of all CS CTAs through distributed shared memory.  Every
+// head needs every row; computed per CTA (CS = 1) the fold costs 2.3 us of L2 bandwidth (128 CTAs x 160 KB), while
+// CS = 8 (one row per CTA) cannot be placed next to the neighbouring kernels' CTAs: measured 12 us between the first
+// and the last CTA passing the dependency wait.
+template <int HT, int CS>  // H = 128 * HT
 __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int sc_cap, int dbg, TL tl) {
   constexpr int H = 128 * HT;
   constexpr int ROWB = 2 * H;  // bytes per bf16 row of H
@@ -106,7 +108,7 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
   const uint32_t wbuf_s = smem_u32(wbuf), xn_s = smem_u32(xn), at_s = smem_u32(at);
   const uint32_t crank = cluster_rank_x();
   tl_start(tl);
-  cluster_arrive();  // "my shared memory is live": peers wait for this before they push rows into it
+  if constexpr (CS > 1) cluster_arrive();  // "my shared memory is live": peers wait for this before they push rows
 
   // ---- before the dependency: everything below only touches immutable data (weights, the cross cache, cache rows of
   // the next self-attention launch that are older than this step)
@@ -166,11 +168,15 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
   const long long c_dep = dbg ? clock64() : 0;
   long long c_st[5] = {0, 0, 0, 0, 0};
 
-  // ---- phase 1: this CTA folds + normalises row b0 + crank (all 256 threads on one row) and pushes it to the cluster
+  // ---- phase 1: fold + LayerNorm; team `team` (TS = 32*CS threads) of this CTA owns row crank*RP + team of the group
   {
-    constexpr int V4 = (H / 4 + XT - 1) / XT;  // float4 per thread (1 at H = 1024, 2 at H = 1536)
-    const bool mine = (int)crank < nrows;
-    const int b = b0 + (int)crank;
+    constexpr int RP = XG / CS;                 // rows normalised by this CTA
+    constexpr int TS = XT / RP;                 // threads per row
+    constexpr int V4 = (H / 4 + TS - 1) / TS;   // float4 per thread
+    const int team = tid / TS, tt = tid % TS;
+    const int row = (int)crank * RP + team;     // row of the group
+    const bool mine = row < nrows;
+    const int b = b0 + row;
     float4 v[V4];
 #pragma unroll
     for (int i = 0; i < V4; ++i) v[i] = make_float4(0.f, 0.f, 0.f, 0.f);
@@ -178,23 +184,24 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
       const float4* hr = reinterpret_cast<const float4*>(p.h + (int64_t)b * H);
 #pragma unroll
       for (int i = 0; i < V4; ++i)
-        if (tid + i * XT < H / 4) v[i] = __ldcg(hr + tid + i * XT);
-      for (int s0 = 0; s0 < p.S_in; s0 += 4) {  // 4 slices in flight, added in slice order (deterministic)
-        float4 t[4][V4];
+        if (tt + i * TS < H / 4) v[i] = __ldcg(hr + tt + i * TS);
+      constexpr int SB = V4 <= 4 ? 4 : (V4 <= 8 ? 2 : 1);  // slices in flight (register budget: K/V rows are held too)
+      for (int s0 = 0; s0 < p.S_in; s0 += SB) {  // added in slice order (deterministic)
+        float4 t[SB][V4];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < SB; ++u)
           if (s0 + u < p.S_in) {
             const float4* ps = reinterpret_cast<const float4*>(p.part_in + (int64_t)(s0 + u) * p.stride + (int64_t)b * H);
 #pragma unroll
             for (int i = 0; i < V4; ++i)
-              if (tid + i * XT < H / 4) t[u][i] = __ldcg(ps + tid + i * XT);
+              if (tt + i * TS < H / 4) t[u][i] = __ldcg(ps + tt + i * TS);
           }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < SB; ++u)
           if (s0 + u < p.S_in) {
 #pragma unroll
             for (int i = 0; i < V4; ++i)
-              if (tid + i * XT < H / 4) {
+              if (tt + i * TS < H / 4) {
                 v[i].x += t[u][i].x; v[i].y += t[u][i].y; v[i].z += t[u][i].z; v[i].w += t[u][i].w;
               }
           }
@@ -202,27 +209,36 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     }
     float s = 0.f;
 #pragma unroll
-    for (int i = 0; i < V4; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);  // lanes past H / 4 hold zeros
+    for (int i = 0; i < V4; ++i) s += (v[i].x + v[i].y) + (v[i].z + v[i].w);  // threads past H / 4 hold zeros
     s = warp_sum(s);
-    if (lane == 0) red[warp] = s;
-    __syncthreads();
-    const float mean = (((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]))) / (float)H;
+    if constexpr (CS > 1) {  // a row spans CS warps
+      if (lane == 0) red[warp] = s;
+      __syncthreads();
+      s = 0.f;
+#pragma unroll
+      for (int w = 0; w < CS; ++w) s += red[team * CS + w];
+    }
+    const float mean = s / (float)H;
     float qq = 0.f;
 #pragma unroll
     for (int i = 0; i < V4; ++i)
-      if (tid + i * XT < H / 4) {
+      if (tt + i * TS < H / 4) {
         const float a = v[i].x - mean, bb = v[i].y - mean, c = v[i].z - mean, d = v[i].w - mean;
         qq += (a * a + bb * bb) + (c * c + d * d);
       }
     qq = warp_sum(qq);
-    if (lane == 0) red[8 + warp] = qq;
-    __syncthreads();
-    const float rstd =
-        rsqrtf((((red[8] + red[9]) + (red[10] + red[11])) + ((red[12] + red[13]) + (red[14] + red[15]))) / (float)H + p.eps);
-    cluster_wait();  // every CTA of the cluster is running: its shared memory may be written
+    if constexpr (CS > 1) {
+      if (lane == 0) red[8 + warp] = qq;
+      __syncthreads();
+      qq = 0.f;
+#pragma unroll
+      for (int w = 0; w < CS; ++w) qq += red[8 + team * CS + w];
+    }
+    const float rstd = rsqrtf(qq / (float)H + p.eps);
+    if constexpr (CS > 1) cluster_wait();  // every CTA of the cluster is running: its shared memory may be written
 #pragma unroll
     for (int i = 0; i < V4; ++i) {
-      const int c4i = tid + i * XT;
+      const int c4i = tt + i * TS;
       if (c4i < H / 4) {
         const int col = c4i * 4;
         uint32_t lo = 0u, hi = 0u;
@@ -234,58 +250,61 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
           lo = *reinterpret_cast<const uint32_t*>(&l2);
           hi = *reinterpret_cast<const uint32_t*>(&h2);
         }
-        const uint32_t dst = xn_s + swz((int)crank, col >> 3, ROWB) + (col & 7) * 2;
+        const uint32_t off = swz(row, col >> 3, ROWB) + (col & 7) * 2;
+        if constexpr (CS > 1) {
 #pragma unroll
-        for (uint32_t r = 0; r < XG; ++r) st_dsmem_v2(dst, r, lo, hi);
+          for (uint32_t r = 0; r < CS; ++r) st_dsmem_v2(xn_s + off, r, lo, hi);
+        } else {
+          *reinterpret_cast<uint2*>(xn + off) = make_uint2(lo, hi);
+        }
       }
     }
   }
   if (dbg) c_st[0] = clock64();
   cp_async_wait<0>();
-  cluster_arrive();
-  cluster_wait();  // all 8 rows of xn are here (pushed by the 8 CTAs), and this CTA's Wq slab has landed
+  if constexpr (CS > 1) {
+    cluster_arrive();
+    cluster_wait();  // all 8 rows of xn are here (pushed by the CS CTAs), and this CTA's Wq slab has landed
+  } else {
+    __syncthreads();
+  }
   if (dbg) c_st[1] = clock64();
 
-  // ---- phase 2: q[8][64] = xn . Wq_head^T, split over K: warp w multiplies k in [w*H/8, (w+1)*H/8) for all 64 features
-  // (every shared-memory operand byte is read exactly once), the 8 partial tiles are summed through the dead xn tile
+  // ---- phase 2: q[8][64] = xn . Wq_head^T; warp w owns output features [8w, 8w + 8)  (splitting K over the warps
+  // instead reads every operand byte once but measured slower: 1.73 us against 1.24 us with its reduction)
   {
-    float acc[8][4];
+    float acc[4][4];
 #pragma unroll
-    for (int i = 0; i < 8; ++i)
+    for (int i = 0; i < 4; ++i)
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
     const int mi = lane >> 3, ri = lane & 7;  // ldmatrix: lane supplies row ri of 8x8 matrix mi (= k chunk kc + mi)
-    constexpr int CPW = ROWB / 16 / 8;        // 16-byte k chunks per warp
-    const uint32_t a_base = xn_s + ri * ROWB, b_base = wbuf_s + ri * ROWB;
-#pragma unroll
-    for (int it = 0; it < CPW / 4; ++it) {  // 32 k per iteration = two k16 steps
-      const int kc = warp * CPW + it * 4;
-      const uint32_t off = (uint32_t)(((kc + mi) ^ ri) << 4);
-      uint32_t a[4];
+    const uint32_t a_base = xn_s + ri * ROWB, b_base = wbuf_s + (warp * 8 + ri) * ROWB;
+#pragma unroll 4
+    for (int kc = 0; kc < ROWB / 16; kc += 8) {  // 64 k per iteration = four k16 steps on four accumulators
+      uint32_t a[4], bq[4], a2[4], bq2[4];
+      const uint32_t off = (uint32_t)(((kc + mi) ^ ri) << 4), off2 = (uint32_t)(((kc + 4 + mi) ^ ri) << 4);
       ldmatrix_x4(a, a_base + off);
-      const uint32_t a0[4] = {a[0], 0u, a[1], 0u}, a1[4] = {a[2], 0u, a[3], 0u};
-#pragma unroll
-      for (int nt = 0; nt < 8; ++nt) {
-        uint32_t bq[4];
-        ldmatrix_x4(bq, b_base + nt * 8 * ROWB + off);
-        mma_bf16(acc[nt], a0, bq[0], bq[1]);
-        mma_bf16(acc[nt], a1, bq[2], bq[3]);
-      }
+      ldmatrix_x4(bq, b_base + off);
+      ldmatrix_x4(a2, a_base + off2);
+      ldmatrix_x4(bq2, b_base + off2);
+      const uint32_t f0[4] = {a[0], 0u, a[1], 0u}, f1[4] = {a[2], 0u, a[3], 0u};
+      const uint32_t f2[4] = {a2[0], 0u, a2[1], 0u}, f3[4] = {a2[2], 0u, a2[3], 0u};
+      mma_bf16(acc[0], f0, bq[0], bq[1]);
+      mma_bf16(acc[1], f1, bq[2], bq[3]);
+      mma_bf16(acc[2], f2, bq2[0], bq2[1]);
+      mma_bf16(acc[3], f3, bq2[2], bq2[3]);
     }
-    __syncthreads();  // every warp is done reading xn (and the Wq slab)
-    float* redq = reinterpret_cast<float*>(xn);  // [8 warps][8 rows][64] fp32 = 16 KB <= 8 * ROWB
     const int g = lane >> 2, t = lane & 3;
-#pragma unroll
-    for (int nt = 0; nt < 8; ++nt)
-      *reinterpret_cast<float2*>(redq + (warp * XG + g) * XD + nt * 8 + 2 * t) = make_float2(acc[nt][0], acc[nt][1]);
-    __syncthreads();
-    for (int i = tid; i < XG * XD; i += XT) {
-      float q = 0.f;
-#pragma unroll
-      for (int w = 0; w < 8; ++w) q += redq[w * XG * XD + i];
-      qs[i] = __bfloat162float(__float2bfloat16_rn(q * p.scale));
-    }
+    const float q0 = (acc[0][0] + acc[1][0]) + (acc[2][0] + acc[3][0]);
+    const float q1 = (acc[0][1] + acc[1][1]) + (acc[2][1] + acc[3][1]);
+    float* qd = qs + g * XD + warp * 8 + 2 * t;
+    qd[0] = __bfloat162float(__float2bfloat16_rn(q0 * p.scale));
+    qd[1] = __bfloat162float(__float2bfloat16_rn(q1 * p.scale));
   }
+  __syncthreads();  // q visible; every warp is done with the Wq slab
+  if (dbg) c_st[2] = clock64();
+
   // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs
   {
     const __nv_bfloat16* src = p.wo + hd * XD;
@@ -295,8 +314,6 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     }
     cp_async_commit();
   }
-  __syncthreads();  // q visible
-  if (dbg) c_st[2] = clock64();
 
   // ---- phase 3: cross-attention of utterance b0 + warp over its S cached keys (4 lanes per key row, 8 rows per pass)
   if (live) {
@@ -482,7 +499,7 @@ static size_t xblock_smem(int H, int S) {
 
 bool xblock_supported(int H, int heads, int d, int S) {
   if (!xblock_enabled()) return false;
-  if (d != XD || heads * d != H || (H != 1024 && H != 1536) || heads % XG != 0 || S < 1) return false;
+  if (d != XD || heads * d != H || (H != 1024 && H != 1536) || heads % 4 != 0 || S < 1) return false;
   return xblock_smem(H, S) <= 227 * 1024;
 }
 
@@ -514,6 +531,13 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
     const char* ev = getenv("PTTS_XB_DBG");
     dbg = ev ? atoi(ev) : 0;
   }
+  // PTTS_XB_CLUSTER = CTAs (heads) that share the fold + LayerNorm of a group: 1, 2 or 4
+  static int cs = -1;
+  if (cs < 0) {
+    const char* ev = getenv("PTTS_XB_CLUSTER");
+    cs = ev ? atoi(ev) : 2;
+    if (cs != 1 && cs != 2 && cs != 4) cs = 2;
+  }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(XT);
@@ -521,11 +545,13 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   cfg.stream = st;
   cudaLaunchAttribute attr[2];
   int na = 0;
-  attr[na].id = cudaLaunchAttributeClusterDimension;
-  attr[na].val.clusterDim.x = XG;
-  attr[na].val.clusterDim.y = 1;
-  attr[na].val.clusterDim.z = 1;
-  ++na;
+  if (cs > 1) {
+    attr[na].id = cudaLaunchAttributeClusterDimension;
+    attr[na].val.clusterDim.x = cs;
+    attr[na].val.clusterDim.y = 1;
+    attr[na].val.clusterDim.z = 1;
+    ++na;
+  }
   if (pdl_enabled()) {
     attr[na].id = cudaLaunchAttributeProgrammaticStreamSerialization;
     attr[na].val.programmaticStreamSerializationAllowed = 1;
@@ -533,22 +559,17 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  cudaError_t e;
-  if (H == 1024) {
-    static size_t configured = 0;
-    if (smem > configured) {
-      cudaFuncSetAttribute(xblock_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      configured = smem;
-    }
-    e = cudaLaunchKernelEx(&cfg, xblock_kernel<8>, p, sc_cap, dbg, tl_next(5));
-  } else {
-    static size_t configured = 0;
-    if (smem > configured) {
-      cudaFuncSetAttribute(xblock_kernel<12>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      configured = smem;
-    }
-    e = cudaLaunchKernelEx(&cfg, xblock_kernel<12>, p, sc_cap, dbg, tl_next(5));
+  using KernelFn = void (*)(const XBlockParams, int, int, TL);
+  KernelFn fn = nullptr;
+  if (H == 1024) fn = cs == 1 ? xblock_kernel<8, 1> : (cs == 2 ? xblock_kernel<8, 2> : xblock_kernel<8, 4>);
+  else fn = cs == 1 ? xblock_kernel<12, 1> : (cs == 2 ? xblock_kernel<12, 2> : xblock_kernel<12, 4>);
+  static size_t configured[2][3] = {{0, 0, 0}, {0, 0, 0}};
+  size_t& conf = configured[H == 1024 ? 0 : 1][cs == 1 ? 0 : (cs == 2 ? 1 : 2)];
+  if (smem > conf) {
+    cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    conf = smem;
   }
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p, sc_cap, dbg, tl_next(5));
   if (e != cudaSuccess) {
     set_error("xblock_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
