@@ -126,10 +126,13 @@ __device__ __forceinline__ void mbar_wait3(uint32_t bar, uint32_t parity) {
   uint32_t done = 0;
   for (uint32_t spin = 0; !done; ++spin) {
     asm volatile(
-        "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+        "{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
         : "=r"(done)
         : "r"(bar), "r"(parity)
         : "memory");
+    // test_wait, not try_wait: a try_wait that finds the phase incomplete suspends the thread for a while - eight
+    // sequential k-block waits cost 4000 cycles that way (measured: X "landed" 5172 instead of 1550 cycles after the
+    // dependency)
     if (spin > 200000000u) __trap();  // a protocol bug must fail loudly, not hang the box
   }
 }
@@ -198,9 +201,14 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
   long long c_w = 0, c_x = 0, c_mma = 0;
   if (tma) {
     if (threadIdx.x == 32) {
-      for (int kb = 0; kb < KB; ++kb) {
-        mbar_expect_tx3(smem_u32(&x_bar[kb]), (uint32_t)XBLK);
-        tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar[kb]), kbeg + kb * KB64, m0);
+      if (dbg & 64) {  // PTTS_GEMM_XBAR=1: one barrier for the whole X slab
+        mbar_expect_tx3(smem_u32(&x_bar[0]), (uint32_t)(KB * XBLK));
+        for (int kb = 0; kb < KB; ++kb) tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar[0]), kbeg + kb * KB64, m0);
+      } else {
+        for (int kb = 0; kb < KB; ++kb) {
+          mbar_expect_tx3(smem_u32(&x_bar[kb]), (uint32_t)XBLK);
+          tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar[kb]), kbeg + kb * KB64, m0);
+        }
       }
     }
   } else {
@@ -226,9 +234,9 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
       if ((dbg & 3) == 3) c_w = clock64();
     }
     for (int kb = 0; kb < KB; ++kb) {
-      if (tma) {
+      if (tma && (kb == 0 || !(dbg & 64))) {
         mbar_wait3(smem_u32(&x_bar[kb]), 0);
-        if ((dbg & 3) == 3 && kb == KB - 1) c_x = clock64();
+        if ((dbg & 3) == 3 && (kb == KB - 1 || (dbg & 64))) c_x = clock64();
         asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
       }
       const uint64_t ad = umma_desc_sw128(sw + kb * WBLK), bd = umma_desc_sw128(sx + kb * XBLK);
@@ -600,7 +608,12 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   memset(&tm_w, 0, sizeof(tm_w));
   memset(&tm_x, 0, sizeof(tm_x));
   const bool tma = use_tma && tensor_map_2d(p.W, p.N, p.K, UM, &tm_w) && tensor_map_2d(p.X, p.M, p.K, UN, &tm_x);
-  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg | (tma ? 32 : 0), hint, tm_w, tm_x,
+  static int xbar = -1;
+  if (xbar < 0) {
+    const char* ev = getenv("PTTS_GEMM_XBAR");
+    xbar = (ev && ev[0] == '1') ? 64 : 0;
+  }
+  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg | (tma ? 32 : 0) | xbar, hint, tm_w, tm_x,
                                      tl_next(10 + EPI));
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
@@ -639,7 +652,7 @@ int umma_plan_splits(int M, int N, int K) {
   static int target = -1;  // PTTS_SPLIT_TARGET: CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold)
   if (target < 0) {
     const char* e = getenv("PTTS_SPLIT_TARGET");
-    target = e ? atoi(e) : 30;
+    target = e ? atoi(e) : 16;  // with TMA slab loads fewer, larger CTAs win: 30 -> 16 measured 1.654 -> 1.559 ms per step
   }
   static int kbmax = -1;  // PTTS_KBMAX: 64-element k-blocks per CTA (8 = 128 KB of W per CTA, 4 = 64 KB)
   if (kbmax < 0) {

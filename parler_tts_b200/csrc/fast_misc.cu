@@ -39,13 +39,16 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   float s = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
-    for (int i0 = 0; i0 < S; i0 += 8) {  // 8 independent loads in flight, summed in split order (deterministic)
-      float4 p[8];
+    // up to 20 independent loads in flight (one L2 round trip for the 4 + 16 slices the fused cross-attention block
+    // leaves behind), summed in split order (deterministic)
+    constexpr int U = 20;
+    for (int i0 = 0; i0 < S; i0 += U) {
+      float4 p[U];
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
+      for (int u = 0; u < U; ++u)
         if (i0 + u < S) p[u] = __ldcg(reinterpret_cast<const float4*>(part + (i0 + u) * part_stride + rin * H + c));
 #pragma unroll
-      for (int u = 0; u < 8; ++u)
+      for (int u = 0; u < U; ++u)
         if (i0 + u < S) { v.x += p[u].x; v.y += p[u].y; v.z += p[u].z; v.w += p[u].w; }
     }
     if (S > 0) *reinterpret_cast<float4*>(hr + c) = v;

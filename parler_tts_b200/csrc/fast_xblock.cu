@@ -361,7 +361,44 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
         }
       }
     };
-    score_batch(rk, 0);
+    {
+      // the first 48 keys on the tensor core: scores[key] = sum_d q[d] K[key][d] as m16n8k16 tiles whose row 0 is the
+      // query and whose 8 columns are the 8 key rows of a pass.  The lane (kg, c4) already holds K[u*8 + kg][c4*16 ..
+      // c4*16 + 15] - exactly a B fragment if the k slots of step kk are mapped to head dims c4*16 + 4kk + {0,1} (b0)
+      // and c4*16 + 4kk + 2 + {0,1} (b1); the A fragment uses the same mapping, so no data moves.
+      uint32_t qa[4][2];
+#pragma unroll
+      for (int kk = 0; kk < 4; ++kk) {
+        const __nv_bfloat162 lo2 = __floats2bfloat162_rn(qv[4 * kk], qv[4 * kk + 1]);      // exact: q is bf16-rounded
+        const __nv_bfloat162 hi2 = __floats2bfloat162_rn(qv[4 * kk + 2], qv[4 * kk + 3]);
+        qa[kk][0] = kg == 0 ? *reinterpret_cast<const uint32_t*>(&lo2) : 0u;
+        qa[kk][1] = kg == 0 ? *reinterpret_cast<const uint32_t*>(&hi2) : 0u;
+      }
+#pragma unroll
+      for (int u = 0; u < UP; ++u) {
+        float c[4] = {0.f, 0.f, 0.f, 0.f};
+        const uint32_t kb0[4] = {rk[u][0].x, rk[u][0].z, rk[u][1].x, rk[u][1].z};
+        const uint32_t kb1[4] = {rk[u][0].y, rk[u][0].w, rk[u][1].y, rk[u][1].w};
+#pragma unroll
+        for (int kk = 0; kk < 4; ++kk) {
+          const uint32_t a[4] = {qa[kk][0], 0u, qa[kk][1], 0u};
+          mma_bf16(c, a, kb0[kk], kb1[kk]);
+        }
+        if (kg == 0) {  // row 0 of the tile: lane c4 holds the scores of keys u*8 + 2*c4 and + 1
+#pragma unroll
+          for (int e = 0; e < 2; ++e) {
+            const int j = u * 8 + 2 * c4 + e;
+            if (j < p.S) {
+              bool keep = true;
+              if (p.key_mask) keep = p.key_mask[(int64_t)bw * p.S + j] != 0;
+              const float sj = keep ? c[e] : neg;
+              scw[j] = sj;
+              lmax = fmaxf(lmax, sj);
+            }
+          }
+        }
+      }
+    }
     for (int j0 = 8 * UP; j0 < p.S; j0 += 8 * UP) {  // descriptions longer than 48 tokens
       uint4 raw[UP][2];
       load_batch(raw, kb, j0);
@@ -405,24 +442,29 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
       load_batch(raw, vb, j0);
       accum_batch(raw, j0);
     }
+    // sum over the 8 key groups of the warp (lane bits 2..4) as a butterfly that halves the values each lane keeps:
+    // 8 + 4 + 2 shuffles instead of 3 x 16, fixed order; the lane ends up with two neighbouring head dims
+    const bool b2 = lane & 4, b3 = lane & 8, b4 = lane & 16;
+    float r8[8], r4[4], r2[2];
 #pragma unroll
-    for (int e = 0; e < 16; ++e) {  // sum over the 8 key groups of the warp (fixed order)
-      acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 4);
-      acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 8);
-      acc[e] += __shfl_xor_sync(0xffffffffu, acc[e], 16);
+    for (int i = 0; i < 8; ++i) {
+      const float send = b2 ? acc[i] : acc[8 + i], keep = b2 ? acc[8 + i] : acc[i];
+      r8[i] = keep + __shfl_xor_sync(0xffffffffu, send, 4);
     }
-    if (kg == 0) {
 #pragma unroll
-      for (int hlf = 0; hlf < 2; ++hlf) {
-        uint4 u;
-        uint32_t* w32 = reinterpret_cast<uint32_t*>(&u);
+    for (int i = 0; i < 4; ++i) {
+      const float send = b3 ? r8[i] : r8[4 + i], keep = b3 ? r8[4 + i] : r8[i];
+      r4[i] = keep + __shfl_xor_sync(0xffffffffu, send, 8);
+    }
 #pragma unroll
-        for (int e = 0; e < 4; ++e) {
-          const __nv_bfloat162 t2 = __floats2bfloat162_rn(acc[hlf * 8 + 2 * e], acc[hlf * 8 + 2 * e + 1]);
-          w32[e] = *reinterpret_cast<const uint32_t*>(&t2);
-        }
-        *reinterpret_cast<uint4*>(at + swz(warp, c4 * 2 + hlf, 128)) = u;
-      }
+    for (int i = 0; i < 2; ++i) {
+      const float send = b4 ? r4[i] : r4[2 + i], keep = b4 ? r4[2 + i] : r4[i];
+      r2[i] = keep + __shfl_xor_sync(0xffffffffu, send, 16);
+    }
+    {
+      const int d0 = c4 * 16 + (b2 ? 8 : 0) + (b3 ? 4 : 0) + (b4 ? 2 : 0);
+      const __nv_bfloat162 t2 = __floats2bfloat162_rn(r2[0], r2[1]);
+      *reinterpret_cast<uint32_t*>(at + swz(warp, d0 >> 3, 128) + (d0 & 7) * 2) = *reinterpret_cast<const uint32_t*>(&t2);
     }
   } else if (lane < 8) {
     *reinterpret_cast<uint4*>(at + swz(warp, lane, 128)) = make_uint4(0u, 0u, 0u, 0u);
