@@ -66,6 +66,7 @@ PROTOTYPES = {
     "ptts_diag_chain": (C.c_int, [c_i32, c_i32, c_i32, c_vp, c_vp]),
     "ptts_diag_gemm_stamps": (C.c_int, [c_vp, c_i32]),
     "ptts_diag_timeline": (C.c_int, [c_i32, c_vp, c_vp, c_i32]),
+    "ptts_diag_xblock": (C.c_int, [c_vp, c_i32]),
     "ptts_build_delay_mask": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "ptts_apply_delay_mask": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
     "ptts_dedelay": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp]),

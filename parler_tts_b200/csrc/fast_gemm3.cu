@@ -522,7 +522,7 @@ struct MapKeyHash {
   }
 };
 // bf16 row-major [rows][cols]; box = 64 columns (128 bytes, SWIZZLE_128B) x box_rows rows; out-of-range rows read as 0
-bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+bool tensor_map_2d_impl(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
   static std::mutex mu;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   EncodeTiledFn fn = encode_tiled_fn();
@@ -607,11 +607,14 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   CUtensorMap tm_w, tm_x;
   memset(&tm_w, 0, sizeof(tm_w));
   memset(&tm_x, 0, sizeof(tm_x));
-  const bool tma = use_tma && tensor_map_2d(p.W, p.N, p.K, UM, &tm_w) && tensor_map_2d(p.X, p.M, p.K, UN, &tm_x);
+  const bool tma = use_tma && tensor_map_2d_impl(p.W, p.N, p.K, UM, &tm_w) && tensor_map_2d_impl(p.X, p.M, p.K, UN, &tm_x);
   static int xbar = -1;
   if (xbar < 0) {
     const char* ev = getenv("PTTS_GEMM_XBAR");
-    xbar = (ev && ev[0] == '1') ? 64 : 0;
+    // one barrier for the whole X slab (default) or one per k-block (PTTS_GEMM_XBAR=0).  Measured on B200: per k-block
+    // the last X block "lands" 5300 cycles after the dependency instead of 1500 (each arrive.expect_tx between two
+    // bulk-tensor issues costs ~500 cycles) - 1.566 against 1.485 ms per decode step
+    xbar = (ev && ev[0] == '0') ? 0 : 64;
   }
   cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg | (tma ? 32 : 0) | xbar, hint, tm_w, tm_x,
                                      tl_next(10 + EPI));
@@ -629,6 +632,9 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
 void gemm_next_trigger_late() { g_late_once = 1; }
 
 namespace gemm {
+bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  return tensor_map_2d_impl(ptr, rows, cols, box_rows, out);
+}
 int umma_read_stamps(unsigned long long* host, int n_launches) {
   if (n_launches == -2) {  // reset the aggregate statistics
     static unsigned long long zero[256 * 8];

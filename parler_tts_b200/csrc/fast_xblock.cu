@@ -90,18 +90,46 @@ __device__ __forceinline__ void st_dsmem_v2(uint32_t local_addr, uint32_t rank, 
 // head needs every row; computed per CTA (CS = 1) the fold costs 2.3 us of L2 bandwidth (128 CTAs x 160 KB), while
 // CS = 8 (one row per CTA) cannot be placed next to the neighbouring kernels' CTAs: measured 12 us between the first
 // and the last CTA passing the dependency wait.
+__device__ __forceinline__ void xb_tma_load_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
+  asm volatile(
+      "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1)
+      : "memory");
+}
+__device__ __forceinline__ void xb_mbar_wait(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > 200000000u) __trap();  // a protocol bug must fail loudly, not hang the box
+  }
+}
+
+// Shared-memory image of both weight slabs = what a SWIZZLE_128B tensor-map copy writes: blocks of [rows][128 bytes]
+// whose 16-byte chunk c of row r sits at chunk position c ^ (r & 7) (base 1024-byte aligned).
+//   Wq head slab: H/64 blocks (one per 64-element k block) of 64 rows   -> block kb at kb * 8 KB
+//   Wo head slab: one block of H rows (the head's 64 input columns)
 template <int HT, int CS>  // H = 128 * HT
-__global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int sc_cap, int dbg, TL tl) {
+__global__ void __launch_bounds__(XT, 1)
+xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__ CUtensorMap tm_wq,
+              const __grid_constant__ CUtensorMap tm_wo, TL tl) {
   constexpr int H = 128 * HT;
   constexpr int ROWB = 2 * H;  // bytes per bf16 row of H
   constexpr int UP = 6;        // key passes (8 keys each) whose K and V rows a warp keeps in registers: 48 keys
-  extern __shared__ __align__(128) unsigned char smraw[];
+  extern __shared__ __align__(128) unsigned char smraw0[];
+  unsigned char* smraw = smraw0 + ((1024u - (smem_u32(smraw0) & 1023u)) & 1023u);  // swizzle atoms: 1024-byte aligned
   unsigned char* wbuf = smraw;                         // Wq head slab [64][H] bf16, later Wo head slab [H][64] bf16
   unsigned char* xn = wbuf + XD * ROWB;                // [8][H] bf16 (swizzled); later the q split-K reduction tile
   float* qs = reinterpret_cast<float*>(xn + XG * ROWB);  // [8][64] scaled q (rounded to bf16 like the q buffer)
   unsigned char* at = reinterpret_cast<unsigned char*>(qs + XG * XD);  // [8][64] bf16 attention output (swizzled)
   float* sc = reinterpret_cast<float*>(at + XG * XD * 2);              // [8][sc_cap] scores -> probabilities
+  float* gb = sc + XG * sc_cap;                        // [2][H] gamma | beta (only when H <= 1024: shared-memory budget)
+  constexpr bool kStageGB = HT <= 8;
   __shared__ float red[16];
+  __shared__ __align__(8) uint64_t wq_bar, wo_bar;
   const int hd = blockIdx.x, b0 = blockIdx.y * XG;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int nrows = min(XG, p.B - b0);
@@ -112,12 +140,19 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
 
   // ---- before the dependency: everything below only touches immutable data (weights, the cross cache, cache rows of
   // the next self-attention launch that are older than this step)
-  {
-    const __nv_bfloat16* src = p.wq + (int64_t)hd * XD * H;
-    constexpr int CPR = ROWB / 16;  // chunks per row
-    for (int i = tid; i < XD * CPR; i += XT) {
-      const int r = i / CPR, c = i % CPR;
-      cp_async16(wbuf_s + swz(r, c, ROWB), src + (int64_t)r * H + c * 8, true);
+  if (tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&wq_bar)), "r"(1) : "memory");
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&wo_bar)), "r"(1) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+    // the head's 64 rows of Wq as H/64 box copies (64 rows x 128 bytes each) - one thread, the TMA engine does the rest
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(&wq_bar)), "r"(XD * ROWB) : "memory");
+    for (int kb = 0; kb < H / 64; ++kb) xb_tma_load_2d(wbuf_s + kb * 8192, &tm_wq, smem_u32(&wq_bar), kb * 64, hd * XD);
+  }
+  if constexpr (kStageGB) {  // gamma / beta are immutable: stage them now, the normalise step reads shared memory
+    for (int i = tid; i < H / 4; i += XT) {
+      cp_async16(smem_u32(gb) + i * 16, p.gamma + i * 4, true);
+      cp_async16(smem_u32(gb + H) + i * 16, p.beta + i * 4, true);
     }
     cp_async_commit();
   }
@@ -163,6 +198,8 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     for (int64_t o = (int64_t)lane * 8192; o < bytes; o += 32 * 8192)
       l2_prefetch_bulk(src + o, (uint32_t)min((int64_t)8192, bytes - o));
   }
+  if constexpr (kStageGB) cp_async_wait<0>();
+  __syncthreads();  // gamma / beta staged; the barrier initialisations are visible to every thread
   pdl_wait();
   tl_dep(tl);
   const long long c_dep = dbg ? clock64() : 0;
@@ -243,8 +280,8 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
         const int col = c4i * 4;
         uint32_t lo = 0u, hi = 0u;
         if (mine) {
-          const float4 g = __ldg(reinterpret_cast<const float4*>(p.gamma + col));
-          const float4 be = __ldg(reinterpret_cast<const float4*>(p.beta + col));
+          const float4 g = kStageGB ? *reinterpret_cast<const float4*>(gb + col) : __ldg(reinterpret_cast<const float4*>(p.gamma + col));
+          const float4 be = kStageGB ? *reinterpret_cast<const float4*>(gb + H + col) : __ldg(reinterpret_cast<const float4*>(p.beta + col));
           const __nv_bfloat162 l2 = __floats2bfloat162_rn((v[i].x - mean) * rstd * g.x + be.x, (v[i].y - mean) * rstd * g.y + be.y);
           const __nv_bfloat162 h2 = __floats2bfloat162_rn((v[i].z - mean) * rstd * g.z + be.z, (v[i].w - mean) * rstd * g.w + be.w);
           lo = *reinterpret_cast<const uint32_t*>(&l2);
@@ -261,7 +298,7 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     }
   }
   if (dbg) c_st[0] = clock64();
-  cp_async_wait<0>();
+  xb_mbar_wait(smem_u32(&wq_bar), 0);  // the Wq slab has landed (async proxy -> visible after the barrier wait)
   if constexpr (CS > 1) {
     cluster_arrive();
     cluster_wait();  // all 8 rows of xn are here (pushed by the CS CTAs), and this CTA's Wq slab has landed
@@ -279,15 +316,16 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
 #pragma unroll
       for (int j = 0; j < 4; ++j) acc[i][j] = 0.f;
     const int mi = lane >> 3, ri = lane & 7;  // ldmatrix: lane supplies row ri of 8x8 matrix mi (= k chunk kc + mi)
-    const uint32_t a_base = xn_s + ri * ROWB, b_base = wbuf_s + (warp * 8 + ri) * ROWB;
+    const uint32_t a_base = xn_s + ri * ROWB, b_base = wbuf_s + (warp * 8 + ri) * 128;
 #pragma unroll 4
-    for (int kc = 0; kc < ROWB / 16; kc += 8) {  // 64 k per iteration = four k16 steps on four accumulators
+    for (int kc = 0; kc < ROWB / 16; kc += 8) {  // 64 k per iteration (= one 8 KB block of the slab): four k16 steps
       uint32_t a[4], bq[4], a2[4], bq2[4];
       const uint32_t off = (uint32_t)(((kc + mi) ^ ri) << 4), off2 = (uint32_t)(((kc + 4 + mi) ^ ri) << 4);
+      const uint32_t bb = b_base + (kc >> 3) * 8192;
       ldmatrix_x4(a, a_base + off);
-      ldmatrix_x4(bq, b_base + off);
+      ldmatrix_x4(bq, bb + ((mi ^ ri) << 4));
       ldmatrix_x4(a2, a_base + off2);
-      ldmatrix_x4(bq2, b_base + off2);
+      ldmatrix_x4(bq2, bb + (((4 + mi) ^ ri) << 4));
       const uint32_t f0[4] = {a[0], 0u, a[1], 0u}, f1[4] = {a[2], 0u, a[3], 0u};
       const uint32_t f2[4] = {a2[0], 0u, a2[1], 0u}, f3[4] = {a2[2], 0u, a2[3], 0u};
       mma_bf16(acc[0], f0, bq[0], bq[1]);
@@ -305,14 +343,11 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
   __syncthreads();  // q visible; every warp is done with the Wq slab
   if (dbg) c_st[2] = clock64();
 
-  // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs
-  {
-    const __nv_bfloat16* src = p.wo + hd * XD;
-    for (int i = tid; i < H * 8; i += XT) {
-      const int r = i >> 3, c = i & 7;
-      cp_async16(wbuf_s + swz(r, c, 128), src + (int64_t)r * H + c * 8, true);
-    }
-    cp_async_commit();
+  // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs: H/256 box copies
+  if (tid == 0) {
+    asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // generic-proxy reads of the Wq slab are done
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(&wo_bar)), "r"(H * 128) : "memory");
+    for (int nb = 0; nb < H / 256; ++nb) xb_tma_load_2d(wbuf_s + nb * 32768, &tm_wo, smem_u32(&wo_bar), hd * XD, nb * 256);
   }
 
   // ---- phase 3: cross-attention of utterance b0 + warp over its S cached keys (4 lanes per key row, 8 rows per pass)
@@ -470,7 +505,7 @@ __global__ void __launch_bounds__(XT, 1) xblock_kernel(const XBlockParams p, int
     *reinterpret_cast<uint4*>(at + swz(warp, lane, 128)) = make_uint4(0u, 0u, 0u, 0u);
   }
   if (dbg) c_st[3] = clock64();
-  cp_async_wait<0>();
+  xb_mbar_wait(smem_u32(&wo_bar), 0);
   __syncthreads();  // attention tile complete, the Wo slab has landed
   if (dbg) c_st[4] = clock64();
 
@@ -535,8 +570,8 @@ bool xblock_enabled() {
 
 static size_t xblock_smem(int H, int S) {
   const int sc_cap = (S + 7) / 8 * 8;
-  return (size_t)XD * 2 * H + (size_t)XG * 2 * H + sizeof(float) * XG * XD + (size_t)XG * XD * 2 +
-         sizeof(float) * XG * sc_cap;
+  return 1024 + (size_t)XD * 2 * H + (size_t)XG * 2 * H + sizeof(float) * XG * XD + (size_t)XG * XD * 2 +
+         sizeof(float) * XG * sc_cap + (H <= 1024 ? sizeof(float) * 2 * H : 0);
 }
 
 bool xblock_supported(int H, int heads, int d, int S) {
@@ -577,8 +612,8 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   static int cs = -1;
   if (cs < 0) {
     const char* ev = getenv("PTTS_XB_CLUSTER");
-    cs = ev ? atoi(ev) : 2;
-    if (cs != 1 && cs != 2 && cs != 4) cs = 2;
+    cs = ev ? atoi(ev) : 1;  // measured (B=64, 860 frames): 1 -> 1.566, 2 -> 1.577, 4 -> 1.697 ms per decode step
+    if (cs != 1 && cs != 2 && cs != 4) cs = 1;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
@@ -601,7 +636,12 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   }
   cfg.attrs = attr;
   cfg.numAttrs = na;
-  using KernelFn = void (*)(const XBlockParams, int, int, TL);
+  CUtensorMap tm_wq, tm_wo;
+  if (!gemm::tensor_map_2d(wq, H, H, XD, &tm_wq) || !gemm::tensor_map_2d(wo, H, H, 256, &tm_wo)) {
+    set_error("xblock_fast: no tensor map (driver entry point missing or misaligned weights)");
+    return PTTS_E_UNSUPPORTED;
+  }
+  using KernelFn = void (*)(const XBlockParams, int, int, const CUtensorMap, const CUtensorMap, TL);
   KernelFn fn = nullptr;
   if (H == 1024) fn = cs == 1 ? xblock_kernel<8, 1> : (cs == 2 ? xblock_kernel<8, 2> : xblock_kernel<8, 4>);
   else fn = cs == 1 ? xblock_kernel<12, 1> : (cs == 2 ? xblock_kernel<12, 2> : xblock_kernel<12, 4>);
@@ -611,7 +651,7 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     conf = smem;
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p, sc_cap, dbg, tl_next(5));
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p, sc_cap, dbg, tm_wq, tm_wo, tl_next(5));
   if (e != cudaSuccess) {
     set_error("xblock_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;

@@ -1,6 +1,8 @@
 // Shared pieces of the bf16 GEMM kernels of the fast family (fast_gemm.cu: pipelined kernel, fast_gemm2.cu: cluster
 // split-K kernel): parameter block, cp.async / ldmatrix / mma.sync wrappers, swizzled tile loader, fused epilogues.
 #pragma once
+#include <cuda.h>
+
 #include "ops.cuh"
 
 namespace ptts {
@@ -89,6 +91,10 @@ __device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g
     cp_async16(sbase + r * 256 + ((c ^ (r & 7)) << 4), src, ok);
   }
 }
+
+// Cached tensor map (fast_gemm3.cu) of a bf16 row-major matrix [rows][cols]: box = 64 columns (128 bytes, SWIZZLE_128B)
+// x box_rows rows, out-of-range rows read as 0.  false: no driver entry point / misaligned matrix.
+bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
 
 // cluster split-K kernel (fast_gemm2.cu); PTTS_E_UNSUPPORTED when the shape does not fit it
 int cluster_gemm_store(const GemmParams& p, cudaStream_t st);

@@ -42,16 +42,18 @@ nz = np.where(a[:, 4] > 0)[0]
 start = [i for i in nz if a[(i - 1) & 255, 4] == 0]
 start = start[0] if start else nz[0]
 order = [(start + i) & 255 for i in range(256) if a[(start + i) & 255, 4] > 0]
-names = ["qkv", "out_proj", "q_cross", "out_cross", "fc1", "fc2"]
+# 6 split-K GEMMs per layer on the unfused chain, 4 when the cross-attention block is one launch (fast_xblock.cu)
+per_layer = 4 if (len(order) - 1) % 24 == 0 and (len(order) - 1) // 24 == 4 else 6
+names = ["qkv", "out_proj", "fc1", "fc2"] if per_layer == 4 else ["qkv", "out_proj", "q_cross", "out_cross", "fc1", "fc2"]
 print(f"context ~{P + N}; {len(order)} GEMM launches per step; cycles after the CTA's dependency wait (mean | max)")
 rows = np.array([[a[i, 0] / a[i, 4], a[i, 1] / a[i, 4], a[i, 2] / a[i, 4], a[i, 3] / a[i, 4], a[i, 4] / 8, a[i, 5],
                   a[i, 7], a[i, 6]] for i in order])
 for j, nm in enumerate(names):
-    r = rows[j:144:6]
+    r = rows[j:24 * per_layer:per_layer]
     m = np.median(r, axis=0)
     print(f"{nm:10s} CTAs {int(m[4]):4d} | mean: W landed {int(m[0]):6d}  X landed {int(m[1]):6d}  MMA done {int(m[2]):6d}  "
           f"end {int(m[3]):6d} | max: W {int(m[5]):6d}  X {int(m[6]):6d}  end {int(m[7]):6d}")
-if len(order) > 144:
-    r = rows[144]
+if len(order) > 24 * per_layer:
+    r = rows[24 * per_layer]
     print(f"{'heads':10s} CTAs {int(r[4]):4d} | mean: W landed {int(r[0]):6d}  X landed {int(r[1]):6d}  MMA done {int(r[2]):6d}  "
           f"end {int(r[3]):6d} | max: W {int(r[5]):6d}  X {int(r[6]):6d}  end {int(r[7]):6d}")

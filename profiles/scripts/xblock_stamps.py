@@ -31,7 +31,6 @@ eng.prefill(st, model.prompt_table(), prompt)
 eng.run_loop(st, use_graph=True, poll_every=64, max_steps=N)
 torch.cuda.synchronize()
 lib = cabi.load()
-lib.ptts_diag_xblock.argtypes = [C.c_void_p, C.c_int32]
 lib.ptts_diag_xblock(None, 1)
 for _ in range(10):
     st.graph.replay()
