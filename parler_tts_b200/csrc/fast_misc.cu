@@ -3,6 +3,8 @@
 //   y[row]  = LN(h[row]) * gamma + beta   (nn.LayerNorm eps 1e-5, /root/reference/parler_tts/modeling_parler_tts.py:446,467,487,959)
 // One CTA per row, the row stays in shared memory between the mean / variance / normalise passes (two-pass variance
 // like the simple family, so fp32 results agree to rounding).
+#include <stdlib.h>
+
 #include "ops.cuh"
 
 namespace ptts {
@@ -13,7 +15,7 @@ template <typename TY>
 __global__ void __launch_bounds__(256)
 ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
                  const float* __restrict__ g, const float* __restrict__ bta, int H, float eps, int row_mul, int row_add,
-                 TY* __restrict__ y, const L2Hint hint, TL tl) {
+                 TY* __restrict__ y, const L2Hint hint, int early, TL tl) {
   extern __shared__ float buf[];  // [H]
   __shared__ float red[8], red2[8];
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
@@ -22,8 +24,9 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   tl_start(tl);
   // Trigger BEFORE waiting: the consumer of a LayerNorm is always a GEMM whose pre-wait section only prefetches
   // immutable weights, so it may become resident (and pull its W slab from HBM) while the kernel before this one is
-  // still running; its own griddepcontrol.wait still orders it after this grid.
-  pdl_launch();
+  // still running; its own griddepcontrol.wait still orders it after this grid.  (early = 0: release after the wait -
+  // with TMA slab loads the consumer needs ~1.5 us of lead, and its burst no longer collides with this kernel's loads.)
+  if (early) pdl_launch();
   float4 gg4[4], bb4[4];  // gamma / beta are immutable too: fetch them while the producer finishes
 #pragma unroll
   for (int i = 0; i < 4; ++i) {
@@ -35,6 +38,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   }
   l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
   pdl_wait();
+  if (!early) pdl_launch();
   tl_dep(tl);
   float s = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
@@ -103,13 +107,18 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   if (rows == 0) return PTTS_OK;
   const size_t smem = sizeof(float) * (size_t)H;
   const L2Hint hint = take_l2_hint();
+  static int early = -1;
+  if (early < 0) {
+    const char* ev = getenv("PTTS_LN_EARLY");
+    early = (ev && ev[0] == '0') ? 0 : 1;
+  }
   cudaError_t e;
   if (ydtype == PTTS_F32)
     e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H, eps,
-                 row_mul, row_add, (float*)y, hint, tl_next(1));
+                 row_mul, row_add, (float*)y, hint, early, tl_next(1));
   else
     e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H,
-                 eps, row_mul, row_add, (__nv_bfloat16*)y, hint, tl_next(1));
+                 eps, row_mul, row_add, (__nv_bfloat16*)y, hint, early, tl_next(1));
   if (e != cudaSuccess) {
     set_error("layernorm_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
@@ -122,11 +131,12 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
 // slice order, deterministic).  One float4 column group per thread; all S loads of a thread are in flight together.
 __global__ void __launch_bounds__(256)
 partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, int64_t n4, int act,
-                   __nv_bfloat16* __restrict__ y, const L2Hint hint, TL tl) {
+                   __nv_bfloat16* __restrict__ y, const L2Hint hint, int early, TL tl) {
   tl_start(tl);
-  pdl_launch();  // before the wait: the consumer (fc2 GEMM) only prefetches immutable weights ahead of its own wait
+  if (early) pdl_launch();  // before the wait: the consumer (fc2 GEMM) only prefetches immutable weights ahead of its own wait
   l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
   pdl_wait();
+  if (!early) pdl_launch();
   tl_dep(tl);
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i < n4) {
@@ -157,8 +167,13 @@ int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, in
   PTTS_CHECK_ARG(part && y && S >= 1 && N % 4 == 0 && part_stride % 4 == 0, "partial_act_fast: bad arguments");
   const int64_t n4 = (int64_t)rows * N / 4;
   if (n4 == 0) return PTTS_OK;
+  static int early = -1;
+  if (early < 0) {
+    const char* ev = getenv("PTTS_ACT_EARLY");
+    early = (ev && ev[0] == '0') ? 0 : 1;
+  }
   cudaError_t e = launch_k(partial_act_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,
-                           part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), tl_next(4));
+                           part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), early, tl_next(4));
   if (e != cudaSuccess) {
     set_error("partial_act_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;

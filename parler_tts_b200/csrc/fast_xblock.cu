@@ -156,7 +156,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
     }
     cp_async_commit();
   }
-  pdl_launch();
+  if (!(dbg & 2)) pdl_launch();  // PTTS_XB_EARLY=0 (dbg bit 1): release the next LayerNorm only after the wait
   // K and V rows of utterance b0 + warp for this head travel into registers now (4 lanes per 128-byte row, 8 rows per
   // pass): by the time q exists they have long landed, and the attention phase is pure arithmetic
   const int kg = lane >> 2, c4 = lane & 3;
@@ -201,8 +201,9 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
   if constexpr (kStageGB) cp_async_wait<0>();
   __syncthreads();  // gamma / beta staged; the barrier initialisations are visible to every thread
   pdl_wait();
+  if (dbg & 2) pdl_launch();
   tl_dep(tl);
-  const long long c_dep = dbg ? clock64() : 0;
+  const long long c_dep = (dbg & 1) ? clock64() : 0;
   long long c_st[5] = {0, 0, 0, 0, 0};
 
   // ---- phase 1: fold + LayerNorm; team `team` (TS = 32*CS threads) of this CTA owns row crank*RP + team of the group
@@ -297,7 +298,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
       }
     }
   }
-  if (dbg) c_st[0] = clock64();
+  if (dbg & 1) c_st[0] = clock64();
   xb_mbar_wait(smem_u32(&wq_bar), 0);  // the Wq slab has landed (async proxy -> visible after the barrier wait)
   if constexpr (CS > 1) {
     cluster_arrive();
@@ -305,7 +306,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
   } else {
     __syncthreads();
   }
-  if (dbg) c_st[1] = clock64();
+  if (dbg & 1) c_st[1] = clock64();
 
   // ---- phase 2: q[8][64] = xn . Wq_head^T; warp w owns output features [8w, 8w + 8)  (splitting K over the warps
   // instead reads every operand byte once but measured slower: 1.73 us against 1.24 us with its reduction)
@@ -341,7 +342,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
     qd[1] = __bfloat162float(__float2bfloat16_rn(q1 * p.scale));
   }
   __syncthreads();  // q visible; every warp is done with the Wq slab
-  if (dbg) c_st[2] = clock64();
+  if (dbg & 1) c_st[2] = clock64();
 
   // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs: H/256 box copies
   if (tid == 0) {
@@ -504,10 +505,10 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
   } else if (lane < 8) {
     *reinterpret_cast<uint4*>(at + swz(warp, lane, 128)) = make_uint4(0u, 0u, 0u, 0u);
   }
-  if (dbg) c_st[3] = clock64();
+  if (dbg & 1) c_st[3] = clock64();
   xb_mbar_wait(smem_u32(&wo_bar), 0);
   __syncthreads();  // attention tile complete, the Wo slab has landed
-  if (dbg) c_st[4] = clock64();
+  if (dbg & 1) c_st[4] = clock64();
 
   // ---- phase 4: part_out[head][b][n] = a[b][0:64] . Wo[n][head*64 : head*64+64]; warp w owns n in [w*H/8, (w+1)*H/8)
   {
@@ -535,7 +536,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
       if (g < nrows) *reinterpret_cast<float2*>(orow + n0) = make_float2(c[0] + d[0], c[1] + d[1]);
     }
   }
-  if (dbg && tid == 0) {
+  if ((dbg & 1) && tid == 0) {
     const long long c_end = clock64();
 #pragma unroll
     for (int i = 0; i < 5; ++i) atomicAdd(g_xb_agg + i, (unsigned long long)(c_st[i] - c_dep));
@@ -606,7 +607,9 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   static int dbg = -1;
   if (dbg < 0) {
     const char* ev = getenv("PTTS_XB_DBG");
-    dbg = ev ? atoi(ev) : 0;
+    dbg = ev ? (atoi(ev) & 1) : 0;
+    const char* xe = getenv("PTTS_XB_EARLY");
+    if (xe && xe[0] == '0') dbg |= 2;
   }
   // PTTS_XB_CLUSTER = CTAs (heads) that share the fold + LayerNorm of a group: 1, 2 or 4
   static int cs = -1;
