@@ -589,8 +589,10 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   }
   static int early = -1;
   if (early < 0) {
-    const char* ev = getenv("PTTS_PDL_EARLY");  // measured: 1.727 ms per decode step against 1.748 ms -> default on
-    early = (ev && ev[0] == '0') ? 0 : 16;
+    // with cp.async slabs the early release won (1.727 against 1.748 ms per decode step); with TMA slabs the slab needs
+    // ~1.5 us of lead only and the late release wins (1.486 against 1.496 ms) -> default late, PTTS_PDL_EARLY=1: early
+    const char* ev = getenv("PTTS_PDL_EARLY");
+    early = (ev && ev[0] == '1') ? 16 : 0;
   }
   int early_now = early;
   if (EPI == EPI_PARTIAL && g_late_once) {

@@ -109,8 +109,10 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   const L2Hint hint = take_l2_hint();
   static int early = -1;
   if (early < 0) {
+    // measured on B200 (B=64, 860 frames, TMA GEMMs): early 1.496, late 1.481 ms per decode step; together with the late
+    // cross-attention block 1.427 -> default late (PTTS_LN_EARLY=1: before the wait)
     const char* ev = getenv("PTTS_LN_EARLY");
-    early = (ev && ev[0] == '0') ? 0 : 1;
+    early = (ev && ev[0] == '1') ? 1 : 0;
   }
   cudaError_t e;
   if (ydtype == PTTS_F32)
@@ -169,7 +171,7 @@ int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, in
   if (n4 == 0) return PTTS_OK;
   static int early = -1;
   if (early < 0) {
-    const char* ev = getenv("PTTS_ACT_EARLY");
+    const char* ev = getenv("PTTS_ACT_EARLY");  // measured: early 1.496, late 1.522 ms per decode step -> early
     early = (ev && ev[0] == '0') ? 0 : 1;
   }
   cudaError_t e = launch_k(partial_act_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,

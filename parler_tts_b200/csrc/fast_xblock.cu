@@ -608,15 +608,18 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   if (dbg < 0) {
     const char* ev = getenv("PTTS_XB_DBG");
     dbg = ev ? (atoi(ev) & 1) : 0;
+    // release the next LayerNorm before (PTTS_XB_EARLY=1) or after the own wait: measured 1.496 against 1.451 ms per
+    // decode step - released early, the LayerNorm releases fc1 in turn, whose TMA slab burst lands on this kernel
     const char* xe = getenv("PTTS_XB_EARLY");
-    if (xe && xe[0] == '0') dbg |= 2;
+    if (!(xe && xe[0] == '1')) dbg |= 2;
   }
   // PTTS_XB_CLUSTER = CTAs (heads) that share the fold + LayerNorm of a group: 1, 2 or 4
   static int cs = -1;
   if (cs < 0) {
     const char* ev = getenv("PTTS_XB_CLUSTER");
-    cs = ev ? atoi(ev) : 1;  // measured (B=64, 860 frames): 1 -> 1.566, 2 -> 1.577, 4 -> 1.697 ms per decode step
-    if (cs != 1 && cs != 2 && cs != 4) cs = 1;
+    cs = ev ? atoi(ev) : 2;  // measured (B=64, 860 frames, TMA slabs): 1 -> 1.497, 2 -> 1.471 ms per decode step; 4 was
+                             // 0.13 ms behind 2 with the cp.async slabs, 8 cannot be placed (12 us dep-spread)
+    if (cs != 1 && cs != 2 && cs != 4) cs = 2;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
