@@ -243,14 +243,15 @@ self_attention_done:
     const bool cross = s->S > 0;
     // In front of the fused cross-attention block the out_proj GEMM releases its dependent only AFTER its own wait:
     // released early, the block's CTAs become resident under the self-attention kernel and their pre-wait traffic
-    // (128 KB of Wq per SM, cross K/V and next-layer K prefetches) competes with the K/V stream (PTTS_XB_LATE=0: early)
+    // (128 KB of Wq per SM, cross K/V and next-layer K prefetches) competes with the K/V stream (PTTS_XB_LATE=0: early,
+    // 2: only when the out_proj's MMA burst is done)
     static int xb_late = -1;
     if (xb_late < 0) {
       const char* e = getenv("PTTS_XB_LATE");
-      xb_late = (e && e[0] == '0') ? 0 : 1;
+      xb_late = e ? atoi(e) : 1;
     }
     if (xb_late && cross && fuse && path.ln && dt == PTTS_BF16 && xblock_supported(H, heads, d, s->S))
-      gemm_next_trigger_late();
+      gemm_next_trigger_late(xb_late == 2);
     PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, fuse ? (cross ? L.ln2_g : L.ln3_g) : nullptr,
                                            fuse ? (cross ? L.ln2_b : L.ln3_b) : nullptr, st));
   }

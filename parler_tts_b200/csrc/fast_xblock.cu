@@ -617,9 +617,9 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   static int cs = -1;
   if (cs < 0) {
     const char* ev = getenv("PTTS_XB_CLUSTER");
-    cs = ev ? atoi(ev) : 2;  // measured (B=64, 860 frames, TMA slabs): 1 -> 1.497, 2 -> 1.471 ms per decode step; 4 was
-                             // 0.13 ms behind 2 with the cp.async slabs, 8 cannot be placed (12 us dep-spread)
-    if (cs != 1 && cs != 2 && cs != 4) cs = 2;
+    cs = ev ? atoi(ev) : 1;  // measured (B=64, 860 frames, TMA slabs, late releases): 1 -> 1.421, 2 -> 1.436 ms per decode
+                             // step; 4 was 0.13 ms behind 2 with the cp.async slabs, 8 cannot be placed (12 us dep-spread)
+    if (cs != 1 && cs != 2 && cs != 4) cs = 1;
   }
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;

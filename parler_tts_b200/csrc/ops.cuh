@@ -33,8 +33,9 @@ int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
 namespace gemm { struct GemmFinish; }
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
                       cudaStream_t st, const gemm::GemmFinish* fin = nullptr);
-// the next gemm_bf16_partial launch releases its dependent kernel only AFTER its own dependency wait (default: before)
-void gemm_next_trigger_late();
+// the next gemm_bf16_partial launch releases its dependent kernel AFTER its own dependency wait whatever PTTS_PDL_EARLY
+// says, or (at_mma_done) only when its MMA burst has completed
+void gemm_next_trigger_late(int at_mma_done);
 bool fast_layernorm_supported(int H);
 // y = act(sum of S split-K partial slices) as bf16 (fast_misc.cu)
 int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, int N, int act, void* y,
