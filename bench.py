@@ -268,10 +268,10 @@ def run_cuda(args):
     step_gbs = step_bytes / (ms_decode * 1e-3) / 1e9
     # dram__bytes_read.sum + dram__bytes_write.sum per launch of this kernel at exactly these arguments, from the
     # committed `ncu --set full` capture profiles/r01_ncu_attn_full_v6.csv (122.31 MB read + 3.68 MB written)
-    traffic = 125996117 if (B, N, es, heads) == (64, 860, 2, 16) and impl == cabi.IMPL_FAST else None
+    traffic = 127686656 if (B, N, es, heads) == (64, 860, 2, 16) and impl == cabi.IMPL_FAST else None
     roofline = {"bound": "hbm", "kernel": "self-attention decode (ptts_attention, ctx=%d)" % ctx, "achieved": achieved,
                 "peak": peak, "unit": "GB/s", "frac": achieved / peak, "traffic": traffic,
-                "traffic_source": "profiles/r01_ncu_attn_full_v6.csv (ncu --set full, mean of 3 launches)",
+                "traffic_source": "profiles/r01_ncu_attn_full_v8.csv (ncu --set full, mean of 3 launches)",
                 "peak_source": peak_src,
                 "algorithmic_bytes_per_launch": attn_bytes, "ms_per_launch": attn_ms,
                 "whole_step": {"algorithmic_bytes": step_bytes, "ms": ms_decode, "achieved": step_gbs,
