@@ -73,6 +73,8 @@ struct Pending {
   int S = 0;
   int64_t stride = 0;
   const float* ln_done = nullptr;  // gamma of the LayerNorm the producing GEMM's finisher has already applied
+  const float* rowblk = nullptr;   // further slices stored row-contiguously [rows][n_blk][H] (cross-attention block)
+  int n_blk = 0;
 };
 
 struct Path {
@@ -99,8 +101,9 @@ static int ln_step(const PttsModel* m, const PttsState* s, const Path& path, Pen
     return PTTS_OK;
   }
   if (path.ln) {
+    PTTS_CHECK_ARG(!pend.rowblk || (row_mul == 1 && row_add == 0), "internal: row block with a row map");
     PTTS_TRY(layernorm_fast(s->h, pend.part, pend.S, pend.stride, g, b, rows_out, H, 1e-5f, row_mul, row_add, s->xn,
-                            m->wdtype, st));
+                            m->wdtype, st, pend.rowblk, pend.n_blk));
     pend = Pending();
     return PTTS_OK;
   }
@@ -270,9 +273,22 @@ self_attention_done:
                                 : nullptr;
       float* xout = work_area(m, s) + (int64_t)pend.S * pend.stride;
       if (wpf_mask() & 4) set_l2_hint(L.w_fc1, (long long)F * H * es);  // fc1 is two launches ahead
+      // PTTS_XB_ROWOUT=0: per-head slices [heads][B][H] folded with strided loads; default: [B][heads][H], which the
+      // next LayerNorm pulls in with one bulk copy per row
+      static int rowout = -1;
+      if (rowout < 0) {
+        const char* e = getenv("PTTS_XB_ROWOUT");
+        rowout = (e && e[0] == '0') ? 0 : 1;
+      }
+      const int by_row = rowout && (int64_t)heads * H * 4 <= 160 * 1024;
       PTTS_TRY(xblock_fast(s->h, pend.part, pend.S, pend.stride, L.ln2_g, L.ln2_b, 1e-5f, L.w_qc, L.w_oc, kc, vc,
-                           s->enc_mask, B, heads, H, s->S, scale, xout, ks_next, s->c_max, ctx_base, ctx_dyn, st));
-      pend.S += heads;
+                           s->enc_mask, B, heads, H, s->S, scale, xout, by_row, ks_next, s->c_max, ctx_base, ctx_dyn, st));
+      if (by_row) {
+        pend.rowblk = xout;
+        pend.n_blk = heads;
+      } else {
+        pend.S += heads;
+      }
       goto cross_attention_done;
     }
     PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));

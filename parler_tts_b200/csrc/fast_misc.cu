@@ -11,13 +11,18 @@ namespace ptts {
 
 namespace {
 
+// rowblk (optional): n_blk further slices stored ROW-contiguously, [row][n_blk][H] (what the fused cross-attention block
+// writes): the 64 KB of a row arrive as ONE bulk copy (cp.async.bulk, TMA engine) into shared memory instead of 4 096
+// 16-byte LSU requests, and are folded from there after the strided slices, in slice order.
 template <typename TY>
 __global__ void __launch_bounds__(256)
 ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
-                 const float* __restrict__ g, const float* __restrict__ bta, int H, float eps, int row_mul, int row_add,
-                 TY* __restrict__ y, const L2Hint hint, int early, TL tl) {
-  extern __shared__ float buf[];  // [H]
+                 const float* __restrict__ rowblk, int n_blk, const float* __restrict__ g,
+                 const float* __restrict__ bta, int H, float eps, int row_mul, int row_add, TY* __restrict__ y,
+                 const L2Hint hint, int early, TL tl) {
+  extern __shared__ __align__(128) float buf[];  // [H] row | [n_blk][H] bulk-copied slices
   __shared__ float red[8], red2[8];
+  __shared__ __align__(8) uint64_t blk_bar;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
   const int64_t rin = (int64_t)blockIdx.x * row_mul + row_add;
   float* hr = h + rin * H;
@@ -37,9 +42,24 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
     }
   }
   l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
+  const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&blk_bar);
+  if (rowblk && tid == 0) {
+    asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(1) : "memory");
+    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+  }
+  if (rowblk) __syncthreads();
   pdl_wait();
   if (!early) pdl_launch();
   tl_dep(tl);
+  float* blk = buf + H;
+  if (rowblk && tid == 0) {
+    const uint32_t bytes = (uint32_t)n_blk * (uint32_t)H * 4u;
+    asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
+    asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(
+                     (uint32_t)__cvta_generic_to_shared(blk)),
+                 "l"(rowblk + rin * (int64_t)n_blk * H), "r"(bytes), "r"(bar)
+                 : "memory");
+  }
   float s = 0.f;
   for (int c = tid * 4; c < H; c += 256 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
@@ -55,7 +75,22 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
       for (int u = 0; u < U; ++u)
         if (i0 + u < S) { v.x += p[u].x; v.y += p[u].y; v.z += p[u].z; v.w += p[u].w; }
     }
-    if (S > 0) *reinterpret_cast<float4*>(hr + c) = v;
+    if (rowblk) {
+      uint32_t done = 0;
+      for (uint32_t spin = 0; !done; ++spin) {
+        asm volatile(
+            "{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+            : "=r"(done)
+            : "r"(bar), "r"(0)
+            : "memory");
+        if (spin > 200000000u) __trap();
+      }
+      for (int k = 0; k < n_blk; ++k) {
+        const float4 t = *reinterpret_cast<const float4*>(blk + (size_t)k * H + c);
+        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+      }
+    }
+    if (S > 0 || rowblk) *reinterpret_cast<float4*>(hr + c) = v;
     *reinterpret_cast<float4*>(buf + c) = v;
     s += (v.x + v.y) + (v.z + v.w);
   }
@@ -103,9 +138,19 @@ bool fast_layernorm_supported(int H) { return H % 4 == 0 && H <= 4096; }  // gam
 
 // rows output rows; output row r reads input row r*row_mul + row_add (of h and of every partial)
 int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, const float* g, const float* b, int rows,
-                   int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st) {
+                   int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st,
+                   const float* rowblk, int n_blk) {
   if (rows == 0) return PTTS_OK;
-  const size_t smem = sizeof(float) * (size_t)H;
+  const size_t smem = sizeof(float) * (size_t)H * (size_t)(1 + (rowblk ? n_blk : 0));
+  PTTS_CHECK_ARG(smem <= 200 * 1024, "layernorm_fast: row block too large for shared memory");
+  if (smem > 48 * 1024) {
+    static size_t configured = 0;
+    if (smem > configured) {
+      cudaFuncSetAttribute(ln_reduce_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      configured = smem;
+    }
+  }
   const L2Hint hint = take_l2_hint();
   static int early = -1;
   if (early < 0) {
@@ -116,10 +161,10 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   }
   cudaError_t e;
   if (ydtype == PTTS_F32)
-    e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H, eps,
+    e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, g, b, H, eps,
                  row_mul, row_add, (float*)y, hint, early, tl_next(1));
   else
-    e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, g, b, H,
+    e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, g, b, H,
                  eps, row_mul, row_add, (__nv_bfloat16*)y, hint, early, tl_next(1));
   if (e != cudaSuccess) {
     set_error("layernorm_fast launch: %s", cudaGetErrorString(e));

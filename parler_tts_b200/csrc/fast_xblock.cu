@@ -49,7 +49,8 @@ struct XBlockParams {
   const int* key_mask;         // [B][S] or null
   int B, heads, S;
   float scale;
-  float* part_out;             // [heads][B][H]
+  float* part_out;             // [heads][B][H], or (out_by_row) [B][heads][H]
+  int out_by_row;
   // L2 prefetch of the next self-attention launch's K rows (see fast_attn.cu)
   const __nv_bfloat16* pf_next;
   int pf_stride, pf_rows_base, pf_pct;
@@ -519,7 +520,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
     const uint32_t f0[4] = {a_lo[0], 0u, a_lo[1], 0u}, f1[4] = {a_lo[2], 0u, a_lo[3], 0u};
     const uint32_t f2[4] = {a_hi[0], 0u, a_hi[1], 0u}, f3[4] = {a_hi[2], 0u, a_hi[3], 0u};
     const int g = lane >> 2, t = lane & 3;
-    float* orow = p.part_out + ((int64_t)hd * p.B + b0 + g) * H + 2 * t;
+    float* orow = p.part_out + (p.out_by_row ? ((int64_t)(b0 + g) * p.heads + hd) : ((int64_t)hd * p.B + b0 + g)) * H + 2 * t;
     constexpr int NTW = H / 8 / 8;  // n-tiles per warp
 #pragma unroll 4
     for (int nt = 0; nt < NTW; ++nt) {
@@ -583,14 +584,14 @@ bool xblock_supported(int H, int heads, int d, int S) {
 
 int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, const float* gamma, const float* beta,
                 float eps, const void* wq, const void* wo, const void* kc, const void* vc, const int* key_mask, int B,
-                int heads, int H, int S, float scale, float* part_out, const void* pf_next, int pf_stride,
-                int pf_rows_base, const int* pf_rows_dyn, cudaStream_t st) {
+                int heads, int H, int S, float scale, float* part_out, int out_by_row, const void* pf_next,
+                int pf_stride, int pf_rows_base, const int* pf_rows_dyn, cudaStream_t st) {
   PTTS_CHECK_ARG(xblock_supported(H, heads, H / heads, S), "xblock_fast: unsupported shape");
   XBlockParams p = {};
   p.h = h; p.part_in = part_in; p.S_in = S_in; p.stride = stride; p.gamma = gamma; p.beta = beta; p.eps = eps;
   p.wq = (const __nv_bfloat16*)wq; p.wo = (const __nv_bfloat16*)wo;
   p.kc = (const __nv_bfloat16*)kc; p.vc = (const __nv_bfloat16*)vc; p.key_mask = key_mask;
-  p.B = B; p.heads = heads; p.S = S; p.scale = scale; p.part_out = part_out;
+  p.B = B; p.heads = heads; p.S = S; p.scale = scale; p.part_out = part_out; p.out_by_row = out_by_row;
   static int pf_pct = -1;  // share of the next self-attention launch's K rows to pull into L2 from here
   if (pf_pct < 0) {
     // measured on B200 with this kernel (B=64, 860 frames): 50 % 1.694, 25 % 1.674, 0 % 1.652 ms per decode step - the

@@ -41,7 +41,8 @@ bool fast_layernorm_supported(int H);
 int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, int N, int act, void* y,
                      cudaStream_t st);
 int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, const float* g, const float* b, int rows,
-                   int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st);
+                   int H, float eps, int row_mul, int row_add, void* y, int ydtype, cudaStream_t st,
+                   const float* rowblk = nullptr, int n_blk = 0);
 int64_t attn_scratch_floats(int B, int heads);
 
 bool fast_attention_supported(int dtype, int d, int Tq);
@@ -75,8 +76,8 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
 bool xblock_supported(int H, int heads, int d, int S);
 int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, const float* gamma, const float* beta,
                 float eps, const void* wq, const void* wo, const void* kc, const void* vc, const int* key_mask, int B,
-                int heads, int H, int S, float scale, float* part_out, const void* pf_next, int pf_stride,
-                int pf_rows_base, const int* pf_rows_dyn, cudaStream_t st);
+                int heads, int H, int S, float scale, float* part_out, int out_by_row, const void* pf_next,
+                int pf_stride, int pf_rows_base, const int* pf_rows_dyn, cudaStream_t st);
 bool fast_conv_supported(int Cin, int Cout, int ksize);
 int dac_conv1d_fast(const float* x, int B, int Cin, int T, const float* w, const float* bias, int Cout, int ksize,
                     int dilation, const float* snake_alpha, const float* residual, int tanh_out, float* y,
