@@ -325,6 +325,25 @@ cross_attention_done:
     if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
       // decode: fc1 as split-K partial sums + one small reduce / activation kernel (no cluster, no on-chip reduction)
       float* fpart = work_area(m, s);
+      // PTTS_FC1_PAIR=1: with two K slices the CTA that stores its partial tile second folds both, applies the activation
+      // and writes the bf16 operand of fc2 itself (no reduce + activation launch); 2: the GEMM also releases fc2 only
+      // when its MMA burst is done.  Measured on B200 (B=64, 860 frames): 1.539 / 1.548 ms per decode step against
+      // 1.457 ms with the separate launch - the 32 "second" CTAs do on 32 SMs (fence, ticket, 64 KB of slices, 8 192
+      // erff each: fc1 8.7 us instead of 3.1 us) what the reduce + activation kernel spreads over all 148 - default 0.
+      // (Its first version, activation fully unrolled, was 160 KB of straight-line code: 29 us per launch of cold
+      // instruction fetch.)
+      static int fc1_pair = -1;
+      if (fc1_pair < 0) {
+        const char* e = getenv("PTTS_FC1_PAIR");
+        fc1_pair = e ? atoi(e) : 0;
+      }
+      const int fc1_tiles = (F / 128) * ((rows + 63) / 64);
+      if (fc1_pair && Sf == 2 && F % 128 == 0 && fc1_tiles <= kScratchHeader - 2 && !(skip_mask() & 64)) {
+        gemm::GemmPairAct pa = {s->ffn, reinterpret_cast<unsigned int*>(s->scratch) + 2, m->act_fn};
+        if (fc1_pair == 2) gemm_next_trigger_late(1);
+        PTTS_TRY(gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st, nullptr, &pa));
+        goto fc1_done;
+      }
       PTTS_UNLESS_SKIPPED(64, gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st));
       if (wpf_mask() & 1) {  // the next layer's QKV matrix (or the LM heads) is three launches ahead
         if (l + 1 < m->n_layers)
@@ -338,6 +357,7 @@ cross_attention_done:
                                               nullptr, nullptr, s->ffn, dt, st));
     }
   }
+fc1_done:
   {
     // decode: the LayerNorm after fc2 is the next layer's first one, or the final one in front of the LM heads
     const bool last = l + 1 == m->n_layers;

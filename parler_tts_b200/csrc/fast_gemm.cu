@@ -230,7 +230,7 @@ int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out) {
 }
 
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st, const GemmFinish* fin) {
+                      cudaStream_t st, const GemmFinish* fin, const GemmPairAct* pair) {
   GemmParams p = {};
   p.X = (const __nv_bfloat16*)x;
   p.W = (const __nv_bfloat16*)w;
@@ -240,6 +240,11 @@ int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int spl
   if (fin) {
     p.fin_h = fin->h; p.fin_g = fin->g; p.fin_b = fin->b; p.fin_y = (__nv_bfloat16*)fin->y; p.fin_ctr = fin->ctr;
     p.fin_eps = fin->eps;
+  }
+  PTTS_CHECK_ARG(!pair || (bn == 0 && splits == 2 && N % 128 == 0),
+                 "gemm_bf16_partial: the pair finisher needs the tcgen05 kernel, two K slices and N % 128 == 0");
+  if (pair) {
+    p.pair_y = (__nv_bfloat16*)pair->y; p.pair_ctr = pair->ctr; p.pair_act = pair->act;
   }
   if (bn == 0) return umma_gemm_partial(p, splits, st);
   return launch_bn<EPI_PARTIAL>(bn, p, splits, st);

@@ -313,6 +313,56 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
       asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
     }
     STAMP(6);
+    if (p.pair_y) {
+      // ---- pair finisher: whoever of the two K-slice CTAs of this output tile arrives second folds both slices
+      __shared__ unsigned int pair_ticket;
+      const unsigned tile = blockIdx.y * gridDim.x + blockIdx.x;
+      __threadfence();  // my partial tile is visible device-wide before I take a ticket
+      __syncthreads();
+      if (threadIdx.x == 0) pair_ticket = atomicAdd(p.pair_ctr + tile, 1u);
+      __syncthreads();
+      if (pair_ticket == 1u) {
+        if (threadIdx.x == 0) p.pair_ctr[tile] = 0u;  // both have arrived: ready for the next launch
+        __threadfence();
+        const float* s0 = p.part + (size_t)m0 * ldn + n0;
+        const float* s1 = s0 + (size_t)p.M * ldn;
+        __nv_bfloat16* yo = p.pair_y + (size_t)m0 * ldn + n0;
+        // tile = 64 rows x 32 float4.  The loads are unrolled (8 + 8 in flight per thread), the sums are parked in the
+        // dead operand slabs, and the activation runs in a ROLLED loop: fully unrolled, its 64 inlined erff() made the
+        // kernel 160 KB of straight-line code and the cold instruction fetch cost 25 us per launch
+        float4* stage = reinterpret_cast<float4*>(smem);
+#pragma unroll
+        for (int it = 0; it < 16; it += 8) {
+          float4 a[8], b[8];
+#pragma unroll
+          for (int u = 0; u < 8; ++u) {
+            const int idx = (it + u) * NTH + (int)threadIdx.x, r = idx >> 5, c4 = idx & 31;
+            if (r < rows) {
+              a[u] = __ldcg(reinterpret_cast<const float4*>(s0 + (size_t)r * ldn) + c4);
+              b[u] = __ldcg(reinterpret_cast<const float4*>(s1 + (size_t)r * ldn) + c4);
+            }
+          }
+#pragma unroll
+          for (int u = 0; u < 8; ++u)
+            stage[(it + u) * NTH + threadIdx.x] =
+                make_float4(a[u].x + b[u].x, a[u].y + b[u].y, a[u].z + b[u].z, a[u].w + b[u].w);
+        }
+        const int act = p.pair_act;
+#pragma unroll 1
+        for (int k = 0; k < 16; ++k) {  // every thread reads back only what it parked itself: no barrier
+          const int idx = k * NTH + (int)threadIdx.x, r = idx >> 5, c4 = idx & 31;
+          if (r < rows) {
+            const float4 v = stage[idx];
+            const __nv_bfloat162 lo = __floats2bfloat162_rn(apply_act(v.x, act), apply_act(v.y, act));
+            const __nv_bfloat162 hi = __floats2bfloat162_rn(apply_act(v.z, act), apply_act(v.w, act));
+            uint2 o;
+            o.x = *reinterpret_cast<const uint32_t*>(&lo);
+            o.y = *reinterpret_cast<const uint32_t*>(&hi);
+            *reinterpret_cast<uint2*>(yo + (size_t)r * ldn + c4 * 4) = o;
+          }
+        }
+      }
+    }
     agg();
     if (p.fin_h) {
       // ---- finisher: grid-wide arrival, then this CTA folds + LayerNorms its share of the rows.  Every CTA of the

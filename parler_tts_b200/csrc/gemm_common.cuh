@@ -40,6 +40,20 @@ struct GemmParams {
   __nv_bfloat16* fin_y;
   unsigned int* fin_ctr;
   float fin_eps;
+  // PARTIAL with two K slices + pair finisher (tcgen05 kernel only, pair_y != null): the CTA of an output tile that
+  // stores its partial tile SECOND (ticket from pair_ctr[tile], zero between launches) adds the two slices in slice
+  // order, applies pair_act and writes bf16 [M][N] to pair_y - the separate reduce + activation launch disappears and
+  // nobody waits (the first CTA just leaves)
+  __nv_bfloat16* pair_y;
+  unsigned int* pair_ctr;
+  int pair_act;
+};
+
+// optional pair finisher of gemm_bf16_partial (see GemmParams)
+struct GemmPairAct {
+  void* y;  // bf16 [M][N]
+  unsigned int* ctr;
+  int act;
 };
 
 // optional finisher of gemm_bf16_partial (see GemmParams)

@@ -30,9 +30,9 @@ int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has
                       void* cv, int H, int heads, int d, int Tq, int c_stride, int pos_base, const int* pos_dyn,
                       cudaStream_t st);
 int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
-namespace gemm { struct GemmFinish; }
+namespace gemm { struct GemmFinish; struct GemmPairAct; }
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st, const gemm::GemmFinish* fin = nullptr);
+                      cudaStream_t st, const gemm::GemmFinish* fin = nullptr, const gemm::GemmPairAct* pair = nullptr);
 // the next gemm_bf16_partial launch releases its dependent kernel AFTER its own dependency wait whatever PTTS_PDL_EARLY
 // says, or (at_mma_done) only when its MMA burst has completed
 void gemm_next_trigger_late(int at_mma_done);

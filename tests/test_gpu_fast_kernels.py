@@ -247,7 +247,8 @@ def test_fused_cross_attention_block_masked_ragged_batch_vs_oracle(H, heads, B, 
 
 def test_fast_path_launches_its_own_kernels_and_graph_replays_match_eager():
     """bf16 fast path: a CUDA-graph replayed generation equals the eager launch sequence token for token, and the
-    library's launch counter shows the fused layer (12 launches per layer instead of the simple family's 15)."""
+    library's launch counter shows the fused layer (12 launches per layer at this width, where the one-launch
+    cross-attention block does not apply, instead of the simple family's 15)."""
     kw = dict(TINY, hidden_size=256, num_attention_heads=4, ffn_dim=1024, num_hidden_layers=2)
     dims = decoder_oracle.DecoderDims(**kw)
     sd = decoder_oracle.random_decoder_state(dims, seed=7, ln_jitter=0.05)
