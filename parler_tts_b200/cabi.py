@@ -7,7 +7,8 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-LIB_PATH = os.path.join(_HERE, "libparler_b200.so")
+# PTTS_LIBRARY: another build of the same library (A/B runs of compile-time variants); default = the in-tree build
+LIB_PATH = os.environ.get("PTTS_LIBRARY") or os.path.join(_HERE, "libparler_b200.so")
 
 PTTS_F32, PTTS_BF16 = 0, 1
 ACT = {"none": 0, "gelu": 1, "relu": 2, "silu": 3, "gelu_new": 4}

@@ -97,11 +97,16 @@ struct QFuse {
 };
 
 // part layout: [(b*heads + h)*splits + s][D + 2] = { running max, sum of exp, unnormalised output[D] }
-template <typename T, int D, bool FUSED>
+// LEAN (FUSED only): no K staging, no L2 prefetches, no tail hint, no timeline - the optional paths are compiled out of
+// the instantiation the decode step launches by default (see the note on one-shot code size in fast_gemm3.cu).
+template <typename T, int D, bool FUSED, bool LEAN = false>
 __global__ void __launch_bounds__(NT, FUSED ? 7 : 8)  // 7 x 148 = 1036 CTA slots >= 64 x 16 (b, head) pairs
 attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
                    int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask, int mask_len,
-                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, int stage_cap, TL tl) {
+                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, int stage_cap_in, TL tl_in) {
+  const int stage_cap = LEAN ? 0 : stage_cap_in;
+  TL tl = tl_in;
+  if constexpr (LEAN) tl.p = nullptr;
   constexpr int E = Chunk<T>::E;     // elements per 16-byte chunk
   constexpr int TPK = D / E;         // threads per key row
   constexpr int KPB = NT / TPK;      // key rows per CTA pass
@@ -174,16 +179,16 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
     if (pre_v) load_batch(nxt, vb, j0);
     // HBM would idle between the K pass and the V pass of the wave, and during the short kernels between two
     // attention launches: queue asynchronous L2 prefetches for what is read next
-    if (qf.pf_own_v && n > 0)
+    if (!LEAN && qf.pf_own_v && n > 0)
       l2_prefetch_range(cv + (((int64_t)b * heads + hd) * c_stride + j0) * D, (int64_t)min(n, old_end - j0) * D * sizeof(T));
-    if (qf.pf_next && sp == 0 && !qf.pf_late) prefetch_next();
+    if (!LEAN && qf.pf_next && sp == 0 && !qf.pf_late) prefetch_next();
   }
   pdl_wait();
   pdl_launch();
   tl_dep(tl);
   // pf_late (opt-in, measured slower): prefetch only after the producer GEMM (cross q projection) has finished
   if constexpr (FUSED)
-    if (qf.pf_next && sp == 0 && qf.pf_late) prefetch_next();
+    if (!LEAN && qf.pf_next && sp == 0 && qf.pf_late) prefetch_next();
   if constexpr (!FUSED) plan();
   float qv[E];
   if constexpr (FUSED) {
@@ -330,7 +335,7 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
       }
     }
   }
-  if constexpr (FUSED)
+  if constexpr (FUSED && !LEAN)
     l2_hint_prefetch(qf.tail, (blockIdx.y * gridDim.x + blockIdx.x) * gridDim.z + blockIdx.z,
                      gridDim.x * gridDim.y * gridDim.z);
   tl_end(tl);
@@ -591,14 +596,28 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
       if (smem > configured) {
         cudaFuncSetAttribute(attn_decode_kernel<T, D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(attn_decode_kernel<T, D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(attn_decode_kernel<T, D, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
       }
     }
     PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
-    if (qf.part)
-      e = launch_k(attn_decode_kernel<T, D, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
-                   (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
-                   splits, cap, stage_cap, tl_next(c_stride > 64 ? 2 : 3));
+    if (qf.part) {
+      const TL tl = tl_next(c_stride > 64 ? 2 : 3);
+      static int lean_ok = -1;  // PTTS_ATTN_LEAN=0: always the full instantiation
+      if (lean_ok < 0) {
+        const char* ev = getenv("PTTS_ATTN_LEAN");
+        lean_ok = (ev && ev[0] == '0') ? 0 : 1;
+      }
+      const bool lean = lean_ok && stage_cap == 0 && !qf.pf_own_v && !qf.pf_next && !qf.tail.ptr && !tl.p;
+      if (lean)
+        e = launch_k(attn_decode_kernel<T, D, true, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
+                     (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
+                     splits, cap, 0, tl);
+      else
+        e = launch_k(attn_decode_kernel<T, D, true, false>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
+                     (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
+                     splits, cap, stage_cap, tl);
+    }
     else
       e = launch_k(attn_decode_kernel<T, D, false>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
                    (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,

@@ -138,10 +138,17 @@ __device__ __forceinline__ void mbar_wait3(uint32_t bar, uint32_t parity) {
 }
 
 // grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
-template <int EPI>
+// LEAN = the instantiation the decode step launches when nothing optional is asked for (TMA loads, single X barrier,
+// no diagnostics, no hint, no finisher): every optional path is compiled out.  It matters: the code of an unused
+// finisher in this one-shot kernel cost 0.24 us per launch (1.457 against 1.434 ms per decode step, same box) - the
+// instruction fetch of a kernel that runs each line once is part of its critical path.
+template <int EPI, bool LEAN>
 __global__ void __launch_bounds__(NTH)
-umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint, const __grid_constant__ CUtensorMap tm_w,
-                 const __grid_constant__ CUtensorMap tm_x, TL tl) {
+umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hint, const __grid_constant__ CUtensorMap tm_w,
+                 const __grid_constant__ CUtensorMap tm_x, TL tl_in) {
+  const int dbg = LEAN ? ((dbg_in & (16 | 128)) | 32 | 64) : dbg_in;
+  TL tl = tl_in;
+  if constexpr (LEAN) tl.p = nullptr;
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t mma_bar;
   __shared__ __align__(8) uint64_t w_bar, x_bar[kMaxKB64];  // one barrier per X k-block: MMAs start as blocks land
@@ -182,9 +189,11 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
       for (int kb = 0; kb < KB; ++kb) tma_load_2d(sw + kb * WBLK, &tm_w, smem_u32(&w_bar), kbeg + kb * KB64, n0);
     }
   }
-  cp_async_commit();  // group 0: the W slab
-  l2_hint_prefetch(hint, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
-                   gridDim.x * gridDim.y * gridDim.z);
+  if constexpr (!LEAN) {
+    cp_async_commit();  // group 0: the W slab
+    l2_hint_prefetch(hint, (blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x,
+                     gridDim.x * gridDim.y * gridDim.z);
+  }
   // dbg bit 4 (split-K partial GEMMs, PTTS_PDL_EARLY=0 to disable): release the dependent kernel BEFORE waiting on
   // the own producer, so that its CTAs are resident and its pre-wait prologue (gamma / beta, first K batch, L2
   // prefetches) has run by the time this grid completes.  Safe because every consumer touches producer data only
@@ -313,7 +322,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
       asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
     }
     STAMP(6);
-    if (p.pair_y) {
+    if (!LEAN && p.pair_y) {
       // ---- pair finisher: whoever of the two K-slice CTAs of this output tile arrives second folds both slices
       __shared__ unsigned int pair_ticket;
       const unsigned tile = blockIdx.y * gridDim.x + blockIdx.x;
@@ -364,7 +373,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg, const L2Hint hint,
       }
     }
     agg();
-    if (p.fin_h) {
+    if (!LEAN && p.fin_h) {
       // ---- finisher: grid-wide arrival, then this CTA folds + LayerNorms its share of the rows.  Every CTA of the
       // grid is resident (grid <= #SMs, and a dependent grid is only launched once all of them have started), so
       // the wait cannot deadlock; it is bounded anyway.
@@ -613,7 +622,8 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   smem += 1024;  // alignment slack
   static size_t configured = 0;
   if (smem > configured) {
-    cudaFuncSetAttribute(umma_gemm_kernel<EPI>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(umma_gemm_kernel<EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    cudaFuncSetAttribute(umma_gemm_kernel<EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = smem;
   }
   cudaLaunchConfig_t cfg = {};
@@ -671,8 +681,17 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     // bulk-tensor issues costs ~500 cycles) - 1.566 against 1.485 ms per decode step
     xbar = (ev && ev[0] == '0') ? 0 : 64;
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI>, p, kb, cs, dbg_arg | (tma ? 32 : 0) | xbar, hint, tm_w, tm_x,
-                                     tl_next(10 + EPI));
+  const TL tl = tl_next(10 + EPI);
+  static int lean_ok = -1;  // PTTS_GEMM_LEAN=0: always the full instantiation
+  if (lean_ok < 0) {
+    const char* ev = getenv("PTTS_GEMM_LEAN");
+    lean_ok = (ev && ev[0] == '0') ? 0 : 1;
+  }
+  const bool lean = lean_ok && tma && xbar && !(dbg_arg & ~(16 | 128)) && !hint.ptr && !p.fin_h && !p.pair_y && !tl.p;
+  cudaError_t e =
+      lean ? cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI, true>, p, kb, cs, dbg_arg, hint, tm_w, tm_x, tl)
+           : cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI, false>, p, kb, cs, dbg_arg | (tma ? 32 : 0) | xbar, hint, tm_w,
+                                tm_x, tl);
   if (e != cudaSuccess) {
     set_error("umma_gemm launch: %s", cudaGetErrorString(e));
     (void)cudaGetLastError();

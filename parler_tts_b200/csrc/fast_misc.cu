@@ -14,7 +14,9 @@ namespace {
 // rowblk (optional): n_blk further slices stored ROW-contiguously, [row][n_blk][H] (what the fused cross-attention block
 // writes): the 64 KB of a row arrive as ONE bulk copy (cp.async.bulk, TMA engine) into shared memory instead of 4 096
 // 16-byte LSU requests, and are folded from there after the strided slices, in slice order.
-template <typename TY>
+// U = strided slice loads a thread keeps in flight per round (2 / 8 / 20, picked from S on the host: predicated-off
+// loads and adds of a larger U are still fetched and issued)
+template <typename TY, int U>
 __global__ void __launch_bounds__(256)
 ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
                  const float* __restrict__ rowblk, int n_blk, const float* __restrict__ g,
@@ -61,11 +63,10 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
                  : "memory");
   }
   float s = 0.f;
+#pragma unroll 1
   for (int c = tid * 4; c < H; c += 256 * 4) {
     float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
-    // up to 20 independent loads in flight (one L2 round trip for the 4 + 16 slices the fused cross-attention block
-    // leaves behind), summed in split order (deterministic)
-    constexpr int U = 20;
+    // up to U independent loads in flight (one L2 round trip), summed in split order (deterministic)
     for (int i0 = 0; i0 < S; i0 += U) {
       float4 p[U];
 #pragma unroll
@@ -100,6 +101,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
   __syncthreads();
   const float mean = (((red[0] + red[1]) + (red[2] + red[3])) + ((red[4] + red[5]) + (red[6] + red[7]))) / (float)H;
   float qq = 0.f;
+#pragma unroll 1
   for (int c = tid * 4; c < H; c += 256 * 4) {
     const float4 v = *reinterpret_cast<const float4*>(buf + c);
     const float a = v.x - mean, b = v.y - mean, cc = v.z - mean, d = v.w - mean;
@@ -146,8 +148,12 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   if (smem > 48 * 1024) {
     static size_t configured = 0;
     if (smem > configured) {
-      cudaFuncSetAttribute(ln_reduce_kernel<float>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<float, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<float, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<float, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
       configured = smem;
     }
   }
@@ -160,12 +166,19 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
     early = (ev && ev[0] == '1') ? 1 : 0;
   }
   cudaError_t e;
-  if (ydtype == PTTS_F32)
-    e = launch_k(ln_reduce_kernel<float>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, g, b, H, eps,
-                 row_mul, row_add, (float*)y, hint, early, tl_next(1));
-  else
-    e = launch_k(ln_reduce_kernel<__nv_bfloat16>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, g, b, H,
-                 eps, row_mul, row_add, (__nv_bfloat16*)y, hint, early, tl_next(1));
+#define PTTS_LN_LAUNCH(TY, UU)                                                                                       \
+  e = launch_k(ln_reduce_kernel<TY, UU>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, g, b, \
+               H, eps, row_mul, row_add, (TY*)y, hint, early, tl_next(1))
+  if (ydtype == PTTS_F32) {
+    if (S <= 2) PTTS_LN_LAUNCH(float, 2);
+    else if (S <= 8) PTTS_LN_LAUNCH(float, 8);
+    else PTTS_LN_LAUNCH(float, 20);
+  } else {
+    if (S <= 2) PTTS_LN_LAUNCH(__nv_bfloat16, 2);
+    else if (S <= 8) PTTS_LN_LAUNCH(__nv_bfloat16, 8);
+    else PTTS_LN_LAUNCH(__nv_bfloat16, 20);
+  }
+#undef PTTS_LN_LAUNCH
   if (e != cudaSuccess) {
     set_error("layernorm_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
@@ -176,8 +189,10 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
 
 // y[r][c] = act(sum_s part[s][r][c]) as bf16: finishes the split-K fc1 of the decode step (partial sums are added in
 // slice order, deterministic).  One float4 column group per thread; all S loads of a thread are in flight together.
+// ACT >= 0: the activation is a compile-time constant (the GELU instantiation is a third of the generic code)
+template <int ACT>
 __global__ void __launch_bounds__(256)
-partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, int64_t n4, int act,
+partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, int64_t n4, int act_in,
                    __nv_bfloat16* __restrict__ y, const L2Hint hint, int early, TL tl) {
   tl_start(tl);
   if (early) pdl_launch();  // before the wait: the consumer (fc2 GEMM) only prefetches immutable weights ahead of its own wait
@@ -185,6 +200,7 @@ partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, i
   pdl_wait();
   if (!early) pdl_launch();
   tl_dep(tl);
+  const int act = ACT >= 0 ? ACT : act_in;
   const int64_t i = (int64_t)blockIdx.x * 256 + threadIdx.x;
   if (i < n4) {
     const float4* p0 = reinterpret_cast<const float4*>(part) + i;
@@ -219,8 +235,11 @@ int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, in
     const char* ev = getenv("PTTS_ACT_EARLY");  // measured: early 1.496, late 1.522 ms per decode step -> early
     early = (ev && ev[0] == '0') ? 0 : 1;
   }
-  cudaError_t e = launch_k(partial_act_kernel, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,
-                           part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), early, tl_next(4));
+  cudaError_t e = act == PTTS_ACT_GELU
+                      ? launch_k(partial_act_kernel<PTTS_ACT_GELU>, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st,
+                                 part, S, part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), early, tl_next(4))
+                      : launch_k(partial_act_kernel<-1>, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,
+                                 part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), early, tl_next(4));
   if (e != cudaSuccess) {
     set_error("partial_act_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;

@@ -113,10 +113,16 @@ __device__ __forceinline__ void xb_mbar_wait(uint32_t bar, uint32_t parity) {
 // whose 16-byte chunk c of row r sits at chunk position c ^ (r & 7) (base 1024-byte aligned).
 //   Wq head slab: H/64 blocks (one per 64-element k block) of 64 rows   -> block kb at kb * 8 KB
 //   Wo head slab: one block of H rows (the head's 64 input columns)
-template <int HT, int CS>  // H = 128 * HT
+// LEAN: S <= 48 keys (all in registers), no hint, no next-layer prefetch, no diagnostics - the optional paths are
+// compiled out of the instantiation the benchmark shape launches (one-shot kernel: instruction fetch is on its
+// critical path, see fast_gemm3.cu).
+template <int HT, int CS, bool LEAN>  // H = 128 * HT
 __global__ void __launch_bounds__(XT, 1)
-xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__ CUtensorMap tm_wq,
-              const __grid_constant__ CUtensorMap tm_wo, TL tl) {
+xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constant__ CUtensorMap tm_wq,
+              const __grid_constant__ CUtensorMap tm_wo, TL tl_in) {
+  const int dbg = LEAN ? (dbg_in & 2) : dbg_in;
+  TL tl = tl_in;
+  if constexpr (LEAN) tl.p = nullptr;
   constexpr int H = 128 * HT;
   constexpr int ROWB = 2 * H;  // bytes per bf16 row of H
   constexpr int UP = 6;        // key passes (8 keys each) whose K and V rows a warp keeps in registers: 48 keys
@@ -184,15 +190,15 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
       }
     }
   }
-  l2_hint_prefetch(p.hint, blockIdx.y * gridDim.x + blockIdx.x, gridDim.x * gridDim.y);
+  if constexpr (!LEAN) l2_hint_prefetch(p.hint, blockIdx.y * gridDim.x + blockIdx.x, gridDim.x * gridDim.y);
   for (int n = tid; n < H; n += XT)  // Wo[:, head]: one 128-byte line per output feature
     asm volatile("prefetch.global.L2 [%0];\n" ::"l"(p.wo + (int64_t)n * H + hd * XD) : "memory");
-  if (p.S > 8 * UP && live && lane < 2) {  // keys beyond the register-held ones: L2 prefetch of K (lane 0) / V (lane 1)
+  if (!LEAN && p.S > 8 * UP && live && lane < 2) {  // keys beyond the register-held ones: L2 prefetch of K (lane 0) / V (lane 1)
     const char* base = reinterpret_cast<const char*>((lane ? p.vc : p.kc) + (((int64_t)bw * p.heads + hd) * p.S + 8 * UP) * XD);
     const int64_t bytes = (int64_t)(p.S - 8 * UP) * XD * 2;
     for (int64_t o = 0; o < bytes; o += 8192) l2_prefetch_bulk(base + o, (uint32_t)min((int64_t)8192, bytes - o));
   }
-  if (p.pf_next && p.pf_pct > 0 && live) {
+  if (!LEAN && p.pf_next && p.pf_pct > 0 && live) {
     const int rows = dyn_value(p.pf_rows_base, p.pf_rows_dyn) * min(p.pf_pct, 100) / 100;
     const int64_t bytes = (int64_t)rows * XD * 2;
     const char* src = reinterpret_cast<const char*>(p.pf_next + ((int64_t)bw * p.heads + hd) * p.pf_stride * XD);
@@ -436,7 +442,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
         }
       }
     }
-    for (int j0 = 8 * UP; j0 < p.S; j0 += 8 * UP) {  // descriptions longer than 48 tokens
+    for (int j0 = 8 * UP; !LEAN && j0 < p.S; j0 += 8 * UP) {  // descriptions longer than 48 tokens
       uint4 raw[UP][2];
       load_batch(raw, kb, j0);
       score_batch(raw, j0);
@@ -474,7 +480,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg, const __grid_constant__
       }
     };
     accum_batch(rv, 0);
-    for (int j0 = 8 * UP; j0 < p.S; j0 += 8 * UP) {
+    for (int j0 = 8 * UP; !LEAN && j0 < p.S; j0 += 8 * UP) {
       uint4 raw[UP][2];
       load_batch(raw, vb, j0);
       accum_batch(raw, j0);
@@ -650,15 +656,27 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   }
   using KernelFn = void (*)(const XBlockParams, int, int, const CUtensorMap, const CUtensorMap, TL);
   KernelFn fn = nullptr;
-  if (H == 1024) fn = cs == 1 ? xblock_kernel<8, 1> : (cs == 2 ? xblock_kernel<8, 2> : xblock_kernel<8, 4>);
-  else fn = cs == 1 ? xblock_kernel<12, 1> : (cs == 2 ? xblock_kernel<12, 2> : xblock_kernel<12, 4>);
-  static size_t configured[2][3] = {{0, 0, 0}, {0, 0, 0}};
-  size_t& conf = configured[H == 1024 ? 0 : 1][cs == 1 ? 0 : (cs == 2 ? 1 : 2)];
+  const TL tl = tl_next(5);
+  static int lean_ok = -1;  // PTTS_XB_LEAN=0: always the full instantiation
+  if (lean_ok < 0) {
+    const char* ev = getenv("PTTS_XB_LEAN");
+    lean_ok = (ev && ev[0] == '0') ? 0 : 1;
+  }
+  const bool lean = lean_ok && S <= 48 && !p.hint.ptr && !(p.pf_next && p.pf_pct > 0) && !(dbg & 1) && !tl.p;
+  if (H == 1024) {
+    if (lean) fn = cs == 1 ? xblock_kernel<8, 1, true> : (cs == 2 ? xblock_kernel<8, 2, true> : xblock_kernel<8, 4, true>);
+    else fn = cs == 1 ? xblock_kernel<8, 1, false> : (cs == 2 ? xblock_kernel<8, 2, false> : xblock_kernel<8, 4, false>);
+  } else {
+    if (lean) fn = cs == 1 ? xblock_kernel<12, 1, true> : (cs == 2 ? xblock_kernel<12, 2, true> : xblock_kernel<12, 4, true>);
+    else fn = cs == 1 ? xblock_kernel<12, 1, false> : (cs == 2 ? xblock_kernel<12, 2, false> : xblock_kernel<12, 4, false>);
+  }
+  static size_t configured[2][2][3] = {};
+  size_t& conf = configured[lean ? 1 : 0][H == 1024 ? 0 : 1][cs == 1 ? 0 : (cs == 2 ? 1 : 2)];
   if (smem > conf) {
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     conf = smem;
   }
-  cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p, sc_cap, dbg, tm_wq, tm_wo, tl_next(5));
+  cudaError_t e = cudaLaunchKernelEx(&cfg, fn, p, sc_cap, dbg, tm_wq, tm_wo, tl);
   if (e != cudaSuccess) {
     set_error("xblock_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
