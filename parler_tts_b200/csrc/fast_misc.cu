@@ -16,12 +16,17 @@ namespace {
 // 16-byte LSU requests, and are folded from there after the strided slices, in slice order.
 // U = strided slice loads a thread keeps in flight per round (2 / 8 / 20, picked from S on the host: predicated-off
 // loads and adds of a larger U are still fetched and issued)
-template <typename TY, int U>
+// BLK: the row-block path exists; LEAN: no hint, no timeline (one-shot kernel: what is not needed is compiled out, see
+// fast_gemm3.cu)
+template <typename TY, int U, bool BLK, bool LEAN>
 __global__ void __launch_bounds__(256)
 ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, int64_t part_stride,
-                 const float* __restrict__ rowblk, int n_blk, const float* __restrict__ g,
+                 const float* __restrict__ rowblk_in, int n_blk, const float* __restrict__ g,
                  const float* __restrict__ bta, int H, float eps, int row_mul, int row_add, TY* __restrict__ y,
-                 const L2Hint hint, int early, TL tl) {
+                 const L2Hint hint, int early, TL tl_in) {
+  const float* rowblk = BLK ? rowblk_in : nullptr;
+  TL tl = tl_in;
+  if constexpr (LEAN) tl.p = nullptr;
   extern __shared__ __align__(128) float buf[];  // [H] row | [n_blk][H] bulk-copied slices
   __shared__ float red[8], red2[8];
   __shared__ __align__(8) uint64_t blk_bar;
@@ -43,7 +48,7 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
       bb4[i] = __ldg(reinterpret_cast<const float4*>(bta + c));
     }
   }
-  l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
+  if constexpr (!LEAN) l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
   const uint32_t bar = (uint32_t)__cvta_generic_to_shared(&blk_bar);
   if (rowblk && tid == 0) {
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(1) : "memory");
@@ -148,12 +153,18 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
   if (smem > 48 * 1024) {
     static size_t configured = 0;
     if (smem > configured) {
-      cudaFuncSetAttribute(ln_reduce_kernel<float, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(ln_reduce_kernel<float, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(ln_reduce_kernel<float, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16, 2>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16, 8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      cudaFuncSetAttribute(ln_reduce_kernel<__nv_bfloat16, 20>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+#define PTTS_LN_ATTR(TY, UU)                                                                                          \
+  cudaFuncSetAttribute(ln_reduce_kernel<TY, UU, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);  \
+  cudaFuncSetAttribute(ln_reduce_kernel<TY, UU, true, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+  cudaFuncSetAttribute(ln_reduce_kernel<TY, UU, false, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem); \
+  cudaFuncSetAttribute(ln_reduce_kernel<TY, UU, false, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem)
+      PTTS_LN_ATTR(float, 2);
+      PTTS_LN_ATTR(float, 8);
+      PTTS_LN_ATTR(float, 20);
+      PTTS_LN_ATTR(__nv_bfloat16, 2);
+      PTTS_LN_ATTR(__nv_bfloat16, 8);
+      PTTS_LN_ATTR(__nv_bfloat16, 20);
+#undef PTTS_LN_ATTR
       configured = smem;
     }
   }
@@ -166,9 +177,21 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
     early = (ev && ev[0] == '1') ? 1 : 0;
   }
   cudaError_t e;
-#define PTTS_LN_LAUNCH(TY, UU)                                                                                       \
-  e = launch_k(ln_reduce_kernel<TY, UU>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, g, b, \
-               H, eps, row_mul, row_add, (TY*)y, hint, early, tl_next(1))
+  const TL tl = tl_next(1);
+  const bool lean = !hint.ptr && !tl.p;
+#define PTTS_LN_LAUNCH2(TY, UU, BB, LL)                                                                               \
+  e = launch_k(ln_reduce_kernel<TY, UU, BB, LL>, dim3(rows), dim3(256), smem, st, h, part, S, part_stride, rowblk, n_blk, \
+               g, b, H, eps, row_mul, row_add, (TY*)y, hint, early, tl)
+#define PTTS_LN_LAUNCH(TY, UU)                                      \
+  do {                                                              \
+    if (rowblk) {                                                   \
+      if (lean) PTTS_LN_LAUNCH2(TY, UU, true, true);                \
+      else PTTS_LN_LAUNCH2(TY, UU, true, false);                    \
+    } else {                                                        \
+      if (lean) PTTS_LN_LAUNCH2(TY, UU, false, true);               \
+      else PTTS_LN_LAUNCH2(TY, UU, false, false);                   \
+    }                                                               \
+  } while (0)
   if (ydtype == PTTS_F32) {
     if (S <= 2) PTTS_LN_LAUNCH(float, 2);
     else if (S <= 8) PTTS_LN_LAUNCH(float, 8);
@@ -178,6 +201,7 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
     else if (S <= 8) PTTS_LN_LAUNCH(__nv_bfloat16, 8);
     else PTTS_LN_LAUNCH(__nv_bfloat16, 20);
   }
+#undef PTTS_LN_LAUNCH2
 #undef PTTS_LN_LAUNCH
   if (e != cudaSuccess) {
     set_error("layernorm_fast launch: %s", cudaGetErrorString(e));
@@ -190,13 +214,15 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
 // y[r][c] = act(sum_s part[s][r][c]) as bf16: finishes the split-K fc1 of the decode step (partial sums are added in
 // slice order, deterministic).  One float4 column group per thread; all S loads of a thread are in flight together.
 // ACT >= 0: the activation is a compile-time constant (the GELU instantiation is a third of the generic code)
-template <int ACT>
+template <int ACT, bool LEAN>
 __global__ void __launch_bounds__(256)
 partial_act_kernel(const float* __restrict__ part, int S, int64_t part_stride, int64_t n4, int act_in,
-                   __nv_bfloat16* __restrict__ y, const L2Hint hint, int early, TL tl) {
+                   __nv_bfloat16* __restrict__ y, const L2Hint hint, int early, TL tl_in) {
+  TL tl = tl_in;
+  if constexpr (LEAN) tl.p = nullptr;
   tl_start(tl);
   if (early) pdl_launch();  // before the wait: the consumer (fc2 GEMM) only prefetches immutable weights ahead of its own wait
-  l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
+  if constexpr (!LEAN) l2_hint_prefetch(hint, blockIdx.x, gridDim.x);
   pdl_wait();
   if (!early) pdl_launch();
   tl_dep(tl);
@@ -235,11 +261,16 @@ int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, in
     const char* ev = getenv("PTTS_ACT_EARLY");  // measured: early 1.496, late 1.522 ms per decode step -> early
     early = (ev && ev[0] == '0') ? 0 : 1;
   }
-  cudaError_t e = act == PTTS_ACT_GELU
-                      ? launch_k(partial_act_kernel<PTTS_ACT_GELU>, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st,
-                                 part, S, part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), early, tl_next(4))
-                      : launch_k(partial_act_kernel<-1>, dim3((unsigned)((n4 + 255) / 256)), dim3(256), 0, st, part, S,
-                                 part_stride, n4, act, (__nv_bfloat16*)y, take_l2_hint(), early, tl_next(4));
+  const L2Hint hint = take_l2_hint();
+  const TL tl = tl_next(4);
+  const dim3 grid((unsigned)((n4 + 255) / 256));
+  cudaError_t e;
+  if (act == PTTS_ACT_GELU && !hint.ptr && !tl.p)
+    e = launch_k(partial_act_kernel<PTTS_ACT_GELU, true>, grid, dim3(256), 0, st, part, S, part_stride, n4, act,
+                 (__nv_bfloat16*)y, hint, early, tl);
+  else
+    e = launch_k(partial_act_kernel<-1, false>, grid, dim3(256), 0, st, part, S, part_stride, n4, act,
+                 (__nv_bfloat16*)y, hint, early, tl);
   if (e != cudaSuccess) {
     set_error("partial_act_fast launch: %s", cudaGetErrorString(e));
     return PTTS_E_LAUNCH;
