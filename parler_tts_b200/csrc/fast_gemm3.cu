@@ -142,7 +142,8 @@ __device__ __forceinline__ void mbar_wait3(uint32_t bar, uint32_t parity) {
 // no diagnostics, no hint, no finisher): every optional path is compiled out.  It matters: the code of an unused
 // finisher in this one-shot kernel cost 0.24 us per launch (1.457 against 1.434 ms per decode step, same box) - the
 // instruction fetch of a kernel that runs each line once is part of its critical path.
-template <int EPI, bool LEAN>
+// FULLM (lean PARTIAL launches with M % 64 == 0): the ragged-tile copy of the store loop is compiled out too
+template <int EPI, bool LEAN, bool FULLM = false>
 __global__ void __launch_bounds__(NTH)
 umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hint, const __grid_constant__ CUtensorMap tm_w,
                  const __grid_constant__ CUtensorMap tm_x, TL tl_in) {
@@ -304,10 +305,10 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
       tmem_ld_32x32b_x32(tmem_d + ((uint32_t)(warp * 32) << 16) + half * 32, v);
       asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
       if (n < p.N) {
-        if (rows == UN) {
+        if (FULLM || rows == UN) {
 #pragma unroll
           for (int j = 0; j < 32; ++j) dst[(size_t)j * ldn] = __uint_as_float(v[j]);
-        } else {
+        } else if constexpr (!FULLM) {
 #pragma unroll
           for (int j = 0; j < 32; ++j)
             if (half * 32 + j < rows) dst[(size_t)j * ldn] = __uint_as_float(v[j]);
@@ -624,6 +625,8 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   if (smem > configured) {
     cudaFuncSetAttribute(umma_gemm_kernel<EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(umma_gemm_kernel<EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    if (EPI == EPI_PARTIAL)
+      cudaFuncSetAttribute(umma_gemm_kernel<EPI_PARTIAL, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     configured = smem;
   }
   cudaLaunchConfig_t cfg = {};
@@ -689,7 +692,9 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   }
   const bool lean = lean_ok && tma && xbar && !(dbg_arg & ~(16 | 128)) && !hint.ptr && !p.fin_h && !p.pair_y && !tl.p;
   cudaError_t e =
-      lean ? cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI, true>, p, kb, cs, dbg_arg, hint, tm_w, tm_x, tl)
+      (lean && EPI == EPI_PARTIAL && p.M % UN == 0)
+          ? cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI_PARTIAL, true, true>, p, kb, cs, dbg_arg, hint, tm_w, tm_x, tl)
+      : lean ? cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI, true>, p, kb, cs, dbg_arg, hint, tm_w, tm_x, tl)
            : cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI, false>, p, kb, cs, dbg_arg | (tma ? 32 : 0) | xbar, hint, tm_w,
                                 tm_x, tl);
   if (e != cudaSuccess) {
