@@ -99,11 +99,15 @@ struct QFuse {
 // part layout: [(b*heads + h)*splits + s][D + 2] = { running max, sum of exp, unnormalised output[D] }
 // LEAN (FUSED only): no K staging, no L2 prefetches, no tail hint, no timeline - the optional paths are compiled out of
 // the instantiation the decode step launches by default (see the note on one-shot code size in fast_gemm3.cu).
-template <typename T, int D, bool FUSED, bool LEAN = false>
+// PLAIN (lean launches without a key mask and without a KV split): the mask test leaves the K pass and the split
+// bookkeeping leaves the epilogue
+template <typename T, int D, bool FUSED, bool LEAN = false, bool PLAIN = false>
 __global__ void __launch_bounds__(NT, FUSED ? 7 : 8)  // 7 x 148 = 1036 CTA slots >= 64 x 16 (b, head) pairs
 attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
-                   int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask, int mask_len,
-                   T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, int stage_cap_in, TL tl_in) {
+                   int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask_in, int mask_len,
+                   T* __restrict__ out, float* __restrict__ part, int splits_in, int sc_cap, int stage_cap_in, TL tl_in) {
+  const int* key_mask = PLAIN ? nullptr : key_mask_in;
+  const int splits = PLAIN ? 1 : splits_in;
   const int stage_cap = LEAN ? 0 : stage_cap_in;
   TL tl = tl_in;
   if constexpr (LEAN) tl.p = nullptr;
@@ -597,6 +601,7 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
         cudaFuncSetAttribute(attn_decode_kernel<T, D, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(attn_decode_kernel<T, D, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         cudaFuncSetAttribute(attn_decode_kernel<T, D, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+        cudaFuncSetAttribute(attn_decode_kernel<T, D, true, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
         configured = smem;
       }
     }
@@ -609,7 +614,11 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
         lean_ok = (ev && ev[0] == '0') ? 0 : 1;
       }
       const bool lean = lean_ok && stage_cap == 0 && !qf.pf_own_v && !qf.pf_next && !qf.tail.ptr && !tl.p;
-      if (lean)
+      if (lean && !key_mask && splits == 1)
+        e = launch_k(attn_decode_kernel<T, D, true, true, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
+                     (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
+                     splits, cap, 0, tl);
+      else if (lean)
         e = launch_k(attn_decode_kernel<T, D, true, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
                      (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
                      splits, cap, 0, tl);
