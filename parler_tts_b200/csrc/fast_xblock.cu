@@ -116,7 +116,8 @@ __device__ __forceinline__ void xb_mbar_wait(uint32_t bar, uint32_t parity) {
 // LEAN: S <= 48 keys (all in registers), no hint, no next-layer prefetch, no diagnostics - the optional paths are
 // compiled out of the instantiation the benchmark shape launches (one-shot kernel: instruction fetch is on its
 // critical path, see fast_gemm3.cu).
-template <int HT, int CS, bool LEAN>  // H = 128 * HT
+// PLAIN (lean launches without a key mask and with B % 8 == 0): no mask tests, no ragged-group predicates
+template <int HT, int CS, bool LEAN, bool PLAIN = false>  // H = 128 * HT
 __global__ void __launch_bounds__(XT, 1)
 xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constant__ CUtensorMap tm_wq,
               const __grid_constant__ CUtensorMap tm_wo, TL tl_in) {
@@ -139,7 +140,8 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constan
   __shared__ __align__(8) uint64_t wq_bar, wo_bar;
   const int hd = blockIdx.x, b0 = blockIdx.y * XG;
   const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int nrows = min(XG, p.B - b0);
+  const int nrows = PLAIN ? XG : min(XG, p.B - b0);
+  const int* key_mask = PLAIN ? nullptr : p.key_mask;
   const uint32_t wbuf_s = smem_u32(wbuf), xn_s = smem_u32(xn), at_s = smem_u32(at);
   const uint32_t crank = cluster_rank_x();
   tl_start(tl);
@@ -387,7 +389,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constan
         dot += __shfl_xor_sync(0xffffffffu, dot, 2);
         if (j < p.S && c4 == 0) {
           bool keep = true;
-          if (p.key_mask) keep = p.key_mask[(int64_t)bw * p.S + j] != 0;
+          if (key_mask) keep = key_mask[(int64_t)bw * p.S + j] != 0;
           const float sj = keep ? dot : neg;
           scw[j] = sj;
           lmax = fmaxf(lmax, sj);
@@ -433,7 +435,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constan
             const int j = u * 8 + 2 * c4 + e;
             if (j < p.S) {
               bool keep = true;
-              if (p.key_mask) keep = p.key_mask[(int64_t)bw * p.S + j] != 0;
+              if (key_mask) keep = key_mask[(int64_t)bw * p.S + j] != 0;
               const float sj = keep ? c[e] : neg;
               scw[j] = sj;
               lmax = fmaxf(lmax, sj);
@@ -664,14 +666,17 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   }
   const bool lean = lean_ok && S <= 48 && !p.hint.ptr && !(p.pf_next && p.pf_pct > 0) && !(dbg & 1) && !tl.p;
   if (H == 1024) {
-    if (lean) fn = cs == 1 ? xblock_kernel<8, 1, true> : (cs == 2 ? xblock_kernel<8, 2, true> : xblock_kernel<8, 4, true>);
+    if (lean && cs == 1 && !key_mask && B % XG == 0) fn = xblock_kernel<8, 1, true, true>;
+    else if (lean) fn = cs == 1 ? xblock_kernel<8, 1, true> : (cs == 2 ? xblock_kernel<8, 2, true> : xblock_kernel<8, 4, true>);
     else fn = cs == 1 ? xblock_kernel<8, 1, false> : (cs == 2 ? xblock_kernel<8, 2, false> : xblock_kernel<8, 4, false>);
   } else {
-    if (lean) fn = cs == 1 ? xblock_kernel<12, 1, true> : (cs == 2 ? xblock_kernel<12, 2, true> : xblock_kernel<12, 4, true>);
+    if (lean && cs == 1 && !key_mask && B % XG == 0) fn = xblock_kernel<12, 1, true, true>;
+    else if (lean) fn = cs == 1 ? xblock_kernel<12, 1, true> : (cs == 2 ? xblock_kernel<12, 2, true> : xblock_kernel<12, 4, true>);
     else fn = cs == 1 ? xblock_kernel<12, 1, false> : (cs == 2 ? xblock_kernel<12, 2, false> : xblock_kernel<12, 4, false>);
   }
-  static size_t configured[2][2][3] = {};
-  size_t& conf = configured[lean ? 1 : 0][H == 1024 ? 0 : 1][cs == 1 ? 0 : (cs == 2 ? 1 : 2)];
+  const bool plain = lean && cs == 1 && !key_mask && B % XG == 0;
+  static size_t configured[3][2][3] = {};
+  size_t& conf = configured[plain ? 2 : (lean ? 1 : 0)][H == 1024 ? 0 : 1][cs == 1 ? 0 : (cs == 2 ? 1 : 2)];
   if (smem > conf) {
     cudaFuncSetAttribute(fn, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     conf = smem;
