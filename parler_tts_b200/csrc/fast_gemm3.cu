@@ -711,6 +711,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
 void gemm_next_trigger_late(int at_mma_done) { g_late_once = at_mma_done ? 2 : 1; }
 
 namespace gemm {
+bool tma_available() { return encode_tiled_fn() != nullptr; }
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
   return tensor_map_2d_impl(ptr, rows, cols, box_rows, out);
 }

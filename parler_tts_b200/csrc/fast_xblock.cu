@@ -587,7 +587,7 @@ static size_t xblock_smem(int H, int S) {
 bool xblock_supported(int H, int heads, int d, int S) {
   if (!xblock_enabled()) return false;
   if (d != XD || heads * d != H || (H != 1024 && H != 1536) || heads % 4 != 0 || S < 1) return false;
-  return xblock_smem(H, S) <= 227 * 1024;
+  return xblock_smem(H, S) <= 227 * 1024 && gemm::tma_available();  // else the 12-launch chain runs
 }
 
 int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, const float* gamma, const float* beta,

@@ -109,6 +109,7 @@ __device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g
 // Cached tensor map (fast_gemm3.cu) of a bf16 row-major matrix [rows][cols]: box = 64 columns (128 bytes, SWIZZLE_128B)
 // x box_rows rows, out-of-range rows read as 0.  false: no driver entry point / misaligned matrix.
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
+bool tma_available();  // the driver entry point for tensor-map creation was found
 
 // cluster split-K kernel (fast_gemm2.cu); PTTS_E_UNSUPPORTED when the shape does not fit it
 int cluster_gemm_store(const GemmParams& p, cudaStream_t st);
