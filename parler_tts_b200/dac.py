@@ -258,6 +258,27 @@ class DacDecoderEngine:
             outs = [self.decode_latents(self.dequant(codes[i : i + per])) for i in range(0, B, per)]
         return torch.cat(outs, dim=0) if len(outs) > 1 else outs[0]
 
+    # frames of context on either side that an output frame of the 44 kHz decoder can see: first conv (k7) 3 frames +
+    # block 1 (stride 8; residual units k7 with dilations 1, 3, 9 = 39 samples, transposed conv 1) 7 frames, the later
+    # blocks add less than one frame each at their rates -> 10; 16 leaves a margin and keeps chunks aligned
+    STREAM_HALO = 16
+
+    def decode_chunks(self, codes, chunk_frames=128, halo=None):
+        """Streaming form of `decode`: yields (first_frame, audio (B, 1, hop*n)) for
+        consecutive chunks of `chunk_frames` frames.  Every chunk is decoded with `halo` frames of real context on
+        both sides (zero padding only at the true ends, exactly like the one-shot decode), so the concatenation of
+        the chunks equals `decode(codes)`; a consumer can start playing / copying chunk i while chunk i+1 decodes."""
+        B, K, F = codes.shape
+        halo = self.STREAM_HALO if halo is None else int(halo)
+        hop = 1
+        for r in self.rates:
+            hop *= r
+        for f0 in range(0, F, chunk_frames):
+            f1 = min(F, f0 + chunk_frames)
+            lo, hi = max(0, f0 - halo), min(F, f1 + halo)
+            wav = self.decode(codes[:, :, lo:hi].contiguous())
+            yield f0, wav[:, :, (f0 - lo) * hop : (f1 - lo) * hop]
+
     def decode_generated(self, codes, bos, pad, eos):
         """modeling_parler_tts.py:2650-2680: batched decode when no special id survived the de-delay, else per sample
         with invalid frames dropped (ptts_filter_frames) and zero right-padding.  Returns (B, T) fp32."""

@@ -174,6 +174,20 @@ def test_dac_44k_architecture_vs_oracle_waveform_1e3(impl):
     assert float((got.cpu() - want).abs().max()) < 1e-3
 
 
+def test_dac_chunked_decode_equals_one_shot_decode():
+    """Streaming form of the DAC decode: chunks decoded with 16 frames of real context on
+    both sides concatenate to the one-shot decode (the decoder's receptive field is 10 frames, see the oracle test)."""
+    sd = dac_oracle.random_dac_state(dac_oracle.DAC_44K, seed=3)
+    eng = DacDecoderEngine(sd, DEV, impl=cabi.IMPL_FAST)
+    codes = torch.randint(0, 1024, (3, 9, 150), generator=torch.Generator().manual_seed(9)).to(DEV)
+    full = eng.decode(codes)
+    chunks = list(eng.decode_chunks(codes, chunk_frames=64))
+    assert [f0 for f0, _ in chunks] == [0, 64, 128]
+    got = torch.cat([w for _, w in chunks], dim=-1)
+    assert got.shape == full.shape
+    assert float((got - full).abs().max()) < 2e-5  # same arithmetic per sample; tile boundaries may differ
+
+
 def test_dac_ragged_path_vs_oracle():
     sd = dac_oracle.random_dac_state(DAC_TINY, seed=31)
     eng = DacDecoderEngine(sd, DEV, DAC_TINY["rates"], cabi.IMPL_SIMPLE)

@@ -142,3 +142,23 @@ def test_dac_encode_vs_transformers(golden_dir):
     assert float((lat - torch.from_numpy(z["z"])).abs().max()) < 1e-5
     assert np.array_equal(dac_oracle.rvq_encode(sd, lat, cfg).numpy(), z["codes"])
     assert dac_oracle.encode_audio(sd, audio[..., : 512 * 8 + 100], cfg).shape == (2, 3, 9)
+
+
+def test_dac_decoder_receptive_field_is_ten_frames():
+    """The chunked (streaming) DAC decode of parler_tts_b200/dac.py relies on this: an output frame of the 44.1 kHz
+    decoder sees exactly 10 frames of context on either side (first conv 3 + block 1: 7), so a chunk decoded with a
+    halo >= 10 equals the same frames of the one-shot decode; 9 is not enough."""
+    import torch
+
+    from oracle import dac_oracle
+
+    sd = dac_oracle.random_dac_state(dac_oracle.DAC_44K, seed=2)
+    F, f0, f1 = 36, 12, 24
+    codes = torch.randint(0, 1024, (1, 9, F), generator=torch.Generator().manual_seed(6))
+    full = dac_oracle.decode_codes(sd, codes, dtype=torch.float64)[:, :, f0 * 512 : f1 * 512]
+    err = {}
+    for halo in (9, 10):
+        lo, hi = f0 - halo, f1 + halo
+        part = dac_oracle.decode_codes(sd, codes[:, :, lo:hi], dtype=torch.float64)
+        err[halo] = float((part[:, :, (f0 - lo) * 512 : (f1 - lo) * 512] - full).abs().max())
+    assert err[10] == 0.0 and err[9] > 1e-7, err
