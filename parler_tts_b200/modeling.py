@@ -154,6 +154,13 @@ class DACModel(nn.Module):
             return (audio,)
         return SimpleNamespace(audio_values=audio)
 
+    def decode_chunks(self, audio_codes, chunk_frames=128):
+        """Streaming form of `decode` (not in the reference): yields (first_frame,
+        audio (B, 1, hop * n)) chunk by chunk; their concatenation equals `decode(audio_codes).audio_values`."""
+        if len(audio_codes) != 1:
+            raise ValueError(f"Expected one frame, got {len(audio_codes)}")
+        yield from self.engine().decode_chunks(audio_codes[0], chunk_frames)
+
     def encoder_engine(self, impl=cabi.IMPL_FAST):
         dev = next(self.parameters()).device
         if self._enc_engine is None or self._enc_engine.device != dev or self._enc_engine.impl != impl:
