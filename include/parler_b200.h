@@ -8,8 +8,17 @@
  * Conventions
  *   - extern "C", plain pointers and sizes.  All tensor pointers are DEVICE pointers owned by the caller (PyTorch
  *     allocates; the library never allocates, frees or keeps a pointer after the call returns).
- *   - ptts_stream_t is a cudaStream_t (torch.cuda.current_stream().cuda_stream).  No call synchronises the host;
- *     no host-side state changes per call, so every call is CUDA-graph capturable and replayable.
+ *   - ptts_stream_t is a cudaStream_t (torch.cuda.current_stream().cuda_stream).  No call synchronises the host and
+ *     no call changes state that a later call's RESULT depends on, so every call is CUDA-graph capturable and
+ *     replayable.  Host state the library does keep (process-wide, guarded by a mutex where it is shared):
+ *       * a cache of CUtensorMap descriptors keyed by (base pointer, rows, cols, row pitch in bytes, box rows, element
+ *         type) for the TMA operand loads of the tcgen05 GEMM / cross-attention block.  A descriptor only encodes that
+ *         key, so a buffer freed and re-allocated at the same address with another shape gets another entry; the
+ *         cache is cleared when it exceeds 4096 entries;
+ *       * per-kernel high-water marks of cudaFuncAttributeMaxDynamicSharedMemorySize (raised on first use);
+ *       * the launch tally behind ptts_launch_count() and the thread-local text behind ptts_last_error_string().
+ *     Environment variables are NOT read by this library (the diagnostic build libparler_b200_diag.so, `make DIAG=1`,
+ *     is the one with PTTS_* knobs and the ptts_diag_* exports of include/parler_b200_diag.h).
  *   - return value: 0 = ok; non-zero = PTTS_E_* (argument or launch error), text in ptts_last_error_string().
  *   - "T" tensors have the element type named by a PTTS_F32 / PTTS_BF16 enum; accumulation is always fp32.
  *   - dynamic scalars that change between graph replays (current sequence length) live in the device-resident
@@ -32,12 +41,12 @@ typedef void* ptts_stream_t;
 #define PTTS_API
 #endif
 
-enum { PTTS_F32 = 0, PTTS_BF16 = 1 };
+enum { PTTS_F32 = 0, PTTS_BF16 = 1, PTTS_FP8 = 2 /* e4m3, self-attention KV cache only */ };
 enum { PTTS_ACT_NONE = 0, PTTS_ACT_GELU = 1, PTTS_ACT_RELU = 2, PTTS_ACT_SILU = 3, PTTS_ACT_GELU_TANH = 4 };
 enum { PTTS_OK = 0, PTTS_E_ARG = 1, PTTS_E_LAUNCH = 2, PTTS_E_UNSUPPORTED = 3 };
 enum { PTTS_IMPL_SIMPLE = 0, PTTS_IMPL_FAST = 1 };
 
-#define PTTS_ABI_VERSION 1
+#define PTTS_ABI_VERSION 2
 #define PTTS_MAX_CODEBOOKS 16
 
 /* Device-resident control block (int32 words), one per generation state.  Written only by kernels. */
@@ -90,7 +99,7 @@ typedef struct {
   uint64_t seed; int64_t row_offset; /* seed: informational (the kernels read the key from PttsCtrl.reserved);
                                         row_offset: global row index of local row 0 (batch sharding) */
   PttsCtrl* ctrl;
-  void* kv_self;           /* [L][2][B][heads][c_max][d]  T */
+  void* kv_self;           /* [L][2][B][heads][c_max][d]  kv_dtype */
   void* kv_cross;          /* [L][2][B][heads][S][d]      T */
   const int32_t* enc_mask; /* [B][S] or NULL */
   const int32_t* prompt_mask; /* [B][P] or NULL */
@@ -104,6 +113,19 @@ typedef struct {
   int64_t* ids;            /* [B*K][max_len] raw generated ids */
   const int64_t* mask;     /* [B*K][max_len] delay-pattern mask */
   int32_t* unfinished;     /* [B*K] */
+  /* ---- ABI 2 */
+  int32_t kv_dtype;        /* element type of kv_self: the weight dtype (PTTS_F32 / PTTS_BF16), or PTTS_FP8: e4m3 rows with
+                              one dequantisation scale per (layer, K|V, head); needs bf16 weights + PTTS_IMPL_FAST */
+  int32_t min_length;      /* epilogue: EOS is suppressed while `ids` holds fewer than this many columns = max(min_length,
+                              T0 + min_new_tokens) of transformers' MinLength / MinNewTokensLength processors; 0 = off */
+  float top_p;             /* epilogue, sampling only: nucleus filter (TopPLogitsWarper, min_tokens_to_keep 1); >= 1 = off */
+  float repetition_penalty;/* epilogue: RepetitionPenaltyLogitsProcessor over the row's own history; 1 = off */
+  int32_t logits_premixed; /* guidance_scale > 1 only: rows [0, B/2*K) of `logits` already hold the guidance-mixed scores
+                              (host-side logits processors ran); the epilogue skips its own mix */
+  int32_t reserved1;
+  float* kv_scale;         /* [L][2][heads] fp32, PTTS_FP8 only: written by ptts_prefill, read by ptts_decode_step */
+  void* kv_stage;          /* [L][2][B][heads][P+T0][d] T, PTTS_FP8 only: staging cache of the prefill */
+  int64_t pad_id, eos_id;  /* generation-config ids used by the epilogue (may differ from the decoder config's) */
 } PttsState;
 
 PTTS_API int32_t ptts_abi_version(void);
@@ -112,21 +134,6 @@ PTTS_API int64_t ptts_scratch_floats(const PttsModel* m, int32_t rows);
 /* Cumulative number of kernel launches this library has enqueued from the calling process (one per PTTS launch
  * site executed on the host; a CUDA-graph replay re-runs the launches recorded at capture time). */
 PTTS_API int64_t ptts_launch_count(void);
-
-/* Diagnostic (not on the product path): enqueues a chain of n dependent trivial kernels (mode 0: empty, mode 1: one
- * load + store per thread over buf[ctas*128]) so that the per-launch latency floor of a graph replay can be measured. */
-PTTS_API int ptts_diag_chain(int32_t n, int32_t mode, int32_t ctas, float* buf, ptts_stream_t s);
-
-/* Diagnostic: globaltimer stamps of the tcgen05 GEMM recorded under PTTS_GEMM_DBG=1 (8 x uint64 per launch). */
-PTTS_API int ptts_diag_gemm_stamps(uint64_t* host, int32_t n_launches);
-
-/* Diagnostic (PTTS_XB_DBG=1): 8 x uint64 per-phase SM-clock sums of the fused cross-attention block; reset != 0
- * clears them. */
-PTTS_API int ptts_diag_xblock(uint64_t* host, int32_t reset);
-
-/* Diagnostic (PTTS_TIMELINE=1): per-launch globaltimer slots {first start, first/last dependency resolved, last end}
- * of the fast-family kernels.  cmd 0 = reset, cmd 1 = read (4 x uint64 per slot + launch-site tag); returns #slots. */
-PTTS_API int ptts_diag_timeline(int32_t cmd, uint64_t* host, int32_t* kinds, int32_t max_slots);
 
 /* ---- integer kernels -------------------------------------------------------------------------------------- */
 /* build_delay_pattern_mask, modeling_parler_tts.py:77-139.  first_start (device int32[1]) receives the number of
@@ -152,6 +159,11 @@ PTTS_API int ptts_filter_frames(const int64_t* codes, int32_t B, int32_t K, int3
 PTTS_API int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T0,
                        const float* prompt_table, const int64_t* prompt_ids, const float* prompt_hidden, int32_t P,
                        float* h_out, ptts_stream_t s);
+/* The same for T token columns without prompt: h_out[b][t] = sum_k embed_tokens[k](ids[b*K+k][t]) + positions[pos0 + t]
+ * (the decode-time branch of modeling_parler_tts.py:836,884-886 with past_key_values_length = pos0); used by
+ * ParlerTTSForCausalLM.forward(past_key_values=...). */
+PTTS_API int ptts_embed_tokens(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T,
+                               int32_t pos0, float* h_out, ptts_stream_t s);
 /* nn.LayerNorm (eps 1e-5), modeling_parler_tts.py:446,467,487,959.  x fp32 [rows][H] -> y T */
 PTTS_API int ptts_layernorm(const float* x, const float* g, const float* b, int32_t rows, int32_t H, float eps, void* y,
                    int32_t ydtype, ptts_stream_t s);
@@ -168,6 +180,19 @@ PTTS_API int ptts_attention(const void* q, const void* cache_k, const void* cach
                    int32_t d, int32_t Tq, int32_t c_stride, int32_t ctx_base, const int32_t* ctx_dyn, int32_t causal,
                    const int32_t* key_mask, int32_t mask_len, void* out, float* scratch, int32_t impl,
                    ptts_stream_t s);
+
+/* The same over an e4m3 cache [B][heads][c_stride][64] (PttsState.kv_dtype = PTTS_FP8): q bf16 [B][H] already
+ * scaled, k_scale / v_scale [heads] fp32 dequantisation multipliers, out bf16 [B][H].  Tq = 1, d = 64. */
+PTTS_API int ptts_attention_fp8(const void* q, const void* cache_k, const void* cache_v, const float* k_scale,
+                                const float* v_scale, int32_t B, int32_t heads, int32_t d, int32_t c_stride,
+                                int32_t ctx_base, const int32_t* ctx_dyn, const int32_t* key_mask, int32_t mask_len,
+                                void* out, float* scratch, ptts_stream_t s);
+/* Quantises staged bf16 cache rows [n_lk][B][heads][slots][64] (n_lk = layers x {K, V}) into the e4m3 cache
+ * [n_lk][B][heads][c_max][64]: scale[n_lk][heads] = 4 * amax / 448 over the staged rows (head-room for later tokens),
+ * rows converted with saturation.  amax_ws: n_lk * heads uint32 of workspace.  ptts_prefill calls this itself when
+ * kv_dtype = PTTS_FP8; exported for tests. */
+PTTS_API int ptts_kv_quantize_fp8(const void* stage, int32_t n_lk, int32_t B, int32_t heads, int32_t d, int32_t slots,
+                                  int32_t c_max, uint32_t* amax_ws, float* scale, void* cache, ptts_stream_t s);
 
 /* ---- the hot path -------------------------------------------------------------------------------------------- */
 /* Cross-attention K/V of all layers from the projected encoder states (modeling_parler_tts.py:297-298), once per
@@ -203,22 +228,19 @@ PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T
                       ptts_stream_t s);
 
 
-/* ---- DAC decode, fast family: channels-last activations [B][T][C] fp32, tensor-core implicit GEMM ---------------- */
-/* weights are pre-split on the host into two bf16 planes (w = hi + mid) laid out [taps][N][Cin]; see
- * parler_tts_b200/dac.py.  Same arithmetic as ptts_dac_conv1d / ptts_dac_convtr1d above.
- * Pre-tiled form (default, feeds the warp-specialised tcgen05 kernel with one bulk copy per pipeline stage): pass
- * w_mid = NULL and w_hi = ONE buffer [n_tile][Cin/32][taps][plane hi|mid][4][bn][8] bf16 with bn = ptts_dac_tile_n(N),
- * N = Cout (conv1d) or stride*Cout (convtr1d), rows n >= N zero-filled.  ptts_dac_pretiled() tells the host which
- * form the library wants (PTTS_DAC=umma|mma selects the older kernels, which take the two planes). */
+/* ---- DAC decode, fast family: channels-last activations [B][T][C] fp32, tcgen05 implicit GEMM ------------------- */
+/* fp32 semantics on the bf16 tensor core: every operand is split x = hi + mid (two bf16) and each product is three
+ * MMAs.  Weights are pre-split and PRE-TILED on the host (parler_tts_b200/dac.py) into ONE buffer
+ * [n_tile][Cin/32][taps][plane hi|mid][4][bn][8] bf16 with bn = ptts_dac_tile_n(N), N = Cout (conv1d) or stride*Cout
+ * (convtr1d), rows n >= N zero-filled: the shared-memory image of one pipeline stage, moved by one bulk copy. */
 PTTS_API int ptts_dac_tile_n(int32_t N);
-PTTS_API int ptts_dac_pretiled(void);
 /* "Planes": an activation tensor stored the way the tensor core wants it - Snake already applied, split into two
  * bf16 planes (x = hi + mid), 8-channel panels: [B][2 (hi, mid)][C/8][PAD_LO + T + PAD_HI][8] bf16 (4 bytes per
  * element, like fp32).  Row PAD_LO - 1 and row PAD_LO + T must be zero (the caller zeroes the pads once), the other pad
  * rows only need to exist.  A conv writes planes for its consumer (out_alpha = the consumer's Snake alpha, NULL = no
  * activation) from its otherwise idle epilogue warps, and the consumer then streams them with bulk copies instead of
  * activating its input again for every column tile (a k=1 conv, or a transposed conv with 6..48 column tiles).
- * Exactly one of x / x_planes; y and/or y_planes; weights pre-tiled (see above); snake_alpha only with x. */
+ * Exactly one of x / x_planes; y and/or y_planes; snake_alpha only with x. */
 #define PTTS_DAC_PLANE_PAD_LO 8
 #define PTTS_DAC_PLANE_PAD_HI 264
 PTTS_API int ptts_dac_conv1d_px(const float* x, const void* x_planes, int32_t B, int32_t T, int32_t Cin,
@@ -230,15 +252,6 @@ PTTS_API int ptts_dac_convtr1d_px(const float* x, const void* x_planes, int32_t 
                                   const float* snake_alpha, float* y, ptts_stream_t s);
 PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
                          const float* tables, int32_t codebook_size, int32_t latent, float* z, ptts_stream_t s);
-/* y[b][t][co] = bias + sum_k sum_ci snake(x)[b][t + (k - (ksize-1)/2)*dilation][ci] * w[k][co][ci] [+ residual] */
-PTTS_API int ptts_dac_conv1d_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const void* w_hi, const void* w_mid,
-                        const float* bias, int32_t Cout, int32_t ksize, int32_t dilation, const float* snake_alpha,
-                        const float* residual, float* y, ptts_stream_t s);
-/* conv_transpose1d(snake(x)), kernel 2*stride, padding ceil(stride/2); w planes [2][stride*Cout][Cin] with
- * w2[tap][ph*Cout + co][ci] = w[ci][co][ph + tap*stride]; y [B][T*stride][Cout] */
-PTTS_API int ptts_dac_convtr1d_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const void* w_hi, const void* w_mid,
-                          const float* bias, int32_t Cout, int32_t stride, const float* snake_alpha, float* y,
-                          ptts_stream_t s);
 /* final conv (Cout = 1, k = 7) + tanh: w [7][Cin] fp32, y [B][T] */
 PTTS_API int ptts_dac_conv_out_nwc(const float* x, int32_t B, int32_t T, int32_t Cin, const float* w, const float* bias,
                           const float* snake_alpha, float* y, ptts_stream_t s);

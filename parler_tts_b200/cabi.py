@@ -7,14 +7,15 @@ import ctypes as C
 import os
 
 _HERE = os.path.dirname(os.path.abspath(__file__))
-# PTTS_LIBRARY: another build of the same library (A/B runs of compile-time variants); default = the in-tree build
+# PTTS_LIBRARY: another build of the same library (the diagnostic build of profiles/scripts, A/B runs of compile-time
+# variants); default = the in-tree product build.  bench.py refuses to run with it set.
 LIB_PATH = os.environ.get("PTTS_LIBRARY") or os.path.join(_HERE, "libparler_b200.so")
 
-PTTS_F32, PTTS_BF16 = 0, 1
+PTTS_F32, PTTS_BF16, PTTS_FP8 = 0, 1, 2
 ACT = {"none": 0, "gelu": 1, "relu": 2, "silu": 3, "gelu_new": 4}
 IMPL_SIMPLE, IMPL_FAST = 0, 1
 MAX_CODEBOOKS = 16
-ABI_VERSION = 1
+ABI_VERSION = 2
 
 c_i32, c_i64, c_f32, c_u64, c_vp = C.c_int32, C.c_int64, C.c_float, C.c_uint64, C.c_void_p
 
@@ -42,7 +43,9 @@ class PttsState(C.Structure):
                 ("suppress_from", c_i32), ("guidance_scale", c_f32), ("seed", c_u64), ("row_offset", c_i64),
                 ("ctrl", c_vp), ("kv_self", c_vp), ("kv_cross", c_vp), ("enc_mask", c_vp), ("prompt_mask", c_vp),
                 ("h", c_vp), ("xn", c_vp), ("q", c_vp), ("attn", c_vp), ("ffn", c_vp), ("logits", c_vp),
-                ("scratch", c_vp), ("ids", c_vp), ("mask", c_vp), ("unfinished", c_vp)]
+                ("scratch", c_vp), ("ids", c_vp), ("mask", c_vp), ("unfinished", c_vp),
+                ("kv_dtype", c_i32), ("min_length", c_i32), ("top_p", c_f32), ("repetition_penalty", c_f32),
+                ("logits_premixed", c_i32), ("reserved1", c_i32), ("kv_scale", c_vp), ("kv_stage", c_vp), ("pad_id", c_i64), ("eos_id", c_i64)]
 
 
 class PttsT5Layer(C.Structure):
@@ -64,20 +67,20 @@ PROTOTYPES = {
     "ptts_last_error_string": (C.c_char_p, []),
     "ptts_scratch_floats": (c_i64, [_PM, c_i32]),
     "ptts_launch_count": (c_i64, []),
-    "ptts_diag_chain": (C.c_int, [c_i32, c_i32, c_i32, c_vp, c_vp]),
-    "ptts_diag_gemm_stamps": (C.c_int, [c_vp, c_i32]),
-    "ptts_diag_timeline": (C.c_int, [c_i32, c_vp, c_vp, c_i32]),
-    "ptts_diag_xblock": (C.c_int, [c_vp, c_i32]),
     "ptts_build_delay_mask": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_vp, c_vp]),
     "ptts_apply_delay_mask": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_vp, c_i64, c_vp]),
     "ptts_dedelay": (C.c_int, [c_vp, c_i64, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "ptts_filter_frames": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i64, c_vp, c_vp, c_vp]),
     "ptts_embed_prefill": (C.c_int, [_PM, c_vp, c_i64, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp]),
+    "ptts_embed_tokens": (C.c_int, [_PM, c_vp, c_i64, c_i32, c_i32, c_i32, c_vp, c_vp]),
     "ptts_layernorm": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_f32, c_vp, c_i32, c_vp]),
     "ptts_linear": (C.c_int, [c_vp, c_i32, c_vp, c_i32, c_vp, c_i32, c_i32, c_i32, c_f32, c_i32, c_vp, c_vp, c_vp,
                               c_i32, c_i32, c_vp]),
     "ptts_attention": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i32,
                                  c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "ptts_attention_fp8": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32,
+                                     c_vp, c_vp, c_vp]),
+    "ptts_kv_quantize_fp8": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "ptts_cross_kv": (C.c_int, [_PM, _PS, c_vp, c_vp]),
     "ptts_prefill": (C.c_int, [_PM, _PS, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp]),
     "ptts_decode_step": (C.c_int, [_PM, _PS, c_i32, c_vp]),
@@ -87,21 +90,26 @@ PROTOTYPES = {
                                   c_vp, c_i32, c_vp]),
     "ptts_dac_convtr1d": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
     "ptts_dac_dequant_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32, c_vp, c_vp]),
-    "ptts_dac_conv1d_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp,
-                                      c_vp, c_vp]),
-    "ptts_dac_convtr1d_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
     "ptts_dac_conv_out_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ptts_dac_tile_n": (C.c_int, [c_i32]),
     "ptts_dac_conv1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp,
                                      c_vp, c_vp, c_vp]),
     "ptts_dac_convtr1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),
-    "ptts_dac_pretiled": (C.c_int, []),
     "ptts_dac_conv1d_strided": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp,
                                           c_vp]),
     "ptts_dac_vq_encode": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp, c_vp,
                                      c_vp, c_vp]),
     "ptts_t5_workspace_bytes": (c_i64, [_PT5, c_i32]),
     "ptts_t5_encode": (C.c_int, [_PT5, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_i32, c_vp]),
+}
+
+# include/parler_b200_diag.h: present only in libparler_b200_diag.so (make DIAG=1; profiles/scripts select it with
+# PTTS_LIBRARY).  Bound when the loaded library exports them, never required.
+DIAG_PROTOTYPES = {
+    "ptts_diag_chain": (C.c_int, [c_i32, c_i32, c_i32, c_vp, c_vp]),
+    "ptts_diag_gemm_stamps": (C.c_int, [c_vp, c_i32]),
+    "ptts_diag_timeline": (C.c_int, [c_i32, c_vp, c_vp, c_i32]),
+    "ptts_diag_xblock": (C.c_int, [c_vp, c_i32]),
 }
 
 _lib = None
@@ -124,6 +132,10 @@ def load():
     for name, (res, args) in PROTOTYPES.items():
         fn = getattr(lib, name)  # AttributeError if the .so does not export a declared symbol
         fn.restype, fn.argtypes = res, args
+    for name, (res, args) in DIAG_PROTOTYPES.items():
+        fn = getattr(lib, name, None)
+        if fn is not None:
+            fn.restype, fn.argtypes = res, args
     v = lib.ptts_abi_version()
     if v != ABI_VERSION:
         raise ParlerB200Error(f"ABI mismatch: library {v}, binding {ABI_VERSION}")

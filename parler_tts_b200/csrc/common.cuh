@@ -38,7 +38,21 @@ void count_launch();  // host-side tally of kernel launches enqueued by this lib
     if (rc__ != PTTS_OK) return rc__;  \
   } while (0)
 
-bool pdl_enabled();  // PTTS_PDL=0 disables programmatic dependent launch (default on)
+// ---- knobs.  The product library is built WITHOUT PTTS_DIAG: every PTTS_KNOB is its compile-time default, nothing
+// reads the environment and the ablation / timeline code is unreachable.  The diagnostic library (make DIAG=1 ->
+// libparler_b200_diag.so, used by profiles/scripts only) reads the named environment variable instead.
+#ifdef PTTS_DIAG
+int knob_env(const char* name, int dflt);  // atoi(getenv(name)) or dflt; cached per call site by the caller
+#define PTTS_KNOB(name, dflt)                              \
+  ([]() -> int {                                           \
+    static const int v__ = ::ptts::knob_env(name, dflt);   \
+    return v__;                                            \
+  }())
+#else
+#define PTTS_KNOB(name, dflt) (dflt)
+#endif
+
+inline bool pdl_enabled() { return PTTS_KNOB("PTTS_PDL", 1) != 0; }  // programmatic dependent launch
 
 // Launch helper of the fast family: cudaLaunchKernelEx, with the programmatic-stream-serialization attribute when
 // PDL is enabled (works eagerly and under stream capture into a CUDA graph).
@@ -115,7 +129,11 @@ __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.laun
 struct TL {
   unsigned long long* p;
 };
+#ifdef PTTS_DIAG
 TL tl_next(int kind);  // host: next timeline slot (null unless PTTS_TIMELINE=1); kind = tag of the launch site
+#else
+inline TL tl_next(int) { return TL{nullptr}; }
+#endif
 __device__ __forceinline__ unsigned long long gtimer_ns() {
   unsigned long long t;
   asm volatile("mov.u64 %0, %%globaltimer;\n" : "=l"(t));
@@ -166,7 +184,8 @@ struct L2Hint {
 };
 void set_l2_hint(const void* ptr, long long bytes);  // host; PTTS_WPF bit mask selects which sites call it
 L2Hint take_l2_hint();                               // host: the pending hint (or {null, 0}); clears it
-int wpf_mask();                                      // PTTS_WPF bit mask of hint sites (default 0, see error.cu)
+// bit mask of hint sites; measured on B200 (B=64, 860 frames): every site costs 0-17 us per decode step -> 0
+inline int wpf_mask() { return PTTS_KNOB("PTTS_WPF", 0); }
 __device__ __forceinline__ void l2_hint_prefetch(const L2Hint& hint, int cta, int n_ctas) {
   if (!hint.ptr) return;
   constexpr long long kPiece = 8192;

@@ -202,9 +202,7 @@ extern "C" int ptts_dac_conv1d(const float* x, int32_t B, int32_t Cin, int32_t T
   PTTS_CHECK_ARG(x && w && y, "dac_conv1d: null pointer");
   PTTS_CHECK_ARG(B > 0 && Cin > 0 && Cout > 0 && T > 0 && dilation > 0, "dac_conv1d: bad dims");
   PTTS_CHECK_ARG(ksize == 1 || ksize == 7, "dac_conv1d: kernel size must be 1 or 7");
-  if (impl == PTTS_IMPL_FAST && fast_conv_supported(Cin, Cout, ksize))
-    return dac_conv1d_fast(x, B, Cin, T, w, bias, Cout, ksize, dilation, snake_alpha, residual, tanh_out, y,
-                           as_stream(s));
+  (void)impl;  // the NCW entry points are the simple family; the fast family is ptts_dac_conv1d_px (channels-last)
   const int halo = dilation * (ksize - 1) / 2;
   const size_t smem = sizeof(float) * (8 * (64 + 2 * halo) + 8 * ksize * 64);
   dim3 grid((T + 63) / 64, (Cout + 63) / 64, B);

@@ -46,11 +46,52 @@ static int check_state(const PttsModel* m, const PttsState* s) {
                      s->ids && s->mask && s->unfinished,
                  "null state tensor");
   PTTS_CHECK_ARG(s->S == 0 || s->kv_cross, "null cross cache");
+  if (s->kv_dtype == PTTS_FP8) {
+    PTTS_CHECK_ARG(m->wdtype == PTTS_BF16 && s->impl == PTTS_IMPL_FAST && attention_fp8_supported(m->head_dim),
+                   "fp8 KV cache needs bf16 weights, the fast kernel family and head_dim 64");
+    PTTS_CHECK_ARG(s->kv_scale && s->kv_stage, "fp8 KV cache: null kv_scale / kv_stage");
+  } else {
+    PTTS_CHECK_ARG(s->kv_dtype == m->wdtype, "kv_dtype must be the weight dtype or PTTS_FP8");
+  }
   return PTTS_OK;
 }
 
 static inline size_t kv_layer_elems(const PttsModel* m, int B, int slots) {
   return (size_t)B * m->n_heads * slots * m->head_dim;
+}
+
+// Self-attention cache of layer l as the kernels of this call see it.  With an fp8 cache the PREFILL (Tq > 1) runs on
+// the bf16 staging cache of P + T0 slots (kv_stage) and ptts_prefill quantises it afterwards; decode steps see the
+// e4m3 cache and the per-(layer, K|V, head) scales.
+struct KvView {
+  void* k;
+  void* v;
+  const float* k_scale;
+  const float* v_scale;
+  int c_stride;
+  int dtype;
+};
+static KvView self_kv(const PttsModel* m, const PttsState* s, int l, int Tq) {
+  KvView kv = {};
+  if (s->kv_dtype == PTTS_FP8 && Tq == 1) {
+    const size_t le = kv_layer_elems(m, s->B, s->c_max);
+    kv.k = (char*)s->kv_self + (size_t)(2 * l) * le;
+    kv.v = (char*)s->kv_self + (size_t)(2 * l + 1) * le;
+    kv.k_scale = s->kv_scale + (size_t)(2 * l) * m->n_heads;
+    kv.v_scale = s->kv_scale + (size_t)(2 * l + 1) * m->n_heads;
+    kv.c_stride = s->c_max;
+    kv.dtype = PTTS_FP8;
+    return kv;
+  }
+  const bool staged = s->kv_dtype == PTTS_FP8;
+  const int slots = staged ? s->P + s->T0 : s->c_max;
+  const size_t es = dtype_size(m->wdtype), le = kv_layer_elems(m, s->B, slots);
+  char* base = (char*)(staged ? s->kv_stage : s->kv_self);
+  kv.k = base + (size_t)(2 * l) * le * es;
+  kv.v = base + (size_t)(2 * l + 1) * le * es;
+  kv.c_stride = slots;
+  kv.dtype = m->wdtype;
+  return kv;
 }
 
 // Scratch layout: [0, 64) grid-barrier counters of the fused GEMM finisher (zero between launches; the caller hands
@@ -72,7 +113,6 @@ struct Pending {
   const float* part = nullptr;
   int S = 0;
   int64_t stride = 0;
-  const float* ln_done = nullptr;  // gamma of the LayerNorm the producing GEMM's finisher has already applied
   const float* rowblk = nullptr;   // further slices stored row-contiguously [rows][n_blk][H] (cross-attention block)
   int n_blk = 0;
 };
@@ -95,11 +135,6 @@ static Path pick_path(const PttsModel* m, const PttsState* s) {
 static int ln_step(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const float* g,
                    const float* b, int rows_out, int row_mul, int row_add, cudaStream_t st) {
   const int H = m->hidden;
-  if (pend.ln_done) {  // the residual GEMM folded its partial sums and wrote this LayerNorm itself
-    PTTS_CHECK_ARG(pend.ln_done == g && row_mul == 1 && row_add == 0, "internal: fused LayerNorm mismatch");
-    pend = Pending();
-    return PTTS_OK;
-  }
   if (path.ln) {
     PTTS_CHECK_ARG(!pend.rowblk || (row_mul == 1 && row_add == 0), "internal: row block with a row map");
     PTTS_TRY(layernorm_fast(s->h, pend.part, pend.S, pend.stride, g, b, rows_out, H, 1e-5f, row_mul, row_add, s->xn,
@@ -112,85 +147,43 @@ static int ln_step(const PttsModel* m, const PttsState* s, const Path& path, Pen
 }
 
 // Residual GEMMs (out_proj, fc2) write split-K partial sums that the next LayerNorm folds into the residual stream in
-// slice order (deterministic, no on-chip reduction); PTTS_GEMM=cluster selects the in-cluster DSMEM reduction instead.
-static bool split_k_partials_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_GEMM");
-    v = (e && e[0] == 'c') ? 0 : 1;
-  }
-  return v == 1;
-}
+// slice order (deterministic, no on-chip reduction); the diagnostic build can fall back to the STORE epilogue with
+// PTTS_SPLITK_PARTIALS=0.
+static bool split_k_partials_enabled() { return PTTS_KNOB("PTTS_SPLITK_PARTIALS", 1) != 0; }
 
-// PTTS_QKV=scatter keeps the cluster GEMM with the scatter epilogue for the decode-step QKV / cross-q projections
-static bool qkv_fusion_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_QKV");
-    v = (e && e[0] == 's') ? 0 : 1;
-  }
-  return v == 1;
-}
+// diagnostic build, PTTS_QKV_FUSE=0: the decode-step QKV / cross-q projections keep the scatter epilogue
+static bool qkv_fusion_enabled() { return PTTS_KNOB("PTTS_QKV_FUSE", 1) != 0; }
 
-// PTTS_FC1=cluster keeps the cluster GEMM with the fused activation epilogue for the decode-step fc1
-static bool fc1_partials_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_FC1");
-    v = (e && e[0] == 'c') ? 0 : 1;
-  }
-  return v == 1;
-}
+// diagnostic build, PTTS_FC1_PARTIALS=0: the decode-step fc1 keeps the STORE epilogue with the fused activation
+static bool fc1_partials_enabled() { return PTTS_KNOB("PTTS_FC1_PARTIALS", 1) != 0; }
 
 // PTTS_SKIP=<bitmask>: timing ablation ONLY (results are garbage): 1 LayerNorm, 2 QKV GEMM, 4 self-attention,
 // 8 residual GEMMs, 16 cross q GEMM, 32 cross-attention, 64 fc1, 128 heads.  Used by profiles/scripts/ablate.sh to get
 // the marginal cost of each kernel class inside the PDL-overlapped graph (ncu serialises launches and cannot).
+// Compiled into the DIAGNOSTIC library only (make DIAG=1): the product library always runs every kernel.
+#ifdef PTTS_DIAG
 static int skip_mask() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_SKIP");
-    v = e ? atoi(e) : 0;
-  }
+  static const int v = PTTS_KNOB("PTTS_SKIP", 0);
   return v;
 }
 #define PTTS_UNLESS_SKIPPED(bit, expr) \
   do {                                  \
     if (!(skip_mask() & (bit))) PTTS_TRY(expr); \
   } while (0)
+#else
+static constexpr int skip_mask() { return 0; }
+#define PTTS_UNLESS_SKIPPED(bit, expr) PTTS_TRY(expr)
+#endif
 
 // h += x . w^T   (out_proj / fc2 with the residual add of modeling_parler_tts.py:460,483,492)
-// PTTS_LNFUSE=1: let the residual GEMM fold its partial sums and apply the next LayerNorm itself behind a grid-wide
-// arrival counter (no separate launch).  Measured on B200 (B=64): 1.99 ms per decode step against 1.78 ms with the
-// separate fold + LayerNorm launch - the fence + atomic + poll of the barrier and two rows per CTA cost more than the
-// 0.8 us kernel hand-over they replace - so it is OFF by default.
-static bool ln_fusion_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_LNFUSE");
-    v = (e && e[0] == '1') ? 1 : 0;
-  }
-  return v == 1;
-}
-
-// next_g / next_b: the LayerNorm that consumes the residual stream next over the SAME rows (or null): with the
-// tcgen05 split-K kernel and a grid small enough to be co-resident, the GEMM finishes it itself (grid barrier).
 static int residual_linear(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const void* x,
-                           const void* w, int rows, int K, const float* next_g, const float* next_b,
-                           cudaStream_t st) {
+                           const void* w, int rows, int K, cudaStream_t st) {
   const int H = m->hidden, dt = m->wdtype;
   if (path.gemm && path.ln && rows <= 256 && split_k_partials_enabled()) {
     int bn = 64;
     const int S = gemm_bf16_plan_splits(rows, H, K, &bn);
     if (S > 1) {
       float* part = work_area(m, s);
-      const int ctas = ((H + 127) / 128) * ((rows + 63) / 64) * S;
-      if (bn == 0 && next_g && next_b && ctas <= 96 && H % 4 == 0 && ln_fusion_enabled()) {
-        gemm::GemmFinish fin = {s->h, next_g, next_b, s->xn, reinterpret_cast<unsigned int*>(s->scratch), 1e-5f};
-        PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st, &fin));
-        pend = Pending();
-        pend.ln_done = next_g;
-        return PTTS_OK;
-      }
       PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st));
       pend.part = part;
       pend.S = S;
@@ -209,163 +202,121 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
   const PttsLayer& L = m->layers[l];
   const int H = m->hidden, F = m->ffn, heads = m->n_heads, d = m->head_dim, B = s->B, dt = m->wdtype;
   const int rows = B * Tq;
-  const size_t es = dtype_size(dt);
-  char* ks = (char*)s->kv_self + (size_t)(2 * l) * kv_layer_elems(m, B, s->c_max) * es;
-  char* vs = (char*)s->kv_self + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->c_max) * es;
+  const KvView kv = self_kv(m, s, l, Tq);
   const float scale = 1.0f / sqrtf((float)d);
-  // self attention block
+  // ---- self attention block
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln1_g, L.ln1_b, rows, 1, 0, st));
   int bn_q = 64;
   const bool fuse = path.gemm && Tq == 1 && d == 64 && qkv_fusion_enabled();
   const int Sq = fuse ? gemm_bf16_plan_splits(rows, 3 * H, H, &bn_q) : 0;
-  if (fuse && Sq > 1 && bn_q == 0) {
+  const bool fused_self = fuse && Sq > 1 && bn_q == 0;
+  PTTS_CHECK_ARG(kv.dtype != PTTS_FP8 || fused_self || Tq > 1,
+                 "fp8 KV cache: the decode step needs the fused tcgen05 path (bf16 weights, head_dim 64)");
+  if (fused_self) {
     // decode: QKV as split-K partial sums; the attention CTA of (b, head) folds them, scales q and writes the new
     // K / V row into the cache itself
     float* qpart = work_area(m, s);
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
-    // weight prefetch hints (common.cuh): the attention CTAs pull out_proj's matrix into L2 as they finish
-    if (wpf_mask() & 2) set_l2_hint(L.w_o, (long long)H * H * es);
-    PTTS_UNLESS_SKIPPED(4, attention_fast_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, 1, scale, ctx_base - 1, ctx_dyn,
-                                                ks, vs, B, heads, s->c_max, ctx_base, ctx_dyn, s->prompt_mask, s->P,
-                                                s->attn, attn_area(s), nullptr, 0, 0, nullptr, st));
-    goto self_attention_done;
-  }
-  if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
-    PTTS_UNLESS_SKIPPED(2, gemm_bf16_scatter(s->xn, L.w_qkv, rows, 3 * H, H, 1, scale, s->q, ks, vs, H, heads, d, Tq, s->c_max,
-                               ctx_base - Tq, ctx_dyn, st));
+    if (wpf_mask() & 2) set_l2_hint(L.w_o, (long long)H * H * dtype_size(dt));
+    if (kv.dtype == PTTS_FP8)
+      PTTS_UNLESS_SKIPPED(4, attention_fp8_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, scale, ctx_base - 1, ctx_dyn,
+                                                 kv.k, kv.v, kv.k_scale, kv.v_scale, B, heads, kv.c_stride, ctx_base,
+                                                 ctx_dyn, s->prompt_mask, s->P, s->attn, attn_area(s), st));
+    else
+      PTTS_UNLESS_SKIPPED(4, attention_fast_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, 1, scale, ctx_base - 1,
+                                                  ctx_dyn, kv.k, kv.v, B, heads, kv.c_stride, ctx_base, ctx_dyn,
+                                                  s->prompt_mask, s->P, s->attn, attn_area(s), nullptr, 0, 0, nullptr,
+                                                  st));
   } else {
-    void* qkv = (void*)work_area(m, s);
-    PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qkv, dt, nullptr, rows, 3 * H, H, 1.0f, PTTS_ACT_NONE, nullptr,
-                             nullptr, qkv, dt, st));
-    PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, s->c_max, ctx_base - Tq, ctx_dyn, scale, s->q, ks, vs, st));
-  }
-  PTTS_UNLESS_SKIPPED(4, attention_dispatch(s->impl, s->q, ks, vs, dt, B, heads, d, Tq, s->c_max, ctx_base, ctx_dyn,
-                                            Tq > 1, s->prompt_mask, s->P, s->attn, attn_area(s), st));
-self_attention_done:
-  {
-    const bool cross = s->S > 0;
-    // In front of the fused cross-attention block the out_proj GEMM releases its dependent only AFTER its own wait:
-    // released early, the block's CTAs become resident under the self-attention kernel and their pre-wait traffic
-    // (128 KB of Wq per SM, cross K/V and next-layer K prefetches) competes with the K/V stream (PTTS_XB_LATE=0: early,
-    // 2: only when the out_proj's MMA burst is done)
-    static int xb_late = -1;
-    if (xb_late < 0) {
-      const char* e = getenv("PTTS_XB_LATE");
-      xb_late = e ? atoi(e) : 1;
+    if (path.gemm) {  // q (scaled) and the new K/V rows go straight to their buffers / cache slots
+      PTTS_UNLESS_SKIPPED(2, gemm_bf16_scatter(s->xn, L.w_qkv, rows, 3 * H, H, 1, scale, s->q, kv.k, kv.v, H, heads, d,
+                                               Tq, kv.c_stride, ctx_base - Tq, ctx_dyn, st));
+    } else {
+      void* qkv = (void*)work_area(m, s);
+      PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, L.w_qkv, dt, nullptr, rows, 3 * H, H, 1.0f, PTTS_ACT_NONE, nullptr,
+                               nullptr, qkv, dt, st));
+      PTTS_TRY(qkv_scatter(qkv, dt, rows, H, heads, d, Tq, kv.c_stride, ctx_base - Tq, ctx_dyn, scale, s->q, kv.k, kv.v,
+                           st));
     }
-    if (xb_late && cross && fuse && path.ln && dt == PTTS_BF16 && xblock_supported(H, heads, d, s->S))
-      gemm_next_trigger_late(xb_late == 2);
-    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, fuse ? (cross ? L.ln2_g : L.ln3_g) : nullptr,
-                                           fuse ? (cross ? L.ln2_b : L.ln3_b) : nullptr, st));
+    PTTS_UNLESS_SKIPPED(4, attention_dispatch(s->impl, s->q, kv.k, kv.v, dt, B, heads, d, Tq, kv.c_stride, ctx_base,
+                                              ctx_dyn, Tq > 1, s->prompt_mask, s->P, s->attn, attn_area(s), st));
   }
-  // cross attention block (modeling_parler_tts.py:465-483)
-  if (s->S > 0) {
+  const bool cross = s->S > 0;
+  const bool use_xblock = cross && fuse && path.ln && dt == PTTS_BF16 && xblock_supported(H, heads, d, s->S);
+  // In front of the fused cross-attention block the out_proj GEMM releases its dependent only AFTER its own wait:
+  // released early, the block's CTAs become resident under the self-attention kernel and their pre-wait traffic
+  // (128 KB of Wq per SM, cross K/V) competes with the K/V stream (diagnostic build: PTTS_XB_LATE=0 early, 2 only when
+  // the out_proj's MMA burst is done)
+  if (use_xblock) {
+    const int xb_late = PTTS_KNOB("PTTS_XB_LATE", 1);
+    if (xb_late) gemm_next_trigger_late(xb_late == 2);
+  }
+  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
+  // ---- cross attention block (modeling_parler_tts.py:465-483)
+  if (cross) {
+    const size_t es = dtype_size(dt);
     char* kc = (char*)s->kv_cross + (size_t)(2 * l) * kv_layer_elems(m, B, s->S) * es;
     char* vc = (char*)s->kv_cross + (size_t)(2 * l + 1) * kv_layer_elems(m, B, s->S) * es;
     // decode: the whole block (fold + LayerNorm, q projection, attention over the cached T5 K/V, out projection as
     // per-head partial sums) is ONE launch (fast_xblock.cu); the next LayerNorm folds the self-attention out_proj
     // slices and the per-head slices, stored back to back, into the residual stream
-    if (fuse && path.ln && dt == PTTS_BF16 && pend.part && !pend.ln_done && pend.part == work_area(m, s) &&
-        pend.stride == (int64_t)rows * H && xblock_supported(H, heads, d, s->S) &&
+    if (use_xblock && pend.part && pend.part == work_area(m, s) && pend.stride == (int64_t)rows * H &&
         (int64_t)(pend.S + heads) * rows * H <= work_area_floats(m, rows) && !(skip_mask() & (1 | 16 | 32))) {
-      const char* ks_next = l + 1 < m->n_layers
-                                ? (char*)s->kv_self + (size_t)(2 * (l + 1)) * kv_layer_elems(m, B, s->c_max) * es
-                                : nullptr;
       float* xout = work_area(m, s) + (int64_t)pend.S * pend.stride;
       if (wpf_mask() & 4) set_l2_hint(L.w_fc1, (long long)F * H * es);  // fc1 is two launches ahead
-      // PTTS_XB_ROWOUT=0: per-head slices [heads][B][H] folded with strided loads; default: [B][heads][H], which the
-      // next LayerNorm pulls in with one bulk copy per row
-      static int rowout = -1;
-      if (rowout < 0) {
-        const char* e = getenv("PTTS_XB_ROWOUT");
-        rowout = (e && e[0] == '0') ? 0 : 1;
-      }
-      const int by_row = rowout && (int64_t)heads * H * 4 <= 160 * 1024;
+      // per-head slices stored [B][heads][H]: the next LayerNorm pulls a row's slices with one bulk copy (diagnostic
+      // build, PTTS_XB_ROWOUT=0: [heads][B][H] folded with strided loads)
+      const int by_row = PTTS_KNOB("PTTS_XB_ROWOUT", 1) && (int64_t)heads * H * 4 <= 160 * 1024;
       PTTS_TRY(xblock_fast(s->h, pend.part, pend.S, pend.stride, L.ln2_g, L.ln2_b, 1e-5f, L.w_qc, L.w_oc, kc, vc,
-                           s->enc_mask, B, heads, H, s->S, scale, xout, by_row, ks_next, s->c_max, ctx_base, ctx_dyn, st));
+                           s->enc_mask, B, heads, H, s->S, scale, xout, by_row, nullptr, 0, 0, nullptr, st));
       if (by_row) {
         pend.rowblk = xout;
         pend.n_blk = heads;
       } else {
         pend.S += heads;
       }
-      goto cross_attention_done;
-    }
-    PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
-    int bn_c = 64;
-    const int Sc = fuse ? gemm_bf16_plan_splits(rows, H, H, &bn_c) : 0;
-    if (fuse && Sc > 1 && bn_c == 0) {
-      float* qpart = work_area(m, s);
-      if (wpf_mask() & 4) set_l2_hint(L.w_fc1, (long long)F * H * es);
-      PTTS_UNLESS_SKIPPED(16, gemm_bf16_partial(s->xn, L.w_qc, rows, H, H, Sc, 0, qpart, st));
-      // the cross-attention CTAs also queue the L2 prefetch of the NEXT layer's self-attention K rows: HBM is
-      // otherwise idle during the six short kernels between here and that launch
-      const char* ks_next = l + 1 < m->n_layers
-                                ? (char*)s->kv_self + (size_t)(2 * (l + 1)) * kv_layer_elems(m, B, s->c_max) * es
-                                : nullptr;
-      PTTS_UNLESS_SKIPPED(32, attention_fast_fused(qpart, Sc, (int64_t)rows * H, H, 0, scale, 0, nullptr, kc, vc, B,
-                                                   heads, s->S, s->S, nullptr, s->enc_mask, s->S, s->attn, attn_area(s),
-                                                   ks_next, s->c_max, ctx_base, ctx_dyn, st));
     } else {
-      PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale,
-                                              PTTS_ACT_NONE, nullptr, nullptr, s->q, dt, st));
-      PTTS_UNLESS_SKIPPED(32, attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0,
-                                                 s->enc_mask, s->S, s->attn, attn_area(s), st));
+      PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln2_g, L.ln2_b, rows, 1, 0, st));
+      int bn_c = 64;
+      const int Sc = fuse ? gemm_bf16_plan_splits(rows, H, H, &bn_c) : 0;
+      if (fuse && Sc > 1 && bn_c == 0) {
+        float* qpart = work_area(m, s);
+        PTTS_UNLESS_SKIPPED(16, gemm_bf16_partial(s->xn, L.w_qc, rows, H, H, Sc, 0, qpart, st));
+        PTTS_UNLESS_SKIPPED(32, attention_fast_fused(qpart, Sc, (int64_t)rows * H, H, 0, scale, 0, nullptr, kc, vc, B,
+                                                     heads, s->S, s->S, nullptr, s->enc_mask, s->S, s->attn,
+                                                     attn_area(s), nullptr, 0, 0, nullptr, st));
+      } else {
+        PTTS_UNLESS_SKIPPED(16, linear_dispatch(s->impl, s->xn, dt, L.w_qc, dt, nullptr, rows, H, H, scale,
+                                                PTTS_ACT_NONE, nullptr, nullptr, s->q, dt, st));
+        PTTS_UNLESS_SKIPPED(32, attention_dispatch(s->impl, s->q, kc, vc, dt, B, heads, d, Tq, s->S, s->S, nullptr, 0,
+                                                   s->enc_mask, s->S, s->attn, attn_area(s), st));
+      }
+      PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, st));
     }
-    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_oc, rows, H, fuse ? L.ln3_g : nullptr,
-                                           fuse ? L.ln3_b : nullptr, st));
   }
-cross_attention_done:
-  // feed forward block
-  if (fuse && (wpf_mask() & 8)) set_l2_hint(L.w_fc2, (long long)F * H * es);  // fc2 is three launches ahead
+  // ---- feed forward block
+  if (fuse && (wpf_mask() & 8)) set_l2_hint(L.w_fc2, (long long)F * H * dtype_size(dt));  // fc2 is three launches ahead
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
-  {
-    int bn_f = 64;
-    const int Sf = (fuse && fc1_partials_enabled()) ? gemm_bf16_plan_splits(rows, F, H, &bn_f) : 0;
-    if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
-      // decode: fc1 as split-K partial sums + one small reduce / activation kernel (no cluster, no on-chip reduction)
-      float* fpart = work_area(m, s);
-      // PTTS_FC1_PAIR=1: with two K slices the CTA that stores its partial tile second folds both, applies the activation
-      // and writes the bf16 operand of fc2 itself (no reduce + activation launch); 2: the GEMM also releases fc2 only
-      // when its MMA burst is done.  Measured on B200 (B=64, 860 frames): 1.539 / 1.548 ms per decode step against
-      // 1.457 ms with the separate launch - the 32 "second" CTAs do on 32 SMs (fence, ticket, 64 KB of slices, 8 192
-      // erff each: fc1 8.7 us instead of 3.1 us) what the reduce + activation kernel spreads over all 148 - default 0.
-      // (Its first version, activation fully unrolled, was 160 KB of straight-line code: 29 us per launch of cold
-      // instruction fetch.)
-      static int fc1_pair = -1;
-      if (fc1_pair < 0) {
-        const char* e = getenv("PTTS_FC1_PAIR");
-        fc1_pair = e ? atoi(e) : 0;
-      }
-      const int fc1_tiles = (F / 128) * ((rows + 63) / 64);
-      if (fc1_pair && Sf == 2 && F % 128 == 0 && fc1_tiles <= kScratchHeader - 2 && !(skip_mask() & 64)) {
-        gemm::GemmPairAct pa = {s->ffn, reinterpret_cast<unsigned int*>(s->scratch) + 2, m->act_fn};
-        if (fc1_pair == 2) gemm_next_trigger_late(1);
-        PTTS_TRY(gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st, nullptr, &pa));
-        goto fc1_done;
-      }
-      PTTS_UNLESS_SKIPPED(64, gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st));
-      if (wpf_mask() & 1) {  // the next layer's QKV matrix (or the LM heads) is three launches ahead
-        if (l + 1 < m->n_layers)
-          set_l2_hint(m->layers[l + 1].w_qkv, (long long)3 * H * H * es);
-        else
-          set_l2_hint(m->w_heads, (long long)m->n_codebooks * m->vocab * H * es);
-      }
-      PTTS_UNLESS_SKIPPED(64, partial_act_fast(fpart, Sf, (int64_t)rows * F, rows, F, m->act_fn, s->ffn, st));
-    } else {
-      PTTS_UNLESS_SKIPPED(64, linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn,
-                                              nullptr, nullptr, s->ffn, dt, st));
+  int bn_f = 64;
+  const int Sf = (fuse && fc1_partials_enabled()) ? gemm_bf16_plan_splits(rows, F, H, &bn_f) : 0;
+  if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
+    // decode: fc1 as split-K partial sums + one small reduce / activation kernel spread over all SMs.  (Folding the
+    // activation into the second-arriving K-slice CTA of each output tile was measured slower: 1.539 against 1.457 ms
+    // per decode step, 32 finishing CTAs do what the separate kernel spreads over 148 SMs.)
+    float* fpart = work_area(m, s);
+    PTTS_UNLESS_SKIPPED(64, gemm_bf16_partial(s->xn, L.w_fc1, rows, F, H, Sf, 0, fpart, st));
+    if (wpf_mask() & 1) {  // the next layer's QKV matrix (or the LM heads) is three launches ahead
+      if (l + 1 < m->n_layers)
+        set_l2_hint(m->layers[l + 1].w_qkv, (long long)3 * H * H * dtype_size(dt));
+      else
+        set_l2_hint(m->w_heads, (long long)m->n_codebooks * m->vocab * H * dtype_size(dt));
     }
+    PTTS_UNLESS_SKIPPED(64, partial_act_fast(fpart, Sf, (int64_t)rows * F, rows, F, m->act_fn, s->ffn, st));
+  } else {
+    PTTS_UNLESS_SKIPPED(64, linear_dispatch(s->impl, s->xn, dt, L.w_fc1, dt, nullptr, rows, F, H, 1.0f, m->act_fn,
+                                            nullptr, nullptr, s->ffn, dt, st));
   }
-fc1_done:
-  {
-    // decode: the LayerNorm after fc2 is the next layer's first one, or the final one in front of the LM heads
-    const bool last = l + 1 == m->n_layers;
-    const float* ng = last ? m->lnf_g : m->layers[l + 1].ln1_g;
-    const float* nb = last ? m->lnf_b : m->layers[l + 1].ln1_b;
-    PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, fuse ? ng : nullptr,
-                                           fuse ? nb : nullptr, st));
-  }
+  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->ffn, L.w_fc2, rows, F, st));
   return PTTS_OK;
 }
 
@@ -402,6 +353,13 @@ extern "C" int ptts_embed_prefill(const PttsModel* m, const int64_t* ids, int64_
                        as_stream(s));
 }
 
+extern "C" int ptts_embed_tokens(const PttsModel* m, const int64_t* ids, int64_t ld_ids, int32_t B, int32_t T,
+                                 int32_t pos0, float* h_out, ptts_stream_t s) {
+  PTTS_TRY(check_model(m));
+  PTTS_CHECK_ARG(ids && h_out && B > 0 && T > 0 && pos0 >= 0 && pos0 + T <= m->max_pos, "embed_tokens: bad arguments");
+  return embed_prefill(m, ids, ld_ids, nullptr, 0, B, B, T, nullptr, nullptr, nullptr, 0, h_out, as_stream(s), pos0);
+}
+
 extern "C" int ptts_layernorm(const float* x, const float* g, const float* b, int32_t rows, int32_t H, float eps,
                               void* y, int32_t ydtype, ptts_stream_t s) {
   PTTS_CHECK_ARG(x && g && b && y && rows >= 0 && H > 0, "layernorm: bad arguments");
@@ -426,6 +384,22 @@ extern "C" int ptts_attention(const void* q, const void* cache_k, const void* ca
   PTTS_CHECK_ARG(B > 0 && heads > 0 && d > 0 && Tq > 0 && c_stride > 0, "attention: bad dims");
   return attention_dispatch(impl, q, cache_k, cache_v, dtype, B, heads, d, Tq, c_stride, ctx_base, ctx_dyn, causal,
                             key_mask, mask_len, out, scratch, as_stream(s));
+}
+
+extern "C" int ptts_attention_fp8(const void* q, const void* cache_k, const void* cache_v, const float* k_scale,
+                                  const float* v_scale, int32_t B, int32_t heads, int32_t d, int32_t c_stride,
+                                  int32_t ctx_base, const int32_t* ctx_dyn, const int32_t* key_mask, int32_t mask_len,
+                                  void* out, float* scratch, ptts_stream_t s) {
+  PTTS_CHECK_ARG(q && cache_k && cache_v && k_scale && v_scale && out, "attention_fp8: null pointer");
+  PTTS_CHECK_ARG(B > 0 && heads > 0 && c_stride > 0 && attention_fp8_supported(d), "attention_fp8: bad dims");
+  return attention_fp8(q, cache_k, cache_v, k_scale, v_scale, B, heads, c_stride, ctx_base, ctx_dyn, key_mask,
+                       mask_len, out, scratch, as_stream(s));
+}
+
+extern "C" int ptts_kv_quantize_fp8(const void* stage, int32_t n_lk, int32_t B, int32_t heads, int32_t d, int32_t slots,
+                                    int32_t c_max, uint32_t* amax_ws, float* scale, void* cache, ptts_stream_t s) {
+  PTTS_CHECK_ARG(attention_fp8_supported(d), "kv_quantize_fp8: head_dim must be 64");
+  return kv_quantize_fp8(stage, n_lk, B, heads, slots, c_max, amax_ws, scale, cache, as_stream(s));
 }
 
 extern "C" int ptts_cross_kv(const PttsModel* m, const PttsState* s, const void* enc, ptts_stream_t stream) {
@@ -481,6 +455,9 @@ extern "C" int ptts_prefill(const PttsModel* m, const PttsState* s, const float*
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
                            nullptr, s->logits, PTTS_F32, st));
   if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));
+  if (s->kv_dtype == PTTS_FP8)  // scales from the staged prompt positions, then the e4m3 rows [0, P + T0) of every layer
+    PTTS_TRY(kv_quantize_fp8(s->kv_stage, 2 * m->n_layers, B, m->n_heads, T, s->c_max,
+                             reinterpret_cast<unsigned int*>(work_area(m, s)), s->kv_scale, s->kv_self, st));
   (void)take_l2_hint();  // a hint never outlives the call that set it (its matrix may be freed afterwards)
   return PTTS_OK;
 }

@@ -1,7 +1,9 @@
+// Compiled into libparler_b200_diag.so only (make DIAG=1).
 // Diagnostics (not on the product path): dependent-launch chains used by profiles/ scripts to measure the per-kernel
 // latency floor of a CUDA-graph replay on the box (empty kernels, one-load kernels, with / without PDL).
 #include <stdlib.h>
 
+#include "../../include/parler_b200_diag.h"
 #include "gemm_common.cuh"
 
 namespace ptts {
@@ -35,8 +37,7 @@ __global__ void tl_reset_kernel(unsigned long long* p, int n) {
 TL tl_next(int kind) {
   static int enabled = -1;
   if (enabled < 0) {
-    const char* e = getenv("PTTS_TIMELINE");
-    enabled = (e && e[0] == '1') ? 1 : 0;
+    enabled = PTTS_KNOB("PTTS_TIMELINE", 0) ? 1 : 0;
     if (enabled) {
       cudaMalloc(&g_tl_dev, sizeof(unsigned long long) * 4 * kTlSlots);
       tl_reset_kernel<<<(kTlSlots + 255) / 256, 256>>>(g_tl_dev, kTlSlots);

@@ -1,6 +1,7 @@
 // The fused per-step epilogue: ONE kernel per decode step that replaces, for every row r = b*K + k,
-//   logits processors (classifier-free guidance, optional vocabulary cut)      transformers logits_process
-//   greedy argmax | temperature + top-k + softmax + draw                        transformers greedy_search / sample
+//   logits processors: repetition penalty, classifier-free guidance,           transformers logits_process
+//     vocabulary cut, minimum length (EOS masked)                              (_get_logits_processor, :2561-2567)
+//   greedy argmax | temperature + top-k + top-p + softmax + draw                transformers greedy_search / sample
 //   next = next*unfinished + pad*(1-unfinished); append; unfinished &= next!=eos     (same)
 //   apply_delay_pattern_mask on the new column                                  modeling_parler_tts.py:68-74, 2107
 //   sum_k embed_tokens[k](input) + position row                                 modeling_parler_tts.py:836, 884-886
@@ -38,7 +39,8 @@ __device__ __forceinline__ float row_max(const float* s, int V, int lane) {
 __global__ void __launch_bounds__(32 * PTTS_MAX_CODEBOOKS)
 step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ pos, int K, int V, int H, int Bu,
                      int cfg, float guidance, int P, int T0, int M, int do_sample, int top_k, float temperature,
-                     int suppress_from, int64_t row_offset, int64_t pad_id, int64_t eos_id,
+                     int suppress_from, int min_length, float top_p, float rep_penalty, int premixed, int64_t row_offset,
+                     int64_t pad_id, int64_t eos_id,
                      PttsCtrl* __restrict__ ctrl, const float* __restrict__ logits, int64_t* __restrict__ ids,
                      const int64_t* __restrict__ mask, int* __restrict__ unfinished, float* __restrict__ h,
                      int h_rows_per_batch) {
@@ -53,29 +55,49 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
   if (threadIdx.x == 0) transitions = 0;
   __syncthreads();
   float* sc = smem + (size_t)k * V;        // this warp's score row
-  int* kept = (int*)(smem + (size_t)K * V) + (size_t)k * V;  // compacted kept indices (sampling only)
+  // compacted kept indices (sampling only); with top-p the warp's region is 2 V words: indices | probabilities
+  int* kept = (int*)(smem + (size_t)K * V) + (size_t)k * V * (top_p < 1.0f ? 2 : 1);
   const int r = b * K + k;
 
-  // ---- logits processors
+  // ---- logits processors, in the order transformers applies them (defaults first, then the caller's list with the
+  // guidance processor last, modeling_parler_tts.py:2556-2567)
   const float* lc = logits + (int64_t)r * V;
-  if (cfg) {
+  const int mix = cfg && !premixed;  // premixed: rows [0, Bu*K) already hold the guidance-mixed scores (host processors)
+  for (int i = lane; i < V; i += 32) sc[i] = lc[i];
+  __syncwarp();
+  if (rep_penalty != 1.0f) {
+    // RepetitionPenaltyLogitsProcessor over this row's own raw history (with guidance: the conditional rows only, which
+    // is what gather/scatter over (B*K, len) ids does to the (2*B*K, V) scores).  Every occurrence of a token writes
+    // the same value computed from the UNmodified logit, so duplicates are penalised once.
+    const int64_t* hist = ids + (int64_t)r * M;
+    for (int i = lane; i < len; i += 32) {
+      const int64_t t = hist[i];
+      if (t >= 0 && t < V) {
+        const float v = lc[t];
+        sc[t] = v < 0.f ? v * rep_penalty : v / rep_penalty;
+      }
+    }
+    __syncwarp();
+  }
+  if (mix) {
     const float* lu = logits + ((int64_t)(b + Bu) * K + k) * V;
     float mc = -INFINITY, mu = -INFINITY;
-    for (int i = lane; i < V; i += 32) { mc = fmaxf(mc, lc[i]); mu = fmaxf(mu, lu[i]); }
+    for (int i = lane; i < V; i += 32) { mc = fmaxf(mc, sc[i]); mu = fmaxf(mu, lu[i]); }
     mc = warp_max(mc); mu = warp_max(mu);
     float sc_ = 0.f, su = 0.f;
-    for (int i = lane; i < V; i += 32) { sc_ += expf(lc[i] - mc); su += expf(lu[i] - mu); }
+    for (int i = lane; i < V; i += 32) { sc_ += expf(sc[i] - mc); su += expf(lu[i] - mu); }
     sc_ = warp_sum(sc_); su = warp_sum(su);
     const float lzc = mc + logf(sc_), lzu = mu + logf(su);
     for (int i = lane; i < V; i += 32) {
-      const float c = lc[i] - lzc, u = lu[i] - lzu;
+      const float c = sc[i] - lzc, u = lu[i] - lzu;
       sc[i] = u + guidance * (c - u);
     }
-  } else {
-    for (int i = lane; i < V; i += 32) sc[i] = lc[i];
   }
   if (suppress_from >= 0)
     for (int i = suppress_from + lane; i < V; i += 32) sc[i] = -INFINITY;
+  // MinLengthLogitsProcessor / MinNewTokensLengthLogitsProcessor: no EOS while the sequence is shorter than min_length
+  // columns.  (Applied after the guidance mix: the reference masks both halves first and its mix then yields NaN.)
+  if (lane == 0 && len < min_length && eos_id >= 0 && eos_id < V) sc[eos_id] = -INFINITY;
   __syncwarp();
 
   // ---- token selection
@@ -121,6 +143,42 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
     }
     __syncwarp();
     const float mx = row_max(sc, V, lane);
+    if (top_p < 1.0f) {
+      // TopPLogitsWarper (min_tokens_to_keep 1): with the candidates sorted ascending, drop those whose cumulative
+      // probability stays <= 1 - top_p.  The dropped set is a down-set in score order, so it is found as the largest
+      // ordered-key threshold T with sum{p_y : key_y < T} <= 1 - top_p (32-step bitwise search), keep key >= T.
+      float* prob = reinterpret_cast<float*>(kept) + V;  // third smem row of this warp (sampling with top_p only)
+      float tot = 0.f;
+      for (int j = lane; j < nk; j += 32) {
+        const float e = expf(sc[kept[j]] - mx);
+        prob[j] = e;
+        tot += e;
+      }
+      tot = warp_sum(tot);
+      __syncwarp();
+      const float budget = (1.0f - top_p) * tot;
+      uint32_t T = 0u;
+      for (int bit = 31; bit >= 0; --bit) {
+        const uint32_t cand = T | (1u << bit);
+        float below = 0.f;
+        for (int j = lane; j < nk; j += 32)
+          if (order_key(sc[kept[j]]) < cand) below += prob[j];
+        below = warp_sum(below);
+        if (below <= budget) T = cand;
+      }
+      int nk2 = 0;
+      for (int j0 = 0; j0 < nk; j0 += 32) {  // in-place ordered compaction (reads run ahead of writes)
+        const int j = j0 + lane;
+        const int idx = j < nk ? kept[j] : 0;
+        const bool keep = j < nk && order_key(sc[idx]) >= T;
+        const unsigned bal = __ballot_sync(0xffffffffu, keep);
+        __syncwarp();
+        if (keep) kept[nk2 + __popc(bal & ((1u << lane) - 1u))] = idx;
+        nk2 += __popc(bal);
+      }
+      nk = nk2;
+      __syncwarp();
+    }
     int choice = 0;
     if (lane == 0) {
       float total = 0.f;
@@ -189,7 +247,9 @@ int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st) {
   const int cfg = s->guidance_scale > 1.0f;
   PTTS_CHECK_ARG(!cfg || (s->B % 2 == 0), "step_epilogue: guidance needs an even model batch");
   const int Bu = cfg ? s->B / 2 : s->B;
-  const size_t smem = (size_t)K * V * sizeof(float) * (s->do_sample ? 2 : 1);
+  const bool nucleus = s->do_sample && s->top_p > 0.0f && s->top_p < 1.0f;
+  // per codebook row: scores | kept indices + (top-p) candidate probabilities
+  const size_t smem = (size_t)K * V * sizeof(float) * (s->do_sample ? (nucleus ? 3 : 2) : 1);
   if (smem > 48 * 1024) {
     static size_t configured = 0;
     if (smem > configured) {
@@ -201,7 +261,10 @@ int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st) {
   // the hidden buffer holds one row per utterance during decode (rows_per_batch = 1)
   step_epilogue_kernel<<<Bu, 32 * K, smem, st>>>(m->embed, m->pos, K, V, m->hidden, Bu, cfg, s->guidance_scale, s->P,
                                                  s->T0, s->max_len, s->do_sample, s->top_k, s->temperature,
-                                                 s->suppress_from, s->row_offset, m->pad_id, m->eos_id,
+                                                 s->suppress_from, s->min_length, nucleus ? s->top_p : 1.0f,
+                                                 s->repetition_penalty > 0.0f ? s->repetition_penalty : 1.0f,
+                                                 s->logits_premixed,
+                                                 s->row_offset, s->pad_id, s->eos_id,
                                                  s->ctrl, s->logits, s->ids, s->mask, s->unfinished, s->h, 1);
   PTTS_CHECK_LAUNCH("step_epilogue");
   return PTTS_OK;

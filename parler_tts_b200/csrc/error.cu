@@ -12,23 +12,13 @@ void set_error(const char* fmt, ...) {
 }
 static int64_t g_launches = 0;
 void count_launch() { ++g_launches; }
-bool pdl_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_PDL");
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v == 1;
+#ifdef PTTS_DIAG
+int knob_env(const char* name, int dflt) {
+  const char* e = getenv(name);
+  return e ? atoi(e) : dflt;
 }
+#endif
 static thread_local L2Hint g_hint = {nullptr, 0};
-int wpf_mask() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_WPF");
-    v = e ? atoi(e) : 0;  // measured on B200 (B=64, 860 frames): every site costs 0-17 us per decode step -> off
-  }
-  return v;
-}
 void set_l2_hint(const void* ptr, long long bytes) {
   g_hint.ptr = ptr;
   g_hint.bytes = ptr ? bytes : 0;

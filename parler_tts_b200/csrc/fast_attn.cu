@@ -345,176 +345,6 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   tl_end(tl);
 }
 
-// ---- bulk-copy (TMA engine, cp.async.bulk) variant: the K rows and then the V rows of this CTA's context stream
-// through a 4-stage shared-memory ring in 8 KB chunks; ONE thread issues the copies (no per-thread global loads, no
-// scoreboard stalls, 32 KB in flight per CTA and ~190 KB per SM), every thread waits on the stage's mbarrier and reads
-// its 16-byte pieces from shared memory.  K and V chunks form one sequence, so V is already travelling while the block
-// reduces the softmax statistics.
-constexpr int BULK_STAGES = 4;
-constexpr int BULK_BYTES = 8192;
-
-__device__ __forceinline__ void mbar_init(uint32_t bar, uint32_t count) {
-  asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(bar), "r"(count) : "memory");
-}
-__device__ __forceinline__ void mbar_wait_parity(uint32_t bar, uint32_t parity) {
-  uint32_t done = 0;
-  for (uint32_t spin = 0; !done; ++spin) {
-    asm volatile(
-        "{\n\t.reg .pred P1;\n\tmbarrier.try_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
-        : "=r"(done)
-        : "r"(bar), "r"(parity)
-        : "memory");
-    if (spin > 100000000u) __trap();  // a protocol bug must fail loudly, not hang the GPU
-  }
-}
-__device__ __forceinline__ void bulk_load(uint32_t dst, const void* src, uint32_t bytes, uint32_t bar) {
-  asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(bar), "r"(bytes) : "memory");
-  asm volatile("cp.async.bulk.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1], %2, [%3];\n" ::"r"(dst),
-               "l"(src), "r"(bytes), "r"(bar)
-               : "memory");
-}
-
-template <typename T, int D>
-__global__ void __launch_bounds__(NT)
-attn_decode_bulk_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads,
-                        int c_stride, int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask,
-                        int mask_len, T* __restrict__ out, float* __restrict__ part, int splits, int sc_cap, TL tl) {
-  constexpr int E = Chunk<T>::E;
-  constexpr int TPK = D / E;                          // threads per key row
-  constexpr int KPB = NT / TPK;                       // key rows per pass of the CTA
-  constexpr int ROWB = D * (int)sizeof(T);            // bytes per key row
-  constexpr int KCH = BULK_BYTES / ROWB;              // key rows per chunk
-  extern __shared__ __align__(128) unsigned char smraw[];
-  __shared__ __align__(8) uint64_t full_bar[BULK_STAGES];
-  unsigned char* ring = smraw;                                            // [BULK_STAGES][BULK_BYTES]
-  float* sc = reinterpret_cast<float*>(smraw + BULK_STAGES * BULK_BYTES);  // [sc_cap]
-  float* red = sc + sc_cap;                                               // [8]
-  float* ored = red + 8;                                                  // [KPB][D]
-  const int hd = blockIdx.x, b = blockIdx.y, sp = blockIdx.z;
-  const int tid = threadIdx.x, lane = tid & 31, warp = tid >> 5;
-  const int g = tid / TPK, c = tid % TPK;
-  const int H = heads * D;
-  tl_start(tl);
-  if (tid == 0) {
-#pragma unroll
-    for (int i = 0; i < BULK_STAGES; ++i) mbar_init(smem_addr(&full_bar[i]), 1);
-    asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
-  }
-  __syncthreads();
-  pdl_wait();
-  pdl_launch();
-  tl_dep(tl);
-  const int ctx = dyn_value(ctx_base, ctx_dyn);
-  const int chunk = (ctx + splits - 1) / splits;
-  const int j0 = sp * chunk;
-  const int j1 = min(ctx, j0 + chunk);
-  const int n = max(j1 - j0, 0);
-  const int nk = (n + KCH - 1) / KCH;  // chunks per operand; sequence = K chunks 0..nk-1, then V chunks 0..nk-1
-  const T* kb = ck + (((int64_t)b * heads + hd) * (int64_t)c_stride + j0) * D;
-  const T* vb = cv + (((int64_t)b * heads + hd) * (int64_t)c_stride + j0) * D;
-  auto issue = [&](int i) {  // thread 0 only
-    const int op = i >= nk, ci = op ? i - nk : i;
-    const int rows = min(KCH, n - ci * KCH);
-    const T* src = (op ? vb : kb) + (int64_t)ci * KCH * D;
-    bulk_load(smem_addr(ring + (i % BULK_STAGES) * BULK_BYTES), src, (uint32_t)(rows * ROWB),
-              smem_addr(&full_bar[i % BULK_STAGES]));
-  };
-  if (tid == 0)
-    for (int i = 0; i < BULK_STAGES && i < 2 * nk; ++i) issue(i);
-  float qv[E];
-  Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
-  const float neg = finfo_min<T>();
-
-  // ---- pass 1: scores
-  float lmax = -INFINITY;
-  for (int i = 0; i < nk; ++i) {
-    mbar_wait_parity(smem_addr(&full_bar[i % BULK_STAGES]), (uint32_t)((i / BULK_STAGES) & 1));
-    const unsigned char* st = ring + (i % BULK_STAGES) * BULK_BYTES;
-    const int rows = min(KCH, n - i * KCH);
-#pragma unroll
-    for (int r0 = 0; r0 < KCH; r0 += KPB) {
-      const int r = r0 + g;
-      float dot = 0.f;
-      if (r < rows) {
-        float kf[E];
-        Chunk<T>::unpack(*reinterpret_cast<const uint4*>(st + r * ROWB + c * 16), kf);
-#pragma unroll
-        for (int e = 0; e < E; ++e) dot = fmaf(qv[e], kf[e], dot);
-      }
-#pragma unroll
-      for (int o = TPK / 2; o > 0; o >>= 1) dot += __shfl_xor_sync(0xffffffffu, dot, o);
-      if (c == 0 && r < rows) {
-        const int j = j0 + i * KCH + r;
-        bool keep = true;
-        if (key_mask && j < mask_len) keep = key_mask[(int64_t)b * mask_len + j] != 0;
-        const float s = keep ? dot : neg;
-        sc[i * KCH + r] = s;
-        lmax = fmaxf(lmax, s);
-      }
-    }
-    __syncthreads();  // everyone is done with this stage
-    if (tid == 0 && i + BULK_STAGES < 2 * nk) issue(i + BULK_STAGES);
-  }
-  lmax = warp_max(lmax);
-  if (lane == 0) red[warp] = lmax;
-  __syncthreads();
-  const float mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
-  float lsum = 0.f;
-  for (int i = tid; i < n; i += NT) {
-    const float e = expf(sc[i] - mx);
-    sc[i] = e;
-    lsum += e;
-  }
-  lsum = warp_sum(lsum);
-  if (lane == 0) red[4 + warp] = lsum;
-  __syncthreads();
-  const float total = red[4] + red[5] + red[6] + red[7];
-  const float inv = (splits == 1 && n > 0) ? 1.0f / total : 1.0f;
-
-  // ---- pass 3: out = sum_j p_j V_j
-  float acc[E];
-#pragma unroll
-  for (int e = 0; e < E; ++e) acc[e] = 0.f;
-  for (int i = nk; i < 2 * nk; ++i) {
-    mbar_wait_parity(smem_addr(&full_bar[i % BULK_STAGES]), (uint32_t)((i / BULK_STAGES) & 1));
-    const unsigned char* st = ring + (i % BULK_STAGES) * BULK_BYTES;
-    const int ci = i - nk;
-    const int rows = min(KCH, n - ci * KCH);
-#pragma unroll
-    for (int r0 = 0; r0 < KCH; r0 += KPB) {
-      const int r = r0 + g;
-      if (r < rows) {
-        float vf[E];
-        Chunk<T>::unpack(*reinterpret_cast<const uint4*>(st + r * ROWB + c * 16), vf);
-        const float pj = sc[ci * KCH + r] * inv;
-#pragma unroll
-        for (int e = 0; e < E; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
-      }
-    }
-    __syncthreads();
-    if (tid == 0 && i + BULK_STAGES < 2 * nk) issue(i + BULK_STAGES);
-  }
-#pragma unroll
-  for (int e = 0; e < E; ++e) ored[g * D + c * E + e] = acc[e];
-  __syncthreads();
-  if (tid < D) {
-    float o = 0.f;
-#pragma unroll
-    for (int gg = 0; gg < KPB; ++gg) o += ored[gg * D + tid];
-    if (splits == 1) {
-      out[(int64_t)b * H + hd * D + tid] = from_f<T>(o);
-    } else {
-      float* pp = part + (((int64_t)b * heads + hd) * splits + sp) * (D + 2);
-      pp[2 + tid] = o;
-      if (tid == 0) {
-        pp[0] = n > 0 ? mx : -INFINITY;
-        pp[1] = n > 0 ? total : 0.f;
-      }
-    }
-  }
-  tl_end(tl);
-}
-
 template <typename T, int D>
 __global__ void __launch_bounds__(D)
 attn_combine_kernel(const float* __restrict__ part, int heads, int splits, T* __restrict__ out) {
@@ -552,42 +382,22 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
   constexpr int KPB = NT / (D / Chunk<T>::E);
   const int splits = plan_splits(B, heads, c_stride);
   const int cap = ((c_stride + splits - 1) / splits + 1 + 63) / 64 * 64 + 64;
-  // PTTS_ATTN=bulk selects the cp.async.bulk (TMA engine) ring variant.  Measured on B200 at B=64, ctx 466 (bench.py
-  // roofline leg): software-pipelined ld.global.cg 23.2 us = 5.26 TB/s (80 % of the measured copy peak); bulk ring
-  // 28.3 us = 4.33 TB/s -> the per-thread vector loads are the default.
-  static int use_bulk = -1;
-  if (use_bulk < 0) {
-    const char* ev = getenv("PTTS_ATTN");
-    use_bulk = (ev && ev[0] == 'b') ? 1 : 0;
-  }
+  // A cp.async.bulk (TMA engine) ring variant of this kernel (4 stages x 8 KB per CTA, one issuing thread) was measured
+  // on B200 at B=64, ctx 466: 28.3 us = 4.33 TB/s against 23.2 us = 5.26 TB/s for the software-pipelined ld.global.cg
+  // below (80 % of the measured copy peak) and removed.
   PTTS_CHECK_ARG(splits == 1 || scratch, "attention_fast: split-KV needs scratch");
   cudaError_t e;
   // Two one-pass (online softmax) variants were tried and removed: a scalar one (33.1 us per launch at B=64, ctx 472
   // against 24.7 us for this three-pass kernel) and a tensor-core one (mma.sync for q.K^T and P.V, 26.8 us).  Even on an
   // L2-resident cache all three top out at 6..7 TB/s (profiles/scripts/attn_l2.py), i.e. the limit is the 16-byte
   // load path per SM, not the arithmetic and not the pass structure.
-  if (use_bulk && !qf.part) {
-    const size_t smem = (size_t)BULK_STAGES * BULK_BYTES + sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
-    static size_t configured = 0;
-    if (smem > 48 * 1024 && smem > configured) {
-      cudaFuncSetAttribute(attn_decode_bulk_kernel<T, D>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-      configured = smem;
-    }
-    PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
-    e = launch_k(attn_decode_bulk_kernel<T, D>, dim3(heads, B, splits), dim3(NT), smem, st, (const T*)q, (const T*)ck,
-                 (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch, splits, cap,
-                 tl_next(c_stride > 64 ? 2 : 3));
-  } else {
+  {
     size_t smem = sizeof(float) * ((size_t)cap + 8 + (size_t)KPB * D);
     // K rows staged in shared memory before the dependency wait (fused self-attention only): what fits next to the
     // score buffer with 7 CTAs per SM, in units of one K-pass batch (64 rows = 8 KB).  PTTS_ATTN_STAGE=<rows>.
     // Measured on B200 (B=64, 860 frames): 0 rows 1.686, 64 rows 1.698, 128 rows 1.707 ms per decode step - the rows
     // are L2-resident anyway and the extra shared memory / barrier costs more than the earlier start saves: OFF.
-    static int stage_req = -1;
-    if (stage_req < 0) {
-      const char* ev = getenv("PTTS_ATTN_STAGE");
-      stage_req = ev ? atoi(ev) : 0;
-    }
+    const int stage_req = PTTS_KNOB("PTTS_ATTN_STAGE", 0);
     int stage_cap = 0;
     if (qf.part && qf.has_kv && sizeof(T) == 2) {
       const int unit = KPB * 4, budget = 31 * 1024;
@@ -608,11 +418,7 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
     PTTS_CHECK_ARG(smem <= 200 * 1024, "attention_fast: cache too long for the score buffer");
     if (qf.part) {
       const TL tl = tl_next(c_stride > 64 ? 2 : 3);
-      static int lean_ok = -1;  // PTTS_ATTN_LEAN=0: always the full instantiation
-      if (lean_ok < 0) {
-        const char* ev = getenv("PTTS_ATTN_LEAN");
-        lean_ok = (ev && ev[0] == '0') ? 0 : 1;
-      }
+      const int lean_ok = PTTS_KNOB("PTTS_ATTN_LEAN", 1);  // diagnostic build, 0: always the full instantiation
       const bool lean = lean_ok && stage_cap == 0 && !qf.pf_own_v && !qf.pf_next && !qf.tail.ptr && !tl.p;
       if (lean && !key_mask && splits == 1)
         e = launch_k(attn_decode_kernel<T, D, true, true, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
@@ -683,26 +489,14 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
   qf.tail = take_l2_hint();
   // PTTS_L2PF: bit 0 = own V rows (self-attention), bit 1 = next launch's K rows.  Measured on B200 (B=64, 860
   // frames): 3 -> 1.748 ms per decode step, 2 -> 1.708 ms (the own-V prefetch competes with the K pass) - default 2.
-  static int pf = -1;
-  if (pf < 0) {
-    const char* e = getenv("PTTS_L2PF");
-    pf = e ? atoi(e) : 2;
-  }
-  static int pf_pct = -1;  // PTTS_L2PF_PCT: share of the next launch's K rows to pull (L2 capacity is finite)
-  if (pf_pct < 0) {
-    const char* e = getenv("PTTS_L2PF_PCT");
-    pf_pct = e ? atoi(e) : 50;  // measured (early release on, own-V prefetch off): 0 % 1.677, 50 % 1.673, 100 % 1.690,
-                                // 160 % 1.711, 200 % (K and V) 1.724 ms per decode step
-  }
+  const int pf = PTTS_KNOB("PTTS_L2PF", 2);
+  // share of the next launch's K rows to pull (L2 capacity is finite).  Measured (early release on, own-V prefetch
+  // off): 0 % 1.677, 50 % 1.673, 100 % 1.690, 160 % 1.711, 200 % (K and V) 1.724 ms per decode step
+  const int pf_pct = PTTS_KNOB("PTTS_L2PF_PCT", 50);
   // PTTS_L2PF_LATE=1 queues the next-launch prefetch after the dependency wait, so that the producer GEMM's epilogue
   // stores do not queue behind it.  Measured on B200 (B=64, 860 frames): 1.838 ms per decode step against 1.745 ms
   // with the early prefetch - the ~5 us longer prefetch window is worth more than the GEMM epilogue it delays - OFF.
-  static int pf_late = -1;
-  if (pf_late < 0) {
-    const char* e = getenv("PTTS_L2PF_LATE");
-    pf_late = e ? atoi(e) : 0;
-  }
-  qf.pf_late = pf_late;
+  qf.pf_late = PTTS_KNOB("PTTS_L2PF_LATE", 0);
   qf.pf_own_v = has_kv && (pf & 1);
   if (pf & 2) {
     qf.pf_next = pf_next; qf.pf_stride = pf_stride; qf.pf_rows_base = pf_rows_base; qf.pf_rows_dyn = pf_rows_dyn;

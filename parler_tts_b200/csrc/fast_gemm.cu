@@ -147,16 +147,9 @@ int pick_bn(int M, int N) {
   return 8;
 }
 
-// PTTS_GEMM = umma (default: tcgen05 swap-AB cluster kernel) | cluster (mma.sync cluster kernel) | ring (mma.sync
-// pipelined single-CTA kernel): kept selectable for the A/B measurements under profiles/
-int gemm_mode() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_GEMM");
-    v = !e ? 2 : (e[0] == 'r' ? 0 : (e[0] == 'c' ? 1 : 2));
-  }
-  return v;
-}
+// 2: the tcgen05 swap-AB kernel (fast_gemm3.cu) wherever its shape constraints hold, this file's mma.sync pipelined
+// kernel for the rest (K % 128 != 0, odd tile counts); diagnostic build, PTTS_GEMM_RING=1: always the latter (A/B runs)
+int gemm_mode() { return PTTS_KNOB("PTTS_GEMM_RING", 0) ? 0 : 2; }
 
 }  // namespace
 
@@ -174,10 +167,6 @@ int gemm_bf16_store(const void* x, const void* w, int M, int N, int K, float alp
     const int rc = umma_gemm_store(p, st);
     if (rc != PTTS_E_UNSUPPORTED) return rc;
   }
-  if (gemm_mode() >= 1) {
-    const int rc = cluster_gemm_store(p, st);
-    if (rc != PTTS_E_UNSUPPORTED) return rc;
-  }
   return launch_bn<EPI_STORE>(pick_bn(M, N), p, 1, st);
 }
 
@@ -193,10 +182,6 @@ int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has
   p.has_q = has_q; p.q_scale = q_scale;
   if (gemm_mode() == 2) {
     const int rc = umma_gemm_scatter(p, st);
-    if (rc != PTTS_E_UNSUPPORTED) return rc;
-  }
-  if (gemm_mode() >= 1) {
-    const int rc = cluster_gemm_scatter(p, st);
     if (rc != PTTS_E_UNSUPPORTED) return rc;
   }
   return launch_bn<EPI_SCATTER>(pick_bn(M, N), p, 1, st);
@@ -230,22 +215,12 @@ int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out) {
 }
 
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st, const GemmFinish* fin, const GemmPairAct* pair) {
+                      cudaStream_t st) {
   GemmParams p = {};
   p.X = (const __nv_bfloat16*)x;
   p.W = (const __nv_bfloat16*)w;
   p.M = M; p.N = N; p.K = K; p.k_per_split = K / splits;
   p.part = part;
-  PTTS_CHECK_ARG(!fin || bn == 0, "gemm_bf16_partial: the fused fold + LayerNorm finisher needs the tcgen05 kernel");
-  if (fin) {
-    p.fin_h = fin->h; p.fin_g = fin->g; p.fin_b = fin->b; p.fin_y = (__nv_bfloat16*)fin->y; p.fin_ctr = fin->ctr;
-    p.fin_eps = fin->eps;
-  }
-  PTTS_CHECK_ARG(!pair || (bn == 0 && splits == 2 && N % 128 == 0),
-                 "gemm_bf16_partial: the pair finisher needs the tcgen05 kernel, two K slices and N % 128 == 0");
-  if (pair) {
-    p.pair_y = (__nv_bfloat16*)pair->y; p.pair_ctr = pair->ctr; p.pair_act = pair->act;
-  }
   if (bn == 0) return umma_gemm_partial(p, splits, st);
   return launch_bn<EPI_PARTIAL>(bn, p, splits, st);
 }

@@ -323,136 +323,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
       asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
     }
     STAMP(6);
-    if (!LEAN && p.pair_y) {
-      // ---- pair finisher: whoever of the two K-slice CTAs of this output tile arrives second folds both slices
-      __shared__ unsigned int pair_ticket;
-      const unsigned tile = blockIdx.y * gridDim.x + blockIdx.x;
-      __threadfence();  // my partial tile is visible device-wide before I take a ticket
-      __syncthreads();
-      if (threadIdx.x == 0) pair_ticket = atomicAdd(p.pair_ctr + tile, 1u);
-      __syncthreads();
-      if (pair_ticket == 1u) {
-        if (threadIdx.x == 0) p.pair_ctr[tile] = 0u;  // both have arrived: ready for the next launch
-        __threadfence();
-        const float* s0 = p.part + (size_t)m0 * ldn + n0;
-        const float* s1 = s0 + (size_t)p.M * ldn;
-        __nv_bfloat16* yo = p.pair_y + (size_t)m0 * ldn + n0;
-        // tile = 64 rows x 32 float4.  The loads are unrolled (8 + 8 in flight per thread), the sums are parked in the
-        // dead operand slabs, and the activation runs in a ROLLED loop: fully unrolled, its 64 inlined erff() made the
-        // kernel 160 KB of straight-line code and the cold instruction fetch cost 25 us per launch
-        float4* stage = reinterpret_cast<float4*>(smem);
-#pragma unroll
-        for (int it = 0; it < 16; it += 8) {
-          float4 a[8], b[8];
-#pragma unroll
-          for (int u = 0; u < 8; ++u) {
-            const int idx = (it + u) * NTH + (int)threadIdx.x, r = idx >> 5, c4 = idx & 31;
-            if (r < rows) {
-              a[u] = __ldcg(reinterpret_cast<const float4*>(s0 + (size_t)r * ldn) + c4);
-              b[u] = __ldcg(reinterpret_cast<const float4*>(s1 + (size_t)r * ldn) + c4);
-            }
-          }
-#pragma unroll
-          for (int u = 0; u < 8; ++u)
-            stage[(it + u) * NTH + threadIdx.x] =
-                make_float4(a[u].x + b[u].x, a[u].y + b[u].y, a[u].z + b[u].z, a[u].w + b[u].w);
-        }
-        const int act = p.pair_act;
-#pragma unroll 1
-        for (int k = 0; k < 16; ++k) {  // every thread reads back only what it parked itself: no barrier
-          const int idx = k * NTH + (int)threadIdx.x, r = idx >> 5, c4 = idx & 31;
-          if (r < rows) {
-            const float4 v = stage[idx];
-            const __nv_bfloat162 lo = __floats2bfloat162_rn(apply_act(v.x, act), apply_act(v.y, act));
-            const __nv_bfloat162 hi = __floats2bfloat162_rn(apply_act(v.z, act), apply_act(v.w, act));
-            uint2 o;
-            o.x = *reinterpret_cast<const uint32_t*>(&lo);
-            o.y = *reinterpret_cast<const uint32_t*>(&hi);
-            *reinterpret_cast<uint2*>(yo + (size_t)r * ldn + c4 * 4) = o;
-          }
-        }
-      }
-    }
     agg();
-    if (!LEAN && p.fin_h) {
-      // ---- finisher: grid-wide arrival, then this CTA folds + LayerNorms its share of the rows.  Every CTA of the
-      // grid is resident (grid <= #SMs, and a dependent grid is only launched once all of them have started), so
-      // the wait cannot deadlock; it is bounded anyway.
-      const unsigned total = gridDim.x * gridDim.y * gridDim.z;
-      __threadfence();  // my partial tile is visible device-wide before I announce it
-      __syncthreads();
-      if (threadIdx.x == 0) {
-        atomicAdd(p.fin_ctr, 1u);
-        const long long t0 = clock64();
-        unsigned seen;
-        do {
-          asm volatile("ld.acquire.gpu.global.u32 %0, [%1];\n" : "=r"(seen) : "l"(p.fin_ctr) : "memory");
-          if (clock64() - t0 > 2000000000ll) __trap();
-        } while (seen < total);
-      }
-      __syncthreads();
-      const unsigned cta = blockIdx.x + gridDim.x * (blockIdx.y + gridDim.y * blockIdx.z);
-      float* rowbuf = reinterpret_cast<float*>(smem);  // operand slabs are dead: N floats
-      float* redbuf = rowbuf + p.N;                    // 8 floats
-      const int S = (int)gridDim.z;
-      for (int row = (int)cta; row < p.M; row += (int)total) {
-        float* hr = p.fin_h + (size_t)row * p.N;
-        float sum = 0.f;
-        for (int c = threadIdx.x * 4; c < p.N; c += NTH * 4) {
-          float4 v = __ldcg(reinterpret_cast<const float4*>(hr + c));
-          for (int s0 = 0; s0 < S; s0 += 4) {  // 4 slices in flight, added in slice order (deterministic)
-            float4 t[4];
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-              if (s0 + u < S)
-                t[u] = __ldcg(reinterpret_cast<const float4*>(p.part + ((size_t)(s0 + u) * p.M + row) * p.N + c));
-#pragma unroll
-            for (int u = 0; u < 4; ++u)
-              if (s0 + u < S) { v.x += t[u].x; v.y += t[u].y; v.z += t[u].z; v.w += t[u].w; }
-          }
-          *reinterpret_cast<float4*>(hr + c) = v;
-          *reinterpret_cast<float4*>(rowbuf + c) = v;
-          sum += (v.x + v.y) + (v.z + v.w);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) sum += __shfl_xor_sync(0xffffffffu, sum, o);
-        if (lane == 0) redbuf[warp] = sum;
-        __syncthreads();
-        const float mean = ((redbuf[0] + redbuf[1]) + (redbuf[2] + redbuf[3])) / (float)p.N;
-        float qq = 0.f;
-        for (int c = threadIdx.x * 4; c < p.N; c += NTH * 4) {
-          const float4 v = *reinterpret_cast<const float4*>(rowbuf + c);
-          const float a = v.x - mean, b = v.y - mean, cc = v.z - mean, d = v.w - mean;
-          qq += (a * a + b * b) + (cc * cc + d * d);
-        }
-#pragma unroll
-        for (int o = 16; o > 0; o >>= 1) qq += __shfl_xor_sync(0xffffffffu, qq, o);
-        if (lane == 0) redbuf[4 + warp] = qq;
-        __syncthreads();
-        const float rstd = rsqrtf(((redbuf[4] + redbuf[5]) + (redbuf[6] + redbuf[7])) / (float)p.N + p.fin_eps);
-        for (int c = threadIdx.x * 4; c < p.N; c += NTH * 4) {
-          const float4 v = *reinterpret_cast<const float4*>(rowbuf + c);
-          const float4 gg = __ldg(reinterpret_cast<const float4*>(p.fin_g + c));
-          const float4 bb = __ldg(reinterpret_cast<const float4*>(p.fin_b + c));
-          const __nv_bfloat162 lo = __floats2bfloat162_rn((v.x - mean) * rstd * gg.x + bb.x, (v.y - mean) * rstd * gg.y + bb.y);
-          const __nv_bfloat162 hi = __floats2bfloat162_rn((v.z - mean) * rstd * gg.z + bb.z, (v.w - mean) * rstd * gg.w + bb.w);
-          uint2 u;
-          u.x = *reinterpret_cast<const uint32_t*>(&lo);
-          u.y = *reinterpret_cast<const uint32_t*>(&hi);
-          *reinterpret_cast<uint2*>(p.fin_y + (size_t)row * p.N + c) = u;
-        }
-        __syncthreads();  // rowbuf / redbuf are reused by the next row
-      }
-      // departure: the last CTA to leave restores both counters to zero for the next launch
-      if (threadIdx.x == 0) {
-        const unsigned d = atomicAdd(p.fin_ctr + 1, 1u);
-        if (d == total - 1) {
-          p.fin_ctr[0] = 0u;
-          p.fin_ctr[1] = 0u;
-          __threadfence();
-        }
-      }
-    }
     tl_end(tl);
     return;
   }
@@ -536,12 +407,10 @@ int plan_cluster3(int M, int N, int K) {
   if (K % 128 != 0) return 0;
   const int kblocks = K / KB64;
   const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
-  static int forced = -1;
-  if (forced < 0) {
-    const char* e = getenv("PTTS_CS");
-    forced = e ? atoi(e) : 0;
-  }
+#ifdef PTTS_DIAG
+  const int forced = PTTS_KNOB("PTTS_CS", 0);
   if (forced > 0 && kblocks % forced == 0 && kblocks / forced <= kMaxKB64) return forced;
+#endif
   for (int cs = 1; cs <= 8; cs <<= 1) {
     if (kblocks % cs) continue;
     const int kb = kblocks / cs;
@@ -573,15 +442,21 @@ EncodeTiledFn encode_tiled_fn() {
   }
   return fn;
 }
+// Everything a descriptor encodes is part of the key (base, extents, row pitch, box, element type): a buffer that is
+// freed and re-allocated at the same address with another shape or pitch gets its own entry, never a stale map.
 struct MapKey {
   const void* ptr;
-  int rows, cols, box_rows;
-  bool operator==(const MapKey& o) const { return ptr == o.ptr && rows == o.rows && cols == o.cols && box_rows == o.box_rows; }
+  int rows, cols, box_rows, dtype;
+  long long pitch_bytes;
+  bool operator==(const MapKey& o) const {
+    return ptr == o.ptr && rows == o.rows && cols == o.cols && box_rows == o.box_rows && dtype == o.dtype &&
+           pitch_bytes == o.pitch_bytes;
+  }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     return std::hash<const void*>()(k.ptr) ^ (size_t)k.rows * 0x9E3779B97F4A7C15ull ^ (size_t)k.cols * 0xC2B2AE3D27D4EB4Full ^
-           (size_t)k.box_rows;
+           (size_t)k.box_rows ^ ((size_t)k.dtype << 20) ^ (size_t)k.pitch_bytes * 0x165667B19E3779F9ull;
   }
 };
 // bf16 row-major [rows][cols]; box = 64 columns (128 bytes, SWIZZLE_128B) x box_rows rows; out-of-range rows read as 0
@@ -591,7 +466,7 @@ bool tensor_map_2d_impl(const void* ptr, int rows, int cols, int box_rows, CUten
   EncodeTiledFn fn = encode_tiled_fn();
   if (!fn || (reinterpret_cast<uintptr_t>(ptr) & 15) || cols % 8) return false;
   std::lock_guard<std::mutex> lock(mu);
-  const MapKey key = {ptr, rows, cols, box_rows};
+  const MapKey key = {ptr, rows, cols, box_rows, PTTS_BF16, (long long)cols * 2};
   auto it = cache.find(key);
   if (it != cache.end()) {
     *out = it->second;
@@ -648,18 +523,11 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   }
   cfg.attrs = attr;
   cfg.numAttrs = n;
-  static int dbg = -1;
-  if (dbg < 0) {
-    const char* ev = getenv("PTTS_GEMM_DBG");
-    dbg = ev ? atoi(ev) : 0;  // 1: globaltimer stamps (256 ns ticks), 2: SM clock cycles (intra-kernel phases)
-  }
-  static int early = -1;
-  if (early < 0) {
-    // with cp.async slabs the early release won (1.727 against 1.748 ms per decode step); with TMA slabs the slab needs
-    // ~1.5 us of lead only and the late release wins (1.486 against 1.496 ms) -> default late, PTTS_PDL_EARLY=1: early
-    const char* ev = getenv("PTTS_PDL_EARLY");
-    early = (ev && ev[0] == '1') ? 16 : 0;
-  }
+  // diagnostic build: 1 globaltimer stamps (256 ns ticks), 2 SM clock cycles (intra-kernel phases), 3 per-CTA sums
+  const int dbg = PTTS_KNOB("PTTS_GEMM_DBG", 0);
+  // with cp.async slabs the early release won (1.727 against 1.748 ms per decode step); with TMA slabs the slab needs
+  // ~1.5 us of lead only and the late release wins (1.486 against 1.496 ms) -> late
+  const int early = PTTS_KNOB("PTTS_PDL_EARLY", 0) ? 16 : 0;
   int early_now = early;
   if (EPI == EPI_PARTIAL && g_late_once) {
     early_now = g_late_once == 2 ? 128 : 0;
@@ -667,30 +535,18 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   }
   const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early_now : 0);
   const L2Hint hint = EPI == EPI_PARTIAL ? take_l2_hint() : L2Hint{nullptr, 0};
-  static int use_tma = -1;
-  if (use_tma < 0) {
-    const char* ev = getenv("PTTS_GEMM_TMA");
-    use_tma = (ev && ev[0] == '0') ? 0 : 1;
-  }
+  const int use_tma = PTTS_KNOB("PTTS_GEMM_TMA", 1);
   CUtensorMap tm_w, tm_x;
   memset(&tm_w, 0, sizeof(tm_w));
   memset(&tm_x, 0, sizeof(tm_x));
   const bool tma = use_tma && tensor_map_2d_impl(p.W, p.N, p.K, UM, &tm_w) && tensor_map_2d_impl(p.X, p.M, p.K, UN, &tm_x);
-  static int xbar = -1;
-  if (xbar < 0) {
-    const char* ev = getenv("PTTS_GEMM_XBAR");
-    // one barrier for the whole X slab (default) or one per k-block (PTTS_GEMM_XBAR=0).  Measured on B200: per k-block
-    // the last X block "lands" 5300 cycles after the dependency instead of 1500 (each arrive.expect_tx between two
-    // bulk-tensor issues costs ~500 cycles) - 1.566 against 1.485 ms per decode step
-    xbar = (ev && ev[0] == '0') ? 0 : 64;
-  }
+  // one barrier for the whole X slab, not one per k-block.  Measured on B200: per k-block the last X block "lands"
+  // 5300 cycles after the dependency instead of 1500 (each arrive.expect_tx between two bulk-tensor issues costs ~500
+  // cycles) - 1.566 against 1.485 ms per decode step
+  const int xbar = PTTS_KNOB("PTTS_GEMM_XBAR", 1) ? 64 : 0;
   const TL tl = tl_next(10 + EPI);
-  static int lean_ok = -1;  // PTTS_GEMM_LEAN=0: always the full instantiation
-  if (lean_ok < 0) {
-    const char* ev = getenv("PTTS_GEMM_LEAN");
-    lean_ok = (ev && ev[0] == '0') ? 0 : 1;
-  }
-  const bool lean = lean_ok && tma && xbar && !(dbg_arg & ~(16 | 128)) && !hint.ptr && !p.fin_h && !p.pair_y && !tl.p;
+  const int lean_ok = PTTS_KNOB("PTTS_GEMM_LEAN", 1);  // diagnostic build, 0: always the full instantiation
+  const bool lean = lean_ok && tma && xbar && !(dbg_arg & ~(16 | 128)) && !hint.ptr && !tl.p;
   cudaError_t e =
       (lean && EPI == EPI_PARTIAL && p.M % UN == 0)
           ? cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI_PARTIAL, true, true>, p, kb, cs, dbg_arg, hint, tm_w, tm_x, tl)
@@ -735,17 +591,12 @@ int umma_plan_splits(int M, int N, int K) {
   if (K % 128 != 0) return 0;
   const int kblocks = K / KB64;
   const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
-  static int target = -1;  // PTTS_SPLIT_TARGET: CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold)
-  if (target < 0) {
-    const char* e = getenv("PTTS_SPLIT_TARGET");
-    target = e ? atoi(e) : 16;  // with TMA slab loads fewer, larger CTAs win: 30 -> 16 measured 1.654 -> 1.559 ms per step
-  }
-  static int kbmax = -1;  // PTTS_KBMAX: 64-element k-blocks per CTA (8 = 128 KB of W per CTA, 4 = 64 KB)
-  if (kbmax < 0) {
-    const char* e = getenv("PTTS_KBMAX");
-    kbmax = e ? atoi(e) : kMaxKB64;
-    if (kbmax < 1 || kbmax > kMaxKB64) kbmax = kMaxKB64;
-  }
+  // CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold): with TMA slab loads fewer, larger CTAs
+  // win, 30 -> 16 measured 1.654 -> 1.559 ms per step
+  const int target = PTTS_KNOB("PTTS_SPLIT_TARGET", 16);
+  // 64-element k-blocks per CTA (8 = 128 KB of W per CTA; 4 = 64 KB measured slower, 1.630 against 1.497 ms)
+  int kbmax = PTTS_KNOB("PTTS_KBMAX", kMaxKB64);
+  if (kbmax < 1 || kbmax > kMaxKB64) kbmax = kMaxKB64;
   int best = 0;
   for (int s = 2; s <= kMaxSplitK; s <<= 1) {
     if (kblocks % s || kblocks / s > kbmax) continue;

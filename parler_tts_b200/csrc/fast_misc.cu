@@ -169,13 +169,9 @@ int layernorm_fast(float* h, const float* part, int S, int64_t part_stride, cons
     }
   }
   const L2Hint hint = take_l2_hint();
-  static int early = -1;
-  if (early < 0) {
-    // measured on B200 (B=64, 860 frames, TMA GEMMs): early 1.496, late 1.481 ms per decode step; together with the late
-    // cross-attention block 1.427 -> default late (PTTS_LN_EARLY=1: before the wait)
-    const char* ev = getenv("PTTS_LN_EARLY");
-    early = (ev && ev[0] == '1') ? 1 : 0;
-  }
+  // measured on B200 (B=64, 860 frames, TMA GEMMs): early 1.496, late 1.481 ms per decode step; together with the late
+  // cross-attention block 1.427 -> late (diagnostic build, PTTS_LN_EARLY=1: before the wait)
+  const int early = PTTS_KNOB("PTTS_LN_EARLY", 0);
   cudaError_t e;
   const TL tl = tl_next(1);
   const bool lean = !hint.ptr && !tl.p;
@@ -256,11 +252,7 @@ int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, in
   PTTS_CHECK_ARG(part && y && S >= 1 && N % 4 == 0 && part_stride % 4 == 0, "partial_act_fast: bad arguments");
   const int64_t n4 = (int64_t)rows * N / 4;
   if (n4 == 0) return PTTS_OK;
-  static int early = -1;
-  if (early < 0) {
-    const char* ev = getenv("PTTS_ACT_EARLY");  // measured: early 1.496, late 1.522 ms per decode step -> early
-    early = (ev && ev[0] == '0') ? 0 : 1;
-  }
+  const int early = PTTS_KNOB("PTTS_ACT_EARLY", 1);  // measured: early 1.496, late 1.522 ms per decode step -> early
   const L2Hint hint = take_l2_hint();
   const TL tl = tl_next(4);
   const dim3 grid((unsigned)((n4 + 255) / 256));

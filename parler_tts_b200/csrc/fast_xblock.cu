@@ -568,15 +568,8 @@ int xblock_read_stamps(unsigned long long* host, int reset) {
   return 8;
 }
 
-// PTTS_XBLOCK=0 keeps the four separate launches (LayerNorm, q GEMM, cross flash-decode, out_proj GEMM)
-bool xblock_enabled() {
-  static int v = -1;
-  if (v < 0) {
-    const char* e = getenv("PTTS_XBLOCK");
-    v = (e && e[0] == '0') ? 0 : 1;
-  }
-  return v == 1;
-}
+// diagnostic build, PTTS_XBLOCK=0: keeps the four separate launches (LayerNorm, q GEMM, cross flash-decode, out_proj GEMM)
+bool xblock_enabled() { return PTTS_KNOB("PTTS_XBLOCK", 1) != 0; }
 
 static size_t xblock_smem(int H, int S) {
   const int sc_cap = (S + 7) / 8 * 8;
@@ -600,36 +593,25 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   p.wq = (const __nv_bfloat16*)wq; p.wo = (const __nv_bfloat16*)wo;
   p.kc = (const __nv_bfloat16*)kc; p.vc = (const __nv_bfloat16*)vc; p.key_mask = key_mask;
   p.B = B; p.heads = heads; p.S = S; p.scale = scale; p.part_out = part_out; p.out_by_row = out_by_row;
-  static int pf_pct = -1;  // share of the next self-attention launch's K rows to pull into L2 from here
-  if (pf_pct < 0) {
-    // measured on B200 with this kernel (B=64, 860 frames): 50 % 1.694, 25 % 1.674, 0 % 1.652 ms per decode step - the
-    // prefetch queues in front of the block's own slab loads, so it is off unless PTTS_XB_L2PF_PCT asks for it
-    const char* x = getenv("PTTS_XB_L2PF_PCT");
-    pf_pct = x ? atoi(x) : 0;
-  }
+  // share of the next self-attention launch's K rows to pull into L2 from here.  Measured on B200 with this kernel
+  // (B=64, 860 frames): 50 % 1.694, 25 % 1.674, 0 % 1.652 ms per decode step - the prefetch queues in front of the
+  // block's own slab loads: 0
+  const int pf_pct = PTTS_KNOB("PTTS_XB_L2PF_PCT", 0);
   p.pf_next = (const __nv_bfloat16*)pf_next; p.pf_stride = pf_stride; p.pf_rows_base = pf_rows_base;
   p.pf_rows_dyn = pf_rows_dyn; p.pf_pct = pf_pct;
   p.hint = take_l2_hint();
   const size_t smem = xblock_smem(H, S);
   const int sc_cap = (S + 7) / 8 * 8;
   const dim3 grid(heads, (B + XG - 1) / XG);
-  static int dbg = -1;
-  if (dbg < 0) {
-    const char* ev = getenv("PTTS_XB_DBG");
-    dbg = ev ? (atoi(ev) & 1) : 0;
-    // release the next LayerNorm before (PTTS_XB_EARLY=1) or after the own wait: measured 1.496 against 1.451 ms per
-    // decode step - released early, the LayerNorm releases fc1 in turn, whose TMA slab burst lands on this kernel
-    const char* xe = getenv("PTTS_XB_EARLY");
-    if (!(xe && xe[0] == '1')) dbg |= 2;
-  }
-  // PTTS_XB_CLUSTER = CTAs (heads) that share the fold + LayerNorm of a group: 1, 2 or 4
-  static int cs = -1;
-  if (cs < 0) {
-    const char* ev = getenv("PTTS_XB_CLUSTER");
-    cs = ev ? atoi(ev) : 1;  // measured (B=64, 860 frames, TMA slabs, late releases): 1 -> 1.421, 2 -> 1.436 ms per decode
-                             // step; 4 was 0.13 ms behind 2 with the cp.async slabs, 8 cannot be placed (12 us dep-spread)
-    if (cs != 1 && cs != 2 && cs != 4) cs = 1;
-  }
+  // bit 0: per-phase stamps (diagnostic build, PTTS_XB_DBG=1); bit 1: release the next LayerNorm AFTER the own wait:
+  // measured 1.496 (before) against 1.451 ms per decode step - released early, the LayerNorm releases fc1 in turn,
+  // whose TMA slab burst lands on this kernel
+  const int dbg = (PTTS_KNOB("PTTS_XB_DBG", 0) & 1) | (PTTS_KNOB("PTTS_XB_EARLY", 0) ? 0 : 2);
+  // CTAs (heads) that share the fold + LayerNorm of a group.  Measured (B=64, 860 frames, TMA slabs, late releases):
+  // 1 -> 1.421, 2 -> 1.436 ms per decode step; 4 was 0.13 ms behind 2 with the cp.async slabs, 8 cannot be placed
+  // (12 us dep-spread).  The cluster instantiations exist in the diagnostic build only (PTTS_XB_CLUSTER=2|4).
+  int cs = PTTS_KNOB("PTTS_XB_CLUSTER", 1);
+  if (cs != 1 && cs != 2 && cs != 4) cs = 1;
   cudaLaunchConfig_t cfg = {};
   cfg.gridDim = grid;
   cfg.blockDim = dim3(XT);
@@ -659,21 +641,23 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   using KernelFn = void (*)(const XBlockParams, int, int, const CUtensorMap, const CUtensorMap, TL);
   KernelFn fn = nullptr;
   const TL tl = tl_next(5);
-  static int lean_ok = -1;  // PTTS_XB_LEAN=0: always the full instantiation
-  if (lean_ok < 0) {
-    const char* ev = getenv("PTTS_XB_LEAN");
-    lean_ok = (ev && ev[0] == '0') ? 0 : 1;
-  }
+  const int lean_ok = PTTS_KNOB("PTTS_XB_LEAN", 1);  // diagnostic build, 0: always the full instantiation
   const bool lean = lean_ok && S <= 48 && !p.hint.ptr && !(p.pf_next && p.pf_pct > 0) && !(dbg & 1) && !tl.p;
+#ifdef PTTS_DIAG
+#define PTTS_XB_PICK(HT, LL) (cs == 1 ? xblock_kernel<HT, 1, LL> : (cs == 2 ? xblock_kernel<HT, 2, LL> : xblock_kernel<HT, 4, LL>))
+#else
+#define PTTS_XB_PICK(HT, LL) xblock_kernel<HT, 1, LL>
+#endif
   if (H == 1024) {
     if (lean && cs == 1 && !key_mask && B % XG == 0) fn = xblock_kernel<8, 1, true, true>;
-    else if (lean) fn = cs == 1 ? xblock_kernel<8, 1, true> : (cs == 2 ? xblock_kernel<8, 2, true> : xblock_kernel<8, 4, true>);
-    else fn = cs == 1 ? xblock_kernel<8, 1, false> : (cs == 2 ? xblock_kernel<8, 2, false> : xblock_kernel<8, 4, false>);
+    else if (lean) fn = PTTS_XB_PICK(8, true);
+    else fn = PTTS_XB_PICK(8, false);
   } else {
     if (lean && cs == 1 && !key_mask && B % XG == 0) fn = xblock_kernel<12, 1, true, true>;
-    else if (lean) fn = cs == 1 ? xblock_kernel<12, 1, true> : (cs == 2 ? xblock_kernel<12, 2, true> : xblock_kernel<12, 4, true>);
-    else fn = cs == 1 ? xblock_kernel<12, 1, false> : (cs == 2 ? xblock_kernel<12, 2, false> : xblock_kernel<12, 4, false>);
+    else if (lean) fn = PTTS_XB_PICK(12, true);
+    else fn = PTTS_XB_PICK(12, false);
   }
+#undef PTTS_XB_PICK
   const bool plain = lean && cs == 1 && !key_mask && B % XG == 0;
   static size_t configured[3][2][3] = {};
   size_t& conf = configured[plain ? 2 : (lean ? 1 : 0)][H == 1024 ? 0 : 1][cs == 1 ? 0 : (cs == 2 ? 1 : 2)];

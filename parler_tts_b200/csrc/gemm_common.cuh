@@ -1,5 +1,5 @@
-// Shared pieces of the bf16 GEMM kernels of the fast family (fast_gemm.cu: pipelined kernel, fast_gemm2.cu: cluster
-// split-K kernel): parameter block, cp.async / ldmatrix / mma.sync wrappers, swizzled tile loader, fused epilogues.
+// Shared pieces of the bf16 GEMM kernels of the fast family (fast_gemm.cu: pipelined mma.sync kernel for the shapes the
+// tcgen05 kernel of fast_gemm3.cu does not take): parameter block, cp.async / ldmatrix / mma.sync wrappers, swizzled tile loader, fused epilogues.
 #pragma once
 #include <cuda.h>
 
@@ -30,40 +30,10 @@ struct GemmParams {
   float q_scale;
   // PARTIAL
   float* part;
-  // PARTIAL + finisher (tcgen05 kernel only, fin_h != null): once every CTA of the grid has stored its partial tile
-  // (arrival counter fin_ctr[0], departure counter fin_ctr[1]; both zero between launches), CTA i folds the split-K
-  // slices of rows i, i + #CTAs, ... into the residual stream fin_h (N = hidden) in slice order and writes their
-  // LayerNorm (fin_g, fin_b, eps) as bf16 to fin_y - the separate fold + LayerNorm launch disappears
-  float* fin_h;
-  const float* fin_g;
-  const float* fin_b;
-  __nv_bfloat16* fin_y;
-  unsigned int* fin_ctr;
-  float fin_eps;
-  // PARTIAL with two K slices + pair finisher (tcgen05 kernel only, pair_y != null): the CTA of an output tile that
-  // stores its partial tile SECOND (ticket from pair_ctr[tile], zero between launches) adds the two slices in slice
-  // order, applies pair_act and writes bf16 [M][N] to pair_y - the separate reduce + activation launch disappears and
-  // nobody waits (the first CTA just leaves)
-  __nv_bfloat16* pair_y;
-  unsigned int* pair_ctr;
-  int pair_act;
-};
-
-// optional pair finisher of gemm_bf16_partial (see GemmParams)
-struct GemmPairAct {
-  void* y;  // bf16 [M][N]
-  unsigned int* ctr;
-  int act;
-};
-
-// optional finisher of gemm_bf16_partial (see GemmParams)
-struct GemmFinish {
-  float* h;
-  const float* g;
-  const float* b;
-  void* y;  // bf16 [M][N]
-  unsigned int* ctr;
-  float eps;
+  // (Two in-kernel finishers of the PARTIAL variant were measured and removed: a grid-wide arrival counter after which
+  // every CTA folds + LayerNorms its share of the rows - 1.99 against 1.78 ms per decode step - and a "pair finisher" in
+  // which the second-arriving K-slice CTA of an fc1 tile folds both slices and applies the activation - 1.539 against
+  // 1.457 ms.  Both lose to the separate small kernels that spread the same work over all SMs.)
 };
 
 __device__ __forceinline__ uint32_t smem_u32(const void* p) { return (uint32_t)__cvta_generic_to_shared(p); }
@@ -111,9 +81,6 @@ __device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
 bool tma_available();  // the driver entry point for tensor-map creation was found
 
-// cluster split-K kernel (fast_gemm2.cu); PTTS_E_UNSUPPORTED when the shape does not fit it
-int cluster_gemm_store(const GemmParams& p, cudaStream_t st);
-int cluster_gemm_scatter(const GemmParams& p, cudaStream_t st);
 // tcgen05 swap-AB cluster split-K kernel (fast_gemm3.cu)
 int umma_gemm_store(const GemmParams& p, cudaStream_t st);
 int umma_gemm_scatter(const GemmParams& p, cudaStream_t st);

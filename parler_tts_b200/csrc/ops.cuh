@@ -6,7 +6,7 @@ namespace ptts {
 
 int embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int B,
                   int ids_batch, int T0, const float* prompt_table,
-                  const int64_t* prompt_ids, const float* prompt_hidden, int P, float* h, cudaStream_t st);
+                  const int64_t* prompt_ids, const float* prompt_hidden, int P, float* h, cudaStream_t st, int pos0 = 0);
 int layernorm(const float* x, const float* g, const float* b, int rows, int H, float eps, int64_t in_stride,
               int64_t in_offset, void* y, int ydtype, cudaStream_t st);
 int linear_simple(const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M, int N, int K,
@@ -30,9 +30,8 @@ int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has
                       void* cv, int H, int heads, int d, int Tq, int c_stride, int pos_base, const int* pos_dyn,
                       cudaStream_t st);
 int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
-namespace gemm { struct GemmFinish; struct GemmPairAct; }
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st, const gemm::GemmFinish* fin = nullptr, const gemm::GemmPairAct* pair = nullptr);
+                      cudaStream_t st);
 // the next gemm_bf16_partial launch releases its dependent kernel AFTER its own dependency wait whatever PTTS_PDL_EARLY
 // says, or (at_mma_done) only when its MMA burst has completed
 void gemm_next_trigger_late(int at_mma_done);
@@ -49,8 +48,6 @@ bool fast_attention_supported(int dtype, int d, int Tq);
 int attention_fast(const void* q, const void* ck, const void* cv, int dtype, int B, int heads, int d, int Tq,
                    int c_stride, int ctx_base, const int* ctx_dyn, int causal, const int* key_mask, int mask_len,
                    void* out, float* scratch, cudaStream_t st);
-bool dac_umma_enabled();
-int dac_conv_umma(const void* conv_params, int B, cudaStream_t st);
 // warp-specialised persistent tcgen05 conv over pre-tiled weights (fast_dac3.cu)
 struct DacConv {
   const float* x;                  // [B][T][Cin] fp32 (Snake `alpha` applied while staging), or null
@@ -78,9 +75,16 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
                 float eps, const void* wq, const void* wo, const void* kc, const void* vc, const int* key_mask, int B,
                 int heads, int H, int S, float scale, float* part_out, int out_by_row, const void* pf_next,
                 int pf_stride, int pf_rows_base, const int* pf_rows_dyn, cudaStream_t st);
-bool fast_conv_supported(int Cin, int Cout, int ksize);
-int dac_conv1d_fast(const float* x, int B, int Cin, int T, const float* w, const float* bias, int Cout, int ksize,
-                    int dilation, const float* snake_alpha, const float* residual, int tanh_out, float* y,
-                    cudaStream_t st);
+// fp8 (e4m3) self-attention cache (fast_attn_fp8.cu)
+bool attention_fp8_supported(int d);
+int attention_fp8_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, float scale, int slot_base,
+                        const int* slot_dyn, void* ck, void* cv, const float* k_scale, const float* v_scale, int B,
+                        int heads, int c_stride, int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len,
+                        void* out, float* scratch, cudaStream_t st);
+int attention_fp8(const void* q, const void* ck, const void* cv, const float* k_scale, const float* v_scale, int B,
+                  int heads, int c_stride, int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len,
+                  void* out, float* scratch, cudaStream_t st);
+int kv_quantize_fp8(const void* stage, int n_lk, int B, int heads, int slots, int c_max, unsigned int* amax_ws,
+                    float* scale, void* cache, cudaStream_t st);
 
 }  // namespace ptts

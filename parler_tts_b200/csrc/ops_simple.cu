@@ -12,12 +12,12 @@ __global__ void embed_prefill_kernel(const float* __restrict__ embed, const floa
                                      int H, const int64_t* __restrict__ ids, int64_t ld_ids,
                                      const int64_t* __restrict__ mask, int64_t ld_mask, int ids_batch, int T0,
                                      const float* __restrict__ prompt_table, const int64_t* __restrict__ prompt_ids,
-                                     const float* __restrict__ prompt_hidden, int P, float* __restrict__ h) {
+                                     const float* __restrict__ prompt_hidden, int P, int pos0, float* __restrict__ h) {
   const int T = P + T0;
   const int b = blockIdx.x / T, t = blockIdx.x % T;
   const int bi = b % ids_batch;  // classifier-free guidance: the unconditional half reuses the same ids
   float* out = h + (int64_t)blockIdx.x * H;
-  const float* prow = pos + (int64_t)t * H;
+  const float* prow = pos + (int64_t)(pos0 + t) * H;
   if (t < P) {
     const float* src = prompt_hidden ? prompt_hidden + ((int64_t)b * P + t) * H
                                      : prompt_table + prompt_ids[(int64_t)b * P + t] * (int64_t)H;
@@ -40,9 +40,10 @@ __global__ void embed_prefill_kernel(const float* __restrict__ embed, const floa
 
 int embed_prefill(const PttsModel* m, const int64_t* ids, int64_t ld_ids, const int64_t* mask, int64_t ld_mask, int B,
                   int ids_batch, int T0, const float* prompt_table,
-                  const int64_t* prompt_ids, const float* prompt_hidden, int P, float* h, cudaStream_t st) {
+                  const int64_t* prompt_ids, const float* prompt_hidden, int P, float* h, cudaStream_t st, int pos0) {
   embed_prefill_kernel<<<B * (P + T0), 256, 0, st>>>(m->embed, m->pos, m->n_codebooks, m->vocab + 1, m->hidden, ids,
-                                                     ld_ids, mask, ld_mask, ids_batch, T0, prompt_table, prompt_ids, prompt_hidden, P, h);
+                                                     ld_ids, mask, ld_mask, ids_batch, T0, prompt_table, prompt_ids,
+                                                     prompt_hidden, P, pos0, h);
   PTTS_CHECK_LAUNCH("embed_prefill");
   return PTTS_OK;
 }

@@ -87,11 +87,9 @@ class DacDecoderEngine:
 
     def _planes(self, w):
         hi, mid = self._split(w)
-        return self._tile(hi, mid) if self.pretiled else (hi, mid)
+        return self._tile(hi, mid)
 
     def _prep_nwc(self):
-        self.pretiled = bool(cabi.load().ptts_dac_pretiled())
-
         def conv(wb):  # [Cout][Cin][k] -> [k][Cout][Cin]
             w, b = wb
             return self._planes(w.permute(2, 0, 1).contiguous()) + (b, w.shape[0], w.shape[2])
@@ -111,22 +109,6 @@ class DacDecoderEngine:
             self.f_blocks.append(fb)
         w, b = self.conv_out
         self.f_conv_out = (w[0].t().contiguous(), b)  # [7][Cin]
-
-    def _conv_nwc(self, x, wt, dil=1, alpha=None, residual=None):
-        hi, mid, bias, cout, k = wt
-        B, T, Cin = x.shape
-        y = torch.empty(B, T, cout, device=x.device, dtype=torch.float32)
-        cabi.call("ptts_dac_conv1d_nwc", cabi.ptr(x), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), cout, k,
-                  dil, cabi.ptr(alpha), cabi.ptr(residual), cabi.ptr(y), cabi.stream_ptr())
-        return y
-
-    def _convt_nwc(self, x, wt, stride, alpha):
-        hi, mid, bias, cout = wt
-        B, T, Cin = x.shape
-        y = torch.empty(B, T * stride, cout, device=x.device, dtype=torch.float32)
-        cabi.call("ptts_dac_convtr1d_nwc", cabi.ptr(x), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), cout,
-                  stride, cabi.ptr(alpha), cabi.ptr(y), cabi.stream_ptr())
-        return y
 
     def dequant_nwc(self, codes):
         """codes (B, K, F) int64 -> z (B, F, latent) fp32, channels-last."""
@@ -192,15 +174,7 @@ class DacDecoderEngine:
         return x
 
     def decode_latents_nwc(self, z):
-        if self.pretiled:
-            x = self._decode_latents_planes(z)
-        else:
-            x = self._conv_nwc(z, self.f_conv_in)
-            for blk in self.f_blocks:
-                x = self._convt_nwc(x, blk["convt"], blk["stride"], blk["alpha"])
-                for r in blk["res"]:
-                    y = self._conv_nwc(x, r["c1"], dil=r["dil"], alpha=r["a1"])
-                    x = self._conv_nwc(y, r["c2"], alpha=r["a2"], residual=x)
+        x = self._decode_latents_planes(z)
         B, T, Cin = x.shape
         w, b = self.f_conv_out
         out = torch.empty(B, 1, T, device=x.device, dtype=torch.float32)

@@ -99,7 +99,8 @@ class GenState:
 
     def __init__(self, weights: DecoderWeights, B, S, P, T0, max_len, impl=cabi.IMPL_FAST, do_sample=False, top_k=50,
                  temperature=1.0, suppress_from=-1, guidance_scale=1.0, seed=0, row_offset=0, enc_mask=None,
-                 prompt_mask=None):
+                 prompt_mask=None, kv_dtype=None, min_length=0, top_p=1.0, repetition_penalty=1.0, pad_token_id=None,
+                 eos_token_id=None, bos_token_id=None):
         d, dev, dt = weights.dims, weights.device, weights.dtype
         self.weights = weights
         self.B, self.S, self.P, self.T0, self.max_len = B, S, P, T0, max_len
@@ -111,7 +112,18 @@ class GenState:
         rows = B * max(P + T0, S, 1)
         z = lambda *shape, dtype=dt: torch.zeros(*shape, device=dev, dtype=dtype)  # noqa: E731
         self.ctrl = z(8, dtype=torch.int32)
-        self.kv_self = z(L, 2, B, heads, self.c_max, hd)
+        # self-attention cache: the weight dtype, or (kv_dtype="fp8") e4m3 bytes + per-(layer, K|V, head) scales + a
+        # staging cache in the weight dtype that only the prefill touches
+        self.kv_dtype = "fp8" if kv_dtype in ("fp8", "fp8_e4m3", torch.float8_e4m3fn) else None
+        if self.kv_dtype == "fp8":
+            if dt != torch.bfloat16 or impl != cabi.IMPL_FAST or hd != 64:
+                raise cabi.ParlerB200Error("kv_dtype='fp8' needs bf16 weights, the fast kernel family and head_dim 64")
+            self.kv_self = z(L, 2, B, heads, self.c_max, hd, dtype=torch.uint8)
+            self.kv_scale = torch.ones(L, 2, heads, device=dev, dtype=torch.float32)
+            self.kv_stage = z(L, 2, B, heads, P + T0, hd)
+        else:
+            self.kv_self = z(L, 2, B, heads, self.c_max, hd)
+            self.kv_scale = self.kv_stage = None
         self.kv_cross = z(L, 2, B, heads, max(S, 1), hd)
         self.h = z(rows, H, dtype=torch.float32)
         self.xn, self.q, self.attn, self.ffn = z(rows, H), z(rows, H), z(rows, H), z(rows, F)
@@ -130,6 +142,17 @@ class GenState:
         s.suppress_from = int(suppress_from if suppress_from is not None else -1)
         s.guidance_scale = float(guidance_scale) if self.cfg else 1.0
         s.seed, s.row_offset = int(seed) & 0xFFFFFFFFFFFFFFFF, int(row_offset)
+        s.kv_dtype = cabi.PTTS_FP8 if self.kv_dtype == "fp8" else cabi.dtype_enum(dt)
+        s.kv_scale = None if self.kv_scale is None else self.kv_scale.data_ptr()
+        s.kv_stage = None if self.kv_stage is None else self.kv_stage.data_ptr()
+        s.min_length, s.top_p = int(min_length or 0), float(1.0 if top_p is None else top_p)
+        s.repetition_penalty = float(1.0 if repetition_penalty is None else repetition_penalty)
+        # generation-config ids (reference: generation_config.{pad,eos}_token_id drive the loop, 2586-2587; the
+        # delay mask uses generation_config.{decoder_start,pad}_token_id, 2530-2535), defaulting to the decoder config's
+        self.pad_id = d.pad_token_id if pad_token_id is None else int(pad_token_id)
+        self.eos_id = d.eos_token_id if eos_token_id is None else int(eos_token_id)
+        self.bos_id = d.bos_token_id if bos_token_id is None else int(bos_token_id)
+        s.pad_id, s.eos_id = self.pad_id, self.eos_id
         for name in ("ctrl", "kv_self", "kv_cross", "h", "xn", "q", "attn", "ffn", "logits", "scratch", "ids", "mask",
                      "unfinished"):
             setattr(s, name, getattr(self, name).data_ptr())
@@ -149,8 +172,8 @@ class GenState:
         K = d.num_codebooks
         start = start_ids.to(self.ids.device, torch.int64).contiguous()
         assert start.shape == (self.Bu * K, self.T0), (start.shape, self.Bu, K, self.T0)
-        cabi.call("ptts_build_delay_mask", cabi.ptr(start), self.Bu, K, self.T0, self.max_len, d.bos_token_id,
-                  d.pad_token_id, cabi.ptr(self.mask), cabi.ptr(self.first_start), cabi.stream_ptr())
+        cabi.call("ptts_build_delay_mask", cabi.ptr(start), self.Bu, K, self.T0, self.max_len, self.bos_id,
+                  self.pad_id, cabi.ptr(self.mask), cabi.ptr(self.first_start), cabi.stream_ptr())
         self.ids.zero_()
         self.ids[:, : self.T0] = start
         self.unfinished.fill_(1)

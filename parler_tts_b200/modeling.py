@@ -240,11 +240,38 @@ def _random_dac_state(config, decoder_dim, rates, codebook_dim, seed=0):
 
 
 # --------------------------------------------------------------------------------------------- generation core
+# Defaults of the transformers (<= 4.40) GenerationConfig the reference was written against.  The installed transformers
+# leaves unset fields at None; the reference's loop would have seen these values (top_k = 50 is the one that matters:
+# `_get_logits_warper`, modeling_parler_tts.py:2597, adds TopKLogitsWarper(50) to every sampling run).
+LEGACY_GENERATION_DEFAULTS = dict(
+    max_length=20, min_length=0, do_sample=False, num_beams=1, num_beam_groups=1, temperature=1.0, top_k=50, top_p=1.0,
+    typical_p=1.0, epsilon_cutoff=0.0, eta_cutoff=0.0, repetition_penalty=1.0, encoder_repetition_penalty=1.0,
+    no_repeat_ngram_size=0, num_return_sequences=1, renormalize_logits=False)
+
+
+def _gcv(gc, name):
+    v = getattr(gc, name, None)
+    return LEGACY_GENERATION_DEFAULTS.get(name) if v is None else v
+
+
 def _default_generation_config(dec_cfg):
     from transformers.generation.configuration_utils import GenerationConfig
 
     return GenerationConfig(bos_token_id=dec_cfg.bos_token_id, pad_token_id=dec_cfg.pad_token_id,
                             eos_token_id=dec_cfg.eos_token_id, decoder_start_token_id=dec_cfg.bos_token_id)
+
+
+class _nvtx:
+    """NVTX range around a phase of generate() (T5 / prefill / loop / DAC): visible in nsys / ncu timelines."""
+
+    def __init__(self, name):
+        self.name = name
+
+    def __enter__(self):
+        torch.cuda.nvtx.range_push(self.name)
+
+    def __exit__(self, *a):
+        torch.cuda.nvtx.range_pop()
 
 
 def _resolve_generation(self_cfg, generation_config, kwargs, input_len_fn):
@@ -254,7 +281,7 @@ def _resolve_generation(self_cfg, generation_config, kwargs, input_len_fn):
     if gc.pad_token_id is None and gc.eos_token_id is not None:
         eos = gc.eos_token_id
         gc.pad_token_id = eos[0] if isinstance(eos, (list, tuple)) else eos
-    if (gc.num_beams or 1) != 1 or (getattr(gc, "num_beam_groups", 1) or 1) != 1:
+    if _gcv(gc, "num_beams") != 1 or _gcv(gc, "num_beam_groups") != 1:
         raise ValueError(
             "Got incompatible mode for generation, should be one of greedy or sampling. "
             "Ensure that beam search is de-activated by setting `num_beams=1` and `num_beam_groups=1`.")
@@ -262,14 +289,112 @@ def _resolve_generation(self_cfg, generation_config, kwargs, input_len_fn):
 
 
 def _final_max_length(gc, kwargs, input_len):
-    has_default = kwargs.get("max_length") is None and gc.max_length is not None
     if gc.max_new_tokens is not None:
         gc.max_length = gc.max_new_tokens + input_len
+    if gc.max_length is None:
+        gc.max_length = LEGACY_GENERATION_DEFAULTS["max_length"]
     if gc.min_length is not None and gc.min_length > gc.max_length:
         raise ValueError(f"Unfeasible length constraints: the minimum length ({gc.min_length}) is larger than"
                          f" the maximum length ({gc.max_length})")
-    del has_default
     return int(gc.max_length)
+
+
+def _first_id(v):
+    return v[0] if isinstance(v, (list, tuple)) else v
+
+
+class _Plan:
+    """What the reference's `_get_logits_processor` / `_get_logits_warper` (modeling_parler_tts.py:2561-2567, 2597) would
+    build from the generation config, split into what the fused epilogue does natively and what has to run as
+    transformers' own processors on the logits tensor between the forward pass and the epilogue (slow loop)."""
+
+    def __init__(self, gc, T0, user_py_procs, cfg, eos_id):
+        from transformers.generation import logits_process as lp
+
+        self.do_sample = bool(_gcv(gc, "do_sample"))
+        rp = float(_gcv(gc, "repetition_penalty"))
+        min_len = int(_gcv(gc, "min_length") or 0)
+        if gc.min_new_tokens is not None and gc.min_new_tokens > 0:
+            min_len = max(min_len, T0 + int(gc.min_new_tokens))
+        if eos_id is None:
+            min_len = 0
+        erp = float(_gcv(gc, "encoder_repetition_penalty"))
+        if erp != 1.0:
+            raise NotImplementedError("encoder_repetition_penalty penalises audio-token logits by description token ids; "
+                                      "not supported on this path")
+        if getattr(gc, "prefix_allowed_tokens_fn", None) is not None or getattr(gc, "constraints", None):
+            raise NotImplementedError("constrained decoding is a beam-search feature; this path is greedy / sampling only")
+        extra = []  # non-native default processors, in transformers' order
+        ngram = int(_gcv(gc, "no_repeat_ngram_size") or 0)
+        if ngram > 0:
+            extra.append(("ngram", lp.NoRepeatNGramLogitsProcessor(ngram)))
+        if getattr(gc, "bad_words_ids", None):
+            extra.append(("bad_words", lp.NoBadWordsLogitsProcessor(gc.bad_words_ids, eos_id)))
+        if getattr(gc, "forced_bos_token_id", None) is not None:
+            extra.append(("forced_bos", lp.ForcedBOSTokenLogitsProcessor(gc.forced_bos_token_id)))
+        if getattr(gc, "forced_eos_token_id", None) is not None:
+            extra.append(("forced_eos", lp.ForcedEOSTokenLogitsProcessor(int(gc.max_length), gc.forced_eos_token_id, "cuda")))
+        if getattr(gc, "exponential_decay_length_penalty", None) is not None:
+            extra.append(("exp_decay", lp.ExponentialDecayLengthPenalty(gc.exponential_decay_length_penalty, eos_id, T0)))
+        if getattr(gc, "suppress_tokens", None):
+            extra.append(("suppress", lp.SuppressTokensLogitsProcessor(gc.suppress_tokens, "cuda")))
+        if getattr(gc, "begin_suppress_tokens", None):
+            extra.append(("begin_suppress", lp.SuppressTokensAtBeginLogitsProcessor(gc.begin_suppress_tokens, T0, "cuda")))
+        if getattr(gc, "sequence_bias", None):
+            extra.insert(0, ("sequence_bias", lp.SequenceBiasLogitsProcessor(gc.sequence_bias)))
+        renorm = bool(_gcv(gc, "renormalize_logits"))
+        self.py_procs = None
+        self.rep_penalty, self.min_length = rp, min_len
+        if extra or user_py_procs or renorm:
+            # everything in python, in the reference's order: defaults, then the caller's list (guidance last, appended by
+            # the loop), then the normaliser
+            procs = []
+            order = ["sequence_bias", "rep", "ngram", "bad_words", "min_len", "forced_bos", "forced_eos", "exp_decay",
+                     "suppress", "begin_suppress"]
+            named = dict(extra)
+            if rp != 1.0:
+                named["rep"] = lp.RepetitionPenaltyLogitsProcessor(rp)
+            if min_len > 0:
+                named["min_len"] = lp.MinLengthLogitsProcessor(min_len, eos_id, "cuda")
+            procs = [named[n] for n in order if n in named] + list(user_py_procs)
+            self.py_procs, self.py_renorm = procs, renorm
+            self.rep_penalty, self.min_length = 1.0, 0
+        # warpers (sampling only): temperature, top-k, top-p natively; the rest through transformers' classes
+        self.temperature, self.top_k, self.top_p, self.py_warpers = 1.0, 0, 1.0, None
+        if self.do_sample:
+            temp, top_k, top_p = float(_gcv(gc, "temperature")), int(_gcv(gc, "top_k") or 0), float(_gcv(gc, "top_p"))
+            if temp <= 0:
+                raise ValueError(f"`temperature` (={temp}) has to be a strictly positive float")
+            if not 0 < top_p <= 1.0:
+                raise ValueError(f"`top_p` has to be a float > 0 and <= 1, but is {top_p}")
+            warp = []
+            min_p = getattr(gc, "min_p", None)
+            if min_p is not None:
+                warp.append(lp.MinPLogitsWarper(float(min_p)))
+            if float(_gcv(gc, "typical_p")) < 1.0:
+                warp.append(lp.TypicalLogitsWarper(mass=float(gc.typical_p)))
+            if float(_gcv(gc, "epsilon_cutoff")) > 0.0:
+                warp.append(lp.EpsilonLogitsWarper(float(gc.epsilon_cutoff)))
+            if float(_gcv(gc, "eta_cutoff")) > 0.0:
+                warp.append(lp.EtaLogitsWarper(float(gc.eta_cutoff), device="cuda"))
+            if warp or renorm:
+                head = []
+                if temp != 1.0:
+                    head.append(lp.TemperatureLogitsWarper(temp))
+                if top_k > 0:
+                    head.append(lp.TopKLogitsWarper(top_k))
+                if top_p < 1.0:
+                    head.append(lp.TopPLogitsWarper(top_p))
+                self.py_warpers = head + warp
+                if self.py_procs is None:
+                    self.py_procs, self.py_renorm = [], renorm
+            else:
+                self.temperature, self.top_k, self.top_p = temp, top_k, top_p
+        self.cfg_in_python = cfg and self.py_procs is not None
+
+    @property
+    def slow(self):
+        return self.py_procs is not None
 
 
 def _draw_seed():
@@ -313,6 +438,12 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
     B = enc.shape[0] if enc is not None else (prompt_ids if prompt_ids is not None else prompt_hidden).shape[0]
     Bu = B // 2 if cfg else B
     bos = gc.decoder_start_token_id if gc.decoder_start_token_id is not None else gc.bos_token_id
+    if bos is None:
+        bos = d.bos_token_id
+    pad = gc.pad_token_id if gc.pad_token_id is not None else d.pad_token_id
+    eos = _first_id(gc.eos_token_id)  # None: rows never finish (the loop runs to max_length), as in the reference
+    if isinstance(gc.eos_token_id, (list, tuple)) and len(gc.eos_token_id) > 1:
+        raise NotImplementedError("a list of several eos_token_id values is not supported by the fused epilogue")
     start = torch.full((Bu * K, 1), bos, dtype=torch.int64, device=dev)
     if decoder_input_ids is not None:
         user = decoder_input_ids.to(dev, torch.int64).reshape(Bu * K, -1)
@@ -331,16 +462,15 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
     if P + max_length > d.max_position_embeddings:
         raise ValueError(f"prompt length {P} + max_length {max_length} exceeds max_position_embeddings "
                          f"{d.max_position_embeddings}")
-    suppress, py_procs = _special_processors(logits_processor)
-    if cfg and py_procs:
-        raise NotImplementedError("python logits_processors together with guidance_scale > 1 are not supported")
-    do_sample = bool(gc.do_sample)
-    top_k = int(gc.top_k) if (do_sample and gc.top_k is not None) else 0
-    temperature = float(gc.temperature) if (do_sample and gc.temperature is not None) else 1.0
+    suppress, user_py = _special_processors(logits_processor)
+    plan = _Plan(gc, T0, user_py, cfg, eos)
+    do_sample, top_k, temperature = plan.do_sample, plan.top_k, plan.temperature
     S = 0 if enc is None else enc.shape[1]
     gscale = float(gc.guidance_scale) if cfg else 1.0
+    kv_dtype = getattr(decoder, "kv_dtype", None)
     key = (id(w), B, S, P, T0, max_length, impl, do_sample, top_k, temperature, suppress, gscale, row_offset,
-           enc_mask is not None, prompt_mask is not None)
+           enc_mask is not None, prompt_mask is not None, kv_dtype, plan.min_length, plan.top_p, plan.rep_penalty,
+           plan.cfg_in_python, bos, pad, eos)
     cached = getattr(decoder, "_state_cache", None)
     if cached is not None and cached[0] == key:  # same shapes: reuse buffers and the captured CUDA graph
         st = cached[1]
@@ -354,7 +484,11 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
                       temperature=temperature, suppress_from=suppress, guidance_scale=gscale, seed=seed,
                       row_offset=row_offset * K,
                       enc_mask=None if enc_mask is None else enc_mask.to(dev, torch.int32).clone(),
-                      prompt_mask=None if prompt_mask is None else prompt_mask.to(dev, torch.int32).clone())
+                      prompt_mask=None if prompt_mask is None else prompt_mask.to(dev, torch.int32).clone(),
+                      kv_dtype=kv_dtype, min_length=plan.min_length, top_p=plan.top_p,
+                      repetition_penalty=plan.rep_penalty, pad_token_id=pad,
+                      eos_token_id=-1 if eos is None else eos, bos_token_id=bos)
+        st.c_state.logits_premixed = int(plan.cfg_in_python)
         decoder._state_cache = (key, st)
     eng = DecoderEngine(w)
     st.reset(start, seed)
@@ -362,12 +496,16 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
         streamer.put(start.cpu())
     if enc is not None:
         eng.cross_kv(st, enc)
-    slow = bool(py_procs) or streamer is not None or bool(stopping_criteria)
+    slow = plan.slow or streamer is not None or bool(stopping_criteria)
     if not slow:
-        eng.prefill(st, prompt_table, prompt_ids, prompt_hidden)
-        ctrl = eng.run_loop(st, use_graph=use_graph)
+        with _nvtx("ptts.prefill"):
+            eng.prefill(st, prompt_table, prompt_ids, prompt_hidden)
+        with _nvtx("ptts.decode_loop"):
+            ctrl = eng.run_loop(st, use_graph=use_graph)
     else:
-        ctrl = _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, py_procs, stopping_criteria, streamer)
+        with _nvtx("ptts.decode_loop_host_processors"):
+            ctrl = _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, plan, gscale, stopping_criteria,
+                              streamer)
     Lout = ctrl["stop_len"] if ctrl["done"] else ctrl["len"]
     seq = st.ids[:, :Lout]
     if T0 == 1:
@@ -376,16 +514,20 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
                   cabi.ptr(codes), cabi.stream_ptr())
     else:  # audio-prompt geometry: the general boolean-mask form of modeling_parler_tts.py:2637-2645
         applied = apply_delay_pattern_mask(seq, st.mask)
-        _, m2 = build_delay_pattern_mask(start, bos, gc.pad_token_id, Lout, K)
-        keep = (m2 != bos) & (m2 != gc.pad_token_id)
+        _, m2 = build_delay_pattern_mask(start, bos, pad, Lout, K)
+        keep = (m2 != bos) & (m2 != pad)
         codes = applied[keep].reshape(Bu, K, -1)
     return codes, seq, st
 
 
-def _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, py_procs, stopping_criteria, streamer):
-    """Step-at-a-time variant used when python logits processors, stopping criteria or a streamer are supplied:
-    forward (kernels) -> python processors on the logits tensor -> fused epilogue kernel."""
+def _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, plan, gscale, stopping_criteria, streamer):
+    """Step-at-a-time variant used when host-side logits processors / warpers, stopping criteria or a streamer are
+    supplied: forward (kernels) -> transformers' processors on the logits tensor, in the reference's order -> fused
+    epilogue kernel (selection, EOS / PAD bookkeeping, delay mask, next embedding)."""
+    procs = plan.py_procs or []
+    warpers = plan.py_warpers or []
     first = True
+    rows = st.ids.shape[0]  # Bu * K
     while True:
         if first:
             eng.prefill(st, prompt_table, prompt_ids, prompt_hidden, run_epilogue=False)
@@ -394,8 +536,21 @@ def _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, py_procs, stopp
             eng.step(st, run_epilogue=False)
         c = st.read_ctrl()
         hist = st.ids[:, : c["len"]]
-        for p in py_procs:
-            st.logits.copy_(p(hist, st.logits))
+        if plan.slow:
+            scores = st.logits
+            for p in procs:  # with guidance the scores hold both halves, the ids one (as in the reference)
+                scores = p(hist, scores)
+            if plan.cfg_in_python:  # ClassifierFreeGuidanceLogitsProcessor, appended last (modeling_parler_tts.py:2556-2558)
+                lsm = torch.log_softmax(scores.float(), dim=-1)
+                cond, unc = lsm[:rows], lsm[rows:]
+                scores = unc + (cond - unc) * gscale
+            if plan.py_renorm:
+                scores = torch.log_softmax(scores.float(), dim=-1)
+            for wproc in warpers:
+                scores = wproc(hist, scores)
+            if warpers and plan.py_renorm:
+                scores = torch.log_softmax(scores.float(), dim=-1)
+            st.logits[: scores.shape[0]].copy_(scores)
         eng.epilogue(st)
         c = st.read_ctrl()
         hist = st.ids[:, : c["len"]]
@@ -436,6 +591,9 @@ class ParlerTTSForCausalLM(nn.Module):
         self._state_cache = None
         self.impl = cabi.IMPL_FAST
         self.use_cuda_graph = True
+        # self-attention KV cache element type: None = the weight dtype; "fp8" = e4m3 with per-(layer, K|V, head) scales
+        # (bf16 weights + fast kernels only; halves the bytes of the dominant stream)
+        self.kv_dtype = None
 
     # ---- plumbing
     @property
@@ -466,33 +624,66 @@ class ParlerTTSForCausalLM(nn.Module):
     def apply_delay_pattern_mask(input_ids, decoder_pad_token_mask):
         return apply_delay_pattern_mask(input_ids, decoder_pad_token_mask)
 
-    # ---- forward: teacher-forced logits of every position (no cache returned)
+    # ---- forward: teacher-forced logits, optionally with the static cache handed back as `past_key_values`
     @torch.no_grad()
     def forward(self, input_ids=None, attention_mask=None, encoder_hidden_states=None, encoder_attention_mask=None,
-                prompt_hidden_states=None, prompt_attention_mask=None, past_key_values=None, **unused):
-        """logits (B*K, P+T, vocab) as ParlerTTSForCausalLM.forward without labels (modeling_parler_tts.py:1096-1185).
-        Only the cache-less call is provided; generation uses the static-cache kernels directly."""
-        if past_key_values is not None:
-            raise NotImplementedError("forward() with past_key_values: use generate(), which owns the static cache")
+                prompt_hidden_states=None, prompt_attention_mask=None, past_key_values=None, use_cache=None,
+                max_cache_len=None, **unused):
+        """logits (B*K, T, vocab) as ParlerTTSForCausalLM.forward without labels (modeling_parler_tts.py:1096-1185).
+
+        First call (past_key_values=None): prompt + all given columns in one pass, logits of every position
+        (B*K, P+T, vocab).  With use_cache=True the static cache comes back as `past_key_values` (a `StaticDecoderCache`,
+        not the reference's tuple of per-layer tensors) and a later call
+        `forward(input_ids=next_column(s), past_key_values=cache)` runs one cached decode step per column through the
+        same kernels generate() uses (encoder / prompt arguments are then ignored, as the reference's cached branch
+        ignores them, modeling_parler_tts.py:292-294, 2132-2133)."""
         if attention_mask is not None:
             raise NotImplementedError("decoder attention_mask is not supported; pass prompt_attention_mask")
         w = self.packed_weights()
         K = self.num_codebooks
         ids = input_ids.to(w.device, torch.int64).reshape(-1, input_ids.shape[-1]).contiguous()
         B, T = ids.shape[0] // K, ids.shape[1]
+        eng = DecoderEngine(w)
+        if past_key_values is not None:
+            if not isinstance(past_key_values, StaticDecoderCache):
+                raise TypeError("past_key_values must be the StaticDecoderCache an earlier forward(use_cache=True) "
+                                "returned; tuples of per-layer tensors are not supported (INTEGRATION.md)")
+            st = past_key_values.state
+            if B != st.B:
+                raise ValueError(f"batch {B} does not match the cache's batch {st.B}")
+            V = self.config.vocab_size
+            out = torch.empty(B * K, T, V, device=w.device, dtype=torch.float32)
+            for t in range(T):
+                n = past_key_values.columns
+                if n + 1 > st.max_len:
+                    raise ValueError(f"cache is full ({st.max_len} columns); pass a larger max_cache_len")
+                st.ids[:, n] = ids[:, t]
+                st.ctrl[0] = n + 1
+                cabi.call("ptts_embed_tokens", eng._m(), cabi.ptr(st.ids[:, n:]), st.max_len, B, 1, st.P + n,
+                          cabi.ptr(st.h), cabi.stream_ptr())
+                eng.step(st, run_epilogue=False)
+                out[:, t] = st.logits
+                past_key_values.columns = n + 1
+            return SimpleNamespace(logits=out, past_key_values=past_key_values)
         P = 0 if prompt_hidden_states is None else prompt_hidden_states.shape[1]
         S = 0 if encoder_hidden_states is None else encoder_hidden_states.shape[1]
-        st = GenState(w, B, S, P, T, max(T + 1, 2), impl=self.impl, enc_mask=encoder_attention_mask,
-                      prompt_mask=prompt_attention_mask)
+        cap = max(T + 1, 2)
+        if use_cache:
+            cap = int(max_cache_len) if max_cache_len is not None else min(
+                self.config.max_position_embeddings - P, T + 512)
+            if cap < T + 1:
+                raise ValueError(f"max_cache_len={cap} is too small for {T} columns")
+        st = GenState(w, B, S, P, T, cap, impl=self.impl, enc_mask=encoder_attention_mask,
+                      prompt_mask=prompt_attention_mask, kv_dtype=self.kv_dtype if use_cache else None)
         st.mask.fill_(-1)
         st.ids[:, :T] = ids
         st.ctrl.copy_(torch.tensor([T, 0, 0, B * K, 0, 0, 0, 0], dtype=torch.int32))
-        eng = DecoderEngine(w)
         if S:
             eng.cross_kv(st, encoder_hidden_states)
         ph = None if prompt_hidden_states is None else prompt_hidden_states.to(w.device, torch.float32).contiguous()
         logits = eng.prefill(st, prompt_hidden=ph, all_logits=True, run_epilogue=False)
-        return SimpleNamespace(logits=logits, past_key_values=None)
+        cache = StaticDecoderCache(st, T) if use_cache else None
+        return SimpleNamespace(logits=logits, past_key_values=cache)
 
     @torch.no_grad()
     def generate(self, inputs=None, generation_config=None, logits_processor=None, stopping_criteria=None,
@@ -527,6 +718,19 @@ class ParlerTTSForCausalLM(nn.Module):
         if gc.return_dict_in_generate:
             return SimpleNamespace(sequences=codes)
         return codes
+
+
+class StaticDecoderCache:
+    """What ParlerTTSForCausalLM.forward(use_cache=True) returns as `past_key_values`: the preallocated self-attention
+    cache [L][2][B][heads][P + max_cache_len][d], the cross-attention cache and the token matrix of one batch (a
+    GenState), plus the number of token columns already in it.  Replaces the reference's growing tuple of per-layer
+    (self_k, self_v, cross_k, cross_v) tensors (modeling_parler_tts.py:303-304, 501)."""
+
+    def __init__(self, state, columns):
+        self.state, self.columns = state, int(columns)
+
+    def get_seq_length(self):
+        return self.state.P + self.columns
 
 
 def _random_decoder_state(dims, std, seed):
@@ -720,10 +924,11 @@ class ParlerTTSForConditionalGeneration(nn.Module):
                 else:
                     attention_mask = torch.ones_like(input_ids)
             attention_mask = attention_mask.to(dev)
-            hs = self.encode_text(input_ids, attention_mask)
+            with _nvtx("ptts.t5_encode"):
+                hs = self.encode_text(input_ids, attention_mask)
         B = hs.shape[0]
-        nret = gc.num_return_sequences or 1
-        if not gc.do_sample and nret > 1:
+        nret = _gcv(gc, "num_return_sequences")
+        if not _gcv(gc, "do_sample") and nret > 1:
             raise ValueError(f"num_return_sequences has to be 1 when doing greedy search, but is {nret}.")
         cfg = gc.guidance_scale is not None and gc.guidance_scale > 1
         prompt_ids = mk.pop("prompt_input_ids", None)
@@ -762,9 +967,11 @@ class ParlerTTSForConditionalGeneration(nn.Module):
                                          _draw_seed() if seed is None else seed, row_offset)
         if return_codes:
             return codes
-        audio = self.audio_encoder.engine(self.decoder.impl).decode_generated(
-            codes, gc.bos_token_id if gc.bos_token_id is not None else self.config.decoder.bos_token_id,
-            gc.pad_token_id, gc.eos_token_id if not isinstance(gc.eos_token_id, (list, tuple)) else gc.eos_token_id[0])
+        with _nvtx("ptts.dac_decode"):
+            audio = self.audio_encoder.engine(self.decoder.impl).decode_generated(
+                codes, gc.bos_token_id if gc.bos_token_id is not None else self.config.decoder.bos_token_id,
+                gc.pad_token_id if gc.pad_token_id is not None else self.config.decoder.pad_token_id,
+                _first_id(gc.eos_token_id) if gc.eos_token_id is not None else self.config.decoder.eos_token_id)
         if gc.return_dict_in_generate:
             return SimpleNamespace(sequences=audio, audio_codes=codes)
         return audio

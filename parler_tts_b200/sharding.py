@@ -49,7 +49,7 @@ def gather_padded(x, pad_value=0, group=None):
     shapes = [torch.empty_like(shape) for _ in range(world)]
     dist.all_gather(shapes, shape, group=group)
     shapes = [tuple(int(v) for v in s.tolist()) for s in shapes]
-    bmax, tmax = max(s[0] for s in shapes), max(s[1] for s in shapes)
+    bmax, tmax = max(max(s[0] for s in shapes), 1), max(s[1] for s in shapes)
     buf = torch.full((bmax,) + tuple(x.shape[1:-1]) + (tmax,), pad_value, dtype=x.dtype, device=x.device)
     buf[: x.shape[0], ..., : x.shape[-1]] = x
     parts = [torch.empty_like(buf) for _ in range(world)]
@@ -66,5 +66,9 @@ def generate_sharded(model, input_ids, prompt_input_ids, attention_mask=None, pr
         kwargs["attention_mask"] = am
     if pm is not None:
         kwargs["prompt_attention_mask"] = pm
-    audio = model.generate(input_ids=ids, prompt_input_ids=prm, row_offset=start, **kwargs)
+    if ids.shape[0] == 0:
+        # more ranks than utterances: this rank has nothing to generate but must still take part in the gather
+        audio = torch.zeros(0, 1, dtype=torch.float32, device=model.device)
+    else:
+        audio = model.generate(input_ids=ids, prompt_input_ids=prm, row_offset=start, **kwargs)
     return gather_padded(audio, 0.0)

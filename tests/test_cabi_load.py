@@ -37,7 +37,31 @@ def test_struct_layout_matches_header():
     assert C.sizeof(cabi.PttsLayer) == 13 * 8
     assert cabi.PttsModel.embed.offset == 56 and C.sizeof(cabi.PttsModel) == 56 + 6 * 8
     assert cabi.PttsState.seed.offset == 48 and cabi.PttsState.ctrl.offset == 64
-    assert C.sizeof(cabi.PttsState) == 64 + 15 * 8
+    assert cabi.PttsState.kv_dtype.offset == 64 + 15 * 8 and cabi.PttsState.kv_scale.offset == 64 + 15 * 8 + 24
+    assert C.sizeof(cabi.PttsState) == 64 + 15 * 8 + 24 + 4 * 8
+
+
+def test_product_library_has_no_knobs_and_no_diag_exports():
+    """The shipped library reads no PTTS_* environment variable and exports none of include/parler_b200_diag.h."""
+    import subprocess
+
+    out = subprocess.run(["nm", "-D", "--defined-only", cabi.LIB_PATH], capture_output=True, text=True).stdout
+    exported = {ln.split()[-1] for ln in out.splitlines() if " T " in ln}
+    assert not [n for n in exported if n.startswith("ptts_diag")], exported
+    assert exported == set(cabi.PROTOTYPES), exported ^ set(cabi.PROTOTYPES)
+    blob = open(cabi.LIB_PATH, "rb").read()
+    assert b"getenv" not in blob or b"PTTS_SKIP" not in blob
+    for knob in (b"PTTS_SKIP", b"PTTS_GEMM", b"PTTS_XB_", b"PTTS_L2PF", b"PTTS_TIMELINE", b"PTTS_PDL"):
+        assert knob not in blob, knob
+
+
+def test_reference_import_name_resolves():
+    import parler_tts
+    import parler_tts_b200
+
+    for name in ("ParlerTTSForConditionalGeneration", "ParlerTTSForCausalLM", "ParlerTTSConfig", "ParlerTTSDecoderConfig",
+                 "DACConfig", "DACModel", "build_delay_pattern_mask", "apply_delay_pattern_mask"):
+        assert getattr(parler_tts, name) is getattr(parler_tts_b200, name), name
 
 
 def test_argument_errors_are_reported_without_a_gpu():
