@@ -278,6 +278,78 @@ def gen_t5():
     np.savez_compressed(os.path.join(GOLD, "t5_tiny.npz"), **out)
 
 
+MINI = dict(vocab_size=1088, hidden_size=1024, num_hidden_layers=24, num_attention_heads=16, ffn_dim=4096,
+            num_codebooks=9, max_position_embeddings=4096, pad_token_id=1024, eos_token_id=1024, bos_token_id=1025)
+# BASELINE.json configs[0] (SURVEY.md section 8d "C1"): Mini v0.1 architecture, random-init, bs=1, greedy, ~2 s of audio
+C1 = dict(B=1, S=48, P=32, max_length=181, weight_seed=0)
+
+
+def c1_inputs(seed):
+    g = torch.Generator().manual_seed(seed)
+    enc = torch.randn(C1["B"], C1["S"], MINI["hidden_size"], generator=g) * 0.3
+    prm = torch.randn(C1["B"], C1["P"], MINI["hidden_size"], generator=g) * 0.02
+    return enc, prm
+
+
+def gen_c1(ref, seeds=(1234, 1235, 1236, 1237, 1238, 1239)):
+    """C1 at full depth on the REFERENCE decoder: the restated greedy loop drives the unmodified
+    ParlerTTSForCausalLM.forward (24 x 1024, fp32, KV-cache tuples) for max_length - 1 = 180 forward passes; ids >= 1024
+    are suppressed (a user logits_processor) so that random weights produce all 172 frames.  The input seed with the
+    largest minimum top-2 logit margin is kept, and that margin is re-measured with the reference decoder in float64:
+    the GPU test asserts the tokens unconditionally and asserts the margin it relies on."""
+    dims = decoder_oracle.DecoderDims(**MINI)
+    sd = decoder_oracle.random_decoder_state(dims, seed=C1["weight_seed"])
+    model = _ref_decoder(ref, dims, sd)
+
+    def run(m, enc, prm, dtype):
+        enc, prm = enc.to(dtype), prm.to(dtype)
+
+        def fwd(inp, prompt, past):
+            with torch.no_grad():
+                o = m(input_ids=inp, encoder_hidden_states=enc, prompt_hidden_states=prompt, past_key_values=past,
+                      use_cache=True)
+            return o.logits, o.past_key_values
+
+        return generate_oracle.generate_codes(sd, dims, enc, prompt_hidden_states=prm, max_length=C1["max_length"],
+                                              do_sample=False, suppress_from=1024, forward_fn=fwd, return_trace=True)
+
+    def min_margin(res):
+        sc = res["scores"][:, :, :1024].double()
+        top2 = sc.topk(2, dim=-1).values
+        gap = (top2[..., 0] - top2[..., 1]).numpy()  # (steps, rows)
+        # only decisions whose token is used matter: row k's column j is overridden by BOS for j <= k and by PAD
+        # for j >= M - K + 1 + k (the delay mask), everything else feeds the next step
+        mask = res["pattern_mask"][:, 1:] == -1  # (rows, steps)
+        return float(gap[mask.T[: gap.shape[0]]].min())
+
+    best = None
+    for seed in seeds:
+        enc, prm = c1_inputs(seed)
+        res = run(model, enc, prm, torch.float32)
+        mm = min_margin(res)
+        print(f"c1 seed {seed}: min top-2 margin (fp32) {mm:.3e}")
+        if best is None or mm > best[1]:
+            best = (seed, mm, res)
+    seed, mm32, res32 = best
+    enc, prm = c1_inputs(seed)
+    torch.set_default_dtype(torch.float64)  # transformers' mask helper builds finfo(dtype).min with the default dtype
+    try:
+        res64 = run(model.double(), enc, prm, torch.float64)
+    finally:
+        torch.set_default_dtype(torch.float32)
+    mm64 = min_margin(res64)
+    same = np.array_equal(res32["sequences"], res64["sequences"])
+    print(f"c1: seed {seed}, fp64 margin {mm64:.3e}, fp32 == fp64 tokens: {same}")
+    assert same, "fp32 and fp64 reference runs disagree: pick another seed"
+    err = float((res32["scores"][:, :, :1024].double() - res64["scores"][:, :, :1024]).abs().max())
+    np.savez_compressed(os.path.join(GOLD, "c1_mini.npz"), enc=enc.numpy(), prm=prm.numpy(),
+                        sequences=res64["sequences"], codes=res64["codes"],
+                        meta=np.array([seed, C1["max_length"], C1["weight_seed"]], dtype=np.int64),
+                        margin=np.array([mm64, err], dtype=np.float64),
+                        last_scores=res64["scores"][-1].float().numpy())
+    print(f"c1_mini.npz written: codes {res64['codes'].shape}, fp32-vs-fp64 reference logit error {err:.2e}")
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = import_reference()
@@ -287,9 +359,12 @@ def main():
     gen_dac()
     gen_dac_encode()
     gen_t5()
+    gen_c1(ref)
 
 
-if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "t5":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "c1":
+    gen_c1(import_reference())
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "t5":
     gen_t5()  # transformers only: does not need /root/reference
 elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "dac_encode":
     gen_dac_encode()

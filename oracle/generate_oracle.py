@@ -74,13 +74,45 @@ def topk_candidates(scores_row, top_k):
     return scores_row >= kth
 
 
-def sample_row(scores_row, u, temperature=1.0, top_k=50):
+def topp_candidates(scores_row, keep, top_p):
+    """TopPLogitsWarper (min_tokens_to_keep=1) over the candidates `keep` (the others are already -inf):
+    sort ascending, cumulative softmax probabilities, remove those with cumsum <= 1 - top_p."""
+    s = np.where(keep, scores_row, -np.inf).astype(np.float32)
+    order = np.argsort(s, kind="stable")
+    ss = s[order]
+    m = ss[-1]
+    p = np.exp((ss - m).astype(np.float32)).astype(np.float32)
+    p = p / p.sum(dtype=np.float32)
+    cum = np.cumsum(p, dtype=np.float32)
+    remove_sorted = cum <= np.float32(1.0 - top_p)
+    remove_sorted[-1:] = False
+    remove = np.zeros_like(remove_sorted)
+    remove[order] = remove_sorted
+    return keep & ~remove
+
+
+def repetition_penalty_(scores, ids, penalty):
+    """RepetitionPenaltyLogitsProcessor: score[t] = score[t] * p if < 0 else / p for every t in the row's raw history.
+    With guidance the scores hold 2R rows and ids R rows: only the first R (conditional) rows are touched, which is what
+    the processor's gather / scatter over mismatched batch sizes does."""
+    s = scores.clone()
+    idx = torch.from_numpy(np.asarray(ids, dtype=np.int64))
+    R = idx.shape[0]
+    g = torch.gather(s[:R], 1, idx)
+    g = torch.where(g < 0, g * penalty, g / penalty)
+    s[:R] = s[:R].scatter(1, idx, g)
+    return s
+
+
+def sample_row(scores_row, u, temperature=1.0, top_k=50, top_p=1.0):
     """Inverse-CDF draw in index order over the kept set, fp32 arithmetic in a fixed order:
     p_i = exp(s_i - max) (kept, else 0); walk i ascending accumulating p_i; first i with cumsum > u * total."""
     s = np.asarray(scores_row, dtype=np.float32)
     if temperature != 1.0:
         s = (s / np.float32(temperature)).astype(np.float32)
-    keep = topk_candidates(s, top_k) if top_k and top_k > 0 else np.ones_like(s, dtype=bool)
+    keep = topk_candidates(s, top_k) if top_k and top_k > 0 else np.isfinite(s) | (s == np.inf)
+    if top_p is not None and top_p < 1.0:
+        keep = topp_candidates(s, keep, top_p)
     m = s[keep].max()
     p = np.where(keep, np.exp((s - m).astype(np.float32)).astype(np.float32), np.float32(0.0)).astype(np.float32)
     idx = np.nonzero(keep)[0]
@@ -96,7 +128,7 @@ def sample_row(scores_row, u, temperature=1.0, top_k=50):
     return int(idx[-1])
 
 
-def select_tokens(scores, do_sample, seed=0, step=0, row_offset=0, temperature=1.0, top_k=50):
+def select_tokens(scores, do_sample, seed=0, step=0, row_offset=0, temperature=1.0, top_k=50, top_p=1.0):
     """scores (R, V) torch -> (R,) int64 numpy."""
     s = scores.detach().to(torch.float32).cpu().numpy()
     if not do_sample:
@@ -104,7 +136,7 @@ def select_tokens(scores, do_sample, seed=0, step=0, row_offset=0, temperature=1
     out = np.empty(s.shape[0], dtype=np.int64)
     for r in range(s.shape[0]):
         u = uniform_for(seed, row_offset + r, step)
-        out[r] = sample_row(s[r], u, temperature, top_k)
+        out[r] = sample_row(s[r], u, temperature, top_k, top_p)
     return out
 
 
@@ -127,6 +159,11 @@ def generate_codes(
     suppress_from=None,
     forward_fn=None,
     return_trace=False,
+    top_p=1.0,
+    repetition_penalty=1.0,
+    min_length=0,
+    min_new_tokens=None,
+    logits_processors=None,
 ):
     """Runs the loop.  Returns dict(sequences (B*K, Lout) raw ids incl. the start column, pattern_mask, codes (B,K,F),
     steps, and optionally per-step logits).  `suppress_from`: if set, logits at vocabulary index >= suppress_from are
@@ -160,6 +197,10 @@ def generate_codes(
         def forward_fn(inp, prompt, past):
             return decoder_forward(sd, dims, inp, enc, enc_mask, prompt, prm_mask, past)
 
+    # MinLength / MinNewTokensLength processors (prompt_length_to_skip = the start columns) as one column threshold
+    min_cols = int(min_length or 0)
+    if min_new_tokens:
+        min_cols = max(min_cols, start.shape[1] + int(min_new_tokens))
     unfinished = np.ones(B * K, dtype=np.int64)
     past = None
     trace = []
@@ -171,14 +212,24 @@ def generate_codes(
             model_in = np.concatenate([model_in, model_in], axis=0)
         logits, past = forward_fn(torch.from_numpy(model_in), prm if past is None else None, past)
         scores = logits[:, -1, :].to(torch.float32)
+        # transformers' order: default processors (repetition penalty, min length), then the caller's list with the
+        # guidance processor last (modeling_parler_tts.py:2556-2567).  Min length is applied after the mix here: the
+        # reference's order turns EOS into NaN under guidance (-inf - -inf); see INTEGRATION.md
+        if repetition_penalty != 1.0:
+            scores = repetition_penalty_(scores, ids, float(repetition_penalty))
+        for proc in (logits_processors or []):  # the caller's list runs before the guidance processor appended to it
+            scores = proc(torch.from_numpy(ids), scores)
         if cfg:
             scores = classifier_free_guidance(scores, guidance_scale)
         if suppress_from is not None:
             scores = scores.clone()
             scores[:, suppress_from:] = -float("inf")
+        if ids.shape[1] < min_cols:
+            scores = scores.clone()
+            scores[:, eos] = -float("inf")
         if return_trace:
             trace.append(scores.clone())
-        tok = select_tokens(scores, do_sample, seed, step, row_offset, temperature, top_k)
+        tok = select_tokens(scores, do_sample, seed, step, row_offset, temperature, top_k, top_p)
         tok = tok * unfinished + pad * (1 - unfinished)
         ids = np.concatenate([ids, tok[:, None]], axis=1)
         unfinished = unfinished * (tok != eos).astype(np.int64)

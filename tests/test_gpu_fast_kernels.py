@@ -272,21 +272,18 @@ def _split(w):
     return hi.contiguous(), (w - hi.float()).to(torch.bfloat16).contiguous()
 
 
-def _weights(w_tnc, tiled):
-    """two bf16 planes [taps][N][Cin], or the pre-tiled single buffer of the warp-specialised tcgen05 kernel"""
+def _weights(w_tnc):
+    """[taps][N][Cin] fp32 -> hi/mid bf16 planes in the pre-tiled stage image of the warp-specialised tcgen05 kernel"""
     hi, mid = _split(w_tnc)
-    if not tiled:
-        return hi, mid
     from parler_tts_b200.dac import DacDecoderEngine
-    return DacDecoderEngine._tile(hi, mid)
+    return DacDecoderEngine._tile(hi, mid)[0]
 
 
-@pytest.mark.parametrize("tiled", [True, False])
 @pytest.mark.parametrize("Cin,Cout,k,dil,T", [(96, 96, 7, 9, 700), (192, 192, 1, 1, 300), (1024, 1536, 7, 1, 37),
                                               (384, 384, 7, 3, 129), (32, 26, 7, 1, 5), (192, 192, 7, 9, 1000),
                                               (96, 96, 1, 1, 257), (64, 40, 7, 3, 256)])
-def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T, tiled):
-    if tiled and Cout % 16:
+def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T):
+    if Cout % 16:
         pytest.skip("pre-tiled kernel works on 16-column groups")
     g = torch.Generator().manual_seed(Cin + k + dil)
     B = 2
@@ -298,18 +295,17 @@ def test_dac_conv1d_nwc_vs_torch(Cin, Cout, k, dil, T, tiled):
     xs = x + (1.0 / (alpha[None, :, None] + 1e-9)) * torch.sin(alpha[None, :, None] * x) ** 2
     want = torch.nn.functional.conv1d(xs.double(), w.double(), bias.double(), dilation=dil,
                                       padding=dil * (k - 1) // 2).float() + res
-    hi, mid = _weights(w.permute(2, 0, 1).contiguous(), tiled)
+    wt = _weights(w.permute(2, 0, 1).contiguous())
     x_nwc, res_nwc = x.transpose(1, 2).contiguous(), res.transpose(1, 2).contiguous()
     y = torch.empty(B, T, Cout, device=DEV)
-    cabi.call("ptts_dac_conv1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, k,
-              dil, cabi.ptr(alpha), cabi.ptr(res_nwc), cabi.ptr(y), cabi.stream_ptr())
+    cabi.call("ptts_dac_conv1d_px", cabi.ptr(x_nwc), None, B, T, Cin, cabi.ptr(wt), cabi.ptr(bias), Cout, k, dil,
+              cabi.ptr(alpha), cabi.ptr(res_nwc), cabi.ptr(y), None, None, cabi.stream_ptr())
     err = float((y.transpose(1, 2) - want).abs().max())
     assert err < 2e-4 * max(1.0, float(want.abs().max())), err
 
 
-@pytest.mark.parametrize("tiled", [True, False])
 @pytest.mark.parametrize("Cin,Cout,s,T", [(1536, 768, 8, 11), (192, 96, 2, 300), (64, 32, 4, 130), (384, 192, 4, 515)])
-def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T, tiled):
+def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T):
     g = torch.Generator().manual_seed(Cin + s)
     B = 2
     x = torch.randn(B, Cin, T, generator=g).to(DEV)
@@ -320,10 +316,10 @@ def test_dac_convtr1d_nwc_vs_torch(Cin, Cout, s, T, tiled):
     want = torch.nn.functional.conv_transpose1d(xs.double(), w.double(), bias.double(), stride=s,
                                                 padding=(s + 1) // 2).float()
     assert want.shape[-1] == T * s
-    hi, mid = _weights(w.permute(2, 1, 0).reshape(2, s * Cout, Cin).contiguous(), tiled)
+    wt = _weights(w.permute(2, 1, 0).reshape(2, s * Cout, Cin).contiguous())
     x_nwc = x.transpose(1, 2).contiguous()
     y = torch.empty(B, T * s, Cout, device=DEV)
-    cabi.call("ptts_dac_convtr1d_nwc", cabi.ptr(x_nwc), B, T, Cin, cabi.ptr(hi), cabi.ptr(mid), cabi.ptr(bias), Cout, s,
+    cabi.call("ptts_dac_convtr1d_px", cabi.ptr(x_nwc), None, B, T, Cin, cabi.ptr(wt), cabi.ptr(bias), Cout, s,
               cabi.ptr(alpha), cabi.ptr(y), cabi.stream_ptr())
     err = float((y.transpose(1, 2) - want).abs().max())
     assert err < 2e-4 * max(1.0, float(want.abs().max())), err

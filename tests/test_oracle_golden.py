@@ -162,3 +162,39 @@ def test_dac_decoder_receptive_field_is_ten_frames():
         part = dac_oracle.decode_codes(sd, codes[:, :, lo:hi], dtype=torch.float64)
         err[halo] = float((part[:, :, (f0 - lo) * 512 : (f1 - lo) * 512] - full).abs().max())
     assert err[10] == 0.0 and err[9] > 1e-7, err
+
+
+def test_oracle_processors_match_transformers_classes():
+    """The oracle's top-p / repetition-penalty restatements against the installed transformers' own classes."""
+    from transformers.generation import logits_process as lp
+
+    g = torch.Generator().manual_seed(0)
+    scores = torch.randn(6, 96, generator=g) * 2
+    ids = torch.randint(0, 96, (6, 11), generator=g)
+    want = lp.RepetitionPenaltyLogitsProcessor(1.7)(ids, scores.clone())
+    got = generate_oracle.repetition_penalty_(scores, ids.numpy(), 1.7)
+    assert torch.equal(want, got)
+    for top_p in (0.3, 0.9):
+        want = lp.TopPLogitsWarper(top_p)(ids, scores.clone())
+        for r in range(6):
+            keep = generate_oracle.topp_candidates(scores[r].numpy(), np.ones(96, dtype=bool), top_p)
+            assert np.array_equal(keep, torch.isfinite(want[r]).numpy()), (top_p, r)
+
+
+def test_c1_fixture_reproduced_by_the_oracle_at_full_depth(golden_dir):
+    """BASELINE.json configs[0] (Mini v0.1, bs=1, greedy, 172 frames): the oracle's own decoder + loop reproduce the
+    tokens the reference decoder produced (oracle/gen_golden.py c1), i.e. the restatement is pinned at 24 layers."""
+    from oracle.gen_golden import C1, MINI
+
+    z = np.load(os.path.join(golden_dir, "c1_mini.npz"))
+    seed, max_length, weight_seed = (int(v) for v in z["meta"])
+    assert max_length == C1["max_length"]
+    dims = decoder_oracle.DecoderDims(**MINI)
+    sd = decoder_oracle.random_decoder_state(dims, seed=weight_seed)
+    res = generate_oracle.generate_codes(sd, dims, torch.from_numpy(z["enc"]), prompt_hidden_states=torch.from_numpy(z["prm"]),
+                                         max_length=max_length, do_sample=False, suppress_from=1024, return_trace=True)
+    assert np.array_equal(res["sequences"], z["sequences"])
+    assert np.array_equal(res["codes"], z["codes"]) and z["codes"].shape == (1, 9, 172)
+    err = float((res["scores"][-1][:, :1024] - torch.from_numpy(z["last_scores"][:, :1024])).abs().max())
+    margin = float(z["margin"][0])
+    assert err < 1e-3 and margin > 10 * err, (margin, err)
