@@ -63,13 +63,9 @@ def test_fused_epilogue_fields_vs_oracle(kw):
     if okw.get("do_sample") and "top_k" not in okw:
         okw["top_k"] = 50
     want = generate_oracle.generate_codes(sd, dims, enc, prompt_hidden_states=prm, max_length=M, **okw)
-    gkw = dict(kw)
-    e = enc
-    if kw.get("guidance_scale"):
-        e = torch.cat([enc, torch.zeros_like(enc)])  # the decoder-only API takes both halves of the encoder states
     for graph in (True, False):
         m.use_cuda_graph = graph
-        codes = m.generate(encoder_hidden_states=e.to(DEV), prompt_hidden_states=prm.to(DEV), max_length=M, **gkw)
+        codes = _generate(m, enc, prm, dict(kw, max_length=M))
         assert np.array_equal(codes.cpu().numpy(), want["codes"]), (kw, graph)
 
 
@@ -105,10 +101,8 @@ def test_python_processors_with_and_without_guidance_vs_oracle():
         want = generate_oracle.generate_codes(sd, dims, enc, prompt_hidden_states=prm, max_length=16, do_sample=False,
                                               guidance_scale=gs, logits_processors=[_BanEven()],
                                               repetition_penalty=1.2, suppress_from=32)
-        e = enc if gs is None else torch.cat([enc, torch.zeros_like(enc)])
-        codes = m.generate(encoder_hidden_states=e.to(DEV), prompt_hidden_states=prm.to(DEV), max_length=16,
-                           do_sample=False, guidance_scale=gs, repetition_penalty=1.2,
-                           logits_processor=[_BanEven(), ptts.SuppressTokensAtOrAbove(32)])
+        codes = _generate(m, enc, prm, dict(max_length=16, do_sample=False, guidance_scale=gs, repetition_penalty=1.2),
+                          logits_processor=[_BanEven(), ptts.SuppressTokensAtOrAbove(32)])
         got = codes.cpu().numpy()
         assert np.array_equal(got, want["codes"]), gs
         assert (got % 2 == 1).all()
@@ -188,13 +182,24 @@ def test_sampling_does_not_depend_on_the_shard_layout():
     del K
 
 
-def _codes(m, enc, prm, row_offset, kw):
+def _codes(m, enc, prm, row_offset, kw, logits_processor=None):
     from parler_tts_b200 import modeling as M
 
     gc, _ = M._resolve_generation(m.generation_config, None, dict(kw), None)
     seed = kw.get("seed", 0)
     return M._generate_codes(m, enc.to(DEV), None, None, None, prm.to(DEV).float().contiguous(), None, None, gc, kw,
-                             None, None, None, m.impl, m.use_cuda_graph, seed, row_offset)
+                             logits_processor, None, None, m.impl, m.use_cuda_graph, seed, row_offset)
+
+
+def _generate(m, enc, prm, kw, logits_processor=None):
+    """generate() of the decoder-only model; with guidance the conditioning is doubled the way the COMPOSITE model does
+    it (null text, prompt repeated: modeling_parler_tts.py:2231-2237, 2115-2118), which is what the oracle restates
+    (the decoder-only generate zeroes the prompt of the unconditional half instead, 1214-1229)."""
+    if kw.get("guidance_scale") and kw["guidance_scale"] > 1:
+        e2, p2 = torch.cat([enc, torch.zeros_like(enc)]), prm.repeat(2, 1, 1)
+        return _codes(m, e2, p2, 0, kw, logits_processor)[0]
+    return m.generate(encoder_hidden_states=enc.to(DEV), prompt_hidden_states=prm.to(DEV),
+                      logits_processor=logits_processor, **kw)
 
 
 def test_num_return_sequences_repeats_inputs_like_the_reference():
