@@ -216,7 +216,6 @@ def run_cuda(args):
     model = build_models(dev, dtype)
     model.decoder.impl = impl
     model.decoder.kv_dtype = kv_dtype
-    model.decoder.kv_prefetch_pct = args.kv_prefetch
     w = model.decoder.packed_weights()
     eng = DecoderEngine(w)
     g = torch.Generator().manual_seed(1234 + rank)
@@ -232,8 +231,7 @@ def run_cuda(args):
     prompt_ids = prompt_ids_h.to(dev)
     table = model.prompt_table()
     st = GenState(w, B, S, P, 1, M, impl=impl, suppress_from=1024, row_offset=rank * B * K,
-                  do_sample=args.do_sample, top_k=50 if args.do_sample else 0, kv_dtype=kv_dtype,
-                  kv_prefetch_pct=args.kv_prefetch)
+                  do_sample=args.do_sample, top_k=50 if args.do_sample else 0, kv_dtype=kv_dtype)
     start = torch.full((B * K, 1), MINI["bos_token_id"], dtype=torch.int64, device=dev)
     codes = torch.empty(B, K, N, dtype=torch.int64, device=dev)
     from parler_tts_b200 import sharding
@@ -422,7 +420,7 @@ def run_cuda(args):
                                        "static KV cache + CUDA graph",
                            "kernels": args.kernels,
                            "kv_dtype": args.kv_dtype if dtype == torch.bfloat16 else "f32",
-                           "kv_prefetch_pct": args.kv_prefetch, "env_knobs": knobs, "library": os.path.basename(cabi.LIB_PATH),
+                           "env_knobs": knobs, "library": os.path.basename(cabi.LIB_PATH),
                            "l2": f"per-step working set (weights {W * es / 1e6:.0f} MB + KV) exceeds the 126 MB L2; no flush needed",
                            "parallelism": f"batch-sharded replicas x{world}, NCCL all_gather of codes only"},
                 "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
@@ -446,8 +444,6 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=8)
     ap.add_argument("--kv-dtype", default="bf16", choices=["bf16", "fp8"],
                     help="self-attention KV cache element type (fp8 = e4m3 with per-(layer, K|V, head) scales, opt-in)")
-    ap.add_argument("--kv-prefetch", type=int, default=0,
-                    help="PttsState.kv_prefetch_pct: L2 prefetch of the next layer's K (<=50) or K+V (>50) rows")
     ap.add_argument("--check-steps", type=int, default=40, help="token columns re-derived eagerly after the timed region")
     ap.add_argument("--skip-check", action="store_true")
     ap.add_argument("--no-graph", action="store_true")

@@ -122,8 +122,7 @@ typedef struct {
   float repetition_penalty;/* epilogue: RepetitionPenaltyLogitsProcessor over the row's own history; 1 = off */
   int32_t logits_premixed; /* guidance_scale > 1 only: rows [0, B/2*K) of `logits` already hold the guidance-mixed scores
                               (host-side logits processors ran); the epilogue skips its own mix */
-  int32_t kv_prefetch_pct; /* decode step: after layer l's self-attention, queue L2 prefetches of the NEXT self-attention
-                              launch's cache rows: <= 50 the K rows of every (b, head), > 50 K and V rows; 0 = off */
+  int32_t reserved1;
   float* kv_scale;         /* [L][2][heads] fp32, PTTS_FP8 only: written by ptts_prefill, read by ptts_decode_step */
   void* kv_stage;          /* [L][2][B][heads][P+T0][d] T, PTTS_FP8 only: staging cache of the prefill */
   int64_t pad_id, eos_id;  /* generation-config ids used by the epilogue (may differ from the decoder config's) */

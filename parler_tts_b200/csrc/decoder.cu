@@ -177,14 +177,14 @@ static constexpr int skip_mask() { return 0; }
 
 // h += x . w^T   (out_proj / fc2 with the residual add of modeling_parler_tts.py:460,483,492)
 static int residual_linear(const PttsModel* m, const PttsState* s, const Path& path, Pending& pend, const void* x,
-                           const void* w, int rows, int K, cudaStream_t st, const KvPrefetch* pf = nullptr) {
+                           const void* w, int rows, int K, cudaStream_t st) {
   const int H = m->hidden, dt = m->wdtype;
   if (path.gemm && path.ln && rows <= 256 && split_k_partials_enabled()) {
     int bn = 64;
     const int S = gemm_bf16_plan_splits(rows, H, K, &bn);
     if (S > 1) {
       float* part = work_area(m, s);
-      PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st, pf));
+      PTTS_TRY(gemm_bf16_partial(x, w, rows, H, K, S, bn, part, st));
       pend.part = part;
       pend.S = S;
       pend.stride = (int64_t)rows * H;
@@ -251,25 +251,11 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     const int xb_late = PTTS_KNOB("PTTS_XB_LATE", 1);
     if (xb_late) gemm_next_trigger_late(xb_late == 2);
   }
-  // L2 prefetch of the NEXT self-attention launch's cache rows (layer l + 1 of this step, or layer 0 of the next step),
-  // queued by this out_proj once the self-attention kernel in front of it has finished: kv_prefetch_pct % of the K
-  // then V bytes ([0, 50]: share of K; (50, 100]: all of K and a share of V)
-  KvPrefetch pf;
-  if (fused_self && s->kv_prefetch_pct > 0) {
-    const int ln = (l + 1) % m->n_layers;
-    const KvView nkv = self_kv(m, s, ln, 1);
-    const int rb = d * (int)(nkv.dtype == PTTS_FP8 ? 1 : dtype_size(nkv.dtype));
-    const int pct = s->kv_prefetch_pct > 100 ? 100 : s->kv_prefetch_pct;
-    // K and V of a layer are adjacent [2][B][heads][c_max][d]: one range per (K|V, b, head)
-    pf.base = nkv.k;
-    pf.ranges = (pct > 50 ? 2 : 1) * B * heads;
-    pf.row_bytes = rb;
-    pf.stride = (long long)nkv.c_stride * rb;
-    pf.rows_base = ctx_base - 1;  // rows already in the cache (this step's row is appended by that launch itself)
-    pf.rows_dyn = ctx_dyn;
-    (void)pct;
-  }
-  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st, pf.base ? &pf : nullptr));
+  // (An L2 prefetch of the NEXT layer's K/V rows queued from this out_proj, right after the self-attention kernel has
+  // finished its stream, was measured on B200 at B=64 / 860 frames: fp8 cache 1.097 -> 1.477 (K) / 1.485 ms (K+V) per
+  // decode step, bf16 cache 1.286 -> 2.024 / 2.050 ms - the prefetch costs its full HBM time in front of the chain's
+  // weight loads and the later attention launch does not find the rows in L2.  Removed; profiles/r02_l2_prefetch.txt.)
+  PTTS_UNLESS_SKIPPED(8, residual_linear(m, s, path, pend, s->attn, L.w_o, rows, H, st));
   // ---- cross attention block (modeling_parler_tts.py:465-483)
   if (cross) {
     const size_t es = dtype_size(dt);

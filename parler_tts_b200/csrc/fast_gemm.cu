@@ -215,16 +215,12 @@ int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out) {
 }
 
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st, const KvPrefetch* pf) {
+                      cudaStream_t st) {
   GemmParams p = {};
   p.X = (const __nv_bfloat16*)x;
   p.W = (const __nv_bfloat16*)w;
   p.M = M; p.N = N; p.K = K; p.k_per_split = K / splits;
   p.part = part;
-  if (pf && pf->base && bn == 0) {  // only the tcgen05 kernel carries the prefetch
-    p.pf_base = (const unsigned char*)pf->base; p.pf_ranges = pf->ranges; p.pf_row_bytes = pf->row_bytes;
-    p.pf_rows_base = pf->rows_base; p.pf_stride = pf->stride; p.pf_rows_dyn = pf->rows_dyn;
-  }
   if (bn == 0) return umma_gemm_partial(p, splits, st);
   return launch_bn<EPI_PARTIAL>(bn, p, splits, st);
 }

@@ -230,21 +230,6 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
     cp_async_wait<0>();
     if ((dbg & 3) == 3) c_x = clock64();
   }
-  if constexpr (EPI == EPI_PARTIAL) {
-    // the self-attention kernel in front of this out_proj has just finished its K/V stream and HBM idles through the
-    // short kernels that follow: queue the NEXT layer's cache rows into L2 now (fire and forget, behind the X copies)
-    if (p.pf_base) {
-      const int rows = dyn_value(p.pf_rows_base, p.pf_rows_dyn);
-      const long long bytes = (long long)rows * p.pf_row_bytes;
-      const int nthr = gridDim.x * gridDim.y * gridDim.z * NTH;
-      const int me = ((blockIdx.z * gridDim.y + blockIdx.y) * gridDim.x + blockIdx.x) * NTH + threadIdx.x;
-      for (int r = me; r < p.pf_ranges; r += nthr) {
-        const unsigned char* src = p.pf_base + (long long)r * p.pf_stride;
-        for (long long o = 0; o < bytes; o += 8192)
-          l2_prefetch_bulk(src + o, (uint32_t)(bytes - o < 8192 ? bytes - o : 8192));
-      }
-    }
-  }
   asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // cp.async (generic proxy) -> UMMA (async proxy)
   asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
   __syncthreads();

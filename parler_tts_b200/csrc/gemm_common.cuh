@@ -30,13 +30,6 @@ struct GemmParams {
   float q_scale;
   // PARTIAL
   float* part;
-  // PARTIAL, optional: once its own dependency has resolved, the grid queues L2 prefetches of cache rows a LATER launch
-  // streams (the next layer's self-attention K/V): pf_ranges contiguous ranges of rows x pf_row_bytes bytes at
-  // pf_base + i * pf_stride, rows = pf_rows_base + *pf_rows_dyn; null = off
-  const unsigned char* pf_base;
-  int pf_ranges, pf_row_bytes, pf_rows_base;
-  long long pf_stride;
-  const int* pf_rows_dyn;
   // (Two in-kernel finishers of the PARTIAL variant were measured and removed: a grid-wide arrival counter after which
   // every CTA folds + LayerNorms its share of the rows - 1.99 against 1.78 ms per decode step - and a "pair finisher" in
   // which the second-arriving K-slice CTA of an fc1 tile folds both slices and applies the activation - 1.539 against

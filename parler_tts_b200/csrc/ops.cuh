@@ -30,15 +30,8 @@ int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has
                       void* cv, int H, int heads, int d, int Tq, int c_stride, int pos_base, const int* pos_dyn,
                       cudaStream_t st);
 int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
-// optional L2 prefetch the launch queues once its dependency has resolved (see GemmParams::pf_base)
-struct KvPrefetch {
-  const void* base = nullptr;
-  int ranges = 0, row_bytes = 0, rows_base = 0;
-  long long stride = 0;
-  const int* rows_dyn = nullptr;
-};
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
-                      cudaStream_t st, const KvPrefetch* pf = nullptr);
+                      cudaStream_t st);
 // the next gemm_bf16_partial launch releases its dependent kernel AFTER its own dependency wait whatever PTTS_PDL_EARLY
 // says, or (at_mma_done) only when its MMA burst has completed
 void gemm_next_trigger_late(int at_mma_done);

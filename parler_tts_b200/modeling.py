@@ -468,8 +468,7 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
     S = 0 if enc is None else enc.shape[1]
     gscale = float(gc.guidance_scale) if cfg else 1.0
     kv_dtype = getattr(decoder, "kv_dtype", None)
-    kv_pf = int(getattr(decoder, "kv_prefetch_pct", 0) or 0)
-    key = (kv_pf, id(w), B, S, P, T0, max_length, impl, do_sample, top_k, temperature, suppress, gscale, row_offset,
+    key = (id(w), B, S, P, T0, max_length, impl, do_sample, top_k, temperature, suppress, gscale, row_offset,
            enc_mask is not None, prompt_mask is not None, kv_dtype, plan.min_length, plan.top_p, plan.rep_penalty,
            plan.cfg_in_python, bos, pad, eos)
     cached = getattr(decoder, "_state_cache", None)
@@ -486,7 +485,7 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
                       row_offset=row_offset * K,
                       enc_mask=None if enc_mask is None else enc_mask.to(dev, torch.int32).clone(),
                       prompt_mask=None if prompt_mask is None else prompt_mask.to(dev, torch.int32).clone(),
-                      kv_dtype=kv_dtype, kv_prefetch_pct=kv_pf, min_length=plan.min_length, top_p=plan.top_p,
+                      kv_dtype=kv_dtype, min_length=plan.min_length, top_p=plan.top_p,
                       repetition_penalty=plan.rep_penalty, pad_token_id=pad,
                       eos_token_id=-1 if eos is None else eos, bos_token_id=bos)
         st.c_state.logits_premixed = int(plan.cfg_in_python)
@@ -595,8 +594,6 @@ class ParlerTTSForCausalLM(nn.Module):
         # self-attention KV cache element type: None = the weight dtype; "fp8" = e4m3 with per-(layer, K|V, head) scales
         # (bf16 weights + fast kernels only; halves the bytes of the dominant stream)
         self.kv_dtype = None
-        # L2 prefetch of the next layer's K/V rows from the self-attention out_proj (PttsState.kv_prefetch_pct)
-        self.kv_prefetch_pct = 0
 
     # ---- plumbing
     @property
