@@ -459,14 +459,16 @@ struct MapKeyHash {
            (size_t)k.box_rows ^ ((size_t)k.dtype << 20) ^ (size_t)k.pitch_bytes * 0x165667B19E3779F9ull;
   }
 };
-// bf16 row-major [rows][cols]; box = 64 columns (128 bytes, SWIZZLE_128B) x box_rows rows; out-of-range rows read as 0
-bool tensor_map_2d_impl(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+// row-major [rows][cols] matrix, box = 64 columns x box_rows rows, out-of-range rows read as 0:
+//   PTTS_BF16: 128-byte box rows, SWIZZLE_128B;  PTTS_FP8 (bytes): 64-byte box rows, SWIZZLE_64B
+bool tensor_map_2d_any(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out) {
   static std::mutex mu;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   EncodeTiledFn fn = encode_tiled_fn();
-  if (!fn || (reinterpret_cast<uintptr_t>(ptr) & 15) || cols % 8) return false;
+  const int es = dtype == PTTS_FP8 ? 1 : 2;
+  if (!fn || (reinterpret_cast<uintptr_t>(ptr) & 15) || (cols * es) % 16) return false;
   std::lock_guard<std::mutex> lock(mu);
-  const MapKey key = {ptr, rows, cols, box_rows, PTTS_BF16, (long long)cols * 2};
+  const MapKey key = {ptr, rows, cols, box_rows, dtype, (long long)cols * es};
   auto it = cache.find(key);
   if (it != cache.end()) {
     *out = it->second;
@@ -474,17 +476,21 @@ bool tensor_map_2d_impl(const void* ptr, int rows, int cols, int box_rows, CUten
   }
   CUtensorMap m;
   const cuuint64_t gdim[2] = {(cuuint64_t)cols, (cuuint64_t)rows};
-  const cuuint64_t gstr[1] = {(cuuint64_t)cols * 2};
+  const cuuint64_t gstr[1] = {(cuuint64_t)cols * es};
   const cuuint32_t box[2] = {(cuuint32_t)KB64, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2, const_cast<void*>(ptr), gdim, gstr, box, estr,
-                        CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
-                        CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  const CUresult r = fn(&m, dtype == PTTS_FP8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+                        const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+                        dtype == PTTS_FP8 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
   if (r != CUDA_SUCCESS) return false;
   if (cache.size() > 4096) cache.clear();
   cache.emplace(key, m);
   *out = m;
   return true;
+}
+bool tensor_map_2d_impl(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
+  return tensor_map_2d_any(ptr, rows, cols, box_rows, PTTS_BF16, out);
 }
 
 template <int EPI>
@@ -570,6 +576,9 @@ namespace gemm {
 bool tma_available() { return encode_tiled_fn() != nullptr; }
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
   return tensor_map_2d_impl(ptr, rows, cols, box_rows, out);
+}
+bool tensor_map_2d_dt(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out) {
+  return tensor_map_2d_any(ptr, rows, cols, box_rows, dtype, out);
 }
 int umma_read_stamps(unsigned long long* host, int n_launches) {
   if (n_launches == -2) {  // reset the aggregate statistics

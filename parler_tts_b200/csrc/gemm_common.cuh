@@ -79,6 +79,8 @@ __device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g
 // Cached tensor map (fast_gemm3.cu) of a bf16 row-major matrix [rows][cols]: box = 64 columns (128 bytes, SWIZZLE_128B)
 // x box_rows rows, out-of-range rows read as 0.  false: no driver entry point / misaligned matrix.
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
+// same for PTTS_BF16 (128-byte box rows, SWIZZLE_128B) or PTTS_FP8 bytes (64-byte box rows, SWIZZLE_64B)
+bool tensor_map_2d_dt(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out);
 bool tma_available();  // the driver entry point for tensor-map creation was found
 
 // tcgen05 swap-AB cluster split-K kernel (fast_gemm3.cu)
