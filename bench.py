@@ -216,6 +216,7 @@ def run_cuda(args):
     model = build_models(dev, dtype)
     model.decoder.impl = impl
     model.decoder.kv_dtype = kv_dtype
+    model.decoder.self_attn_kernel = args.self_attn_kernel
     w = model.decoder.packed_weights()
     eng = DecoderEngine(w)
     g = torch.Generator().manual_seed(1234 + rank)
@@ -231,7 +232,8 @@ def run_cuda(args):
     prompt_ids = prompt_ids_h.to(dev)
     table = model.prompt_table()
     st = GenState(w, B, S, P, 1, M, impl=impl, suppress_from=1024, row_offset=rank * B * K,
-                  do_sample=args.do_sample, top_k=50 if args.do_sample else 0, kv_dtype=kv_dtype)
+                  do_sample=args.do_sample, top_k=50 if args.do_sample else 0, kv_dtype=kv_dtype,
+                  self_attn_kernel=args.self_attn_kernel)
     start = torch.full((B * K, 1), MINI["bos_token_id"], dtype=torch.int64, device=dev)
     codes = torch.empty(B, K, N, dtype=torch.int64, device=dev)
     from parler_tts_b200 import sharding
@@ -420,7 +422,7 @@ def run_cuda(args):
                                        "static KV cache + CUDA graph",
                            "kernels": args.kernels,
                            "kv_dtype": args.kv_dtype if dtype == torch.bfloat16 else "f32",
-                           "env_knobs": knobs, "library": os.path.basename(cabi.LIB_PATH),
+                           "self_attn_kernel": args.self_attn_kernel, "env_knobs": knobs, "library": os.path.basename(cabi.LIB_PATH),
                            "l2": f"per-step working set (weights {W * es / 1e6:.0f} MB + KV) exceeds the 126 MB L2; no flush needed",
                            "parallelism": f"batch-sharded replicas x{world}, NCCL all_gather of codes only"},
                 "clocks": clocks.summary(), "e2e": e2e, "gpu_launches": launches, "roofline": roofline,
@@ -444,6 +446,8 @@ def main():
     ap.add_argument("--cpu-steps", type=int, default=8)
     ap.add_argument("--kv-dtype", default="bf16", choices=["bf16", "fp8"],
                     help="self-attention KV cache element type (fp8 = e4m3 with per-(layer, K|V, head) scales, opt-in)")
+    ap.add_argument("--self-attn-kernel", type=int, default=0, choices=[0, 1, 2],
+                    help="PttsState.self_attn_kernel: 0 automatic, 1 one CTA per (utterance, head), 2 persistent tcgen05")
     ap.add_argument("--check-steps", type=int, default=40, help="token columns re-derived eagerly after the timed region")
     ap.add_argument("--skip-check", action="store_true")
     ap.add_argument("--no-graph", action="store_true")

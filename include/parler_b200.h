@@ -122,7 +122,9 @@ typedef struct {
   float repetition_penalty;/* epilogue: RepetitionPenaltyLogitsProcessor over the row's own history; 1 = off */
   int32_t logits_premixed; /* guidance_scale > 1 only: rows [0, B/2*K) of `logits` already hold the guidance-mixed scores
                               (host-side logits processors ran); the epilogue skips its own mix */
-  int32_t reserved1;
+  int32_t self_attn_kernel;/* decode-step self-attention kernel: 0 = automatic (today: one CTA per (utterance, head) item,
+                              split-KV for small batches), 1 = always one CTA per item, 2 = the warp-specialised persistent
+                              TMA + tcgen05 kernel whenever its shape constraints hold (bf16 weights, d = 64, >= 2 items / SM) */
   float* kv_scale;         /* [L][2][heads] fp32, PTTS_FP8 only: written by ptts_prefill, read by ptts_decode_step */
   void* kv_stage;          /* [L][2][B][heads][P+T0][d] T, PTTS_FP8 only: staging cache of the prefill */
   int64_t pad_id, eos_id;  /* generation-config ids used by the epilogue (may differ from the decoder config's) */
@@ -187,6 +189,16 @@ PTTS_API int ptts_attention_fp8(const void* q, const void* cache_k, const void* 
                                 const float* v_scale, int32_t B, int32_t heads, int32_t d, int32_t c_stride,
                                 int32_t ctx_base, const int32_t* ctx_dyn, const int32_t* key_mask, int32_t mask_len,
                                 void* out, float* scratch, ptts_stream_t s);
+/* The decode-step self-attention of ptts_decode_step alone, on the warp-specialised persistent kernel (TMA-staged
+ * 128-row tiles, both products on tcgen05): q | k | v of the new token arrive as S split-K partial slices
+ * part[s][b][3H] (fp32, summed in slice order), q is scaled by `scale`, the new K / V row is appended at slot
+ * slot_base + *slot_dyn (= rows already cached) and the bf16 output row out[b][H] attends over rows [0, slot].
+ * kv_dtype PTTS_BF16 or PTTS_FP8 (k_scale / v_scale [heads]).  Returns PTTS_E_UNSUPPORTED for shapes it does not take
+ * (d != 64, fewer than 2 items per SM). */
+PTTS_API int ptts_attention_ws(const float* part, int32_t S, int64_t part_stride, int32_t ncols, float scale,
+                               int32_t slot_base, const int32_t* slot_dyn, void* cache_k, void* cache_v, int32_t kv_dtype,
+                               const float* k_scale, const float* v_scale, int32_t B, int32_t heads, int32_t d,
+                               int32_t c_stride, const int32_t* key_mask, int32_t mask_len, void* out, ptts_stream_t s);
 /* Quantises staged bf16 cache rows [n_lk][B][heads][slots][64] (n_lk = layers x {K, V}) into the e4m3 cache
  * [n_lk][B][heads][c_max][64]: scale[n_lk][heads] = 4 * amax / 448 over the staged rows (head-room for later tokens),
  * rows converted with saturation.  amax_ws: n_lk * heads uint32 of workspace.  ptts_prefill calls this itself when

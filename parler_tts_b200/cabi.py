@@ -45,7 +45,7 @@ class PttsState(C.Structure):
                 ("h", c_vp), ("xn", c_vp), ("q", c_vp), ("attn", c_vp), ("ffn", c_vp), ("logits", c_vp),
                 ("scratch", c_vp), ("ids", c_vp), ("mask", c_vp), ("unfinished", c_vp),
                 ("kv_dtype", c_i32), ("min_length", c_i32), ("top_p", c_f32), ("repetition_penalty", c_f32),
-                ("logits_premixed", c_i32), ("reserved1", c_i32), ("kv_scale", c_vp), ("kv_stage", c_vp), ("pad_id", c_i64), ("eos_id", c_i64)]
+                ("logits_premixed", c_i32), ("self_attn_kernel", c_i32), ("kv_scale", c_vp), ("kv_stage", c_vp), ("pad_id", c_i64), ("eos_id", c_i64)]
 
 
 class PttsT5Layer(C.Structure):
@@ -80,6 +80,8 @@ PROTOTYPES = {
                                  c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
     "ptts_attention_fp8": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32,
                                      c_vp, c_vp, c_vp]),
+    "ptts_attention_ws": (C.c_int, [c_vp, c_i32, c_i64, c_i32, c_f32, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i32,
+                                    c_i32, c_i32, c_i32, c_vp, c_i32, c_vp, c_vp]),
     "ptts_kv_quantize_fp8": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp]),
     "ptts_cross_kv": (C.c_int, [_PM, _PS, c_vp, c_vp]),
     "ptts_prefill": (C.c_int, [_PM, _PS, c_vp, c_vp, c_vp, c_vp, c_i32, c_vp]),

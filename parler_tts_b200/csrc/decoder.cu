@@ -218,7 +218,17 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     float* qpart = work_area(m, s);
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
     if (wpf_mask() & 2) set_l2_hint(L.w_o, (long long)H * H * dtype_size(dt));
-    if (kv.dtype == PTTS_FP8)
+    // self-attention kernel choice (PttsState.self_attn_kernel): one CTA per (utterance, head) item (split-KV for small
+    // batches), or - opt-in, 2 - the persistent warp-specialised TMA + tcgen05 kernel.  Measured on B200 (B=64, 860
+    // frames, profiles/r02_attn_ws_v1.txt): per item 1.285 (bf16 cache) / 1.097 ms (fp8) per decode step, persistent v1
+    // 1.759 / 1.626 ms - its CTAs walk their ~7 items strictly one after the other, so the score -> softmax -> P.V
+    // latency chain of an item is exposed 7 times per launch; automatic (0) therefore stays with the per-item kernels
+    const bool ws = s->self_attn_kernel == 2 && dt == PTTS_BF16 && attention_ws_supported(B, heads, d, kv.c_stride);
+    if (ws)
+      PTTS_UNLESS_SKIPPED(4, attention_ws_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, scale, ctx_base - 1, ctx_dyn,
+                                                kv.k, kv.v, kv.dtype, kv.k_scale, kv.v_scale, B, heads, kv.c_stride,
+                                                s->prompt_mask, s->P, s->attn, st));
+    else if (kv.dtype == PTTS_FP8)
       PTTS_UNLESS_SKIPPED(4, attention_fp8_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, scale, ctx_base - 1, ctx_dyn,
                                                  kv.k, kv.v, kv.k_scale, kv.v_scale, B, heads, kv.c_stride, ctx_base,
                                                  ctx_dyn, s->prompt_mask, s->P, s->attn, attn_area(s), st));
@@ -398,6 +408,22 @@ extern "C" int ptts_attention_fp8(const void* q, const void* cache_k, const void
   PTTS_CHECK_ARG(B > 0 && heads > 0 && c_stride > 0 && attention_fp8_supported(d), "attention_fp8: bad dims");
   return attention_fp8(q, cache_k, cache_v, k_scale, v_scale, B, heads, c_stride, ctx_base, ctx_dyn, key_mask,
                        mask_len, out, scratch, as_stream(s));
+}
+
+extern "C" int ptts_attention_ws(const float* part, int32_t S, int64_t part_stride, int32_t ncols, float scale,
+                                 int32_t slot_base, const int32_t* slot_dyn, void* cache_k, void* cache_v,
+                                 int32_t kv_dtype, const float* k_scale, const float* v_scale, int32_t B, int32_t heads,
+                                 int32_t d, int32_t c_stride, const int32_t* key_mask, int32_t mask_len, void* out,
+                                 ptts_stream_t s) {
+  PTTS_CHECK_ARG(part && cache_k && cache_v && out && S > 0 && B > 0 && heads > 0 && c_stride > 0,
+                 "attention_ws: bad arguments");
+  PTTS_CHECK_ARG(kv_dtype == PTTS_BF16 || (kv_dtype == PTTS_FP8 && k_scale && v_scale), "attention_ws: bad kv_dtype");
+  if (!attention_ws_supported(B, heads, d, c_stride)) {
+    set_error("attention_ws: unsupported shape (head_dim 64, at least 2 items per SM)");
+    return PTTS_E_UNSUPPORTED;
+  }
+  return attention_ws_fused(part, S, part_stride, ncols, scale, slot_base, slot_dyn, cache_k, cache_v, kv_dtype, k_scale,
+                            v_scale, B, heads, c_stride, key_mask, mask_len, out, as_stream(s));
 }
 
 extern "C" int ptts_kv_quantize_fp8(const void* stage, int32_t n_lk, int32_t B, int32_t heads, int32_t d, int32_t slots,

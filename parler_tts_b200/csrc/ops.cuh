@@ -69,6 +69,11 @@ int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int 
                          int ctx_base, const int* ctx_dyn, const int* key_mask, int mask_len, void* out, float* scratch,
                          const void* pf_next, int pf_stride, int pf_rows_base, const int* pf_rows_dyn,
                          cudaStream_t st);
+// warp-specialised, TMA-staged persistent flash-decode on tcgen05 (fast_attn_ws.cu): bf16 or fp8 cache
+bool attention_ws_supported(int B, int heads, int d, int c_stride);
+int attention_ws_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, float scale, int slot_base,
+                       const int* slot_dyn, void* ck, void* cv, int kv_dtype, const float* k_scale, const float* v_scale,
+                       int B, int heads, int c_stride, const int* key_mask, int mask_len, void* out, cudaStream_t st);
 // the cross-attention block of a decode step in one launch (fast_xblock.cu)
 bool xblock_supported(int H, int heads, int d, int S);
 int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, const float* gamma, const float* beta,

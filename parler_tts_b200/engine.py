@@ -100,7 +100,7 @@ class GenState:
     def __init__(self, weights: DecoderWeights, B, S, P, T0, max_len, impl=cabi.IMPL_FAST, do_sample=False, top_k=50,
                  temperature=1.0, suppress_from=-1, guidance_scale=1.0, seed=0, row_offset=0, enc_mask=None,
                  prompt_mask=None, kv_dtype=None, min_length=0, top_p=1.0, repetition_penalty=1.0, pad_token_id=None,
-                 eos_token_id=None, bos_token_id=None):
+                 eos_token_id=None, bos_token_id=None, self_attn_kernel=0):
         d, dev, dt = weights.dims, weights.device, weights.dtype
         self.weights = weights
         self.B, self.S, self.P, self.T0, self.max_len = B, S, P, T0, max_len
@@ -142,6 +142,7 @@ class GenState:
         s.suppress_from = int(suppress_from if suppress_from is not None else -1)
         s.guidance_scale = float(guidance_scale) if self.cfg else 1.0
         s.seed, s.row_offset = int(seed) & 0xFFFFFFFFFFFFFFFF, int(row_offset)
+        s.self_attn_kernel = int(self_attn_kernel or 0)
         s.kv_dtype = cabi.PTTS_FP8 if self.kv_dtype == "fp8" else cabi.dtype_enum(dt)
         s.kv_scale = None if self.kv_scale is None else self.kv_scale.data_ptr()
         s.kv_stage = None if self.kv_stage is None else self.kv_stage.data_ptr()

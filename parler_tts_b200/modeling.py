@@ -468,7 +468,8 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
     S = 0 if enc is None else enc.shape[1]
     gscale = float(gc.guidance_scale) if cfg else 1.0
     kv_dtype = getattr(decoder, "kv_dtype", None)
-    key = (id(w), B, S, P, T0, max_length, impl, do_sample, top_k, temperature, suppress, gscale, row_offset,
+    sak = int(getattr(decoder, "self_attn_kernel", 0) or 0)
+    key = (sak, id(w), B, S, P, T0, max_length, impl, do_sample, top_k, temperature, suppress, gscale, row_offset,
            enc_mask is not None, prompt_mask is not None, kv_dtype, plan.min_length, plan.top_p, plan.rep_penalty,
            plan.cfg_in_python, bos, pad, eos)
     cached = getattr(decoder, "_state_cache", None)
@@ -485,7 +486,7 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
                       row_offset=row_offset * K,
                       enc_mask=None if enc_mask is None else enc_mask.to(dev, torch.int32).clone(),
                       prompt_mask=None if prompt_mask is None else prompt_mask.to(dev, torch.int32).clone(),
-                      kv_dtype=kv_dtype, min_length=plan.min_length, top_p=plan.top_p,
+                      kv_dtype=kv_dtype, self_attn_kernel=sak, min_length=plan.min_length, top_p=plan.top_p,
                       repetition_penalty=plan.rep_penalty, pad_token_id=pad,
                       eos_token_id=-1 if eos is None else eos, bos_token_id=bos)
         st.c_state.logits_premixed = int(plan.cfg_in_python)
@@ -594,6 +595,9 @@ class ParlerTTSForCausalLM(nn.Module):
         # self-attention KV cache element type: None = the weight dtype; "fp8" = e4m3 with per-(layer, K|V, head) scales
         # (bf16 weights + fast kernels only; halves the bytes of the dominant stream)
         self.kv_dtype = None
+        # decode-step self-attention kernel (PttsState.self_attn_kernel): 0 automatic, 1 one CTA per (utterance, head),
+        # 2 the persistent warp-specialised tcgen05 kernel whenever its shape constraints hold
+        self.self_attn_kernel = 0
 
     # ---- plumbing
     @property
@@ -674,7 +678,8 @@ class ParlerTTSForCausalLM(nn.Module):
             if cap < T + 1:
                 raise ValueError(f"max_cache_len={cap} is too small for {T} columns")
         st = GenState(w, B, S, P, T, cap, impl=self.impl, enc_mask=encoder_attention_mask,
-                      prompt_mask=prompt_attention_mask, kv_dtype=self.kv_dtype if use_cache else None)
+                      prompt_mask=prompt_attention_mask, kv_dtype=self.kv_dtype if use_cache else None,
+                      self_attn_kernel=self.self_attn_kernel)
         st.mask.fill_(-1)
         st.ids[:, :T] = ids
         st.ctrl.copy_(torch.tensor([T, 0, 0, B * K, 0, 0, 0, 0], dtype=torch.int32))
