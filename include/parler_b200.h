@@ -183,6 +183,17 @@ PTTS_API int ptts_attention(const void* q, const void* cache_k, const void* cach
                    const int32_t* key_mask, int32_t mask_len, void* out, float* scratch, int32_t impl,
                    ptts_stream_t s);
 
+/* No counterpart in the reference.  ptts_attention (fast family, Tq = 1,
+ * d = 64, T = PTTS_F32 | PTTS_BF16) for callers that cannot allocate device memory: the split-KV scratch is a static
+ * __device__ array inside the library (ptts_attention_noalloc_max_floats() = 262144 floats = 1 MiB per GPU, held until
+ * the process exits) instead of a caller buffer; the call allocates nothing.  Limit: B * heads <= 3363 (the scratch
+ * ptts_attention would need must fit), larger sizes return PTTS_E_ARG with a message.  All calls share the array, which
+ * keeps the last call's contents (nothing needs clearing: every slot read is written within the same call); calls that
+ * overlap on the GPU (different streams / threads) race on it - serialise them or use ptts_attention. */
+PTTS_API int64_t ptts_attention_noalloc_max_floats(void);
+PTTS_API int ptts_attention_noalloc(const void* q, const void* cache_k, const void* cache_v, int32_t dtype, int32_t B,
+                                    int32_t heads, int32_t d, int32_t c_stride, int32_t ctx_base, const int32_t* ctx_dyn,
+                                    const int32_t* key_mask, int32_t mask_len, void* out, ptts_stream_t s);
 /* The same over an e4m3 cache [B][heads][c_stride][64] (PttsState.kv_dtype = PTTS_FP8): q bf16 [B][H] already
  * scaled, k_scale / v_scale [heads] fp32 dequantisation multipliers, out bf16 [B][H].  Tq = 1, d = 64. */
 PTTS_API int ptts_attention_fp8(const void* q, const void* cache_k, const void* cache_v, const float* k_scale,

@@ -78,6 +78,9 @@ PROTOTYPES = {
                               c_i32, c_i32, c_vp]),
     "ptts_attention": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_i32,
                                  c_vp, c_i32, c_vp, c_vp, c_i32, c_vp]),
+    "ptts_attention_noalloc_max_floats": (c_i64, []),
+    "ptts_attention_noalloc": (C.c_int, [c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32,
+                                         c_vp, c_vp]),
     "ptts_attention_fp8": (C.c_int, [c_vp, c_vp, c_vp, c_vp, c_vp, c_i32, c_i32, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32,
                                      c_vp, c_vp, c_vp]),
     "ptts_attention_ws": (C.c_int, [c_vp, c_i32, c_i64, c_i32, c_f32, c_i32, c_vp, c_vp, c_vp, c_i32, c_vp, c_vp, c_i32,
