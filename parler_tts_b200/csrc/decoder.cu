@@ -220,9 +220,10 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     if (wpf_mask() & 2) set_l2_hint(L.w_o, (long long)H * H * dtype_size(dt));
     // self-attention kernel choice (PttsState.self_attn_kernel): one CTA per (utterance, head) item (split-KV for small
     // batches), or - opt-in, 2 - the persistent warp-specialised TMA + tcgen05 kernel.  Measured on B200 (B=64, 860
-    // frames, profiles/r02_attn_ws_v1.txt): per item 1.285 (bf16 cache) / 1.097 ms (fp8) per decode step, persistent v1
-    // 1.759 / 1.626 ms - its CTAs walk their ~7 items strictly one after the other, so the score -> softmax -> P.V
-    // latency chain of an item is exposed 7 times per launch; automatic (0) therefore stays with the per-item kernels
+    // frames, profiles/r02_attn_ws.txt): per item 1.285 (bf16 cache) / 1.097 ms (fp8) per decode step, persistent 1.475 /
+    // 1.372 ms - its exact two-pass softmax parks the V tiles of an item in the shared-memory ring until the item's
+    // probabilities exist, the ring holds ~1.5 items, and the HBM latency is exposed once per item; automatic (0)
+    // therefore stays with the per-item kernels
     const bool ws = s->self_attn_kernel == 2 && dt == PTTS_BF16 && attention_ws_supported(B, heads, d, kv.c_stride);
     if (ws)
       PTTS_UNLESS_SKIPPED(4, attention_ws_fused(qpart, Sq, (int64_t)rows * 3 * H, 3 * H, scale, ctx_base - 1, ctx_dyn,

@@ -9,13 +9,14 @@
 //   warp 0      producer: one lane issues the tile copies of K(item), V(item), K(next item), ... - everything streamed
 //               is immutable during the step (rows below the slot this step appends), so the producer runs ahead of the
 //               dependency on the QKV GEMM and of the softmax of earlier items; up to ~190 KB in flight per SM;
-//   warp 1      MMA issuer (one lane): S[128 keys x 16] = Ktile . q^T  (tcgen05.mma M=128 N=16, A K-major)
-//                                      O[64 dims x 8] += Vtile^T . P^T (tcgen05.mma M=64  N=8, A MN-major = the very
-//               [key][dim] tile the copy wrote), accumulators in tensor memory, completion by tcgen05.commit;
-//   warps 2-3   helper: folds the split-K partial sums of the QKV GEMM for the NEXT item (q scaled, new K / V row),
+//   warp 1      score-MMA issuer (one lane): S[128 keys x 16] = Ktile . q^T (tcgen05.mma M=128 N=16, A K-major) into a
+//               ring of 8 accumulators in tensor memory, completion by tcgen05.commit;
+//   warp 2      P.V-MMA issuer (one lane): O[64 dims x 8] += Vtile^T . P^T (tcgen05.mma M=64 N=8, A MN-major = the very
+//               [key][dim] tile the copy wrote); a thread of its own, so S(i+1) never queues behind the wait for P(i);
+//   warp 3      helper: folds the split-K partial sums of the QKV GEMM for the items ahead (q scaled, new K / V row),
 //               appends the new row to the cache, builds the q operand tile, scores the new row in fp32;
-//   warps 4-7   softmax: tcgen05.ld of the scores, mask, running max, probabilities as the B operand of the second
-//               product, final normalisation and the bf16 output row.
+//   warps 4-11  two softmax groups of 128 threads taking alternate items: tcgen05.ld of the scores, mask, max,
+//               probabilities as the B operand of the second product, final normalisation and the bf16 output row.
 // Narrow operands keep fp32-class accuracy by splitting the small operand over the idle N columns: q = q_hi + q_lo and
 // p = p_hi + p_lo (bf16), or three e4m3 digits q1 + q2/16 + q3/256 (fp8); the big operand (the cache) is used as stored.
 // The new row (slot ctx-1) never travels through the ring: its score and its p.v term come from registers.
@@ -30,10 +31,10 @@ using gemm::smem_u32;
 
 namespace {
 
-constexpr int WS_THREADS = 256;
+constexpr int WS_THREADS = 384;
 constexpr int TILE = 128;  // keys per tile = TMEM lanes of the score accumulator
 constexpr int WD = 64;     // head dim
-constexpr uint32_t kTmemCols = 64;  // [0,16) and [16,32): score accumulators (N = 16), [32,40): output accumulator (N = 8)
+constexpr uint32_t kTmemCols = 512;  // [0,480): 30 score accumulators (N = 16), [480,496): one output accumulator (N = 8) per softmax group
 constexpr uint32_t kSpinLimit = 1u << 22;  // ~1 s of try_wait polls
 constexpr int kMaxRing = 24;
 
@@ -170,6 +171,16 @@ __device__ __forceinline__ int off_sw64(int r, int byte_in_row) {
 
 namespace {
 
+// Score accumulators in tensor memory (16 columns each).  mbarrier waits are by phase PARITY, so a waiter that is a whole
+// phase ahead of its barrier gets a false positive: a softmax group's first wait of an item is only ordered behind the
+// buffer's previous use if that use belongs to an item the group has seen complete, which needs NS > tiles per item
+// (profiles/scripts/attn_ws_protocol_sim.py replays the protocol with parity semantics and random schedules).
+constexpr int NS = 30;
+
+// v2 roles (384 threads): warp 0 TMA producer | warp 1 score-MMA issuer | warp 2 P.V-MMA issuer | warp 3 helper (q operand,
+// new K / V row) | warps 4-7 softmax group 0 | warps 8-11 softmax group 1 (groups take alternate items; warp % 4 = the TMEM
+// lane quadrant a warp may read).  The two MMA issuers are independent threads, so S(i+1) is issued while P.V(i) still
+// waits for its probabilities: consecutive items of a CTA overlap instead of paying their latency chains back to back.
 template <bool FP8>
 __global__ void __launch_bounds__(WS_THREADS, 1)
 attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const __grid_constant__ CUtensorMap tm_v) {
@@ -180,48 +191,56 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
   constexpr int KS_PV = FP8 ? 4 : 8;           // 128 keys / UMMA_K
   constexpr uint32_t IDESC_QK = idesc(FP8 ? 0 : 1, 0, 128, 16);  // E4M3 = 0, BF16 = 1
   constexpr uint32_t IDESC_PV = idesc(FP8 ? 0 : 1, 1, 64, 8);
+  constexpr uint32_t O_COL = NS * 16;          // output accumulators (8 columns per softmax group) behind the scores
   extern __shared__ unsigned char smem_raw[];
   __shared__ __align__(8) uint64_t bar_full[kMaxRing], bar_empty[kMaxRing];
-  __shared__ __align__(8) uint64_t bar_qfull[2], bar_done[2], bar_sfull[2], bar_sempty[2], bar_pfull[2], bar_pempty[2];
-  __shared__ __align__(8) uint64_t bar_ofull, bar_oempty;
+  __shared__ __align__(8) uint64_t bar_qfull[4], bar_done[4], bar_sfull[NS], bar_sempty[NS];
+  __shared__ __align__(8) uint64_t bar_pfull[2][2], bar_pempty[2][2], bar_ofull[2], bar_oempty[2];
   __shared__ uint32_t tmem_slot;
-  __shared__ float vnew[2][WD], snew[2], sfac_s[2], red_max[4], red_sum[4], hred_a[2][2], hred_b[2][2];
+  __shared__ float vnew[4][WD], snew[4], sfac_s[4], red_max[2][4], red_sum[2][4];
 
   const int tid = threadIdx.x, warp = tid >> 5, lane = tid & 31;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;
   unsigned char* smem = smem_raw + (sbase - smem_u32(smem_raw));
   const int ring = p.ring;
   const uint32_t s_ring = sbase;
-  const uint32_t s_ptile = s_ring + (uint32_t)ring * TB;  // 2 x 2 KB
-  const uint32_t s_qtile = s_ptile + 2 * 2048;            // 2 x 2 KB (16 rows: N = 16 of the first product)
+  const uint32_t s_ptile = s_ring + (uint32_t)ring * TB;  // [group][buffer] x 2 KB
+  const uint32_t s_qtile = s_ptile + 4 * 2048;            // [item & 3] x 2 KB (16 rows: N = 16 of the first product)
   unsigned char* g_ptile = smem + (size_t)ring * TB;
-  unsigned char* g_qtile = g_ptile + 2 * 2048;
-  float* sc = reinterpret_cast<float*>(g_qtile + 2 * 2048);
+  unsigned char* g_qtile = g_ptile + 4 * 2048;
+  float* sc_all = reinterpret_cast<float*>(g_qtile + 4 * 2048);  // [group][sc_cap]
 
   // rows already in the cache; immutable for the whole step, and the counter itself is two launches old (decode-step
   // contract, see fast_attn.cu): everything below may run before griddepcontrol.wait
   const int n_old = dyn_value(p.slot_base, p.slot_dyn);
   const int nt = (n_old + TILE - 1) / TILE;
   const int H = p.heads * WD;
+  const int n_it = ((int)p.n_items - (int)blockIdx.x + (int)gridDim.x - 1) / (int)gridDim.x;  // items of this CTA
 
   // ---- one-time setup
-  for (int i = tid; i < (2 * 2048 + 2 * 2048) / 16; i += WS_THREADS)
+  for (int i = tid; i < (4 * 2048 + 4 * 2048) / 16; i += WS_THREADS)
     reinterpret_cast<uint4*>(g_ptile)[i] = make_uint4(0u, 0u, 0u, 0u);  // unused operand rows stay zero
   if (tid == 0) {
     for (int i = 0; i < ring; ++i) {
       mbar_init(smem_u32(&bar_full[i]), 1);
       mbar_init(smem_u32(&bar_empty[i]), 1);
     }
-    for (int i = 0; i < 2; ++i) {
-      mbar_init(smem_u32(&bar_qfull[i]), 64);
+    for (int i = 0; i < 4; ++i) {
+      mbar_init(smem_u32(&bar_qfull[i]), 32);
       mbar_init(smem_u32(&bar_done[i]), 128);
+    }
+    for (int i = 0; i < NS; ++i) {
       mbar_init(smem_u32(&bar_sfull[i]), 1);
       mbar_init(smem_u32(&bar_sempty[i]), 128);
-      mbar_init(smem_u32(&bar_pfull[i]), 128);
-      mbar_init(smem_u32(&bar_pempty[i]), 1);
     }
-    mbar_init(smem_u32(&bar_ofull), 1);
-    mbar_init(smem_u32(&bar_oempty), 128);
+    for (int g = 0; g < 2; ++g) {
+      for (int i = 0; i < 2; ++i) {
+        mbar_init(smem_u32(&bar_pfull[g][i]), 128);
+        mbar_init(smem_u32(&bar_pempty[g][i]), 1);
+      }
+      mbar_init(smem_u32(&bar_ofull[g]), 1);
+      mbar_init(smem_u32(&bar_oempty[g]), 128);
+    }
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
   }
   if (warp == 1) {
@@ -237,11 +256,11 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
   const uint32_t tmem = tmem_slot;
 
   if (warp == 0) {
-    // ================================================================ producer
+    // ================================================================ producer: K(0) V(0) K(1) V(1) ... in ring order
     if (lane == 0) {
       uint32_t cnt = 0;
-      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x) {
-        const int row0 = item * p.c_stride;
+      for (int it = 0; it < n_it; ++it) {
+        const int row0 = ((int)blockIdx.x + it * (int)gridDim.x) * p.c_stride;
         for (int pass = 0; pass < 2; ++pass)
           for (int t = 0; t < nt; ++t, ++cnt) {
             const uint32_t slot = cnt % (uint32_t)ring, use = cnt / (uint32_t)ring;
@@ -252,140 +271,162 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
       }
     }
   } else if (warp == 1) {
-    // ================================================================ MMA issuer
+    // ================================================================ score-MMA issuer: S = Ktile . q^T
     if (lane == 0) {
-      uint32_t cnt = 0, sb_cnt = 0, pb_cnt = 0;
-      int it = 0;
-      for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
-        const int par = it & 1;
-        mbar_wait(smem_u32(&bar_qfull[par]), (uint32_t)(it >> 1) & 1u);
-        for (int t = 0; t < nt; ++t, ++cnt, ++sb_cnt) {  // S = Ktile . q^T
-          const uint32_t slot = cnt % (uint32_t)ring, sb = sb_cnt & 1u;
-          mbar_wait(smem_u32(&bar_full[slot]), (cnt / (uint32_t)ring) & 1u);
-          if (sb_cnt >= 2) mbar_wait(smem_u32(&bar_sempty[sb]), ((sb_cnt >> 1) & 1u) ^ 1u);
+      for (int it = 0; it < n_it; ++it) {
+        const int par = it & 3;
+        mbar_wait(smem_u32(&bar_qfull[par]), (uint32_t)(it >> 2) & 1u);
+        for (int t = 0; t < nt; ++t) {
+          const uint32_t cnt = (uint32_t)(it * 2 * nt + t), slot = cnt % (uint32_t)ring;
+          const uint32_t n = (uint32_t)(it * nt + t), buf = n % NS;
+          // the slot's previous use (possibly a V tile the other issuer consumes) must be CONSUMED before this thread
+          // may interpret the parity of `full`: otherwise a wait one phase ahead returns at once (needs ring >= nt + 2)
+          const uint32_t use = cnt / (uint32_t)ring;
+          if (use > 0) mbar_wait(smem_u32(&bar_empty[slot]), (use & 1u) ^ 1u);
+          mbar_wait(smem_u32(&bar_full[slot]), use & 1u);
+          if (n >= NS) mbar_wait(smem_u32(&bar_sempty[buf]), ((n / NS) & 1u) ^ 1u);
           tc_fence_after();
           const uint32_t a0 = s_ring + slot * TB, b0 = s_qtile + par * 2048;
 #pragma unroll
           for (int ks = 0; ks < KS_QK; ++ks)
-            umma<FP8>(tmem + sb * 16, FP8 ? desc_sw64(a0 + ks * 32) : desc_sw128(a0 + ks * 32),
+            umma<FP8>(tmem + buf * 16, FP8 ? desc_sw64(a0 + ks * 32) : desc_sw128(a0 + ks * 32),
                       FP8 ? desc_sw64(b0 + ks * 32) : desc_sw128(b0 + ks * 32), IDESC_QK, ks > 0);
-          umma_commit(smem_u32(&bar_sfull[sb]));
+          umma_commit(smem_u32(&bar_sfull[buf]));
           umma_commit(smem_u32(&bar_empty[slot]));
-        }
-        for (int t = 0; t < nt; ++t, ++cnt, ++pb_cnt) {  // O += Vtile^T . P^T
-          const uint32_t slot = cnt % (uint32_t)ring, pb = pb_cnt & 1u;
-          mbar_wait(smem_u32(&bar_full[slot]), (cnt / (uint32_t)ring) & 1u);
-          mbar_wait(smem_u32(&bar_pfull[pb]), (pb_cnt >> 1) & 1u);
-          if (t == 0 && it > 0) mbar_wait(smem_u32(&bar_oempty), (uint32_t)(it - 1) & 1u);
-          tc_fence_after();
-          const uint32_t a0 = s_ring + slot * TB, b0 = s_ptile + pb * 2048;
-#pragma unroll
-          for (int ks = 0; ks < KS_PV; ++ks) {
-            const uint32_t bk = FP8 ? b0 + ks * 32 : b0 + (ks >> 2) * 1024 + (ks & 3) * 32;
-            umma<FP8>(tmem + 32, FP8 ? desc_sw64(a0 + ks * 2048) : desc_sw128(a0 + ks * 2048), desc_sw128(bk), IDESC_PV,
-                      (t > 0 || ks > 0) ? 1u : 0u);
-          }
-          umma_commit(smem_u32(&bar_empty[slot]));
-          umma_commit(smem_u32(&bar_pempty[pb]));
-          if (t == nt - 1) umma_commit(smem_u32(&bar_ofull));
         }
       }
     }
-  } else if (warp < 4) {
-    // ================================================================ helper: q operand, new row (64 threads, h = dim)
-    const int h = (warp - 2) * 32 + lane;
+  } else if (warp == 2) {
+    // ================================================================ P.V-MMA issuer: O[g] += Vtile^T . P^T
+    if (lane == 0) {
+      for (int it = 0; it < n_it; ++it) {
+        const int g = it & 1, my = it >> 1;
+        for (int t = 0; t < nt; ++t) {
+          const uint32_t cnt = (uint32_t)(it * 2 * nt + nt + t), slot = cnt % (uint32_t)ring;
+          const uint32_t pb_cnt = (uint32_t)(my * nt + t), pb = pb_cnt & 1u;
+          // probabilities first: P(i, t) ready means S(i) is complete, hence every earlier tile of this slot has been
+          // consumed and the parity of `full` is unambiguous (this thread waits on `full` from kernel start otherwise)
+          mbar_wait(smem_u32(&bar_pfull[g][pb]), (pb_cnt >> 1) & 1u);
+          mbar_wait(smem_u32(&bar_full[slot]), (cnt / (uint32_t)ring) & 1u);
+          if (t == 0 && my > 0) mbar_wait(smem_u32(&bar_oempty[g]), (uint32_t)(my - 1) & 1u);
+          tc_fence_after();
+          const uint32_t a0 = s_ring + slot * TB, b0 = s_ptile + (uint32_t)(g * 2 + (int)pb) * 2048;
+#pragma unroll
+          for (int ks = 0; ks < KS_PV; ++ks) {
+            const uint32_t bk = FP8 ? b0 + ks * 32 : b0 + (ks >> 2) * 1024 + (ks & 3) * 32;
+            umma<FP8>(tmem + O_COL + g * 8, FP8 ? desc_sw64(a0 + ks * 2048) : desc_sw128(a0 + ks * 2048), desc_sw128(bk),
+                      IDESC_PV, (t > 0 || ks > 0) ? 1u : 0u);
+          }
+          umma_commit(smem_u32(&bar_empty[slot]));
+          umma_commit(smem_u32(&bar_pempty[g][pb]));
+          if (t == nt - 1) umma_commit(smem_u32(&bar_ofull[g]));
+        }
+      }
+    }
+  } else if (warp == 3) {
+    // ================================================================ helper: q operand, new K / V row (lane = dims lane, lane + 32)
     pdl_wait();    // the QKV partial sums are the only producer-dependent input of this kernel
     pdl_launch();
-    int it = 0;
-    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
-      const int par = it & 1;
+    for (int it = 0; it < n_it; ++it) {
+      const int par = it & 3;
+      const int item = (int)blockIdx.x + it * (int)gridDim.x;
       const int b = item / p.heads, hd = item - b * p.heads;
-      if (it >= 2) mbar_wait(smem_u32(&bar_done[par]), (uint32_t)((it >> 1) - 1) & 1u);
-      const float* p0 = p.part + (long long)b * p.ncols + hd * WD + h;
-      float aq = 0.f, ak = 0.f, av = 0.f;
-      for (int s0 = 0; s0 < p.S; s0 += 4) {  // 4 slices (12 loads) in flight, added in slice order
-        float tq[4], tk[4], tv[4];
+      if (it >= 4) mbar_wait(smem_u32(&bar_done[par]), (uint32_t)((it >> 2) - 1) & 1u);
+      const float* p0 = p.part + (long long)b * p.ncols + hd * WD + lane;
+      float aq[2] = {0.f, 0.f}, ak[2] = {0.f, 0.f}, av[2] = {0.f, 0.f};
+      for (int s0 = 0; s0 < p.S; s0 += 2) {  // 2 slices (12 loads) in flight, added in slice order
+        float tq[2][2], tk[2][2], tv[2][2];
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 2; ++u)
           if (s0 + u < p.S) {
             const float* ps = p0 + (long long)(s0 + u) * p.stride;
-            tq[u] = __ldcg(ps);
-            tk[u] = __ldcg(ps + H);
-            tv[u] = __ldcg(ps + 2 * H);
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              tq[u][e] = __ldcg(ps + e * 32);
+              tk[u][e] = __ldcg(ps + H + e * 32);
+              tv[u][e] = __ldcg(ps + 2 * H + e * 32);
+            }
           }
 #pragma unroll
-        for (int u = 0; u < 4; ++u)
+        for (int u = 0; u < 2; ++u)
           if (s0 + u < p.S) {
-            aq += tq[u];
-            ak += tk[u];
-            av += tv[u];
+#pragma unroll
+            for (int e = 0; e < 2; ++e) {
+              aq[e] += tq[u][e];
+              ak[e] += tk[u][e];
+              av[e] += tv[u][e];
+            }
           }
       }
-      const float q = aq * p.scale;
-      const long long o = ((long long)item * p.c_stride + n_old) * WD + h;
+      const long long o = ((long long)item * p.c_stride + n_old) * WD + lane;
       unsigned char* qt = g_qtile + par * 2048;
-      float qrec, kf, vf, sf = 1.0f;
+      float dot = 0.f, sf = 1.0f;
       if constexpr (FP8) {
-        float m = warp_max(fabsf(q));
-        if (lane == 0) hred_a[par][warp - 2] = m;
-        bar_named(2, 64);
-        const float qmax = fmaxf(hred_a[par][0], hred_a[par][1]);
-        unsigned char dgt[3];
-        split3_e4m3(qmax > 0.f ? q * (256.0f / qmax) : 0.f, dgt, qrec);
-#pragma unroll
-        for (int r = 0; r < 3; ++r) qt[off_sw64(r, h)] = dgt[r];
+        const float q0 = aq[0] * p.scale, q1 = aq[1] * p.scale;
+        const float qmax = warp_max(fmaxf(fabsf(q0), fabsf(q1)));
+        const float qs = qmax > 0.f ? 256.0f / qmax : 0.f;
         const float ks = p.k_scale[hd], vs = p.v_scale[hd];
-        const unsigned char k8 = to_e4m3(ak / ks), v8 = to_e4m3(av / vs);
-        reinterpret_cast<unsigned char*>(p.ck)[o] = k8;
-        reinterpret_cast<unsigned char*>(p.cv)[o] = v8;
-        kf = from_e4m3(k8);
-        vf = from_e4m3(v8);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          unsigned char dgt[3];
+          float qrec;
+          split3_e4m3((e ? q1 : q0) * qs, dgt, qrec);
+#pragma unroll
+          for (int r = 0; r < 3; ++r) qt[off_sw64(r, lane + e * 32)] = dgt[r];
+          const unsigned char k8 = to_e4m3(ak[e] / ks), v8 = to_e4m3(av[e] / vs);
+          reinterpret_cast<unsigned char*>(p.ck)[o + e * 32] = k8;
+          reinterpret_cast<unsigned char*>(p.cv)[o + e * 32] = v8;
+          dot += qrec * from_e4m3(k8);
+          vnew[par][lane + e * 32] = from_e4m3(v8);
+        }
         sf = qmax * (1.0f / 256.0f) * ks;
       } else {
-        const __nv_bfloat16 qh = __float2bfloat16_rn(q);
-        const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
-        qrec = __bfloat162float(qh) + __bfloat162float(ql);
-        *reinterpret_cast<__nv_bfloat16*>(qt + off_sw128(0, h * 2)) = qh;
-        *reinterpret_cast<__nv_bfloat16*>(qt + off_sw128(1, h * 2)) = ql;
-        const __nv_bfloat16 kr = __float2bfloat16_rn(ak), vr = __float2bfloat16_rn(av);
-        reinterpret_cast<__nv_bfloat16*>(p.ck)[o] = kr;
-        reinterpret_cast<__nv_bfloat16*>(p.cv)[o] = vr;
-        kf = __bfloat162float(kr);
-        vf = __bfloat162float(vr);
+#pragma unroll
+        for (int e = 0; e < 2; ++e) {
+          const float q = aq[e] * p.scale;
+          const __nv_bfloat16 qh = __float2bfloat16_rn(q);
+          const __nv_bfloat16 ql = __float2bfloat16_rn(q - __bfloat162float(qh));
+          *reinterpret_cast<__nv_bfloat16*>(qt + off_sw128(0, (lane + e * 32) * 2)) = qh;
+          *reinterpret_cast<__nv_bfloat16*>(qt + off_sw128(1, (lane + e * 32) * 2)) = ql;
+          const __nv_bfloat16 kr = __float2bfloat16_rn(ak[e]), vr = __float2bfloat16_rn(av[e]);
+          reinterpret_cast<__nv_bfloat16*>(p.ck)[o + e * 32] = kr;
+          reinterpret_cast<__nv_bfloat16*>(p.cv)[o + e * 32] = vr;
+          dot += (__bfloat162float(qh) + __bfloat162float(ql)) * __bfloat162float(kr);
+          vnew[par][lane + e * 32] = __bfloat162float(vr);
+        }
       }
-      float dot = warp_sum(qrec * kf);  // score of the new row, fp32, from the values the cache now holds
-      if (lane == 0) hred_b[par][warp - 2] = dot;
-      vnew[par][h] = vf;
-      bar_named(2, 64);
-      if (h == 0) {
-        snew[par] = (hred_b[par][0] + hred_b[par][1]) * sf;
+      dot = warp_sum(dot);  // score of the new row, fp32, from the values the cache now holds
+      if (lane == 0) {
+        snew[par] = dot * sf;
         sfac_s[par] = sf;
       }
       fence_async_smem();  // the q tile is read by the tensor core (async proxy)
       mbar_arrive(smem_u32(&bar_qfull[par]));
     }
   } else {
-    // ================================================================ softmax: 128 threads, thread = key of a tile
-    const int quad = warp - 4;          // TMEM lane quadrant this warp may read
+    // ================================================================ softmax groups: 128 threads, thread = key of a tile
+    const int g = (warp - 4) >> 2;      // group 0: warps 4-7, group 1: warps 8-11
+    const int quad = warp & 3;          // TMEM lane quadrant this warp may read
     const int lt = quad * 32 + lane;    // key within the tile
     const uint32_t t_lane = tmem + ((uint32_t)(quad * 32) << 16);
     const float neg = -3.3895313892515355e38f;  // finfo(bf16).min, the reference's additive mask value
-    uint32_t sb_cnt = 0, pb_cnt = 0;
-    int it = 0;
-    for (int item = blockIdx.x; item < p.n_items; item += gridDim.x, ++it) {
-      const int par = it & 1;
+    float* sc = sc_all + (size_t)g * p.sc_cap;
+    int my = 0;
+    for (int it = g; it < n_it; it += 2, ++my) {
+      const int par = it & 3;
+      const int item = (int)blockIdx.x + it * (int)gridDim.x;
       const int b = item / p.heads, hd = item - b * p.heads;
-      mbar_wait(smem_u32(&bar_qfull[par]), (uint32_t)(it >> 1) & 1u);
+      mbar_wait(smem_u32(&bar_qfull[par]), (uint32_t)(it >> 2) & 1u);
       const float sf = sfac_s[par], s_new = snew[par];
       float lmax = s_new;
-      for (int t = 0; t < nt; ++t, ++sb_cnt) {
-        const uint32_t sb = sb_cnt & 1u;
-        mbar_wait(smem_u32(&bar_sfull[sb]), (sb_cnt >> 1) & 1u);
+      for (int t = 0; t < nt; ++t) {
+        const uint32_t n = (uint32_t)(it * nt + t), buf = n % NS;
+        mbar_wait(smem_u32(&bar_sfull[buf]), (n / NS) & 1u);
         tc_fence_after();
         uint32_t v[8];
-        tmem_ld_x8(t_lane + sb * 16, v);
+        tmem_ld_x8(t_lane + buf * 16, v);
         tc_fence_before();
-        mbar_arrive(smem_u32(&bar_sempty[sb]));
+        mbar_arrive(smem_u32(&bar_sempty[buf]));
         const int j = t * TILE + lt;
         float s = FP8 ? (__uint_as_float(v[0]) + __uint_as_float(v[1]) * 0.0625f + __uint_as_float(v[2]) * 0.00390625f)
                       : (__uint_as_float(v[0]) + __uint_as_float(v[1]));
@@ -398,16 +439,16 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
         lmax = fmaxf(lmax, s);
       }
       lmax = warp_max(lmax);
-      if (lane == 0) red_max[quad] = lmax;
-      bar_named(1, 128);
-      const float mx = fmaxf(fmaxf(red_max[0], red_max[1]), fmaxf(red_max[2], red_max[3]));
+      if (lane == 0) red_max[g][quad] = lmax;
+      bar_named(1 + g, 128);
+      const float mx = fmaxf(fmaxf(red_max[g][0], red_max[g][1]), fmaxf(red_max[g][2], red_max[g][3]));
       float lsum = 0.f;
-      for (int t = 0; t < nt; ++t, ++pb_cnt) {
-        const uint32_t pb = pb_cnt & 1u;
-        if (pb_cnt >= 2) mbar_wait(smem_u32(&bar_pempty[pb]), ((pb_cnt >> 1) & 1u) ^ 1u);
+      for (int t = 0; t < nt; ++t) {
+        const uint32_t pb_cnt = (uint32_t)(my * nt + t), pb = pb_cnt & 1u;
+        if (pb_cnt >= 2) mbar_wait(smem_u32(&bar_pempty[g][pb]), ((pb_cnt >> 1) & 1u) ^ 1u);
         const float pj = __expf(sc[t * TILE + lt] - mx);
         lsum += pj;
-        unsigned char* pt = g_ptile + pb * 2048;
+        unsigned char* pt = g_ptile + (g * 2 + (int)pb) * 2048;
         if constexpr (FP8) {
           unsigned char dgt[3];
           float rec;
@@ -421,21 +462,21 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
           *reinterpret_cast<__nv_bfloat16*>(pt + off_sw128(1, lt * 2)) = pl;
         }
         fence_async_smem();
-        mbar_arrive(smem_u32(&bar_pfull[pb]));
+        mbar_arrive(smem_u32(&bar_pfull[g][pb]));
       }
       const float p_new = __expf(s_new - mx);
       lsum = warp_sum(lsum);
-      if (lane == 0) red_sum[quad] = lsum;
-      bar_named(1, 128);
-      const float total = ((red_sum[0] + red_sum[1]) + (red_sum[2] + red_sum[3])) + p_new;
+      if (lane == 0) red_sum[g][quad] = lsum;
+      bar_named(1 + g, 128);
+      const float total = ((red_sum[g][0] + red_sum[g][1]) + (red_sum[g][2] + red_sum[g][3])) + p_new;
       float o = 0.f;
       if (nt > 0) {
-        mbar_wait(smem_u32(&bar_ofull), (uint32_t)it & 1u);
+        mbar_wait(smem_u32(&bar_ofull[g]), (uint32_t)my & 1u);
         tc_fence_after();
         uint32_t v[8];
-        tmem_ld_x8(t_lane + 32, v);  // M = 64: output row m sits in lane (m % 16) + 32 * (m / 16)
+        tmem_ld_x8(t_lane + O_COL + g * 8, v);  // M = 64: output row m sits in lane (m % 16) + 32 * (m / 16)
         tc_fence_before();
-        mbar_arrive(smem_u32(&bar_oempty));
+        mbar_arrive(smem_u32(&bar_oempty[g]));
         o = FP8 ? (__uint_as_float(v[0]) + __uint_as_float(v[1]) * 0.0625f + __uint_as_float(v[2]) * 0.00390625f) *
                       0.00390625f
                 : (__uint_as_float(v[0]) + __uint_as_float(v[1]));
@@ -467,7 +508,12 @@ bool attention_ws_supported(int B, int heads, int d, int c_stride) {
     cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   }
   // a persistent CTA per SM pays off once every SM has several items; smaller batches keep the split-KV kernels
-  return B * heads >= 2 * sms && c_stride <= 8192;
+  const int nt = (c_stride + TILE - 1) / TILE;
+  // protocol constraints (see NS): fewer tiles per pass than score accumulators, and a ring of 16 KB slots (bf16, the
+  // larger case) that holds more than one pass next to the operand tiles and the two score buffers
+  const long long fixed = 1024 + 4 * 2048 + 4 * 2048 + 2LL * 4 * nt * TILE;
+  const long long ring = (225LL * 1024 - fixed) / (TILE * WD * 2);
+  return B * heads >= 2 * sms && nt < NS && ring >= nt + 2;
 }
 
 template <bool FP8>
@@ -479,11 +525,15 @@ static int launch_ws(WsParams p, int B, cudaStream_t st) {
   cudaDeviceGetAttribute(&sms, cudaDevAttrMultiProcessorCount, dev);
   p.n_items = B * p.heads;
   p.sc_cap = (p.c_stride + TILE - 1) / TILE * TILE;
-  const size_t fixed = 1024 + 2 * 2048 + 2 * 2048 + sizeof(float) * (size_t)p.sc_cap;
+  const size_t fixed = 1024 + 4 * 2048 + 4 * 2048 + 2 * sizeof(float) * (size_t)p.sc_cap;
   const size_t budget = 225 * 1024;
   PTTS_CHECK_ARG(fixed + 4 * TB <= budget, "attention_ws: cache too long for the score buffer");
   int ring = (int)((budget - fixed) / TB);
   if (ring > kMaxRing) ring = kMaxRing;
+  if (ring < p.sc_cap / TILE + 2) {  // protocol constraint (see NS): the ring must hold more than one pass of an item
+    set_error("attention_ws: cache too long for the tile ring (%d slots, %d tiles per pass)", ring, p.sc_cap / TILE);
+    return PTTS_E_UNSUPPORTED;
+  }
   p.ring = ring;
   const size_t smem = fixed + (size_t)ring * TB;
   CUtensorMap tm_k, tm_v;
