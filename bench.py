@@ -294,8 +294,10 @@ def run_cuda(args):
 
         def teacher_forced(which_impl, kvd):
             dec.impl, dec.kv_dtype = which_impl, kvd
+            # small batches run split-KV attention whose split plan depends on the cache length: give the eager pass the
+            # run's own cache length there, so that both sum in the same order
             o = dec(input_ids=applied[:, :1], encoder_hidden_states=enc, prompt_hidden_states=prm, use_cache=True,
-                    max_cache_len=n_chk + 2)
+                    max_cache_len=M if B * dec.config.num_attention_heads < 512 else n_chk + 2)
             first = o.logits[:, -1:].clone()
             rest = dec(input_ids=applied[:, 1 : 1 + n_chk], past_key_values=o.past_key_values).logits
             dec.impl, dec.kv_dtype = impl, kv_dtype

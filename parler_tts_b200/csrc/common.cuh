@@ -121,6 +121,15 @@ __device__ __forceinline__ float apply_act(float x, int act) {
 // ---- programmatic dependent launch (PDL): every kernel of the fast family calls pdl_wait() before it touches data
 // written by an earlier kernel, and pdl_launch() as early as possible so that the next kernel's prologue (weight
 // prefetch, smem carve-up) overlaps this kernel's tail.  Both are no-ops for a launch without the attribute.
+// Election of ONE lane of a converged warp (elect.sync).  Code guarded by it directly - `if (elect_one()) { ... }` -
+// is known to ptxas to run in a single lane, so cp.async.bulk.tensor / tcgen05.mma / tcgen05.commit are issued from
+// uniform registers back to back; guarded by `lane == 0` instead, every such instruction becomes an
+// ELECT ... R2UR ... BRA.U.ANY loop over the (one) active lane: ~10 SASS instructions per MMA on the issuing thread.
+__device__ __forceinline__ bool elect_one() {
+  uint32_t pred;
+  asm volatile("{\n\t.reg .pred p;\n\telect.sync _|p, 0xffffffff;\n\tselp.b32 %0, 1, 0, p;\n\t}\n" : "=r"(pred));
+  return pred != 0;
+}
 __device__ __forceinline__ void pdl_wait() { asm volatile("griddepcontrol.wait;" ::: "memory"); }
 __device__ __forceinline__ void pdl_launch() { asm volatile("griddepcontrol.launch_dependents;" ::: "memory"); }
 

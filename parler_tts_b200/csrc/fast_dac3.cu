@@ -281,7 +281,7 @@ __global__ void __launch_bounds__(NTHR, 1) dac_conv_ws_kernel(const ConvParams3 
   if (warp == 0) {
     // ------------------------------------------------------------------ producer: bulk copies of weight stages and,
     // for "planes" input, of the activation panels (8 copies of xrows x 16 B per 32-channel chunk)
-    if (lane == 0) {
+    if (elect_one()) {
       uint32_t k = 0, g = 0;
       const int Tp = p.T + PAD_LO + PAD_HI;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x) {
@@ -313,7 +313,7 @@ __global__ void __launch_bounds__(NTHR, 1) dac_conv_ws_kernel(const ConvParams3 
     __syncwarp();
   } else if (warp == 1) {
     // ------------------------------------------------------------------ MMA issuer
-    if (lane == 0) {
+    if (elect_one()) {  // single-lane issue from uniform registers (common.cuh)
       uint32_t k = 0, g = 0, tt = 0;
       for (int tile = blockIdx.x; tile < ntiles; tile += gridDim.x, ++tt) {
         const uint32_t a = DBL ? (tt & 1) : 0, ak = DBL ? (tt >> 1) : tt;

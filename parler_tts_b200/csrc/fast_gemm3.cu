@@ -137,6 +137,25 @@ __device__ __forceinline__ void mbar_wait3(uint32_t bar, uint32_t parity) {
   }
 }
 
+// 3-D box copy: tensor map dims {64 elements, rows, k-blocks}, box {64, box_rows, box_kb} = box_kb consecutive
+// SWIZZLE_128B k-blocks of box_rows rows, laid out back to back exactly like box_kb 2-D copies
+__device__ __forceinline__ void tma_load_3d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1, int c2) {
+  asm volatile(
+      "cp.async.bulk.tensor.3d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4, %5}], [%2];\n" ::"r"(dst),
+      "l"(reinterpret_cast<uint64_t>(map)), "r"(bar), "r"(c0), "r"(c1), "r"(c2)
+      : "memory");
+}
+// tcgen05.mma from the 32-bit low words of two K-major SWIZZLE_128B descriptors (high word: SBO 1024 B, version 1,
+// SWIZZLE_128B = 0x40004040, see umma_desc_sw128)
+__device__ __forceinline__ void umma_f16_lo(uint32_t tmem_d, uint32_t a_lo, uint32_t b_lo, uint32_t accumulate) {
+  asm volatile(
+      "{\n\t.reg .pred p;\n\t.reg .b64 da, db;\n\tsetp.ne.b32 p, %4, 0;\n\t"
+      "mov.b64 da, {%1, %5};\n\tmov.b64 db, {%2, %5};\n\t"
+      "tcgen05.mma.cta_group::1.kind::f16 [%0], da, db, %3, p;\n\t}\n" ::"r"(tmem_d),
+      "r"(a_lo), "r"(b_lo), "r"(kIdesc), "r"(accumulate), "r"(0x40004040u)
+      : "memory");
+}
+
 // grid = (N/128, M/64, CS), cluster (1,1,CS); KB = 64-element k-blocks per CTA (<= 8)
 // LEAN = the instantiation the decode step launches when nothing optional is asked for (TMA loads, single X barrier,
 // no diagnostics, no hint, no finisher): every optional path is compiled out.  It matters: the code of an unused
@@ -403,6 +422,93 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
 }
 
 
+// ---- lean split-K partial kernel, second generation (round 2).  Same math and the same output as
+// umma_gemm_kernel<EPI_PARTIAL, true, true>, rebuilt around what its SASS showed: the single issuing thread was the
+// critical path.  Issued from a lane of a divergent branch, every cp.async.bulk.tensor / tcgen05.mma became an
+// ELECT ... BRA.U.ANY loop with R2UR moves and a 64-bit descriptor rebuild in front of it (~45 instructions per
+// k-block: ~2500 cycles from "X landed" to "MMA done" for a burst the tensor core finishes in ~1100, and ~100 instructions
+// for the eight X box copies after the dependency wait).  Here
+//   * one warp-uniform branch + elect.sync, so the uniform datapath issues without the per-lane loops;
+//   * ONE 3-D box copy for the whole X slab (tensor map viewed as [k-block][row][64]), two for the W slab;
+//   * the KB*4 MMAs fully unrolled, descriptors = a 32-bit low word + compile-time offset (the high word is constant);
+//   * barrier init / TMEM allocation / the only __syncthreads in front of the dependency wait.
+template <int KB>
+__global__ void __launch_bounds__(NTH)
+umma_partial_lean_kernel(float* __restrict__ part, int M, int N, int late, const __grid_constant__ CUtensorMap tm_w,
+                         const __grid_constant__ CUtensorMap tm_x) {
+  extern __shared__ unsigned char smem_raw[];
+  __shared__ __align__(8) uint64_t bars[3];  // W slab, X slab, MMA burst
+  __shared__ uint32_t tmem_base_slot;
+  const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
+  const uint32_t sw = sbase, sx = sbase + KB * WBLK;
+  const int n0 = blockIdx.x * UM, m0 = blockIdx.y * UN, rank = blockIdx.z;
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const uint32_t w_bar = smem_u32(&bars[0]), x_bar = smem_u32(&bars[1]), mma_bar = smem_u32(&bars[2]);
+  if (warp == 0) {
+    asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tmem_base_slot)),
+                 "r"(TMEM_COLS)
+                 : "memory");
+    asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
+  } else if (warp == 1) {
+    if (elect_one()) {
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(w_bar) : "memory");
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(x_bar) : "memory");
+      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mma_bar) : "memory");
+      asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
+      asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
+      // the whole W slab of this CTA, before the dependency resolves (weights are immutable)
+      mbar_expect_tx3(w_bar, (uint32_t)(KB * WBLK));
+      tma_load_3d(sw, &tm_w, w_bar, 0, n0, rank * KB);
+      tma_load_3d(sw + (KB / 2) * WBLK, &tm_w, w_bar, 0, n0, rank * KB + KB / 2);
+    }
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();  // barrier inits and the TMEM base address are visible to everybody - still in front of the wait
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+  const uint32_t tmem_d = tmem_base_slot;
+  pdl_wait();
+  if (!late) pdl_launch();
+  if (warp == 1 && elect_one()) {
+    mbar_expect_tx3(x_bar, (uint32_t)(KB * XBLK));
+    tma_load_3d(sx, &tm_x, x_bar, 0, m0, rank * KB);
+    mbar_wait3(w_bar, 0);
+    mbar_wait3(x_bar, 0);
+    asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+    const uint32_t a0 = ((sw >> 4) & 0x3FFFu) | (1u << 16), b0 = ((sx >> 4) & 0x3FFFu) | (1u << 16);
+    // k-block loop rolled (fully unrolled, ptxas hoists all 2 * 4 * KB descriptor pairs and spills uniform registers)
+#pragma unroll 1
+    for (int kb = 0; kb < KB; ++kb)
+#pragma unroll
+      for (int k = 0; k < KB64 / 16; ++k)  // +32 bytes (2 x 16 B) per UMMA_K = 16 inside the swizzle atom
+        umma_f16_lo(tmem_d, a0 + kb * (WBLK >> 4) + 2 * k, b0 + kb * (XBLK >> 4) + 2 * k, (kb | k) ? 1u : 0u);
+    asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(mma_bar) : "memory");
+  }
+  __syncwarp();
+  mbar_wait3(mma_bar, 0);
+  asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+  if (late) pdl_launch();
+  // split-K partial sums straight to global memory [slice][m][n] (coalesced along n); the consumer folds them in slice
+  // order.  Thread (warp w, lane l) owns weight row n0 + 32 w + l and its 64 batch-row columns.
+  const int n = n0 + warp * 32 + lane;
+  const size_t ldn = (size_t)N;
+  float* dst = part + ((size_t)rank * M + m0) * ldn + n;
+  uint32_t v0[32], v1[32];
+  tmem_ld_32x32b_x32(tmem_d + ((uint32_t)(warp * 32) << 16), v0);
+  tmem_ld_32x32b_x32(tmem_d + ((uint32_t)(warp * 32) << 16) + 32, v1);
+  asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+  if (n < N) {
+#pragma unroll
+    for (int j = 0; j < 32; ++j) dst[(size_t)j * ldn] = __uint_as_float(v0[j]);
+    dst += 32 * ldn;
+#pragma unroll
+    for (int j = 0; j < 32; ++j) dst[(size_t)j * ldn] = __uint_as_float(v1[j]);
+  }
+  asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
+  __syncthreads();
+  if (warp == 0)
+    asm volatile("tcgen05.dealloc.cta_group::1.sync.aligned.b32 %0, %1;\n" ::"r"(tmem_d), "r"(TMEM_COLS) : "memory");
+}
+
 int plan_cluster3(int M, int N, int K) {
   if (K % 128 != 0) return 0;
   const int kblocks = K / KB64;
@@ -448,27 +554,32 @@ struct MapKey {
   const void* ptr;
   int rows, cols, box_rows, dtype;
   long long pitch_bytes;
+  int box_kb;  // 0: 2-D map; > 0: 3-D map [k-block][row][64] whose box spans box_kb k-blocks
   bool operator==(const MapKey& o) const {
     return ptr == o.ptr && rows == o.rows && cols == o.cols && box_rows == o.box_rows && dtype == o.dtype &&
-           pitch_bytes == o.pitch_bytes;
+           pitch_bytes == o.pitch_bytes && box_kb == o.box_kb;
   }
 };
 struct MapKeyHash {
   size_t operator()(const MapKey& k) const {
     return std::hash<const void*>()(k.ptr) ^ (size_t)k.rows * 0x9E3779B97F4A7C15ull ^ (size_t)k.cols * 0xC2B2AE3D27D4EB4Full ^
-           (size_t)k.box_rows ^ ((size_t)k.dtype << 20) ^ (size_t)k.pitch_bytes * 0x165667B19E3779F9ull;
+           (size_t)k.box_rows ^ ((size_t)k.dtype << 20) ^ (size_t)k.pitch_bytes * 0x165667B19E3779F9ull ^
+           ((size_t)k.box_kb << 40);
   }
 };
 // row-major [rows][cols] matrix, box = 64 columns x box_rows rows, out-of-range rows read as 0:
 //   PTTS_BF16: 128-byte box rows, SWIZZLE_128B;  PTTS_FP8 (bytes): 64-byte box rows, SWIZZLE_64B
-bool tensor_map_2d_any(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out) {
+//   box_kb > 0 (bf16 only): the same matrix viewed as [cols/64][rows][64] with box {64, box_rows, box_kb} - ONE copy
+//   brings box_kb consecutive SWIZZLE_128B k-blocks, laid out back to back like box_kb 2-D copies
+bool tensor_map_2d_any(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out, int box_kb = 0) {
   static std::mutex mu;
   static std::unordered_map<MapKey, CUtensorMap, MapKeyHash> cache;
   EncodeTiledFn fn = encode_tiled_fn();
   const int es = dtype == PTTS_FP8 ? 1 : 2;
   if (!fn || (reinterpret_cast<uintptr_t>(ptr) & 15) || (cols * es) % 16) return false;
   std::lock_guard<std::mutex> lock(mu);
-  const MapKey key = {ptr, rows, cols, box_rows, dtype, (long long)cols * es};
+  if (box_kb > 0 && (dtype != PTTS_BF16 || cols % KB64)) return false;
+  const MapKey key = {ptr, rows, cols, box_rows, dtype, (long long)cols * es, box_kb};
   auto it = cache.find(key);
   if (it != cache.end()) {
     *out = it->second;
@@ -479,10 +590,21 @@ bool tensor_map_2d_any(const void* ptr, int rows, int cols, int box_rows, int dt
   const cuuint64_t gstr[1] = {(cuuint64_t)cols * es};
   const cuuint32_t box[2] = {(cuuint32_t)KB64, (cuuint32_t)box_rows};
   const cuuint32_t estr[2] = {1, 1};
-  const CUresult r = fn(&m, dtype == PTTS_FP8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
-                        const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
-                        dtype == PTTS_FP8 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
-                        CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  CUresult r;
+  if (box_kb > 0) {
+    const cuuint64_t gdim3[3] = {(cuuint64_t)KB64, (cuuint64_t)rows, (cuuint64_t)(cols / KB64)};
+    const cuuint64_t gstr3[2] = {(cuuint64_t)cols * es, (cuuint64_t)KB64 * es};
+    const cuuint32_t box3[3] = {(cuuint32_t)KB64, (cuuint32_t)box_rows, (cuuint32_t)box_kb};
+    const cuuint32_t estr3[3] = {1, 1, 1};
+    r = fn(&m, CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 3, const_cast<void*>(ptr), gdim3, gstr3, box3, estr3,
+           CU_TENSOR_MAP_INTERLEAVE_NONE, CU_TENSOR_MAP_SWIZZLE_128B, CU_TENSOR_MAP_L2_PROMOTION_L2_256B,
+           CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  } else {
+    r = fn(&m, dtype == PTTS_FP8 ? CU_TENSOR_MAP_DATA_TYPE_UINT8 : CU_TENSOR_MAP_DATA_TYPE_BFLOAT16, 2,
+           const_cast<void*>(ptr), gdim, gstr, box, estr, CU_TENSOR_MAP_INTERLEAVE_NONE,
+           dtype == PTTS_FP8 ? CU_TENSOR_MAP_SWIZZLE_64B : CU_TENSOR_MAP_SWIZZLE_128B,
+           CU_TENSOR_MAP_L2_PROMOTION_L2_256B, CU_TENSOR_MAP_FLOAT_OOB_FILL_NONE);
+  }
   if (r != CUDA_SUCCESS) return false;
   if (cache.size() > 4096) cache.clear();
   cache.emplace(key, m);
@@ -506,8 +628,12 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   if (smem > configured) {
     cudaFuncSetAttribute(umma_gemm_kernel<EPI, false>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
     cudaFuncSetAttribute(umma_gemm_kernel<EPI, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
-    if (EPI == EPI_PARTIAL)
+    if (EPI == EPI_PARTIAL) {
       cudaFuncSetAttribute(umma_gemm_kernel<EPI_PARTIAL, true, true>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(umma_partial_lean_kernel<8>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(umma_partial_lean_kernel<6>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+      cudaFuncSetAttribute(umma_partial_lean_kernel<4>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
+    }
     configured = smem;
   }
   cudaLaunchConfig_t cfg = {};
@@ -553,6 +679,25 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const TL tl = tl_next(10 + EPI);
   const int lean_ok = PTTS_KNOB("PTTS_GEMM_LEAN", 1);  // diagnostic build, 0: always the full instantiation
   const bool lean = lean_ok && tma && xbar && !(dbg_arg & ~(16 | 128)) && !hint.ptr && !tl.p;
+  // second-generation lean kernel (3-D box copies, unrolled issue): k-block counts the decode step uses
+  if (lean && EPI == EPI_PARTIAL && p.M % UN == 0 && p.N % UM == 0 && (kb == 8 || kb == 6 || kb == 4) &&
+      PTTS_KNOB("PTTS_GEMM_GEN2", 1)) {
+    CUtensorMap t3w, t3x;
+    if (tensor_map_2d_any(p.W, p.N, p.K, UM, PTTS_BF16, &t3w, kb / 2) &&
+        tensor_map_2d_any(p.X, p.M, p.K, UN, PTTS_BF16, &t3x, kb)) {
+      const int late = (dbg_arg & 128) ? 1 : 0;
+      cudaError_t e2 = kb == 8   ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<8>, p.part, p.M, p.N, late, t3w, t3x)
+                       : kb == 6 ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<6>, p.part, p.M, p.N, late, t3w, t3x)
+                                 : cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<4>, p.part, p.M, p.N, late, t3w, t3x);
+      if (e2 != cudaSuccess) {
+        set_error("umma_partial_lean launch: %s", cudaGetErrorString(e2));
+        (void)cudaGetLastError();
+        return PTTS_E_LAUNCH;
+      }
+      PTTS_CHECK_LAUNCH("umma_partial_lean");
+      return PTTS_OK;
+    }
+  }
   cudaError_t e =
       (lean && EPI == EPI_PARTIAL && p.M % UN == 0)
           ? cudaLaunchKernelEx(&cfg, umma_gemm_kernel<EPI_PARTIAL, true, true>, p, kb, cs, dbg_arg, hint, tm_w, tm_x, tl)

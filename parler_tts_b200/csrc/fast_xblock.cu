@@ -149,7 +149,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constan
 
   // ---- before the dependency: everything below only touches immutable data (weights, the cross cache, cache rows of
   // the next self-attention launch that are older than this step)
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {  // single-lane issue from uniform registers (common.cuh)
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&wq_bar)), "r"(1) : "memory");
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&wo_bar)), "r"(1) : "memory");
     asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
@@ -354,7 +354,7 @@ xblock_kernel(const XBlockParams p, int sc_cap, int dbg_in, const __grid_constan
   if (dbg & 1) c_st[2] = clock64();
 
   // ---- the Wo head slab (L2-resident by now) replaces the Wq slab while the attention phase runs: H/256 box copies
-  if (tid == 0) {
+  if (warp == 0 && elect_one()) {
     asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");  // generic-proxy reads of the Wq slab are done
     asm volatile("mbarrier.arrive.expect_tx.shared::cta.b64 _, [%0], %1;\n" ::"r"(smem_u32(&wo_bar)), "r"(H * 128) : "memory");
     for (int nb = 0; nb < H / 256; ++nb) xb_tma_load_2d(wbuf_s + nb * 32768, &tm_wo, smem_u32(&wo_bar), hd * XD, nb * 256);
