@@ -12,9 +12,10 @@ from .modeling import (
     apply_delay_pattern_mask,
     build_delay_pattern_mask,
 )
+from .streaming import AudioChunkStreamer
 
 __all__ = [
-    "DACConfig", "DACModel", "ParlerTTSConfig", "ParlerTTSDecoderConfig", "ParlerTTSForCausalLM",
+    "AudioChunkStreamer", "DACConfig", "DACModel", "ParlerTTSConfig", "ParlerTTSDecoderConfig", "ParlerTTSForCausalLM",
     "ParlerTTSForConditionalGeneration", "SuppressTokensAtOrAbove", "apply_delay_pattern_mask",
     "build_delay_pattern_mask",
 ]

@@ -233,8 +233,10 @@ class DecoderEngine:
         st.graph = g
         return g
 
-    def run_loop(self, st: GenState, use_graph=True, poll_every=16, max_steps=None):
-        """Runs decode steps until the control block says done (or max_steps).  Returns the control block."""
+    def run_loop(self, st: GenState, use_graph=True, poll_every=16, max_steps=None, on_progress=None):
+        """Runs decode steps until the control block says done (or max_steps).  Returns the control block.
+        on_progress(steps): called on the host after every batch of enqueued steps (streaming.ChunkPipeline hangs the
+        overlapped chunk decode here); it must not synchronise with the loop's stream."""
         budget = st.max_len - st.T0 - 1 if max_steps is None else max_steps
         if budget <= 0:
             return st.read_ctrl()
@@ -255,6 +257,8 @@ class DecoderEngine:
                 else:
                     self.step(st)
             done_steps += n
+            if on_progress is not None:
+                on_progress(done_steps)
             if ev is not None:
                 ev.synchronize()
                 if int(st._ctrl_host[1]) != 0:

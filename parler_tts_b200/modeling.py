@@ -19,6 +19,7 @@ from . import cabi
 from .configuration import DACConfig, ParlerTTSConfig, ParlerTTSDecoderConfig
 from .dac import DacDecoderEngine, DacEncoderEngine
 from .engine import DecoderDims, DecoderEngine, DecoderWeights, GenState
+from .streaming import AudioChunkStreamer, ChunkPipeline
 
 
 # --------------------------------------------------------------------------------------------- helpers
@@ -428,8 +429,11 @@ class SuppressTokensAtOrAbove:
 
 
 def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hidden, prompt_mask, decoder_input_ids,
-                    gc, kwargs, logits_processor, stopping_criteria, streamer, impl, use_graph, seed, row_offset):
-    """The loop of transformers greedy_search / sample on the CUDA path.  Returns (codes (Bu,K,F), sequences, state)."""
+                    gc, kwargs, logits_processor, stopping_criteria, streamer, impl, use_graph, seed, row_offset,
+                    audio_engine=None):
+    """The loop of transformers greedy_search / sample on the CUDA path.  Returns (codes (Bu,K,F), sequences, state).
+    With an `AudioChunkStreamer` and the codec engine (`audio_engine`), finished frames are de-delayed and decoded on
+    a second stream while the loop runs (streaming.ChunkPipeline, left on `state.audio_pipeline` for the caller)."""
     w = decoder.packed_weights()
     d = w.dims
     K = d.num_codebooks
@@ -493,16 +497,23 @@ def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hid
         decoder._state_cache = (key, st)
     eng = DecoderEngine(w)
     st.reset(start, seed)
+    audio_streamer = streamer if isinstance(streamer, AudioChunkStreamer) else None
+    if audio_streamer is not None:
+        streamer = None  # audio chunks, not token ids: the token-level hook of the host loop is not needed
     if streamer is not None:
         streamer.put(start.cpu())
     if enc is not None:
         eng.cross_kv(st, enc)
     slow = plan.slow or streamer is not None or bool(stopping_criteria)
+    st.audio_pipeline = None
     if not slow:
+        if audio_streamer is not None and audio_engine is not None and T0 == 1:
+            st.audio_pipeline = ChunkPipeline(audio_engine, st, audio_streamer, K)
         with _nvtx("ptts.prefill"):
             eng.prefill(st, prompt_table, prompt_ids, prompt_hidden)
         with _nvtx("ptts.decode_loop"):
-            ctrl = eng.run_loop(st, use_graph=use_graph)
+            ctrl = eng.run_loop(st, use_graph=use_graph,
+                                on_progress=st.audio_pipeline.progress if st.audio_pipeline is not None else None)
     else:
         with _nvtx("ptts.decode_loop_host_processors"):
             ctrl = _slow_loop(eng, st, prompt_table, prompt_ids, prompt_hidden, plan, gscale, stopping_criteria,
@@ -969,14 +980,24 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         codes, seq, st = _generate_codes(self.decoder, enc, attention_mask, prompt_table, prompt_ids, prompt_hidden,
                                          prompt_mask, dec_ids, gc, kwargs, logits_processor, stopping_criteria,
                                          streamer, self.decoder.impl, self.decoder.use_cuda_graph,
-                                         _draw_seed() if seed is None else seed, row_offset)
+                                         _draw_seed() if seed is None else seed, row_offset,
+                                         audio_engine=None if return_codes or not isinstance(streamer, AudioChunkStreamer)
+                                         else self.audio_encoder.engine(self.decoder.impl))
         if return_codes:
             return codes
+        dac = self.audio_encoder.engine(self.decoder.impl)
+        special_ids = (gc.bos_token_id if gc.bos_token_id is not None else self.config.decoder.bos_token_id,
+                       gc.pad_token_id if gc.pad_token_id is not None else self.config.decoder.pad_token_id,
+                       _first_id(gc.eos_token_id) if gc.eos_token_id is not None else self.config.decoder.eos_token_id)
         with _nvtx("ptts.dac_decode"):
-            audio = self.audio_encoder.engine(self.decoder.impl).decode_generated(
-                codes, gc.bos_token_id if gc.bos_token_id is not None else self.config.decoder.bos_token_id,
-                gc.pad_token_id if gc.pad_token_id is not None else self.config.decoder.pad_token_id,
-                _first_id(gc.eos_token_id) if gc.eos_token_id is not None else self.config.decoder.eos_token_id)
+            if st.audio_pipeline is not None:  # chunks were decoded during the loop: the remainder, then the whole
+                audio = st.audio_pipeline.finish(codes, lambda c: dac.decode_generated(c, *special_ids))
+                st.audio_pipeline = None
+            else:
+                audio = dac.decode_generated(codes, *special_ids)
+                if isinstance(streamer, AudioChunkStreamer):  # host-processor loop / audio prompt: one chunk at the end
+                    streamer.put_audio(0, audio.cpu() if streamer.to_host else audio)
+                    streamer.end()
         if gc.return_dict_in_generate:
             return SimpleNamespace(sequences=audio, audio_codes=codes)
         return audio

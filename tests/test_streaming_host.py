@@ -1,0 +1,39 @@
+"""Host-side arithmetic of the streaming path (no GPU): which token columns a chunk needs, and that the chunk
+schedule tiles the frames.  The de-delay geometry is checked against the oracle's restatement of
+/root/reference/parler_tts/modeling_parler_tts.py:2633-2648."""
+import numpy as np
+
+from oracle import delay_pattern
+from parler_tts_b200.streaming import chunk_ready_columns, chunk_schedule
+
+
+def test_chunk_schedule_tiles_the_frames():
+    for total, chunk, halo in ((860, 128, 16), (116, 16, 16), (40, 16, 16), (16, 16, 16), (1, 16, 16), (300, 64, 10)):
+        sched = chunk_schedule(total, chunk, halo)
+        assert sched[0][0] == 0 and sched[-1][1] == total
+        for (f0, f1, lo, hi), nxt in zip(sched, sched[1:] + [None]):
+            assert lo == max(0, f0 - halo) and lo <= f0 < f1 <= hi <= total
+            if nxt is not None:
+                assert f1 == nxt[0] and f1 - f0 == chunk and hi == f1 + halo  # full chunks see their whole right halo
+            else:
+                assert hi == total  # the last chunk ends at the true end (zero padding there, like the one-shot decode)
+
+
+def test_window_is_complete_when_chunk_ready_columns_exist():
+    """codes[b, k, f] = ids[b*K + k, f + k + 1]: with `chunk_ready_columns` columns generated, every frame of the window
+    [lo, f1 + halo) only reads columns that already exist, and one frame more would not."""
+    K, M, B = 9, 200, 2
+    rng = np.random.default_rng(0)
+    start = np.full((B * K, 1), 1025, dtype=np.int64)
+    _, mask = delay_pattern.build_delay_pattern_mask(start, 1025, 1024, M, K)
+    ids = rng.integers(0, 1024, size=(B * K, M)).astype(np.int64)
+    applied = delay_pattern.apply_delay_pattern_mask(ids, mask)
+    full = delay_pattern.revert_delay_pattern(ids, start, mask, 1025, 1024, K)  # (B, K, M - K)
+    for f1, halo in ((16, 16), (64, 16), (128, 10)):
+        cols = chunk_ready_columns(f1, halo, K)
+        hi = f1 + halo
+        need = max(f + k + 1 for f in range(hi) for k in range(K))
+        assert need == cols - 1          # the last column read is cols - 1: exactly the generated ones
+        assert max(hi + k + 1 for k in range(K)) == cols  # frame `hi` would need one more column
+        win = np.stack([[applied[b * K + k, np.arange(hi) + k + 1] for k in range(K)] for b in range(B)])
+        assert np.array_equal(win, full[:, :, :hi])
