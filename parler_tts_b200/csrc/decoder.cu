@@ -12,8 +12,15 @@ namespace ptts {
 static int linear_dispatch(int impl, const void* x, int xdtype, const void* w, int wdtype, const float* bias, int M,
                            int N, int K, float alpha, int act, const float* residual, const int* row_mask, void* y,
                            int ydtype, cudaStream_t st) {
-  if (impl == PTTS_IMPL_FAST && xdtype == PTTS_BF16 && wdtype == PTTS_BF16 && gemm_bf16_supported(M, N, K))
+  if (impl == PTTS_IMPL_FAST && xdtype == PTTS_BF16 && wdtype == PTTS_BF16 && gemm_bf16_supported(M, N, K)) {
+    // decode-sized activation GEMM (fc1): full-K tiles with the activation in the epilogue (fast_gemm_act.cu)
+    if (act != PTTS_ACT_NONE && !bias && !residual && !row_mask && alpha == 1.0f && ydtype == PTTS_BF16 && M <= 128 &&
+        gemm_bf16_act_supported(M, N, K)) {
+      const int rc = gemm_bf16_act(x, w, M, N, K, act, y, st);
+      if (rc != PTTS_E_UNSUPPORTED) return rc;
+    }
     return gemm_bf16_store(x, w, M, N, K, alpha, act, bias, residual, row_mask, y, ydtype, st);
+  }
   return linear_simple(x, xdtype, w, wdtype, bias, M, N, K, alpha, act, residual, row_mask, y, ydtype, st);
 }
 
@@ -314,7 +321,14 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
   PTTS_UNLESS_SKIPPED(1, ln_step(m, s, path, pend, L.ln3_g, L.ln3_b, rows, 1, 0, st));
   int bn_f = 64;
   const int Sf = (fuse && fc1_partials_enabled()) ? gemm_bf16_plan_splits(rows, F, H, &bn_f) : 0;
-  if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
+#ifndef PTTS_FC1_ACT
+#define PTTS_FC1_ACT 1
+#endif
+  // decode: fc1 over the whole K with the activation in its own epilogue - one launch instead of split-K partial sums +
+  // reduce / activation.  Measured on B200 (B=64, 860 frames, same box): see profiles/r02_fc1_act.txt
+  if (PTTS_FC1_ACT && fuse && rows <= 128 && gemm_bf16_act_supported(rows, F, H) && !(skip_mask() & 64)) {
+    PTTS_TRY(gemm_bf16_act(s->xn, L.w_fc1, rows, F, H, m->act_fn, s->ffn, st));
+  } else if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
     // decode: fc1 as split-K partial sums + one small reduce / activation kernel spread over all SMs.  (Folding the
     // activation into the second-arriving K-slice CTA of each output tile was measured slower: 1.539 against 1.457 ms
     // per decode step, 32 finishing CTAs do what the separate kernel spreads over 148 SMs.)

@@ -179,6 +179,9 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
     const int jg = j0 + staged;  // first row of the register-pipelined (global) part of the K pass
     pre_k = jg < j1 && min(j1, jg + KPB * U) <= old_end;
     if (pre_k) load_batch(cur, kb, jg);
+    // (Requesting the SECOND K batch here too - 2 x 8 KB per CTA in flight while the prologue folds q / k / v - was
+    // measured on B200 at B=64, 860 frames: 1.2321 against 1.2247 ms per decode step; the 72-register cap of 7 CTAs per
+    // SM makes the extra live batch spill.)
     pre_v = pre_k && !qf.has_kv && n <= KPB * U;
     if (pre_v) load_batch(nxt, vb, j0);
     // HBM would idle between the K pass and the V pass of the wave, and during the short kernels between two
@@ -365,6 +368,9 @@ attn_combine_kernel(const float* __restrict__ part, int heads, int splits, T* __
   out[((int64_t)b * heads + hd) * D + t] = from_f<T>(o / l);
 }
 
+// (Two KV splits per pair when the pairs already fill the GPU - 2048 CTAs in two waves, so that the K / softmax / V
+// phases of co-resident CTAs de-synchronise and the tail shortens - were measured on B200 at B=64, 860 frames with the
+// combine kernel: 27.7 against 23.4 us per launch, 1.374 against 1.243 ms per decode step.)
 int plan_splits(int B, int heads, int c_stride) {
   const int pairs = B * heads;
   if (pairs >= 512) return 1;

@@ -79,6 +79,19 @@ __device__ __forceinline__ void mbar_wait(uint32_t bar, uint32_t parity) {
     if (spin > kSpinLimit) __trap();
   }
 }
+// the single issuing lanes spin with test_wait: a try_wait that finds the phase incomplete suspends the thread for a
+// while (measured in fast_gemm3.cu: eight sequential waits cost ~4000 cycles that way)
+__device__ __forceinline__ void mbar_spin(uint32_t bar, uint32_t parity) {
+  uint32_t done = 0;
+  for (uint32_t spin = 0; !done; ++spin) {
+    asm volatile(
+        "{\n\t.reg .pred P1;\n\tmbarrier.test_wait.parity.shared::cta.b64 P1, [%1], %2;\n\tselp.b32 %0, 1, 0, P1;\n\t}\n"
+        : "=r"(done)
+        : "r"(bar), "r"(parity)
+        : "memory");
+    if (spin > kSpinLimit) __trap();
+  }
+}
 __device__ __forceinline__ void tma_tile_2d(uint32_t dst, const CUtensorMap* map, uint32_t bar, int c0, int c1) {
   asm volatile(
       "cp.async.bulk.tensor.2d.shared::cluster.global.mbarrier::complete_tx::bytes [%0], [%1, {%3, %4}], [%2];\n" ::"r"(dst),
@@ -257,14 +270,14 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
 
   if (warp == 0) {
     // ================================================================ producer: K(0) V(0) K(1) V(1) ... in ring order
-    if (lane == 0) {
+    if (elect_one()) {  // single-lane issue from uniform registers (common.cuh)
       uint32_t cnt = 0;
       for (int it = 0; it < n_it; ++it) {
         const int row0 = ((int)blockIdx.x + it * (int)gridDim.x) * p.c_stride;
         for (int pass = 0; pass < 2; ++pass)
           for (int t = 0; t < nt; ++t, ++cnt) {
             const uint32_t slot = cnt % (uint32_t)ring, use = cnt / (uint32_t)ring;
-            if (use > 0) mbar_wait(smem_u32(&bar_empty[slot]), (use & 1u) ^ 1u);
+            if (use > 0) mbar_spin(smem_u32(&bar_empty[slot]), (use & 1u) ^ 1u);
             mbar_expect_tx(smem_u32(&bar_full[slot]), TB);
             tma_tile_2d(s_ring + slot * TB, pass ? &tm_v : &tm_k, smem_u32(&bar_full[slot]), 0, row0 + t * TILE);
           }
@@ -272,19 +285,19 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
     }
   } else if (warp == 1) {
     // ================================================================ score-MMA issuer: S = Ktile . q^T
-    if (lane == 0) {
+    if (elect_one()) {  // single-lane issue from uniform registers (common.cuh)
       for (int it = 0; it < n_it; ++it) {
         const int par = it & 3;
-        mbar_wait(smem_u32(&bar_qfull[par]), (uint32_t)(it >> 2) & 1u);
+        mbar_spin(smem_u32(&bar_qfull[par]), (uint32_t)(it >> 2) & 1u);
         for (int t = 0; t < nt; ++t) {
           const uint32_t cnt = (uint32_t)(it * 2 * nt + t), slot = cnt % (uint32_t)ring;
           const uint32_t n = (uint32_t)(it * nt + t), buf = n % NS;
           // the slot's previous use (possibly a V tile the other issuer consumes) must be CONSUMED before this thread
           // may interpret the parity of `full`: otherwise a wait one phase ahead returns at once (needs ring >= nt + 2)
           const uint32_t use = cnt / (uint32_t)ring;
-          if (use > 0) mbar_wait(smem_u32(&bar_empty[slot]), (use & 1u) ^ 1u);
-          mbar_wait(smem_u32(&bar_full[slot]), use & 1u);
-          if (n >= NS) mbar_wait(smem_u32(&bar_sempty[buf]), ((n / NS) & 1u) ^ 1u);
+          if (use > 0) mbar_spin(smem_u32(&bar_empty[slot]), (use & 1u) ^ 1u);
+          mbar_spin(smem_u32(&bar_full[slot]), use & 1u);
+          if (n >= NS) mbar_spin(smem_u32(&bar_sempty[buf]), ((n / NS) & 1u) ^ 1u);
           tc_fence_after();
           const uint32_t a0 = s_ring + slot * TB, b0 = s_qtile + par * 2048;
 #pragma unroll
@@ -298,7 +311,7 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
     }
   } else if (warp == 2) {
     // ================================================================ P.V-MMA issuer: O[g] += Vtile^T . P^T
-    if (lane == 0) {
+    if (elect_one()) {  // single-lane issue from uniform registers (common.cuh)
       for (int it = 0; it < n_it; ++it) {
         const int g = it & 1, my = it >> 1;
         for (int t = 0; t < nt; ++t) {
@@ -306,9 +319,9 @@ attn_ws_kernel(const WsParams p, const __grid_constant__ CUtensorMap tm_k, const
           const uint32_t pb_cnt = (uint32_t)(my * nt + t), pb = pb_cnt & 1u;
           // probabilities first: P(i, t) ready means S(i) is complete, hence every earlier tile of this slot has been
           // consumed and the parity of `full` is unambiguous (this thread waits on `full` from kernel start otherwise)
-          mbar_wait(smem_u32(&bar_pfull[g][pb]), (pb_cnt >> 1) & 1u);
-          mbar_wait(smem_u32(&bar_full[slot]), (cnt / (uint32_t)ring) & 1u);
-          if (t == 0 && my > 0) mbar_wait(smem_u32(&bar_oempty[g]), (uint32_t)(my - 1) & 1u);
+          mbar_spin(smem_u32(&bar_pfull[g][pb]), (pb_cnt >> 1) & 1u);
+          mbar_spin(smem_u32(&bar_full[slot]), (cnt / (uint32_t)ring) & 1u);
+          if (t == 0 && my > 0) mbar_spin(smem_u32(&bar_oempty[g]), (uint32_t)(my - 1) & 1u);
           tc_fence_after();
           const uint32_t a0 = s_ring + slot * TB, b0 = s_ptile + (uint32_t)(g * 2 + (int)pb) * 2048;
 #pragma unroll

@@ -195,7 +195,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
                  : "memory");
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
   }
-  if (threadIdx.x == 32) {
+  if (warp == 1 && elect_one()) {  // single-lane issue from uniform registers (common.cuh)
     asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&mma_bar)), "r"(1) : "memory");
     if (tma) {
       asm volatile("mbarrier.init.shared::cta.b64 [%0], %1;\n" ::"r"(smem_u32(&w_bar)), "r"(1) : "memory");
@@ -229,7 +229,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
   const long long c_dep = (dbg & 3) == 3 ? clock64() : 0;
   long long c_w = 0, c_x = 0, c_mma = 0;
   if (tma) {
-    if (threadIdx.x == 32) {
+    if (warp == 1 && elect_one()) {
       if (dbg & 64) {  // PTTS_GEMM_XBAR=1: one barrier for the whole X slab
         mbar_expect_tx3(smem_u32(&x_bar[0]), (uint32_t)(KB * XBLK));
         for (int kb = 0; kb < KB; ++kb) tma_load_2d(sx + kb * XBLK, &tm_x, smem_u32(&x_bar[0]), kbeg + kb * KB64, m0);
@@ -256,7 +256,7 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
   const uint32_t tmem_d = tmem_base_slot;
   STAMP(2);
 
-  if (threadIdx.x == 0) {
+  if (warp == 0 && elect_one()) {
     if (tma) {  // barrier inits are visible since the __syncthreads above; the slabs arrive through the async proxy
       mbar_wait3(smem_u32(&w_bar), 0);
       if ((dbg & 3) == 3) c_w = clock64();
@@ -432,18 +432,24 @@ umma_gemm_kernel(const GemmParams p, int KB, int CS, int dbg_in, const L2Hint hi
 //   * ONE 3-D box copy for the whole X slab (tensor map viewed as [k-block][row][64]), two for the W slab;
 //   * the KB*4 MMAs fully unrolled, descriptors = a 32-bit low word + compile-time offset (the high word is constant);
 //   * barrier init / TMEM allocation / the only __syncthreads in front of the dependency wait.
+// X slab as XP box copies with a barrier each: the MMAs of a part run while the later parts land.  Measured on B200
+// (B=64, 860 frames, same box): 1 part 1.2514, 2 parts 1.2403 ms per decode step
+#ifndef PTTS_GEMM_XPARTS
+#define PTTS_GEMM_XPARTS 2
+#endif
 template <int KB>
 __global__ void __launch_bounds__(NTH)
 umma_partial_lean_kernel(float* __restrict__ part, int M, int N, int late, const __grid_constant__ CUtensorMap tm_w,
                          const __grid_constant__ CUtensorMap tm_x) {
   extern __shared__ unsigned char smem_raw[];
-  __shared__ __align__(8) uint64_t bars[3];  // W slab, X slab, MMA burst
+  constexpr int XP = (KB % PTTS_GEMM_XPARTS == 0) ? PTTS_GEMM_XPARTS : 1;
+  __shared__ __align__(8) uint64_t bars[2 + XP];  // W slab, MMA burst, X parts
   __shared__ uint32_t tmem_base_slot;
   const uint32_t sbase = (smem_u32(smem_raw) + 1023u) & ~1023u;  // SWIZZLE_128B atoms need 1024-byte alignment
   const uint32_t sw = sbase, sx = sbase + KB * WBLK;
   const int n0 = blockIdx.x * UM, m0 = blockIdx.y * UN, rank = blockIdx.z;
   const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
-  const uint32_t w_bar = smem_u32(&bars[0]), x_bar = smem_u32(&bars[1]), mma_bar = smem_u32(&bars[2]);
+  const uint32_t w_bar = smem_u32(&bars[0]), mma_bar = smem_u32(&bars[1]), x_bar = smem_u32(&bars[2]);
   if (warp == 0) {
     asm volatile("tcgen05.alloc.cta_group::1.sync.aligned.shared::cta.b32 [%0], %1;\n" ::"r"(smem_u32(&tmem_base_slot)),
                  "r"(TMEM_COLS)
@@ -451,9 +457,8 @@ umma_partial_lean_kernel(float* __restrict__ part, int M, int N, int late, const
     asm volatile("tcgen05.relinquish_alloc_permit.cta_group::1.sync.aligned;\n" ::: "memory");
   } else if (warp == 1) {
     if (elect_one()) {
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(w_bar) : "memory");
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(x_bar) : "memory");
-      asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(mma_bar) : "memory");
+#pragma unroll
+      for (int i = 0; i < 2 + XP; ++i) asm volatile("mbarrier.init.shared::cta.b64 [%0], 1;\n" ::"r"(w_bar + 8 * i) : "memory");
       asm volatile("fence.mbarrier_init.release.cluster;\n" ::: "memory");
       asm volatile("fence.proxy.async.shared::cta;\n" ::: "memory");
       // the whole W slab of this CTA, before the dependency resolves (weights are immutable)
@@ -469,18 +474,25 @@ umma_partial_lean_kernel(float* __restrict__ part, int M, int N, int late, const
   pdl_wait();
   if (!late) pdl_launch();
   if (warp == 1 && elect_one()) {
-    mbar_expect_tx3(x_bar, (uint32_t)(KB * XBLK));
-    tma_load_3d(sx, &tm_x, x_bar, 0, m0, rank * KB);
-    mbar_wait3(w_bar, 0);
-    mbar_wait3(x_bar, 0);
-    asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
     const uint32_t a0 = ((sw >> 4) & 0x3FFFu) | (1u << 16), b0 = ((sx >> 4) & 0x3FFFu) | (1u << 16);
-    // k-block loop rolled (fully unrolled, ptxas hoists all 2 * 4 * KB descriptor pairs and spills uniform registers)
-#pragma unroll 1
-    for (int kb = 0; kb < KB; ++kb)
+    // all expectations first, then the copies back to back (an arrive between two copies delays the second)
 #pragma unroll
-      for (int k = 0; k < KB64 / 16; ++k)  // +32 bytes (2 x 16 B) per UMMA_K = 16 inside the swizzle atom
-        umma_f16_lo(tmem_d, a0 + kb * (WBLK >> 4) + 2 * k, b0 + kb * (XBLK >> 4) + 2 * k, (kb | k) ? 1u : 0u);
+    for (int i = 0; i < XP; ++i) mbar_expect_tx3(x_bar + 8 * i, (uint32_t)(KB / XP * XBLK));
+#pragma unroll
+    for (int i = 0; i < XP; ++i)
+      tma_load_3d(sx + i * (KB / XP) * XBLK, &tm_x, x_bar + 8 * i, 0, m0, rank * KB + i * (KB / XP));
+    mbar_wait3(w_bar, 0);
+#pragma unroll
+    for (int i = 0; i < XP; ++i) {
+      mbar_wait3(x_bar + 8 * i, 0);
+      asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
+      // k-block loop rolled (fully unrolled, ptxas hoists all 2 * 4 * KB descriptor pairs and spills uniform registers)
+#pragma unroll 1
+      for (int kb = i * (KB / XP); kb < (i + 1) * (KB / XP); ++kb)
+#pragma unroll
+        for (int k = 0; k < KB64 / 16; ++k)  // +32 bytes (2 x 16 B) per UMMA_K = 16 inside the swizzle atom
+          umma_f16_lo(tmem_d, a0 + kb * (WBLK >> 4) + 2 * k, b0 + kb * (XBLK >> 4) + 2 * k, (kb | k) ? 1u : 0u);
+    }
     asm volatile("tcgen05.commit.cta_group::1.mbarrier::arrive::one.shared::cluster.b64 [%0];\n" ::"r"(mma_bar) : "memory");
   }
   __syncwarp();
@@ -684,7 +696,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
       PTTS_KNOB("PTTS_GEMM_GEN2", 1)) {
     CUtensorMap t3w, t3x;
     if (tensor_map_2d_any(p.W, p.N, p.K, UM, PTTS_BF16, &t3w, kb / 2) &&
-        tensor_map_2d_any(p.X, p.M, p.K, UN, PTTS_BF16, &t3x, kb)) {
+        tensor_map_2d_any(p.X, p.M, p.K, UN, PTTS_BF16, &t3x, kb % PTTS_GEMM_XPARTS == 0 ? kb / PTTS_GEMM_XPARTS : kb)) {
       const int late = (dbg_arg & 128) ? 1 : 0;
       cudaError_t e2 = kb == 8   ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<8>, p.part, p.M, p.N, late, t3w, t3x)
                        : kb == 6 ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<6>, p.part, p.M, p.N, late, t3w, t3x)
@@ -721,6 +733,9 @@ namespace gemm {
 bool tma_available() { return encode_tiled_fn() != nullptr; }
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out) {
   return tensor_map_2d_impl(ptr, rows, cols, box_rows, out);
+}
+bool tensor_map_3d(const void* ptr, int rows, int cols, int box_rows, int box_kb, CUtensorMap* out) {
+  return tensor_map_2d_any(ptr, rows, cols, box_rows, PTTS_BF16, out, box_kb);
 }
 bool tensor_map_2d_dt(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out) {
   return tensor_map_2d_any(ptr, rows, cols, box_rows, dtype, out);

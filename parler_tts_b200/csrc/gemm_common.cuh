@@ -81,6 +81,8 @@ __device__ __forceinline__ void load_tile(uint32_t sbase, const __nv_bfloat16* g
 bool tensor_map_2d(const void* ptr, int rows, int cols, int box_rows, CUtensorMap* out);
 // same for PTTS_BF16 (128-byte box rows, SWIZZLE_128B) or PTTS_FP8 bytes (64-byte box rows, SWIZZLE_64B)
 bool tensor_map_2d_dt(const void* ptr, int rows, int cols, int box_rows, int dtype, CUtensorMap* out);
+// bf16 [rows][cols] viewed as [cols/64][rows][64]: box {64, box_rows, box_kb} = box_kb consecutive SWIZZLE_128B k-blocks
+bool tensor_map_3d(const void* ptr, int rows, int cols, int box_rows, int box_kb, CUtensorMap* out);
 bool tma_available();  // the driver entry point for tensor-map creation was found
 
 // tcgen05 swap-AB cluster split-K kernel (fast_gemm3.cu)

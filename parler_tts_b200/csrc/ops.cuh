@@ -29,6 +29,9 @@ int gemm_bf16_store(const void* x, const void* w, int M, int N, int K, float alp
 int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has_q, float q_scale, void* q, void* ck,
                       void* cv, int H, int heads, int d, int Tq, int c_stride, int pos_base, const int* pos_dyn,
                       cudaStream_t st);
+// y (bf16) = act(x . w^T) over the whole K in one launch, activation in the GEMM epilogue (fast_gemm_act.cu; decode sizes)
+bool gemm_bf16_act_supported(int M, int N, int K);
+int gemm_bf16_act(const void* x, const void* w, int M, int N, int K, int act, void* y, cudaStream_t st);
 int gemm_bf16_plan_splits(int M, int N, int K, int* bn_out);
 int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int splits, int bn, float* part,
                       cudaStream_t st);

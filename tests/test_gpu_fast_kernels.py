@@ -54,6 +54,29 @@ def test_skinny_gemm_vs_torch_fp32(M, N, K):
     assert float((simple - ref).abs().max()) < tol
 
 
+@pytest.mark.parametrize("M,N,K", [(64, 4096, 1024), (64, 256, 512), (128, 1024, 768), (64, 64, 256)])
+def test_activation_gemm_full_k_vs_torch_fp32(M, N, K):
+    """fc1 shape family of fast_gemm_act.cu (tcgen05 M = 64 tiles over the whole K, activation in the epilogue; K = 1024
+    streams X through the ring with slot re-use, K <= 768 does not): bf16 out = act(x . w^T), no bias / residual."""
+    g = torch.Generator().manual_seed(M + N + K)
+    x = (torch.randn(M, K, generator=g) * 0.5).to(DEV, torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) * 0.05).to(DEV, torch.bfloat16)
+    ref = x.float() @ w.float().t()
+    for name, fn in (("gelu", torch.nn.functional.gelu), ("relu", torch.relu)):
+        want = fn(ref)
+        got = _linear(x, w, act=cabi.ACT[name], ydtype=torch.bfloat16).float()
+        assert float((got - want).abs().max()) < 1e-2 * float(want.abs().max()), name
+        simple = _linear(x, w, act=cabi.ACT[name], ydtype=torch.bfloat16, impl=cabi.IMPL_SIMPLE).float()
+        assert float((got - simple).abs().max()) < 1e-2 * float(want.abs().max()), name
+    # every element is written exactly once: a second call into a poisoned buffer gives the same result
+    y = torch.full((M, N), float("nan"), device=DEV, dtype=torch.bfloat16)
+    cabi.call("ptts_linear", cabi.ptr(x), cabi.dtype_enum(x.dtype), cabi.ptr(w), cabi.dtype_enum(w.dtype), None, M, N, K,
+              1.0, cabi.ACT["gelu"], None, None, cabi.ptr(y), cabi.dtype_enum(torch.bfloat16), cabi.IMPL_FAST,
+              cabi.stream_ptr())
+    assert not bool(torch.isnan(y.float()).any())
+    assert float((y.float() - torch.nn.functional.gelu(ref)).abs().max()) < 1e-2 * float(ref.abs().max())
+
+
 def _attention(q, ck, cv, ctx, key_mask, impl):
     B, heads, c_stride, d = ck.shape
     out = torch.empty(B, heads * d, device=DEV, dtype=q.dtype)

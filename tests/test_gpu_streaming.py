@@ -1,0 +1,110 @@
+"""Streaming audio out of generate(): the chunks an AudioChunkStreamer receives while the
+CUDA-graph loop is still running concatenate to the audio generate() returns, which equals the one-shot result."""
+import threading
+
+import numpy as np
+import pytest
+import torch
+
+pytestmark = pytest.mark.gpu
+
+import parler_tts_b200 as ptts  # noqa: E402
+from parler_tts_b200.streaming import chunk_schedule  # noqa: E402
+
+from test_gpu_generate import DEV, _composite  # noqa: E402
+
+
+def _inputs(B, seed=2):
+    g = torch.Generator().manual_seed(seed)
+    return torch.randint(2, 100, (B, 7), generator=g).to(DEV), torch.randint(2, 100, (B, 4), generator=g).to(DEV)
+
+
+def _long_model(max_length=56):
+    model, dims, sd, dac_sd = _composite()
+    model.generation_config.max_length = max_length  # TINY: max_position_embeddings 64, prompt 4
+    return model
+
+
+def test_streamed_chunks_equal_one_shot_audio():
+    model = _long_model()
+    ids, pids = _inputs(3)
+    procs = [ptts.SuppressTokensAtOrAbove(32)]  # ids >= 32 are not codebook entries: every frame stays valid
+    want = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=procs)
+    got_chunks, pinned = [], []
+
+    def on_chunk(first_frame, a):
+        pinned.append(a.device.type == "cpu" and a.is_pinned())
+        got_chunks.append((first_frame, a.clone()))
+
+    streamer = ptts.AudioChunkStreamer(chunk_frames=16, on_chunk=on_chunk)
+    audio = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=procs,
+                           streamer=streamer)
+    assert audio.shape == want.shape
+    np.testing.assert_allclose(audio.cpu().numpy(), want.cpu().numpy(), atol=1e-5)
+    F, hop = 56 - 4, 512
+    sched = chunk_schedule(F, 16, 16)
+    assert [f for f, _ in got_chunks] == [s[0] for s in sched]
+    assert all(pinned)  # to_host=True: every chunk arrives in pinned host memory, copy completed
+    cat = torch.cat([a for _, a in got_chunks], dim=1)
+    assert cat.shape == (3, F * hop)
+    np.testing.assert_allclose(cat.numpy(), want.cpu().numpy(), atol=1e-5)
+    # the first chunk was handed over while decode steps were still being queued (overlap, not a decode at the end)
+    assert streamer.stats[0]["steps_enqueued"] < 56 - 2
+    # iterator protocol: the same chunks, then StopIteration
+    assert [f for f, _ in streamer] == [s[0] for s in sched]
+
+
+def test_streaming_from_a_consumer_thread_and_on_device():
+    model = _long_model()
+    ids, pids = _inputs(2, seed=5)
+    procs = [ptts.SuppressTokensAtOrAbove(32)]
+    want = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=True, top_k=8, seed=3, logits_processor=procs)
+    streamer = ptts.AudioChunkStreamer(chunk_frames=16, to_host=False, timeout=60)
+    got = []
+    t = threading.Thread(target=lambda: got.extend((f, a.cpu()) for f, a in streamer))
+    t.start()
+    audio = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=True, top_k=8, seed=3,
+                           logits_processor=procs, streamer=streamer)
+    t.join(60)
+    assert not t.is_alive()
+    np.testing.assert_allclose(audio.cpu().numpy(), want.cpu().numpy(), atol=1e-5)
+    np.testing.assert_allclose(torch.cat([a for _, a in got], dim=1).numpy(), want.cpu().numpy(), atol=1e-5)
+
+
+def test_streaming_with_rows_that_finish_early():
+    """No suppression: rows emit EOS / unused ids, the ragged path of modeling_parler_tts.py:2668-2677 applies.  What was
+    streamed before the first invalid window is a prefix of every sample's final audio; the rest arrives in one piece."""
+    model = _long_model()
+    ids, pids = _inputs(3, seed=9)
+    for seed in (1, 2, 3):
+        kw = dict(input_ids=ids, prompt_input_ids=pids, do_sample=True, top_k=40, seed=seed)
+        want = model.generate(**kw)
+        chunks = []
+        streamer = ptts.AudioChunkStreamer(chunk_frames=16, on_chunk=lambda f, a: chunks.append((f, a.clone())))
+        audio = model.generate(streamer=streamer, **kw)
+        assert audio.shape == want.shape
+        np.testing.assert_allclose(audio.cpu().numpy(), want.cpu().numpy(), atol=1e-5)
+        cat = torch.cat([a for _, a in chunks], dim=1)
+        assert cat.shape == want.shape
+        np.testing.assert_allclose(cat.numpy(), want.cpu().numpy(), atol=1e-5)
+
+
+def test_streamer_falls_back_to_one_chunk_with_host_processors():
+    """Python logits processors run the step-at-a-time host loop: no overlap, the audio arrives as one chunk."""
+    model = _long_model(24)
+    ids, pids = _inputs(2, seed=4)
+
+    class Cut:
+        def __call__(self, input_ids, scores):
+            scores = scores.clone()
+            scores[:, 32:] = -float("inf")
+            return scores
+
+    want = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=[Cut()])
+    streamer = ptts.AudioChunkStreamer(chunk_frames=16)
+    audio = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=[Cut()],
+                           streamer=streamer)
+    got = list(streamer)
+    assert len(got) == 1 and got[0][0] == 0
+    np.testing.assert_allclose(got[0][1].numpy(), want.cpu().numpy(), atol=1e-6)
+    np.testing.assert_allclose(audio.cpu().numpy(), want.cpu().numpy(), atol=1e-6)
