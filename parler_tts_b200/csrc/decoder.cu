@@ -30,6 +30,11 @@ static int attention_dispatch(int impl, const void* q, const void* ck, const voi
   if (impl == PTTS_IMPL_FAST && fast_attention_supported(dtype, d, Tq))
     return attention_fast(q, ck, cv, dtype, B, heads, d, Tq, c_stride, ctx_base, ctx_dyn, causal, key_mask, mask_len,
                           out, scratch, st);
+  // prefill (Tq > 1): K / V of a (head, utterance) pair staged in shared memory once for all its queries
+  const int ctx_max = ctx_dyn ? c_stride : ctx_base;
+  if (impl == PTTS_IMPL_FAST && attention_prefill_supported(dtype, d, Tq, ctx_max))
+    return attention_prefill(q, ck, cv, dtype, B, heads, Tq, c_stride, ctx_base, ctx_dyn, ctx_max, causal, key_mask,
+                             mask_len, out, st);
   return attention_simple(q, ck, cv, dtype, B, heads, d, Tq, c_stride, ctx_base, ctx_dyn, causal, key_mask, mask_len,
                           out, st);
 }
@@ -517,6 +522,21 @@ extern "C" int ptts_decode_step(const PttsModel* m, const PttsState* s, int32_t 
   Pending pend;
   for (int l = 0; l < m->n_layers; ++l) PTTS_TRY(run_layer(m, s, path, pend, l, 1, s->P, &s->ctrl->len, st));
   PTTS_TRY(ln_step(m, s, path, pend, m->lnf_g, m->lnf_b, B, 1, 0, st));
+#ifndef PTTS_HEADS_PARTIAL
+#define PTTS_HEADS_PARTIAL 1
+#endif
+  // The fused step (epilogue in the same call): the 9 lm_heads as split-K partial sums of the lean tcgen05 kernel - 4
+  // K slices, 308 CTAs of 96 KB, two per SM - that the epilogue kernel adds up while it reads them; the logits matrix is
+  // only materialised when somebody else reads it (host-side processors, forward()).  Measured: profiles/r02_heads_partial.txt
+  constexpr int kHeadSlices = 4;  // <= 4: the epilogue kernel folds at most four slices
+  if (PTTS_HEADS_PARTIAL && run_epilogue && path.gemm && path.ln && B % 64 == 0 && H % (64 * kHeadSlices) == 0 &&
+      H / 64 / kHeadSlices <= 8 && (int64_t)kHeadSlices * B * K * V <= work_area_floats(m, B)) {
+    float* hpart = work_area(m, s);
+    PTTS_TRY(gemm_bf16_partial(s->xn, m->w_heads, B, K * V, H, kHeadSlices, 0, hpart, st));
+    PTTS_TRY(step_epilogue(m, s, st, hpart, kHeadSlices, (int64_t)B * K * V));
+    (void)take_l2_hint();
+    return PTTS_OK;
+  }
   PTTS_TRY(linear_dispatch(s->impl, s->xn, dt, m->w_heads, dt, nullptr, B, K * V, H, 1.0f, PTTS_ACT_NONE, nullptr,
                            nullptr, s->logits, PTTS_F32, st));
   if (run_epilogue) PTTS_TRY(step_epilogue(m, s, st));

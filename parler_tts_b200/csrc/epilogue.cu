@@ -43,7 +43,7 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
                      int64_t pad_id, int64_t eos_id,
                      PttsCtrl* __restrict__ ctrl, const float* __restrict__ logits, int64_t* __restrict__ ids,
                      const int64_t* __restrict__ mask, int* __restrict__ unfinished, float* __restrict__ h,
-                     int h_rows_per_batch) {
+                     int h_rows_per_batch, int nslice, int64_t slice_stride) {
   extern __shared__ float smem[];
   __shared__ int64_t next_in[PTTS_MAX_CODEBOOKS];
   __shared__ int transitions;
@@ -61,9 +61,20 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
 
   // ---- logits processors, in the order transformers applies them (defaults first, then the caller's list with the
   // guidance processor last, modeling_parler_tts.py:2556-2567)
+  // nslice > 1: the logits arrive as split-K partial sums [nslice][B*K][V] of the heads GEMM (decode step of the captured
+  // graph) and are added up here in slice order (deterministic); nslice == 1: the plain logits matrix
   const float* lc = logits + (int64_t)r * V;
+  // (all slice loads of an element are issued before the first add: with a rolled loop every load waits for the one
+  // before it - measured 17 us per step)
+  auto raw = [&](const float* row, int i) {
+    float t[4];
+#pragma unroll
+    for (int sl = 0; sl < 4; ++sl) t[sl] = sl < nslice ? __ldcg(row + (int64_t)sl * slice_stride + i) : 0.f;
+    return ((t[0] + t[1]) + t[2]) + t[3];
+  };
   const int mix = cfg && !premixed;  // premixed: rows [0, Bu*K) already hold the guidance-mixed scores (host processors)
-  for (int i = lane; i < V; i += 32) sc[i] = lc[i];
+#pragma unroll 4
+  for (int i = lane; i < V; i += 32) sc[i] = raw(lc, i);
   __syncwarp();
   if (rep_penalty != 1.0f) {
     // RepetitionPenaltyLogitsProcessor over this row's own raw history (with guidance: the conditional rows only, which
@@ -73,7 +84,7 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
     for (int i = lane; i < len; i += 32) {
       const int64_t t = hist[i];
       if (t >= 0 && t < V) {
-        const float v = lc[t];
+        const float v = raw(lc, (int)t);
         sc[t] = v < 0.f ? v * rep_penalty : v / rep_penalty;
       }
     }
@@ -82,14 +93,14 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
   if (mix) {
     const float* lu = logits + ((int64_t)(b + Bu) * K + k) * V;
     float mc = -INFINITY, mu = -INFINITY;
-    for (int i = lane; i < V; i += 32) { mc = fmaxf(mc, sc[i]); mu = fmaxf(mu, lu[i]); }
+    for (int i = lane; i < V; i += 32) { mc = fmaxf(mc, sc[i]); mu = fmaxf(mu, raw(lu, i)); }
     mc = warp_max(mc); mu = warp_max(mu);
     float sc_ = 0.f, su = 0.f;
-    for (int i = lane; i < V; i += 32) { sc_ += expf(sc[i] - mc); su += expf(lu[i] - mu); }
+    for (int i = lane; i < V; i += 32) { sc_ += expf(sc[i] - mc); su += expf(raw(lu, i) - mu); }
     sc_ = warp_sum(sc_); su = warp_sum(su);
     const float lzc = mc + logf(sc_), lzu = mu + logf(su);
     for (int i = lane; i < V; i += 32) {
-      const float c = sc[i] - lzc, u = lu[i] - lzu;
+      const float c = sc[i] - lzc, u = raw(lu, i) - lzu;
       sc[i] = u + guidance * (c - u);
     }
   }
@@ -242,7 +253,8 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
   }
 }
 
-int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st) {
+int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st, const float* logit_parts, int nslice,
+                  int64_t slice_stride) {
   const int K = m->n_codebooks, V = m->vocab;
   const int cfg = s->guidance_scale > 1.0f;
   PTTS_CHECK_ARG(!cfg || (s->B % 2 == 0), "step_epilogue: guidance needs an even model batch");
@@ -265,7 +277,9 @@ int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st) {
                                                  s->repetition_penalty > 0.0f ? s->repetition_penalty : 1.0f,
                                                  s->logits_premixed,
                                                  s->row_offset, s->pad_id, s->eos_id,
-                                                 s->ctrl, s->logits, s->ids, s->mask, s->unfinished, s->h, 1);
+                                                 s->ctrl, logit_parts ? logit_parts : s->logits, s->ids, s->mask,
+                                                 s->unfinished, s->h, 1, logit_parts ? nslice : 1,
+                                                 logit_parts ? slice_stride : 0);
   PTTS_CHECK_LAUNCH("step_epilogue");
   return PTTS_OK;
 }

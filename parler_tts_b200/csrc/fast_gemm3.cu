@@ -692,7 +692,8 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const int lean_ok = PTTS_KNOB("PTTS_GEMM_LEAN", 1);  // diagnostic build, 0: always the full instantiation
   const bool lean = lean_ok && tma && xbar && !(dbg_arg & ~(16 | 128)) && !hint.ptr && !tl.p;
   // second-generation lean kernel (3-D box copies, unrolled issue): k-block counts the decode step uses
-  if (lean && EPI == EPI_PARTIAL && p.M % UN == 0 && p.N % UM == 0 && (kb == 8 || kb == 6 || kb == 4) &&
+  // (a ragged last weight tile is fine: the box copy zero-fills rows >= N and the store loop skips them)
+  if (lean && EPI == EPI_PARTIAL && p.M % UN == 0 && (kb == 8 || kb == 6 || kb == 4) &&
       PTTS_KNOB("PTTS_GEMM_GEN2", 1)) {
     CUtensorMap t3w, t3x;
     if (tensor_map_2d_any(p.W, p.N, p.K, UM, PTTS_BF16, &t3w, kb / 2) &&

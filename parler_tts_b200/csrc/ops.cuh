@@ -19,7 +19,9 @@ int kv_scatter(const void* kv, int dtype, int rows, int H, int heads, int d, int
 int attention_simple(const void* q, const void* ck, const void* cv, int dtype, int B, int heads, int d, int Tq,
                      int c_stride, int ctx_base, const int* ctx_dyn, int causal, const int* key_mask, int mask_len,
                      void* out, cudaStream_t st);
-int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st);
+// logit_parts (optional): split-K partial sums [nslice][B*K][V] of the heads GEMM instead of s->logits
+int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st, const float* logit_parts = nullptr,
+                  int nslice = 1, int64_t slice_stride = 0);
 
 // fast family -- fast_*.cu
 constexpr int kMaxSplitK = 16;
@@ -38,6 +40,11 @@ int gemm_bf16_partial(const void* x, const void* w, int M, int N, int K, int spl
 // the next gemm_bf16_partial launch releases its dependent kernel AFTER its own dependency wait whatever PTTS_PDL_EARLY
 // says, or (at_mma_done) only when its MMA burst has completed
 void gemm_next_trigger_late(int at_mma_done);
+// prefill attention (Tq > 1) with the pair's K / V staged in shared memory (fast_attn_prefill.cu)
+bool attention_prefill_supported(int dtype, int d, int Tq, int ctx_max);
+int attention_prefill(const void* q, const void* ck, const void* cv, int dtype, int B, int heads, int Tq, int c_stride,
+                      int ctx_base, const int* ctx_dyn, int ctx_max, int causal, const int* key_mask, int mask_len,
+                      void* out, cudaStream_t st);
 bool fast_layernorm_supported(int H);
 // y = act(sum of S split-K partial slices) as bf16 (fast_misc.cu)
 int partial_act_fast(const float* part, int S, int64_t part_stride, int rows, int N, int act, void* y,

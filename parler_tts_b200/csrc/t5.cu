@@ -90,6 +90,67 @@ t5_attention_kernel(const T* __restrict__ qkv, const int32_t* __restrict__ mask,
   }
 }
 
+// The same arithmetic with the K and V rows of (b, head) staged in shared memory once per CTA: K transposed [dkv][S + 1]
+// (lanes = keys read consecutive words), V row-major [S][dkv] (lanes = dims), both already converted to float.  One CTA
+// per (head, b), warp w takes queries w, w + NW, ...; every dot product and every P.V sum runs in the order of the kernel
+// above, so the results are bit-identical - the 2-byte strided global loads (455 us per launch at B=64, S=48, 58 % of
+// the encoder) become shared-memory reads.  Used when the staged rows fit (S <= ~380 at dkv = 64).
+template <typename T, int NW>
+__global__ void __launch_bounds__(NW * 32)
+t5_attention_staged_kernel(const T* __restrict__ qkv, const int32_t* __restrict__ mask, const float* __restrict__ rel_bias,
+                           const int32_t* __restrict__ bucket_of, int max_rel, int S, int heads, int dkv,
+                           T* __restrict__ out) {
+  extern __shared__ float sm[];
+  const int warp = threadIdx.x >> 5, lane = threadIdx.x & 31;
+  const int hd = blockIdx.x, b = blockIdx.y;
+  const int inner = heads * dkv, SP = S + 1;
+  float* kt = sm;                       // [dkv][SP]
+  float* vs = kt + (size_t)dkv * SP;    // [S][dkv]
+  float* qs = vs + (size_t)S * dkv + warp * (dkv + S);  // per warp: [dkv] query, [S] scores
+  float* sc = qs + dkv;
+  const T* base = qkv + (int64_t)b * S * 3 * inner + hd * dkv;
+  for (int e = threadIdx.x; e < S * dkv; e += NW * 32) {
+    const int j = e / dkv, d = e - j * dkv;
+    const T* row = base + (int64_t)j * 3 * inner;
+    kt[d * SP + j] = to_f(row[inner + d]);
+    vs[e] = to_f(row[2 * inner + d]);
+  }
+  __syncthreads();
+  const float neg = finfo_min<T>();
+  for (int i = warp; i < S; i += NW) {
+    for (int d = lane; d < dkv; d += 32) qs[d] = to_f(base[(int64_t)i * 3 * inner + d]);
+    __syncwarp();
+    float lmax = -INFINITY;
+    for (int j = lane; j < S; j += 32) {
+      float dot = 0.f;
+      for (int d = 0; d < dkv; ++d) dot = fmaf(qs[d], kt[d * SP + j], dot);
+      int rel = j - i;
+      rel = rel < -max_rel ? -max_rel : (rel > max_rel ? max_rel : rel);
+      float pb = to_f(from_f<T>(rel_bias[bucket_of[rel + max_rel] * heads + hd]));
+      if (mask && mask[(int64_t)b * S + j] == 0) pb = to_f(from_f<T>(pb + neg));
+      const float sv = to_f(from_f<T>(to_f(from_f<T>(dot)) + pb));
+      sc[j] = sv;
+      lmax = fmaxf(lmax, sv);
+    }
+    lmax = warp_max(lmax);
+    float lsum = 0.f;
+    for (int j = lane; j < S; j += 32) {
+      const float e = expf(sc[j] - lmax);
+      sc[j] = e;
+      lsum += e;
+    }
+    lsum = warp_sum(lsum);
+    __syncwarp();
+    const float inv = 1.0f / lsum;
+    for (int d = lane; d < dkv; d += 32) {
+      float acc = 0.f;
+      for (int j = 0; j < S; ++j) acc = fmaf(to_f(from_f<T>(sc[j] * inv)), vs[j * dkv + d], acc);
+      out[((int64_t)b * S + i) * inner + hd * dkv + d] = from_f<T>(acc);
+    }
+    __syncwarp();  // the next query overwrites qs / sc
+  }
+}
+
 // g = T(act(a)) * b over rows of [a | b] (wi_0 | wi_1), modeling_t5.py:116-118
 template <typename T>
 __global__ void t5_gated_act_kernel(const T* __restrict__ ab, int64_t rows, int F, int act, T* __restrict__ g) {
@@ -144,6 +205,12 @@ int t5_encode_t(const PttsT5* m, const int64_t* ids, const int32_t* mask, int B,
   PTTS_CHECK_ARG(att_smem <= 200 * 1024, "t5_encode: sequence too long for the score buffer");
   if (att_smem > 48 * 1024)
     cudaFuncSetAttribute(t5_attention_kernel<T, QW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)att_smem);
+  // K / V of a (b, head) staged in shared memory when they fit (fast family; the simple family keeps the plain kernel)
+  constexpr int SNW = 8;
+  const size_t staged_smem = ((size_t)dkv * (S + 1) + (size_t)S * dkv + (size_t)SNW * (dkv + S)) * sizeof(float);
+  const bool staged = impl == PTTS_IMPL_FAST && staged_smem <= 200 * 1024;
+  if (staged && staged_smem > 48 * 1024)
+    cudaFuncSetAttribute(t5_attention_staged_kernel<T, SNW>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)staged_smem);
   t5_embed_kernel<<<rows, 192, 0, st>>>(ids, m->embed, m->vocab, D, w.h);
   PTTS_CHECK_LAUNCH("t5_embed");
   for (int l = 0; l < m->n_layers; ++l) {
@@ -151,9 +218,14 @@ int t5_encode_t(const PttsT5* m, const int64_t* ids, const int32_t* mask, int B,
     t5_rmsnorm_kernel<T><<<rows, 256, 0, st>>>(w.h, L.ln0, D, m->eps, reinterpret_cast<T*>(w.xn));
     PTTS_CHECK_LAUNCH("t5_rmsnorm");
     PTTS_TRY(t5_linear(impl, w.xn, L.w_qkv, dt, rows, 3 * inner, D, PTTS_ACT_NONE, nullptr, w.qkv, dt, st));
-    t5_attention_kernel<T, QW><<<dim3((S + QW - 1) / QW, heads, B), QW * 32, att_smem, st>>>(
-        reinterpret_cast<const T*>(w.qkv), mask, m->rel_bias, m->bucket_of, m->max_rel, S, heads, dkv,
-        reinterpret_cast<T*>(w.attn));
+    if (staged)
+      t5_attention_staged_kernel<T, SNW><<<dim3(heads, B), SNW * 32, staged_smem, st>>>(
+          reinterpret_cast<const T*>(w.qkv), mask, m->rel_bias, m->bucket_of, m->max_rel, S, heads, dkv,
+          reinterpret_cast<T*>(w.attn));
+    else
+      t5_attention_kernel<T, QW><<<dim3((S + QW - 1) / QW, heads, B), QW * 32, att_smem, st>>>(
+          reinterpret_cast<const T*>(w.qkv), mask, m->rel_bias, m->bucket_of, m->max_rel, S, heads, dkv,
+          reinterpret_cast<T*>(w.attn));
     PTTS_CHECK_LAUNCH("t5_attention");
     PTTS_TRY(t5_linear(impl, w.attn, L.w_o, dt, rows, D, inner, PTTS_ACT_NONE, w.h, w.h, PTTS_F32, st));
     t5_rmsnorm_kernel<T><<<rows, 256, 0, st>>>(w.h, L.ln1, D, m->eps, reinterpret_cast<T*>(w.xn));

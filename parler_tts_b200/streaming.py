@@ -60,15 +60,18 @@ class AudioChunkStreamer:
         self.to_host = bool(to_host)
         self.timeout = timeout
         self.queue = queue.Queue()
-        self.stats = []  # one dict per chunk: first_frame, frames, steps_enqueued (decode steps queued when it was handed over)
+        # one dict per chunk: first_frame, samples, steps_enqueued (decode steps the host had queued when the chunk was
+        # handed over), decode_queued_at (decode steps queued when the chunk's de-delay + DAC decode were enqueued on
+        # the second stream; None for the remainder decoded after the loop)
+        self.stats = []
         self._stop = object()
 
     def put(self, value):  # token ids of the reference's streamer protocol: not needed, the path de-delays on the device
         pass
 
-    def put_audio(self, first_frame, audio, steps_enqueued=None):
-        self.stats.append(dict(first_frame=int(first_frame), frames=None, samples=int(audio.shape[-1]),
-                               steps_enqueued=steps_enqueued))
+    def put_audio(self, first_frame, audio, steps_enqueued=None, decode_queued_at=None):
+        self.stats.append(dict(first_frame=int(first_frame), samples=int(audio.shape[-1]),
+                               steps_enqueued=steps_enqueued, decode_queued_at=decode_queued_at))
         if self.on_chunk is not None:
             self.on_chunk(first_frame, audio)
         self.queue.put((first_frame, audio))
@@ -147,11 +150,11 @@ class ChunkPipeline:
             flag.copy_(bad.to(torch.int32).reshape(1), non_blocking=True)
             done = torch.cuda.Event()
             done.record(self.side)
-        self.pending.append((f0, f1, host, flag, done))
+        self.pending.append((f0, f1, host, flag, done, self.steps_enqueued))
 
     def _poll(self, block):
         while self.pending:
-            f0, f1, host, flag, done = self.pending[0]
+            f0, f1, host, flag, done, queued_at = self.pending[0]
             if block:
                 done.synchronize()
             elif not done.query():
@@ -163,7 +166,7 @@ class ChunkPipeline:
                 self.stopped = True  # later windows are dropped; finish() decodes the remainder the reference's way
                 continue
             out = host if host is not None else self.audio[:, f0 * self.hop : f1 * self.hop]
-            self.streamer.put_audio(f0, out, self.steps_enqueued)
+            self.streamer.put_audio(f0, out, self.steps_enqueued, queued_at)
             self.emitted_f = f1
 
     # ---- after the loop

@@ -77,6 +77,32 @@ def test_activation_gemm_full_k_vs_torch_fp32(M, N, K):
     assert float((y.float() - torch.nn.functional.gelu(ref)).abs().max()) < 1e-2 * float(ref.abs().max())
 
 
+@pytest.mark.parametrize("kw", [dict(do_sample=False), dict(do_sample=True, top_k=20, temperature=0.9, seed=7),
+                                dict(do_sample=False, guidance_scale=2.0)])
+def test_fused_step_heads_partials_equal_materialised_logits(kw):
+    """Captured decode step at B=64: the 9 lm_heads run as split-K partial sums that the epilogue kernel folds while it
+    reads them; the step-at-a-time host loop (stopping criteria present) materialises the logits matrix with the STORE
+    GEMM and runs the same epilogue on it.  Same K slices, same summation order: the tokens must be identical."""
+    kw2 = dict(vocab_size=1088, hidden_size=1024, num_hidden_layers=2, num_attention_heads=16, ffn_dim=4096,
+               num_codebooks=9, max_position_embeddings=128, pad_token_id=1024, eos_token_id=1024, bos_token_id=1025)
+    dims = decoder_oracle.DecoderDims(**kw2)
+    sd = decoder_oracle.random_decoder_state(dims, seed=5)
+    m = ptts.ParlerTTSForCausalLM(ptts.ParlerTTSDecoderConfig(**kw2), state_dict=sd).to(DEV).to(torch.bfloat16)
+    m.impl = cabi.IMPL_FAST
+    g = torch.Generator().manual_seed(1)
+    B = 64
+    nb = 2 * B if "guidance_scale" in kw else B
+    enc = (torch.randn(nb, 12, 1024, generator=g) * 0.3).to(DEV)
+    prm = (torch.randn(B, 6, 1024, generator=g) * 0.02).to(DEV)
+    procs = [ptts.SuppressTokensAtOrAbove(1024)]
+    fused = m.generate(encoder_hidden_states=enc, prompt_hidden_states=prm, max_length=40, logits_processor=procs, **kw)
+    never = [lambda ids, scores: False]
+    stepwise = m.generate(encoder_hidden_states=enc, prompt_hidden_states=prm, max_length=40, logits_processor=procs,
+                          stopping_criteria=never, **kw)
+    assert fused.shape == stepwise.shape == (B, 9, 40 - 9)
+    assert torch.equal(fused, stepwise)
+
+
 def _attention(q, ck, cv, ctx, key_mask, impl):
     B, heads, c_stride, d = ck.shape
     out = torch.empty(B, heads * d, device=DEV, dtype=q.dtype)
