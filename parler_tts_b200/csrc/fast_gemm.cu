@@ -163,6 +163,13 @@ int gemm_bf16_store(const void* x, const void* w, int M, int N, int K, float alp
   p.M = M; p.N = N; p.K = K; p.k_per_split = K;
   p.alpha = alpha; p.act = act; p.bias = bias; p.residual = residual; p.row_mask = row_mask; p.y = y;
   p.ydtype = ydtype;
+#ifndef PTTS_GEMM_BIG
+#define PTTS_GEMM_BIG 1
+#endif
+  if (PTTS_GEMM_BIG && gemm_mode() == 2 && M >= 256) {  // prefill / T5 / cross-KV sizes: the plain tile kernel
+    const int rc = big_gemm_store(p, st);
+    if (rc != PTTS_E_UNSUPPORTED) return rc;
+  }
   if (gemm_mode() == 2) {
     const int rc = umma_gemm_store(p, st);
     if (rc != PTTS_E_UNSUPPORTED) return rc;
@@ -180,6 +187,10 @@ int gemm_bf16_scatter(const void* x, const void* w, int M, int N, int K, int has
   p.q = (__nv_bfloat16*)q; p.ck = (__nv_bfloat16*)ck; p.cv = (__nv_bfloat16*)cv;
   p.H = H; p.heads = heads; p.d = d; p.Tq = Tq; p.c_stride = c_stride; p.pos_base = pos_base; p.pos_dyn = pos_dyn;
   p.has_q = has_q; p.q_scale = q_scale;
+  if (PTTS_GEMM_BIG && gemm_mode() == 2 && M >= 256) {
+    const int rc = big_gemm_scatter(p, st);
+    if (rc != PTTS_E_UNSUPPORTED) return rc;
+  }
   if (gemm_mode() == 2) {
     const int rc = umma_gemm_scatter(p, st);
     if (rc != PTTS_E_UNSUPPORTED) return rc;

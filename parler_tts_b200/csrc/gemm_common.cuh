@@ -85,6 +85,9 @@ bool tensor_map_2d_dt(const void* ptr, int rows, int cols, int box_rows, int dty
 bool tensor_map_3d(const void* ptr, int rows, int cols, int box_rows, int box_kb, CUtensorMap* out);
 bool tma_available();  // the driver entry point for tensor-map creation was found
 
+// plain 128 x 128 tile kernel for M >= 256 (fast_gemm_big.cu: prefill, cross K/V, T5)
+int big_gemm_store(const GemmParams& p, cudaStream_t st);
+int big_gemm_scatter(const GemmParams& p, cudaStream_t st);
 // tcgen05 swap-AB cluster split-K kernel (fast_gemm3.cu)
 int umma_gemm_store(const GemmParams& p, cudaStream_t st);
 int umma_gemm_scatter(const GemmParams& p, cudaStream_t st);

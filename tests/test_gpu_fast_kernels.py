@@ -54,6 +54,30 @@ def test_skinny_gemm_vs_torch_fp32(M, N, K):
     assert float((simple - ref).abs().max()) < tol
 
 
+@pytest.mark.parametrize("M,N,K", [(2112, 3072, 1024), (3072, 2304, 768), (3072, 768, 2048), (256, 130, 64),
+                                   (1000, 1024, 4096), (257, 9792, 1024)])
+def test_large_m_tile_gemm_vs_torch_fp32(M, N, K):
+    """fast_gemm_big.cu (M >= 256: prompt prefill, cross K/V, T5 encoder shapes; ragged last tiles in M and N): persistent
+    128 x 128 tcgen05 tiles with the fused STORE epilogue."""
+    g = torch.Generator().manual_seed(M + 3 * N + K)
+    x = (torch.randn(M, K, generator=g) * 0.5).to(DEV, torch.bfloat16)
+    w = (torch.randn(N, K, generator=g) * 0.05).to(DEV, torch.bfloat16)
+    ref = x.float() @ w.float().t()
+    got = _linear(x, w)
+    assert float((got - ref).abs().max()) < 2e-3 * float(ref.abs().max())
+    bias = torch.randn(N, generator=g).to(DEV)
+    rm = (torch.rand(M, generator=g) > 0.3).to(DEV, torch.int32)
+    res = torch.randn(M, N, generator=g).to(DEV)
+    want = torch.nn.functional.gelu(0.125 * ref + bias) * rm[:, None] + res
+    got = _linear(x, w, bias=bias, alpha=0.125, act=cabi.ACT["gelu"], residual=res.clone(), row_mask=rm)
+    assert float((got - want).abs().max()) < 2e-3 * float(want.abs().max()) + 1e-3
+    got16 = _linear(x, w, bias=bias, ydtype=torch.bfloat16)
+    assert float((got16.float() - (ref + bias)).abs().max()) < 1e-2 * float((ref + bias).abs().max())
+    # twice in a row (persistent CTAs, barrier phases start from scratch in every launch)
+    again = _linear(x, w)
+    assert float((again - ref).abs().max()) < 2e-3 * float(ref.abs().max())
+
+
 @pytest.mark.parametrize("M,N,K", [(64, 4096, 1024), (64, 256, 512), (128, 1024, 768), (64, 64, 256)])
 def test_activation_gemm_full_k_vs_torch_fp32(M, N, K):
     """fc1 shape family of fast_gemm_act.cu (tcgen05 M = 64 tiles over the whole K, activation in the epilogue; K = 1024
