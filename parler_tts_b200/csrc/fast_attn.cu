@@ -190,8 +190,11 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
       l2_prefetch_range(cv + (((int64_t)b * heads + hd) * c_stride + j0) * D, (int64_t)min(n, old_end - j0) * D * sizeof(T));
     if (!LEAN && qf.pf_next && sp == 0 && !qf.pf_late) prefetch_next();
   }
+#ifndef PTTS_DFLT_ATTN_LATE
+#define PTTS_DFLT_ATTN_LATE 0
+#endif
   pdl_wait();
-  pdl_launch();
+  if (PTTS_DFLT_ATTN_LATE == 0) pdl_launch();
   tl_dep(tl);
   // pf_late (opt-in, measured slower): prefetch only after the producer GEMM (cross q projection) has finished
   if constexpr (FUSED)
@@ -288,6 +291,7 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
     for (int u = 0; u < U; ++u) cur[u] = nxt[u];
   }
   if (!pre_v) load_batch(cur, vb, j0);  // first V rows travel while the block reduces max / sum (pre_v: cur = nxt)
+  if (PTTS_DFLT_ATTN_LATE == 1) pdl_launch();  // variant builds: release the dependent after the K pass
   lmax = warp_max(lmax);
   if (lane == 0) red[warp] = lmax;
   __syncthreads();

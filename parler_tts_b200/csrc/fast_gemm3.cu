@@ -471,8 +471,9 @@ umma_partial_lean_kernel(float* __restrict__ part, int M, int N, int late, const
   __syncthreads();  // barrier inits and the TMEM base address are visible to everybody - still in front of the wait
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
   const uint32_t tmem_d = tmem_base_slot;
+  if (late == 2) pdl_launch();  // before the own wait (diagnostic / variant builds only)
   pdl_wait();
-  if (!late) pdl_launch();
+  if (late == 0) pdl_launch();
   if (warp == 1 && elect_one()) {
     const uint32_t a0 = ((sw >> 4) & 0x3FFFu) | (1u << 16), b0 = ((sx >> 4) & 0x3FFFu) | (1u << 16);
     // all expectations first, then the copies back to back (an arrive between two copies delays the second)
@@ -498,7 +499,7 @@ umma_partial_lean_kernel(float* __restrict__ part, int M, int N, int late, const
   __syncwarp();
   mbar_wait3(mma_bar, 0);
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
-  if (late) pdl_launch();
+  if (late == 1) pdl_launch();
   // split-K partial sums straight to global memory [slice][m][n] (coalesced along n); the consumer folds them in slice
   // order.  Thread (warp w, lane l) owns weight row n0 + 32 w + l and its 64 batch-row columns.
   const int n = n0 + warp * 32 + lane;
@@ -671,7 +672,10 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const int dbg = PTTS_KNOB("PTTS_GEMM_DBG", 0);
   // with cp.async slabs the early release won (1.727 against 1.748 ms per decode step); with TMA slabs the slab needs
   // ~1.5 us of lead only and the late release wins (1.486 against 1.496 ms) -> late
-  const int early = PTTS_KNOB("PTTS_PDL_EARLY", 0) ? 16 : 0;
+  #ifndef PTTS_DFLT_PDL_EARLY
+#define PTTS_DFLT_PDL_EARLY 0
+#endif
+  const int early = PTTS_KNOB("PTTS_PDL_EARLY", PTTS_DFLT_PDL_EARLY) ? 16 : 0;
   int early_now = early;
   if (EPI == EPI_PARTIAL && g_late_once) {
     early_now = g_late_once == 2 ? 128 : 0;
@@ -698,7 +702,10 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     CUtensorMap t3w, t3x;
     if (tensor_map_2d_any(p.W, p.N, p.K, UM, PTTS_BF16, &t3w, kb / 2) &&
         tensor_map_2d_any(p.X, p.M, p.K, UN, PTTS_BF16, &t3x, kb % PTTS_GEMM_XPARTS == 0 ? kb / PTTS_GEMM_XPARTS : kb)) {
-      const int late = (dbg_arg & 128) ? 1 : 0;
+      #ifndef PTTS_DFLT_GEMM_LATE
+#define PTTS_DFLT_GEMM_LATE 0
+#endif
+      const int late = (dbg_arg & 16) ? 2 : ((dbg_arg & 128) || PTTS_DFLT_GEMM_LATE) ? 1 : 0;
       cudaError_t e2 = kb == 8   ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<8>, p.part, p.M, p.N, late, t3w, t3x)
                        : kb == 6 ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<6>, p.part, p.M, p.N, late, t3w, t3x)
                                  : cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<4>, p.part, p.M, p.N, late, t3w, t3x);
@@ -763,7 +770,10 @@ int umma_plan_splits(int M, int N, int K) {
   const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
   // CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold): with TMA slab loads fewer, larger CTAs
   // win, 30 -> 16 measured 1.654 -> 1.559 ms per step
-  const int target = PTTS_KNOB("PTTS_SPLIT_TARGET", 16);
+  #ifndef PTTS_DFLT_SPLIT_TARGET
+#define PTTS_DFLT_SPLIT_TARGET 16
+#endif
+  const int target = PTTS_KNOB("PTTS_SPLIT_TARGET", PTTS_DFLT_SPLIT_TARGET);
   // 64-element k-blocks per CTA (8 = 128 KB of W per CTA; 4 = 64 KB measured slower, 1.630 against 1.497 ms)
   int kbmax = PTTS_KNOB("PTTS_KBMAX", kMaxKB64);
   if (kbmax < 1 || kbmax > kMaxKB64) kbmax = kMaxKB64;
