@@ -246,7 +246,7 @@ def run_cuda(args):
         eng.prefill(st, table, prompt_ids)
         e0, e1 = ev(), ev()
         e0.record()
-        eng.run_loop(st, use_graph=not args.no_graph, poll_every=64)
+        eng.run_loop(st, use_graph=not args.no_graph, poll_every=64, steps_per_graph=args.steps_per_graph)
         e1.record()
         cabi.call("ptts_dedelay", cabi.ptr(st.ids), M, cabi.ptr(st.mask), M, B, K, M, cabi.ptr(codes),
                   cabi.stream_ptr())
@@ -453,6 +453,8 @@ def main():
     ap.add_argument("--check-steps", type=int, default=40, help="token columns re-derived eagerly after the timed region")
     ap.add_argument("--skip-check", action="store_true")
     ap.add_argument("--no-graph", action="store_true")
+    ap.add_argument("--steps-per-graph", type=int, default=None,
+                    help="decode steps per CUDA-graph replay (default: the engine's, DecoderEngine.steps_per_graph)")
     ap.add_argument("--do-sample", action="store_true", help="top-k 50 sampling instead of greedy (configs[1] wording)")
     ap.add_argument("--arch", default="mini", choices=["mini", "scaled"])
     ap.add_argument("--skip-e2e", action="store_true")

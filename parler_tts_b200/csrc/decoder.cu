@@ -170,7 +170,7 @@ static bool qkv_fusion_enabled() { return PTTS_KNOB("PTTS_QKV_FUSE", 1) != 0; }
 static bool fc1_partials_enabled() { return PTTS_KNOB("PTTS_FC1_PARTIALS", 1) != 0; }
 
 // PTTS_SKIP=<bitmask>: timing ablation ONLY (results are garbage): 1 LayerNorm, 2 QKV GEMM, 4 self-attention,
-// 8 residual GEMMs, 16 cross q GEMM, 32 cross-attention, 64 fc1, 128 heads.  Used by profiles/scripts/ablate.sh to get
+// 8 residual GEMMs, 16 cross q GEMM, 32 cross-attention, 64 fc1, 128 heads, 256 the one-launch cross-attention block.  Used by profiles/scripts/ablate.sh to get
 // the marginal cost of each kernel class inside the PDL-overlapped graph (ncu serialises launches and cannot).
 // Compiled into the DIAGNOSTIC library only (make DIAG=1): the product library always runs every kernel.
 #ifdef PTTS_DIAG
@@ -294,8 +294,9 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
       // per-head slices stored [B][heads][H]: the next LayerNorm pulls a row's slices with one bulk copy (diagnostic
       // build, PTTS_XB_ROWOUT=0: [heads][B][H] folded with strided loads)
       const int by_row = PTTS_KNOB("PTTS_XB_ROWOUT", 1) && (int64_t)heads * H * 4 <= 160 * 1024;
-      PTTS_TRY(xblock_fast(s->h, pend.part, pend.S, pend.stride, L.ln2_g, L.ln2_b, 1e-5f, L.w_qc, L.w_oc, kc, vc,
-                           s->enc_mask, B, heads, H, s->S, scale, xout, by_row, nullptr, 0, 0, nullptr, st));
+      PTTS_UNLESS_SKIPPED(256, xblock_fast(s->h, pend.part, pend.S, pend.stride, L.ln2_g, L.ln2_b, 1e-5f, L.w_qc, L.w_oc,
+                                           kc, vc, s->enc_mask, B, heads, H, s->S, scale, xout, by_row, nullptr, 0, 0,
+                                           nullptr, st));
       if (by_row) {
         pend.rowblk = xout;
         pend.n_blk = heads;

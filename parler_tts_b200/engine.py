@@ -162,6 +162,7 @@ class GenState:
         self.c_state = s
         self.seed = int(seed) & 0xFFFFFFFFFFFFFFFF
         self.graph, self.graph_launches, self.replays = None, 0, 0
+        self.graph_multi, self.steps_per_graph = None, 1  # optional second graph holding several consecutive steps
         self._ctrl_host = torch.zeros(8, dtype=torch.int32).pin_memory() if dev.type == "cuda" else None
 
     # ---- control block helpers
@@ -189,6 +190,8 @@ class GenState:
 
 
 class DecoderEngine:
+    steps_per_graph = 1  # decode steps per CUDA-graph replay of run_loop (see capture_multi)
+
     def __init__(self, weights: DecoderWeights):
         self.weights = weights
         self.lib = cabi.load()
@@ -233,7 +236,22 @@ class DecoderEngine:
         st.graph = g
         return g
 
-    def run_loop(self, st: GenState, use_graph=True, poll_every=16, max_steps=None, on_progress=None):
+    def capture_multi(self, st: GenState, steps):
+        """A second graph of `steps` consecutive decode steps (the position counter lives on the device, so the steps
+        of one replay advance like separate replays): removes the graph-to-graph hand-over between them.  Within the
+        graph every kernel still waits (griddepcontrol.wait) for the one before it, the epilogue never releases its
+        dependent early, so no kernel of step i + 1 can read the counter before step i's epilogue has written it."""
+        if st.graph_multi is not None and st.steps_per_graph == steps:
+            return st.graph_multi
+        g = torch.cuda.CUDAGraph()
+        with torch.cuda.graph(g):
+            for _ in range(steps):
+                self.step(st)
+        st.graph_multi, st.steps_per_graph = g, steps
+        return g
+
+    def run_loop(self, st: GenState, use_graph=True, poll_every=16, max_steps=None, on_progress=None,
+                 steps_per_graph=None):
         """Runs decode steps until the control block says done (or max_steps).  Returns the control block.
         on_progress(steps): called on the host after every batch of enqueued steps (streaming.ChunkPipeline hangs the
         overlapped chunk decode here); it must not synchronise with the loop's stream."""
@@ -247,10 +265,17 @@ class DecoderEngine:
                 self.step(st)
                 done_steps = 1
             g = self.capture(st)
+        U = int(steps_per_graph if steps_per_graph is not None else self.steps_per_graph)
+        gm = self.capture_multi(st, U) if (g is not None and U > 1) else None
         ev = None
         while done_steps < budget:
             n = min(poll_every, budget - done_steps)
-            for _ in range(n):
+            left = n
+            while gm is not None and left >= U:  # whole multi-step graphs first, single steps for the remainder
+                gm.replay()
+                st.replays += U
+                left -= U
+            for _ in range(left):
                 if g is not None:
                     g.replay()
                     st.replays += 1
