@@ -104,6 +104,22 @@ __device__ __forceinline__ void tmem_ld16b(uint32_t taddr, uint32_t (&v)[16]) {
       : "memory");
 }
 
+// 32-byte accesses (LDG.256 / STG.256, sm_100): a lane moves a whole 32-byte sector of its row per instruction - the
+// fp32 rows of the epilogue are 64 bytes per (time step, 16-channel group), i.e. two instructions instead of four
+#ifndef PTTS_DAC_WIDE
+#define PTTS_DAC_WIDE 1
+#endif
+__device__ __forceinline__ void ld_f8(const float* p, float4& a, float4& b) {
+  asm volatile("ld.global.v8.f32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
+               : "=f"(a.x), "=f"(a.y), "=f"(a.z), "=f"(a.w), "=f"(b.x), "=f"(b.y), "=f"(b.z), "=f"(b.w)
+               : "l"(p));
+}
+__device__ __forceinline__ void st_f8(float* p, const float4& a, const float4& b) {
+  asm volatile("st.global.v8.f32 [%0], {%1,%2,%3,%4,%5,%6,%7,%8};\n" ::"l"(p), "f"(a.x), "f"(a.y), "f"(a.z), "f"(a.w),
+               "f"(b.x), "f"(b.y), "f"(b.z), "f"(b.w)
+               : "memory");
+}
+
 struct Tile {
   int b, m0, n0, nt;
 };
@@ -206,9 +222,16 @@ __global__ void __launch_bounds__(NTHR, 1) dac_conv_ws_kernel(const ConvParams3 
         bool ok;
         locate(gi, to, co, ok);
 #pragma unroll
-        for (int i = 0; i < 4; ++i) {
-          res[i] = make_float4(0.f, 0.f, 0.f, 0.f);
-          if (resb && ok) res[i] = *reinterpret_cast<const float4*>(resb + (int64_t)to * p.Cout + co + 4 * i);
+        for (int i = 0; i < 4; ++i) res[i] = make_float4(0.f, 0.f, 0.f, 0.f);
+        if (resb && ok) {
+          const float* rp = resb + (int64_t)to * p.Cout + co;
+          if (PTTS_DAC_WIDE) {
+            ld_f8(rp, res[0], res[1]);
+            ld_f8(rp + 8, res[2], res[3]);
+          } else {
+#pragma unroll
+            for (int i = 0; i < 4; ++i) res[i] = *reinterpret_cast<const float4*>(rp + 4 * i);
+          }
         }
       };
       fetch_res(g_first);  // the residual rows do not depend on the accumulator: request them before waiting for it
@@ -237,10 +260,15 @@ __global__ void __launch_bounds__(NTHR, 1) dac_conv_ws_kernel(const ConvParams3 
             o[4 * i + 3] = __uint_as_float(v[4 * i + 3]) + bb.w + r[i].w;
           }
           if (yb) {
+            float* yp = yb + (int64_t)to * p.Cout + co;
+            if (PTTS_DAC_WIDE) {
+              st_f8(yp, make_float4(o[0], o[1], o[2], o[3]), make_float4(o[4], o[5], o[6], o[7]));
+              st_f8(yp + 8, make_float4(o[8], o[9], o[10], o[11]), make_float4(o[12], o[13], o[14], o[15]));
+            } else {
 #pragma unroll
-            for (int i = 0; i < 4; ++i)
-              *reinterpret_cast<float4*>(yb + (int64_t)to * p.Cout + co + 4 * i) =
-                  make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+              for (int i = 0; i < 4; ++i)
+                *reinterpret_cast<float4*>(yp + 4 * i) = make_float4(o[4 * i], o[4 * i + 1], o[4 * i + 2], o[4 * i + 3]);
+            }
           }
           if (p.y_planes) {
             // the consumer's Snake and hi/mid split, written as two 8-channel panels per plane: lanes are consecutive
