@@ -71,43 +71,10 @@ template <> struct Chunk<float> {
   }
 };
 
-// 32-byte chunks (ld.global.v8, LDG.256 - new with sm_100): a bf16 key row is covered by 4 threads instead of 8, a warp
-// instruction moves 8 rows (1 KB) instead of 4; two loads of 32 bytes in flight per thread and batch instead of four of 16
-struct Raw32 {
-  uint4 lo, hi;
-};
-template <typename T, bool WIDE> struct ChunkSel : Chunk<T> {
-  using Raw = uint4;
-  static constexpr int U = 4;
-};
-template <> struct ChunkSel<__nv_bfloat16, true> {
-  using Raw = Raw32;
-  static constexpr int E = 16;
-  static constexpr int U = 2;
-  static __device__ __forceinline__ Raw32 load_raw(const __nv_bfloat16* p) {
-    Raw32 r;
-    asm volatile("ld.global.cg.v8.u32 {%0,%1,%2,%3,%4,%5,%6,%7}, [%8];\n"
-                 : "=r"(r.lo.x), "=r"(r.lo.y), "=r"(r.lo.z), "=r"(r.lo.w), "=r"(r.hi.x), "=r"(r.hi.y), "=r"(r.hi.z), "=r"(r.hi.w)
-                 : "l"(p));
-    return r;
-  }
-  static __device__ __forceinline__ void unpack(const Raw32& r, float (&f)[16]) {
-    const __nv_bfloat162* h = reinterpret_cast<const __nv_bfloat162*>(&r);
-#pragma unroll
-    for (int i = 0; i < 8; ++i) {
-      const float2 t = __bfloat1622float2(h[i]);
-      f[2 * i] = t.x;
-      f[2 * i + 1] = t.y;
-    }
-  }
-  static __device__ __forceinline__ void load(const __nv_bfloat16* p, float (&f)[16]) {
-    Raw32 r;
-    r.lo = __ldcg(reinterpret_cast<const uint4*>(p));
-    r.hi = __ldcg(reinterpret_cast<const uint4*>(p) + 1);
-    unpack(r, f);
-  }
-};
-
+// (32-byte chunks - ld.global.v8 / LDG.256, new with sm_100: 4 threads per bf16 key row, two 32-byte loads in flight per
+// thread and batch instead of four of 16 - were measured in this kernel on B200 at B=64, 860 frames: 1.2832 / 1.2845
+// against 1.2203 / 1.2212 ms per decode step, same box; removed.  The DAC conv epilogue keeps its 32-byte row accesses:
+// 138.9 against 147 - 151 ms for 32 x 860 frames, profiles/r02_wide_access.txt.)
 // Optional fused prologue: the q (and, for self-attention, the new k / v) projections arrive as split-K partial sums
 // [S][rows][ncols] of the tcgen05 GEMM; the CTA of (b, head) adds them up in slice order (deterministic), scales q,
 // writes the new K / V row into its static-cache slot (replaces torch.cat, modeling_parler_tts.py:303-304) and goes on -
@@ -138,7 +105,7 @@ struct QFuse {
 // the instantiation the decode step launches by default (see the note on one-shot code size in fast_gemm3.cu).
 // PLAIN (lean launches without a key mask and without a KV split): the mask test leaves the K pass and the split
 // bookkeeping leaves the epilogue
-template <typename T, int D, bool FUSED, bool LEAN = false, bool PLAIN = false, bool WIDE = false>
+template <typename T, int D, bool FUSED, bool LEAN = false, bool PLAIN = false>
 __global__ void __launch_bounds__(NT, FUSED ? 7 : 8)  // 7 x 148 = 1036 CTA slots >= 64 x 16 (b, head) pairs
 attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict__ ck, const T* __restrict__ cv, int heads, int c_stride,
                    int ctx_base, const int* __restrict__ ctx_dyn, const int* __restrict__ key_mask_in, int mask_len,
@@ -148,13 +115,10 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   const int stage_cap = LEAN ? 0 : stage_cap_in;
   TL tl = tl_in;
   if constexpr (LEAN) tl.p = nullptr;
-  using CH = ChunkSel<T, WIDE>;
-  using Raw = typename CH::Raw;
-  constexpr int E = CH::E;           // elements per chunk (16 bytes; 32 bytes in the WIDE instantiation)
-  constexpr int CB = E * (int)sizeof(T);
+  constexpr int E = Chunk<T>::E;     // elements per 16-byte chunk
   constexpr int TPK = D / E;         // threads per key row
   constexpr int KPB = NT / TPK;      // key rows per CTA pass
-  constexpr int U = CH::U;           // independent loads in flight per thread
+  constexpr int U = 4;               // independent loads in flight per thread
   constexpr int ROWB = D * (int)sizeof(T);  // bytes per cache row
   __shared__ __align__(16) T qs[D];
   extern __shared__ float sm[];
@@ -179,14 +143,14 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   };
   // Loads are software-pipelined: the next batch of U rows per thread is requested before the current one is
   // consumed, and the first V batch is requested before the softmax reductions, so HBM never idles behind a barrier.
-  auto load_batch = [&](Raw (&raw)[U], const T* base_ptr, int base) {
+  auto load_batch = [&](uint4 (&raw)[U], const T* base_ptr, int base) {
 #pragma unroll
     for (int u = 0; u < U; ++u) {
       const int j = base + u * KPB + g;
-      if (j < j1) raw[u] = CH::load_raw(base_ptr + (int64_t)j * D);
+      if (j < j1) raw[u] = Chunk<T>::load_raw(base_ptr + (int64_t)j * D);
     }
   };
-  Raw cur[U], nxt[U];
+  uint4 cur[U], nxt[U];
   bool pre_k = false, pre_v = false;
   int staged = 0;
   auto prefetch_next = [&]() {
@@ -208,7 +172,7 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
     const int old_end = qf.has_kv ? dyn_value(qf.slot_base, qf.slot_dyn) : ctx;
     // Self-attention: while the QKV GEMM still runs, the first `staged` (immutable) K rows of this CTA travel into
     // shared memory with cp.async - that share of the stream no longer sits behind the dependency.
-    if (!WIDE && stage_cap > 0 && qf.has_kv) {
+    if (stage_cap > 0 && qf.has_kv) {
       staged = min(stage_cap, max(min(j1, old_end) - j0, 0) / (KPB * U) * (KPB * U));
       const uint32_t dst0 = smem_addr(ksm) + c * 16;
       for (int r = g; r < staged; r += KPB)
@@ -277,15 +241,15 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
     }
     asm volatile("cp.async.wait_group 0;\n" ::: "memory");  // my share of the staged K rows has landed
     __syncthreads();  // q in shared memory, the new cache row and the staged K rows visible to the whole CTA
-    CH::unpack(*reinterpret_cast<const Raw*>(reinterpret_cast<const unsigned char*>(qs) + c * CB), qv);
+    Chunk<T>::unpack(*reinterpret_cast<const uint4*>(reinterpret_cast<const unsigned char*>(qs) + c * 16), qv);
   } else {
-    CH::load(q + (int64_t)b * H + hd * D + c * E, qv);
+    Chunk<T>::load(q + (int64_t)b * H + hd * D + c * E, qv);
   }
   const float neg = finfo_min<T>();
   // ---- pass 1: scores = q . K^T (masked)
   float lmax = -INFINITY;
   if (!pre_k) load_batch(cur, kb, j0 + staged);
-  if constexpr (FUSED && !WIDE) {
+  if constexpr (FUSED) {
     for (int r0 = 0; r0 < staged; r0 += KPB) {  // staged rows: all below j1 and below the append slot
       const int r = r0 + g;
       float kf[E];
@@ -313,7 +277,7 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
       float dot = 0.f;
       if (j < j1) {
         float kf[E];
-        CH::unpack(cur[u], kf);
+        Chunk<T>::unpack(cur[u], kf);
 #pragma unroll
         for (int e = 0; e < E; ++e) dot = fmaf(qv[e], kf[e], dot);
       }
@@ -359,7 +323,7 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
       const int j = base + u * KPB + g;
       if (j < j1) {
         float vf[E];
-        CH::unpack(cur[u], vf);
+        Chunk<T>::unpack(cur[u], vf);
         const float pj = sc[j - j0] * inv;
 #pragma unroll
         for (int e = 0; e < E; ++e) acc[e] = fmaf(pj, vf[e], acc[e]);
@@ -470,20 +434,7 @@ int launch_decode(const QFuse& qf, const void* q, const void* ck, const void* cv
       const TL tl = tl_next(c_stride > 64 ? 2 : 3);
       const int lean_ok = PTTS_KNOB("PTTS_ATTN_LEAN", 1);  // diagnostic build, 0: always the full instantiation
       const bool lean = lean_ok && stage_cap == 0 && !qf.pf_own_v && !qf.pf_next && !qf.tail.ptr && !tl.p;
-#ifndef PTTS_ATTN_WIDE
-#define PTTS_ATTN_WIDE 0
-#endif
-      if (PTTS_ATTN_WIDE && lean && !key_mask && splits == 1 && sizeof(T) == 2) {
-        // 32-byte loads: 4 threads per key row, 32 rows per CTA pass (the per-pass output partials double)
-        constexpr int KPBW = NT / (D / 16);
-        const size_t smem_w = sizeof(float) * ((size_t)cap + 8 + (size_t)KPBW * D);
-        if constexpr (sizeof(T) == 2)
-          e = launch_k(attn_decode_kernel<T, D, true, true, true, true>, dim3(heads, B, splits), dim3(NT), smem_w, st, qf,
-                       (const T*)q, (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len,
-                       (T*)out, scratch, splits, cap, 0, tl);
-        else
-          e = cudaErrorInvalidValue;
-      } else if (lean && !key_mask && splits == 1)
+      if (lean && !key_mask && splits == 1)
         e = launch_k(attn_decode_kernel<T, D, true, true, true>, dim3(heads, B, splits), dim3(NT), smem, st, qf, (const T*)q,
                      (const T*)ck, (const T*)cv, heads, c_stride, ctx_base, ctx_dyn, key_mask, mask_len, (T*)out, scratch,
                      splits, cap, 0, tl);
