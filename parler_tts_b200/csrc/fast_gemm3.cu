@@ -678,7 +678,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const int early = PTTS_KNOB("PTTS_PDL_EARLY", PTTS_DFLT_PDL_EARLY) ? 16 : 0;
   int early_now = early;
   if (EPI == EPI_PARTIAL && g_late_once) {
-    early_now = g_late_once == 2 ? 128 : 0;
+    early_now = g_late_once == 2 ? 128 : g_late_once == 3 ? 16 : 0;  // 3: release BEFORE the own wait (variant builds)
     g_late_once = 0;
   }
   const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early_now : 0);
@@ -735,7 +735,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
 
 }  // namespace
 
-void gemm_next_trigger_late(int at_mma_done) { g_late_once = at_mma_done ? 2 : 1; }
+void gemm_next_trigger_late(int at_mma_done) { g_late_once = at_mma_done < 0 ? 3 : at_mma_done ? 2 : 1; }
 
 namespace gemm {
 bool tma_available() { return encode_tiled_fn() != nullptr; }

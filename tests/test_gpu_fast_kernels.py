@@ -339,6 +339,32 @@ def test_fast_path_launches_its_own_kernels_and_graph_replays_match_eager():
     assert st.graph is not None and st.graph_launches == 2 * 12 + 3, st.graph_launches
 
 
+def test_several_decode_steps_per_graph_replay_equal_single_step_replays():
+    """engine.capture_multi: a graph of 4 consecutive steps (the position counter lives on the device) selects the same
+    tokens as single-step replays, also when the step budget is not a multiple of 4 (the remainder replays single steps)."""
+    from parler_tts_b200.engine import DecoderEngine
+
+    kw = dict(TINY, hidden_size=256, num_attention_heads=4, ffn_dim=1024, num_hidden_layers=2)
+    dims = decoder_oracle.DecoderDims(**kw)
+    sd = decoder_oracle.random_decoder_state(dims, seed=7, ln_jitter=0.05)
+    m = ptts.ParlerTTSForCausalLM(ptts.ParlerTTSDecoderConfig(**kw), state_dict=sd).to(DEV).to(torch.bfloat16)
+    m.impl = cabi.IMPL_FAST
+    g = torch.Generator().manual_seed(5)
+    enc, prm = torch.randn(3, 7, 256, generator=g).to(DEV), torch.randn(3, 4, 256, generator=g).to(DEV)
+    kwargs = dict(encoder_hidden_states=enc, prompt_hidden_states=prm, max_length=31, do_sample=True, top_k=12, seed=4,
+                  logits_processor=[ptts.SuppressTokensAtOrAbove(32)])
+    want = m.generate(**kwargs).cpu()
+    old = DecoderEngine.steps_per_graph
+    try:
+        DecoderEngine.steps_per_graph = 4
+        m.reset_engine()
+        got = m.generate(**kwargs).cpu()
+        assert m._state_cache[1].graph_multi is not None and m._state_cache[1].steps_per_graph == 4
+    finally:
+        DecoderEngine.steps_per_graph = old
+    assert torch.equal(got, want)
+
+
 # ------------------------------------------------------------------------------------------------ DAC fast family
 def _split(w):
     hi = w.to(torch.bfloat16)
