@@ -47,9 +47,13 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
   extern __shared__ float smem[];
   __shared__ int64_t next_in[PTTS_MAX_CODEBOOKS];
   __shared__ int transitions;
+  // Launched with the programmatic-serialization attribute: the CTAs are resident when the lm_heads GEMM finishes.  The
+  // control block was last written by the PREVIOUS step's epilogue (this kernel never releases its dependent early, so the
+  // next step's first kernel starts only when this grid has completed): safe to read before the wait.
   if (ctrl->done) return;
   const int len = ctrl->len;
   if (len >= M) return;
+  pdl_wait();
   const int b = blockIdx.x;
   const int k = threadIdx.x >> 5, lane = threadIdx.x & 31;
   if (threadIdx.x == 0) transitions = 0;
@@ -309,15 +313,18 @@ int step_epilogue(const PttsModel* m, const PttsState* s, cudaStream_t st, const
   }
   PTTS_CHECK_ARG(smem <= 200 * 1024, "step_epilogue: K*vocab too large");
   // the hidden buffer holds one row per utterance during decode (rows_per_batch = 1)
-  step_epilogue_kernel<<<Bu, 32 * K, smem, st>>>(m->embed, m->pos, K, V, m->hidden, Bu, cfg, s->guidance_scale, s->P,
-                                                 s->T0, s->max_len, s->do_sample, s->top_k, s->temperature,
-                                                 s->suppress_from, s->min_length, nucleus ? s->top_p : 1.0f,
-                                                 s->repetition_penalty > 0.0f ? s->repetition_penalty : 1.0f,
-                                                 s->logits_premixed,
-                                                 s->row_offset, s->pad_id, s->eos_id,
-                                                 s->ctrl, logit_parts ? logit_parts : s->logits, s->ids, s->mask,
-                                                 s->unfinished, s->h, 1, logit_parts ? nslice : 1,
-                                                 logit_parts ? slice_stride : 0);
+  const cudaError_t e = launch_k(step_epilogue_kernel, dim3(Bu), dim3(32 * K), smem, st, m->embed, m->pos, K, V, m->hidden,
+                                 Bu, cfg, s->guidance_scale, s->P, s->T0, s->max_len, s->do_sample, s->top_k,
+                                 s->temperature, s->suppress_from, s->min_length, nucleus ? s->top_p : 1.0f,
+                                 s->repetition_penalty > 0.0f ? s->repetition_penalty : 1.0f, s->logits_premixed,
+                                 s->row_offset, s->pad_id, s->eos_id, s->ctrl, logit_parts ? logit_parts : s->logits,
+                                 s->ids, s->mask, s->unfinished, s->h, 1, logit_parts ? nslice : 1,
+                                 logit_parts ? slice_stride : (int64_t)0);
+  if (e != cudaSuccess) {
+    set_error("step_epilogue launch: %s", cudaGetErrorString(e));
+    (void)cudaGetLastError();
+    return PTTS_E_LAUNCH;
+  }
   PTTS_CHECK_LAUNCH("step_epilogue");
   return PTTS_OK;
 }
