@@ -12,7 +12,8 @@
  *     no call changes state that a later call's RESULT depends on, so every call is CUDA-graph capturable and
  *     replayable.  Host state the library does keep (process-wide, guarded by a mutex where it is shared):
  *       * a cache of CUtensorMap descriptors keyed by (base pointer, rows, cols, row pitch in bytes, box rows, element
- *         type) for the TMA operand loads of the tcgen05 GEMM / cross-attention block.  A descriptor only encodes that
+ *         type, k-blocks per box: 0 for a 2-D map, > 0 for the 3-D [k-block][row][64] view whose one copy brings several
+ *         swizzled k-blocks) for the TMA operand loads of the tcgen05 GEMMs / cross-attention block.  A descriptor only encodes that
  *         key, so a buffer freed and re-allocated at the same address with another shape gets another entry; the
  *         cache is cleared when it exceeds 4096 entries;
  *       * per-kernel high-water marks of cudaFuncAttributeMaxDynamicSharedMemorySize (raised on first use);
