@@ -294,6 +294,8 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
 #pragma unroll
     for (int u = 0; u < U; ++u) cur[u] = nxt[u];
   }
+  // (Requesting these first V rows one step earlier - under the LAST K batch, when nxt is free - was measured on B200 at
+  // B=64, 860 frames: 1.2149 / 1.2159 against 1.2115 / 1.2095 ms per decode step, fp8 cache 1.0302 against 1.0257 / 1.0271.)
   if (!pre_v) load_batch(cur, vb, j0);  // first V rows travel while the block reduces max / sum (pre_v: cur = nxt)
   if (PTTS_DFLT_ATTN_LATE == 1) pdl_launch();  // variant builds: release the dependent after the K pass
   lmax = warp_max(lmax);
