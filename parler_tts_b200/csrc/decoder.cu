@@ -228,12 +228,8 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
     // decode: QKV as split-K partial sums; the attention CTA of (b, head) folds them, scales q and writes the new
     // K / V row into the cache itself
     float* qpart = work_area(m, s);
-#ifndef PTTS_QKV_EARLY
-#define PTTS_QKV_EARLY 0
-#endif
-    // (variant builds: the QKV GEMM releases the self-attention kernel BEFORE its own wait, so that the attention CTAs are
-    // resident and their first K batch is in flight while LayerNorm / QKV still run - profiles/r02_fc1_act.txt)
-    if (PTTS_QKV_EARLY) gemm_next_trigger_late(-1);
+    // (The QKV GEMM releasing the self-attention kernel BEFORE its own wait - attention CTAs resident, first K batch in
+    // flight while LayerNorm / QKV still run - was measured: 1.2200 / 1.2202 against 1.2209 / 1.2219 ms, noise level.)
     PTTS_UNLESS_SKIPPED(2, gemm_bf16_partial(s->xn, L.w_qkv, rows, 3 * H, H, Sq, 0, qpart, st));
     if (wpf_mask() & 2) set_l2_hint(L.w_o, (long long)H * H * dtype_size(dt));
     // self-attention kernel choice (PttsState.self_attn_kernel): one CTA per (utterance, head) item (split-KV for small

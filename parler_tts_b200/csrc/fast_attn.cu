@@ -194,11 +194,8 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
       l2_prefetch_range(cv + (((int64_t)b * heads + hd) * c_stride + j0) * D, (int64_t)min(n, old_end - j0) * D * sizeof(T));
     if (!LEAN && qf.pf_next && sp == 0 && !qf.pf_late) prefetch_next();
   }
-#ifndef PTTS_DFLT_ATTN_LATE
-#define PTTS_DFLT_ATTN_LATE 0
-#endif
   pdl_wait();
-  if (PTTS_DFLT_ATTN_LATE == 0) pdl_launch();
+  pdl_launch();  // (release after the K pass: 1.2205, only at exit: 1.2367 against 1.2194 / 1.2205 ms per decode step)
   tl_dep(tl);
   // pf_late (opt-in, measured slower): prefetch only after the producer GEMM (cross q projection) has finished
   if constexpr (FUSED)
@@ -297,7 +294,6 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   // (Requesting these first V rows one step earlier - under the LAST K batch, when nxt is free - was measured on B200 at
   // B=64, 860 frames: 1.2149 / 1.2159 against 1.2115 / 1.2095 ms per decode step, fp8 cache 1.0302 against 1.0257 / 1.0271.)
   if (!pre_v) load_batch(cur, vb, j0);  // first V rows travel while the block reduces max / sum (pre_v: cur = nxt)
-  if (PTTS_DFLT_ATTN_LATE == 1) pdl_launch();  // variant builds: release the dependent after the K pass
   lmax = warp_max(lmax);
   if (lane == 0) red[warp] = lmax;
   __syncthreads();

@@ -672,13 +672,11 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
   const int dbg = PTTS_KNOB("PTTS_GEMM_DBG", 0);
   // with cp.async slabs the early release won (1.727 against 1.748 ms per decode step); with TMA slabs the slab needs
   // ~1.5 us of lead only and the late release wins (1.486 against 1.496 ms) -> late
-  #ifndef PTTS_DFLT_PDL_EARLY
-#define PTTS_DFLT_PDL_EARLY 0
-#endif
-  const int early = PTTS_KNOB("PTTS_PDL_EARLY", PTTS_DFLT_PDL_EARLY) ? 16 : 0;
+    // (re-measured on the round-2 kernels: early 1.3299 against 1.2206 ms; release at MMA done 1.2664)
+  const int early = PTTS_KNOB("PTTS_PDL_EARLY", 0) ? 16 : 0;
   int early_now = early;
   if (EPI == EPI_PARTIAL && g_late_once) {
-    early_now = g_late_once == 2 ? 128 : g_late_once == 3 ? 16 : 0;  // 3: release BEFORE the own wait (variant builds)
+    early_now = g_late_once == 2 ? 128 : 0;
     g_late_once = 0;
   }
   const int dbg_arg = (dbg == 3 ? (3 | ((g_agg_seq++ & 255) << 8)) : dbg) | (EPI == EPI_PARTIAL ? early_now : 0);
@@ -702,10 +700,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
     CUtensorMap t3w, t3x;
     if (tensor_map_2d_any(p.W, p.N, p.K, UM, PTTS_BF16, &t3w, kb / 2) &&
         tensor_map_2d_any(p.X, p.M, p.K, UN, PTTS_BF16, &t3x, kb % PTTS_GEMM_XPARTS == 0 ? kb / PTTS_GEMM_XPARTS : kb)) {
-      #ifndef PTTS_DFLT_GEMM_LATE
-#define PTTS_DFLT_GEMM_LATE 0
-#endif
-      const int late = (dbg_arg & 16) ? 2 : ((dbg_arg & 128) || PTTS_DFLT_GEMM_LATE) ? 1 : 0;
+            const int late = (dbg_arg & 16) ? 2 : (dbg_arg & 128) ? 1 : 0;
       cudaError_t e2 = kb == 8   ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<8>, p.part, p.M, p.N, late, t3w, t3x)
                        : kb == 6 ? cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<6>, p.part, p.M, p.N, late, t3w, t3x)
                                  : cudaLaunchKernelEx(&cfg, umma_partial_lean_kernel<4>, p.part, p.M, p.N, late, t3w, t3x);
@@ -735,7 +730,7 @@ int launch_umma(const GemmParams& p, cudaStream_t st, int splits = 0) {
 
 }  // namespace
 
-void gemm_next_trigger_late(int at_mma_done) { g_late_once = at_mma_done < 0 ? 3 : at_mma_done ? 2 : 1; }
+void gemm_next_trigger_late(int at_mma_done) { g_late_once = at_mma_done ? 2 : 1; }
 
 namespace gemm {
 bool tma_available() { return encode_tiled_fn() != nullptr; }
@@ -770,10 +765,7 @@ int umma_plan_splits(int M, int N, int K) {
   const int nt = ((N + UM - 1) / UM) * ((M + UN - 1) / UN);
   // CTAs wanted per residual GEMM (fewer slices = cheaper LayerNorm fold): with TMA slab loads fewer, larger CTAs
   // win, 30 -> 16 measured 1.654 -> 1.559 ms per step
-  #ifndef PTTS_DFLT_SPLIT_TARGET
-#define PTTS_DFLT_SPLIT_TARGET 16
-#endif
-  const int target = PTTS_KNOB("PTTS_SPLIT_TARGET", PTTS_DFLT_SPLIT_TARGET);
+    const int target = PTTS_KNOB("PTTS_SPLIT_TARGET", 16);  // 32 re-measured in round 2: 1.2811 against 1.2206 ms
   // 64-element k-blocks per CTA (8 = 128 KB of W per CTA; 4 = 64 KB measured slower, 1.630 against 1.497 ms)
   int kbmax = PTTS_KNOB("PTTS_KBMAX", kMaxKB64);
   if (kbmax < 1 || kbmax > kMaxKB64) kbmax = kMaxKB64;

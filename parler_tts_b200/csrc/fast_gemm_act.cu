@@ -119,11 +119,8 @@ umma_act_kernel(__nv_bfloat16* __restrict__ y, int N, int KBT, int act_in, const
   __syncthreads();  // barrier inits and the TMEM base address are visible to everybody - still in front of the wait
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
   const uint32_t tmem_d = tmem_base_slot;
-#ifndef PTTS_DFLT_ACT_LATE
-#define PTTS_DFLT_ACT_LATE 0
-#endif
   pdl_wait();
-  if (!PTTS_DFLT_ACT_LATE) pdl_launch();
+  pdl_launch();  // (releasing fc2 only when the MMAs are done was measured: 1.2317 against 1.2194 ms per decode step)
   if (warp == 1 && elect_one()) {
     const int first = groups < ring_groups ? groups : ring_groups;
     for (int g = 0; g < first; ++g) act_expect_tx(x_bar + 8 * g, (uint32_t)(AGRP * ABLK));
@@ -153,7 +150,6 @@ umma_act_kernel(__nv_bfloat16* __restrict__ y, int N, int KBT, int act_in, const
   __syncwarp();
   act_wait(mma_bar, 0);
   asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
-  if (PTTS_DFLT_ACT_LATE) pdl_launch();
   // ---- epilogue.  Warp w reads TMEM lanes [32 q, 32 q + 32), q = w % 4, of which lanes 0..15 hold weight rows
   // 16 q .. 16 q + 15; warps 0-3 take batch columns 0..31, warps 4-7 columns 32..63.
   const int q = warp & 3, c0 = (warp >> 2) * 32;

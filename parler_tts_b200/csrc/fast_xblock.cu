@@ -19,9 +19,6 @@
 
 #include "gemm_common.cuh"
 
-#ifndef PTTS_DFLT_XB_EARLY
-#define PTTS_DFLT_XB_EARLY 0
-#endif
 namespace ptts {
 
 namespace {
@@ -609,7 +606,7 @@ int xblock_fast(const float* h, const float* part_in, int S_in, int64_t stride, 
   // bit 0: per-phase stamps (diagnostic build, PTTS_XB_DBG=1); bit 1: release the next LayerNorm AFTER the own wait:
   // measured 1.496 (before) against 1.451 ms per decode step - released early, the LayerNorm releases fc1 in turn,
   // whose TMA slab burst lands on this kernel
-  const int dbg = (PTTS_KNOB("PTTS_XB_DBG", 0) & 1) | (PTTS_KNOB("PTTS_XB_EARLY", PTTS_DFLT_XB_EARLY) ? 0 : 2);
+  const int dbg = (PTTS_KNOB("PTTS_XB_DBG", 0) & 1) | (PTTS_KNOB("PTTS_XB_EARLY", 0) ? 0 : 2);
   // CTAs (heads) that share the fold + LayerNorm of a group.  Measured (B=64, 860 frames, TMA slabs, late releases):
   // 1 -> 1.421, 2 -> 1.436 ms per decode step; 4 was 0.13 ms behind 2 with the cp.async slabs, 8 cannot be placed
   // (12 us dep-spread).  The cluster instantiations exist in the diagnostic build only (PTTS_XB_CLUSTER=2|4).
