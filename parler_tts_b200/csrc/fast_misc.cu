@@ -91,9 +91,17 @@ ln_reduce_kernel(float* __restrict__ h, const float* __restrict__ part, int S, i
             : "memory");
         if (spin > 200000000u) __trap();
       }
-      for (int k = 0; k < n_blk; ++k) {
-        const float4 t = *reinterpret_cast<const float4*>(blk + (size_t)k * H + c);
-        v.x += t.x; v.y += t.y; v.z += t.z; v.w += t.w;
+      // eight shared-memory loads in flight before the first add (rolled, every add waited for its own load); the adds
+      // keep the slice order
+#pragma unroll 1
+      for (int k0 = 0; k0 < n_blk; k0 += 8) {
+        float4 t[8];
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (k0 + u < n_blk) t[u] = *reinterpret_cast<const float4*>(blk + (size_t)(k0 + u) * H + c);
+#pragma unroll
+        for (int u = 0; u < 8; ++u)
+          if (k0 + u < n_blk) { v.x += t[u].x; v.y += t[u].y; v.z += t[u].z; v.w += t[u].w; }
       }
     }
     if (S > 0 || rowblk) *reinterpret_cast<float4*>(hr + c) = v;
