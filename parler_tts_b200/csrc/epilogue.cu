@@ -134,6 +134,7 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
   int64_t tok;
   if (!do_sample) {
     float bv = -INFINITY; int bi = 0x7fffffff;
+#pragma unroll 8
     for (int i = lane; i < V; i += 32) {
       const float v = sc[i];
       if (v > bv || (v == bv && i < bi)) { bv = v; bi = i; }

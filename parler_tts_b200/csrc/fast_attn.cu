@@ -300,6 +300,7 @@ attn_decode_kernel(const QFuse qf, const T* __restrict__ q, const T* __restrict_
   const float mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
   // ---- pass 2: exp and sum
   float lsum = 0.f;
+#pragma unroll 4
   for (int i = tid; i < n; i += NT) {
     const float e = expf(sc[i] - mx);
     sc[i] = e;

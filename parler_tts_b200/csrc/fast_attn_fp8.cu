@@ -208,6 +208,7 @@ attn_fp8_kernel(const Fp8Fuse qf, const __nv_bfloat16* __restrict__ q, unsigned 
   __syncthreads();
   const float mx = fmaxf(fmaxf(red[0], red[1]), fmaxf(red[2], red[3]));
   float lsum = 0.f;
+#pragma unroll 4
   for (int i = tid; i < n; i += NT) {
     const float e = expf(sc[i] - mx);
     sc[i] = e;
