@@ -139,6 +139,47 @@ def _attention(q, ck, cv, ctx, key_mask, impl):
 
 
 @pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
+@pytest.mark.parametrize("B,heads,Tq,c_stride,ctx,causal,masked", [(64, 16, 33, 901, 33, 1, False), (3, 4, 33, 48, 48, 0, True),
+                                                                  (2, 2, 7, 300, 257, 1, True), (1, 1, 2, 9, 2, 1, False)])
+def test_prefill_attention_staged_vs_torch_fp32(dtype, B, heads, Tq, c_stride, ctx, causal, masked):
+    """fast_attn_prefill.cu (Tq > 1: prompt prefill self-attention with the causal mask, cross-attention over the cached T5
+    keys): K / V of a (head, utterance) pair staged in shared memory once for all its queries; masked keys take
+    finfo(dtype).min like the reference's additive mask.  Also checked against the simple family on the same inputs."""
+    g = torch.Generator().manual_seed(Tq * 131 + ctx)
+    d = 64
+    q = (torch.randn(B, Tq, heads * d, generator=g) * 0.3).to(DEV, dtype)
+    ck = torch.randn(B, heads, c_stride, d, generator=g).to(DEV, dtype)
+    cv = torch.randn(B, heads, c_stride, d, generator=g).to(DEV, dtype)
+    km = None
+    if masked:
+        km = (torch.rand(B, ctx, generator=g) > 0.25).to(torch.int32)
+        km[:, -1] = 1
+        km = km.to(DEV)
+    outs = {}
+    for impl in (cabi.IMPL_FAST, cabi.IMPL_SIMPLE):
+        out = torch.full((B, Tq, heads * d), float("nan"), device=DEV, dtype=dtype)
+        cabi.call("ptts_attention", cabi.ptr(q), cabi.ptr(ck), cabi.ptr(cv), cabi.dtype_enum(dtype), B, heads, d, Tq,
+                  c_stride, ctx, None, causal, cabi.ptr(km), 0 if km is None else ctx, cabi.ptr(out), None, impl,
+                  cabi.stream_ptr())
+        outs[impl] = out.float()
+    qf = q.float().view(B, Tq, heads, d).transpose(1, 2)                      # (B, heads, Tq, d)
+    sc = qf @ ck.float()[:, :, :ctx].transpose(-1, -2)                        # (B, heads, Tq, ctx)
+    neg = torch.finfo(dtype).min
+    keep = torch.ones(B, 1, Tq, ctx, dtype=torch.bool, device=DEV)
+    if causal:
+        t = torch.arange(Tq, device=DEV)[:, None]
+        j = torch.arange(ctx, device=DEV)[None, :]
+        keep = keep & (j < ctx - Tq + t + 1)[None, None]
+    if km is not None:
+        keep = keep & (km[:, None, None, :] != 0)
+    sc = torch.where(keep, sc, torch.full_like(sc, neg))
+    want = (torch.softmax(sc, dim=-1) @ cv.float()[:, :, :ctx]).transpose(1, 2).reshape(B, Tq, heads * d)
+    tol = 2e-5 if dtype == torch.float32 else 2e-2
+    assert float((outs[cabi.IMPL_FAST] - want).abs().max()) < tol * max(1.0, float(want.abs().max()))
+    assert float((outs[cabi.IMPL_FAST] - outs[cabi.IMPL_SIMPLE]).abs().max()) < tol * max(1.0, float(want.abs().max()))
+
+
+@pytest.mark.parametrize("dtype", [torch.float32, torch.bfloat16])
 @pytest.mark.parametrize("B,heads,c_stride,ctx", [(64, 16, 901, 466), (2, 16, 2700, 2609), (1, 2, 64, 1),
                                                   (3, 4, 130, 129), (16, 16, 48, 48)])
 def test_flash_decode_attention_vs_torch_fp32(dtype, B, heads, c_stride, ctx):
