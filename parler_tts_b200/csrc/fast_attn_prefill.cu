@@ -37,10 +37,25 @@ attn_prefill_kernel(const T* __restrict__ q, const T* __restrict__ ck, const T* 
   float* sc = qs + PD;
   const T* kb = ck + ((int64_t)b * heads + hd) * (int64_t)c_stride * PD;
   const T* vb = cv + ((int64_t)b * heads + hd) * (int64_t)c_stride * PD;
-  for (int e = threadIdx.x; e < ctx * PD; e += PNW * 32) {
-    const int j = e / PD, d = e - j * PD;
-    kt[d * CP + j] = kb[e];
-    vs[e] = vb[e];
+  for (int e0 = threadIdx.x; e0 < ctx * PD; e0 += PNW * 32 * 4) {  // eight loads in flight per thread
+    T kk[4], vv[4];
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * PNW * 32;
+      if (e < ctx * PD) {
+        kk[u] = kb[e];
+        vv[u] = vb[e];
+      }
+    }
+#pragma unroll
+    for (int u = 0; u < 4; ++u) {
+      const int e = e0 + u * PNW * 32;
+      if (e < ctx * PD) {
+        const int j = e / PD, d = e - j * PD;
+        kt[d * CP + j] = kk[u];
+        vs[e] = vv[u];
+      }
+    }
   }
   __syncthreads();
   const float neg = finfo_min<T>();
