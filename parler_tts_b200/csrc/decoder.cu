@@ -332,9 +332,12 @@ static int run_layer(const PttsModel* m, const PttsState* s, const Path& path, P
 #ifndef PTTS_FC1_ACT
 #define PTTS_FC1_ACT 1
 #endif
+#ifndef PTTS_FC1_ACT_MAXROWS
+#define PTTS_FC1_ACT_MAXROWS 128
+#endif
   // decode: fc1 over the whole K with the activation in its own epilogue - one launch instead of split-K partial sums +
   // reduce / activation.  Measured on B200 (B=64, 860 frames, same box): see profiles/r02_fc1_act.txt
-  if (PTTS_FC1_ACT && fuse && rows <= 128 && gemm_bf16_act_supported(rows, F, H) && !(skip_mask() & 64)) {
+  if (PTTS_FC1_ACT && fuse && rows <= PTTS_FC1_ACT_MAXROWS && gemm_bf16_act_supported(rows, F, H) && !(skip_mask() & 64)) {
     PTTS_TRY(gemm_bf16_act(s->xn, L.w_fc1, rows, F, H, m->act_fn, s->ffn, st));
   } else if (Sf > 1 && bn_f == 0 && (int64_t)Sf * rows * F <= work_area_floats(m, rows)) {
     // decode: fc1 as split-K partial sums + one small reduce / activation kernel spread over all SMs.  (Folding the

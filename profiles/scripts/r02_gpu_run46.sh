@@ -1,0 +1,27 @@
+#!/bin/bash
+# round 2, call 46 (1 GPU): fc1 + activation - ring kernel at 64 rows, 32-row ring-less kernel above (default); B = 256 with
+# the fused kernel (r256) against the split-K partial sums + activation kernel (default), same box
+cd "$GRAFT_REPO_ROOT" || exit 1
+mkdir -p gpurun_out
+timeout 900 python -m pytest tests/test_gpu_fast_kernels.py -m gpu -x -q -k "activation_gemm or heads_partials or several_decode" > gpurun_out/r2_46_pytest.log 2>&1; echo "pytest rc=$?"; tail -3 gpurun_out/r2_46_pytest.log
+line() { python - "$1" <<'PY'
+import json,sys
+try:
+    d=json.loads(open(sys.argv[1]).read().strip().splitlines()[-1])
+    print("  ms/step", round(d["ms_per_decode_step"],4), "value", round(d["value"]), "check", d["check"].get("ok"), d["check"].get("codes_sha16"))
+except Exception as e:
+    print("   no line:", e)
+PY
+}
+cp parler_tts_b200/libparler_b200.so /tmp/default.so
+for b in 64 128; do
+for v in default base; do
+  if [ $v = default ]; then cp /tmp/default.so parler_tts_b200/libparler_b200.so; else cp parler_tts_b200/libparler_b200_$v.so parler_tts_b200/libparler_b200.so; fi
+  timeout 900 python bench.py --skip-cpu --skip-e2e --steps 2 --batch $b > gpurun_out/r2_46_bench_b${b}_$v.json 2> gpurun_out/r2_46_bench_b${b}_$v.err; echo "b$b $v rc=$?"; line gpurun_out/r2_46_bench_b${b}_$v.json
+done
+done
+for v in default r256 default r256; do
+  if [ $v = default ]; then cp /tmp/default.so parler_tts_b200/libparler_b200.so; else cp parler_tts_b200/libparler_b200_$v.so parler_tts_b200/libparler_b200.so; fi
+  timeout 900 python bench.py --skip-cpu --skip-e2e --steps 2 --batch 256 > gpurun_out/r2_46_bench_b256_$v.json 2> gpurun_out/r2_46_bench_b256_$v.err; echo "b256 $v rc=$?"; line gpurun_out/r2_46_bench_b256_$v.json
+done
+cp /tmp/default.so parler_tts_b200/libparler_b200.so

@@ -78,10 +78,11 @@ def test_large_m_tile_gemm_vs_torch_fp32(M, N, K):
     assert float((again - ref).abs().max()) < 2e-3 * float(ref.abs().max())
 
 
-@pytest.mark.parametrize("M,N,K", [(64, 4096, 1024), (64, 256, 512), (128, 1024, 768), (64, 64, 256)])
+@pytest.mark.parametrize("M,N,K", [(64, 4096, 1024), (64, 256, 512), (128, 1024, 768), (64, 64, 256), (32, 128, 1024),
+                                   (96, 192, 256)])
 def test_activation_gemm_full_k_vs_torch_fp32(M, N, K):
-    """fc1 shape family of fast_gemm_act.cu (tcgen05 M = 64 tiles over the whole K, activation in the epilogue; K = 1024
-    streams X through the ring with slot re-use, K <= 768 does not): bf16 out = act(x . w^T), no bias / residual."""
+    """fc1 shape family of fast_gemm_act.cu (tcgen05 M = 64 weight rows x N = 32 batch rows per CTA over the whole K,
+    activation in the epilogue): bf16 out = act(x . w^T), no bias / residual."""
     g = torch.Generator().manual_seed(M + N + K)
     x = (torch.randn(M, K, generator=g) * 0.5).to(DEV, torch.bfloat16)
     w = (torch.randn(N, K, generator=g) * 0.05).to(DEV, torch.bfloat16)
