@@ -258,6 +258,11 @@ PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T
  * [n_tile][Cin/32][taps][plane hi|mid][4][bn][8] bf16 with bn = ptts_dac_tile_n(N), N = Cout (conv1d) or stride*Cout
  * (convtr1d), rows n >= N zero-filled: the shared-memory image of one pipeline stage, moved by one bulk copy. */
 PTTS_API int ptts_dac_tile_n(int32_t N);
+/* CTAs the persistent conv kernels (ptts_dac_conv1d_px / ptts_dac_convtr1d_px) launched from now on may occupy; 0 = one
+ * per SM (default).  Returns the previous value.  Host-side launch setting of the calling process (one process per GPU),
+ * not synchronised: the chunked decode that runs beside the token loop (streaming.py) sets it around its launches so that
+ * the loop's kernels keep SMs of their own.  The results do not depend on it. */
+PTTS_API int ptts_dac_set_cta_limit(int32_t n);
 /* "Planes": an activation tensor stored the way the tensor core wants it - Snake already applied, split into two
  * bf16 planes (x = hi + mid), 8-channel panels: [B][2 (hi, mid)][C/8][PAD_LO + T + PAD_HI][8] bf16 (4 bytes per
  * element, like fp32).  Row PAD_LO - 1 and row PAD_LO + T must be zero (the caller zeroes the pads once), the other pad

@@ -97,6 +97,7 @@ PROTOTYPES = {
     "ptts_dac_dequant_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_i64, c_i64, c_vp, c_i32, c_i32, c_vp, c_vp]),
     "ptts_dac_conv_out_nwc": (C.c_int, [c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp, c_vp, c_vp]),
     "ptts_dac_tile_n": (C.c_int, [c_i32]),
+    "ptts_dac_set_cta_limit": (C.c_int, [c_i32]),
     "ptts_dac_conv1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_vp,
                                      c_vp, c_vp, c_vp]),
     "ptts_dac_convtr1d_px": (C.c_int, [c_vp, c_vp, c_i32, c_i32, c_i32, c_vp, c_vp, c_i32, c_i32, c_vp, c_vp, c_vp]),

@@ -135,6 +135,8 @@ using namespace ptts;
 
 extern "C" PTTS_API int ptts_dac_tile_n(int32_t N) { return dac_tile_n(N); }
 
+extern "C" PTTS_API int ptts_dac_set_cta_limit(int32_t n) { return dac_set_cta_limit(n); }
+
 extern "C" PTTS_API int ptts_dac_dequant_nwc(const int64_t* codes, int32_t B, int32_t K, int32_t F, int64_t ld_b, int64_t ld_k,
                                     const float* tables, int32_t codebook_size, int32_t latent, float* z,
                                     ptts_stream_t s) {

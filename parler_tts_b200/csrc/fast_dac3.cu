@@ -473,6 +473,10 @@ int sm_count() {
   return n;
 }
 
+// CTAs a conv launch may occupy (0 = one per SM): the streamed chunk decode runs next to the token loop and leaves
+// the other SMs to the loop's kernels (ptts_dac_set_cta_limit)
+int g_cta_limit = 0;
+
 template <int BN, bool DBL>
 int launch_ws(const ConvParams3& p, int B, cudaStream_t st) {
   const size_t xbuf = (size_t)2 * 4 * (TMW + p.span) * 16, wring = (size_t)WST3 * 2 * 4 * BN * 16;
@@ -489,13 +493,20 @@ int launch_ws(const ConvParams3& p, int B, cudaStream_t st) {
   }
   const int MT = (p.Mrows + TMW - 1) / TMW, NTn = (p.N + BN - 1) / BN;
   const int ntiles = MT * NTn * B;
-  const int grid = ntiles < sm_count() ? ntiles : sm_count();
+  int grid = ntiles < sm_count() ? ntiles : sm_count();
+  if (g_cta_limit > 0 && grid > g_cta_limit) grid = g_cta_limit;  // persistent CTAs: any grid walks all tiles
   dac_conv_ws_kernel<BN, DBL><<<grid, NTHR, smem, st>>>(p, MT, NTn, ntiles, nxb);
   PTTS_CHECK_LAUNCH("dac_conv_ws");
   return PTTS_OK;
 }
 
 }  // namespace
+
+int dac_set_cta_limit(int n) {
+  const int prev = g_cta_limit;
+  g_cta_limit = n > 0 ? n : 0;
+  return prev;
+}
 
 // column-tile width of the pre-tiled weight layout for a conv with N output columns (ptts_dac_tile_n)
 int dac_tile_n(int N) {

@@ -73,6 +73,7 @@ struct DacConv {
   int Mrows, out_stride, out_pad, Tout;
 };
 int dac_tile_n(int N);
+int dac_set_cta_limit(int n);  // persistent conv grids; returns the previous limit (0 = one CTA per SM)
 int dac_conv_ws(const DacConv& conv, int B, cudaStream_t st);
 int attention_fast_fused(const float* qkv_part, int S, int64_t part_stride, int ncols, int has_kv, float scale,
                          int slot_base, const int* slot_dyn, void* ck, void* cv, int B, int heads, int c_stride,

@@ -223,6 +223,13 @@ class DecoderEngine:
     def epilogue(self, st: GenState):
         cabi.call("ptts_step_epilogue", self._m(), C.byref(st.c_state), cabi.stream_ptr())
 
+    # stream priority the step graph is captured with (kernel nodes keep the priority of the capturing stream): -1 puts
+    # the loop's kernels in front of the chunked codec decode that shares the GPU with them (streaming.py); 0 = default
+    graph_priority = 0
+
+    def _capture_stream(self):
+        return torch.cuda.Stream(priority=self.graph_priority) if self.graph_priority else None
+
     def capture(self, st: GenState):
         """Captures one whole decode step (all layers + heads + epilogue) into a CUDA graph.  Sequence length lives in
         the device control block, so the same graph is replayed for every step."""
@@ -230,7 +237,7 @@ class DecoderEngine:
             return st.graph
         g = torch.cuda.CUDAGraph()
         n0 = self.lib.ptts_launch_count()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, stream=self._capture_stream()):
             self.step(st)
         st.graph_launches = int(self.lib.ptts_launch_count() - n0)
         st.graph = g
@@ -244,7 +251,7 @@ class DecoderEngine:
         if st.graph_multi is not None and st.steps_per_graph == steps:
             return st.graph_multi
         g = torch.cuda.CUDAGraph()
-        with torch.cuda.graph(g):
+        with torch.cuda.graph(g, stream=self._capture_stream()):
             for _ in range(steps):
                 self.step(st)
         st.graph_multi, st.steps_per_graph = g, steps

@@ -19,7 +19,7 @@ from . import cabi
 from .configuration import DACConfig, ParlerTTSConfig, ParlerTTSDecoderConfig
 from .dac import DacDecoderEngine, DacEncoderEngine
 from .engine import DecoderDims, DecoderEngine, DecoderWeights, GenState
-from .streaming import AudioChunkStreamer, ChunkPipeline
+from .streaming import AudioChunkStreamer, ChunkPipeline, SilentChunks
 
 
 # --------------------------------------------------------------------------------------------- helpers
@@ -809,6 +809,10 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         self.generation_config = _default_generation_config(config.decoder)
         self._prompt_table = None
         self.text_encoder_impl = "native"  # CUDA T5 encoder (ptts_t5_encode); "torch" = the third-party module
+        # codec decode beside the token loop when no streamer was passed (streaming.SilentChunks): frames per chunk
+        # (0 = decode after the loop) and the CTAs a chunk decode may occupy while the loop runs (None = one per SM)
+        self.overlap_decode_chunk_frames = 0
+        self.overlap_decode_ctas = None
         self._t5_engine = None
 
     # ---- reference accessors
@@ -977,6 +981,8 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         elif prompt_ids is not None:
             prompt_ids = prompt_ids.to(dev, torch.int64).contiguous()
             prompt_table = self.prompt_table()
+        if streamer is None and not return_codes and self.overlap_decode_chunk_frames > 0 and dec_ids is None:
+            streamer = SilentChunks(self.overlap_decode_chunk_frames, self.overlap_decode_ctas)
         codes, seq, st = _generate_codes(self.decoder, enc, attention_mask, prompt_table, prompt_ids, prompt_hidden,
                                          prompt_mask, dec_ids, gc, kwargs, logits_processor, stopping_criteria,
                                          streamer, self.decoder.impl, self.decoder.use_cuda_graph,

@@ -52,10 +52,13 @@ class AudioChunkStreamer:
     yields the same `(first_frame, audio)` pairs (like transformers' TextIteratorStreamer).  `put(token_ids)` - the
     reference's token-level hook - is accepted and ignored, so the object is also a valid BaseStreamer."""
 
-    def __init__(self, chunk_frames=128, on_chunk=None, to_host=True, timeout=None):
+    def __init__(self, chunk_frames=128, on_chunk=None, to_host=True, timeout=None, decode_ctas=None):
         if chunk_frames < 16:
             raise ValueError("chunk_frames must be at least 16")
         self.chunk_frames = int(chunk_frames)
+        # CTAs the chunk decodes that run beside the token loop may occupy (None = one per SM): the codec's conv kernels
+        # are persistent, one CTA per SM, and with all SMs taken the loop's kernels queue behind every conv launch
+        self.decode_ctas = None if decode_ctas is None else int(decode_ctas)
         self.on_chunk = on_chunk
         self.to_host = bool(to_host)
         self.timeout = timeout
@@ -89,6 +92,20 @@ class AudioChunkStreamer:
         return item
 
 
+class SilentChunks(AudioChunkStreamer):
+    """generate()'s own consumer when no streamer was passed: the chunks stay on the device and only the assembled
+    waveform is returned - the codec work then overlaps the token loop instead of following it."""
+
+    def __init__(self, chunk_frames, decode_ctas=None):
+        super().__init__(chunk_frames=chunk_frames, to_host=False, decode_ctas=decode_ctas)
+
+    def put_audio(self, first_frame, audio, steps_enqueued=None, decode_queued_at=None):
+        pass
+
+    def end(self):
+        pass
+
+
 class ChunkPipeline:
     """Host side of the overlapped chunk decode for one generate() call (no audio prompt: T0 == 1)."""
 
@@ -110,6 +127,11 @@ class ChunkPipeline:
         self.stopped = False  # a window held an id outside the codebook (EOS / PAD / BOS / unused): the rest is decoded at the end
         self.pending = []
         self.steps_enqueued = 0
+        # timeline for profiles/scripts/overlap_time.py: events with timing only when the streamer asks (trace = True)
+        self.trace = [] if getattr(streamer, "trace", False) else None
+        if self.trace is not None:
+            self.t_ref = torch.cuda.Event(enable_timing=True)
+            self.t_ref.record(self.main)
 
     # ---- called by the loop after every batch of enqueued decode steps
     def progress(self, done_steps):
@@ -137,9 +159,18 @@ class ChunkPipeline:
         ready.record(self.main)
         with torch.cuda.stream(self.side):
             self.side.wait_event(ready)
+            if self.trace is not None:
+                t_a = torch.cuda.Event(enable_timing=True)
+                t_a.record(self.side)
             win = self._decode_window(lo, hi)
             bad = ((win < 0) | (win >= self.dac.codebook_size)).any() | (st.ctrl[0] < hi + self.K)
-            wav = self.dac.decode(win)
+            lib, limit = cabi.load(), self.streamer.decode_ctas
+            prev = lib.ptts_dac_set_cta_limit(limit) if limit else 0
+            try:
+                wav = self.dac.decode(win)
+            finally:
+                if limit:
+                    lib.ptts_dac_set_cta_limit(prev)
             piece = wav[:, 0, (f0 - lo) * hop : (f1 - lo) * hop]
             self.audio[:, f0 * hop : f1 * hop].copy_(piece)
             host = None
@@ -148,8 +179,10 @@ class ChunkPipeline:
                 host.copy_(piece, non_blocking=True)
             flag = torch.empty(1, dtype=torch.int32, pin_memory=True)
             flag.copy_(bad.to(torch.int32).reshape(1), non_blocking=True)
-            done = torch.cuda.Event()
+            done = torch.cuda.Event(enable_timing=self.trace is not None)
             done.record(self.side)
+            if self.trace is not None:
+                self.trace.append((f0, f1, self.steps_enqueued, t_a, done))
         self.pending.append((f0, f1, host, flag, done, self.steps_enqueued))
 
     def _poll(self, block):
@@ -173,6 +206,9 @@ class ChunkPipeline:
     def finish(self, codes, decode_generated):
         """codes (Bu, K, F): the final de-delayed codes.  Returns the full audio (Bu, T) like the one-shot path and hands
         the part not streamed yet to the streamer."""
+        if self.trace is not None:
+            self.t_loop_end = torch.cuda.Event(enable_timing=True)
+            self.t_loop_end.record(self.main)
         self._poll(block=True)
         hop, F = self.hop, codes.shape[2]
         tail_from = self.emitted_f
@@ -202,4 +238,12 @@ class ChunkPipeline:
                 out.copy_(rest, non_blocking=False)
             self.streamer.put_audio(tail_from, out, self.steps_enqueued)
         self.streamer.end()
+        if self.trace is not None:
+            t_end = torch.cuda.Event(enable_timing=True)
+            t_end.record(self.main)
+            t_end.synchronize()
+            self.streamer.timeline = dict(
+                loop_end_ms=self.t_ref.elapsed_time(self.t_loop_end), end_ms=self.t_ref.elapsed_time(t_end),
+                chunks=[(f0, f1, steps, self.t_ref.elapsed_time(a), self.t_ref.elapsed_time(b))
+                        for f0, f1, steps, a, b in self.trace])
         return audio

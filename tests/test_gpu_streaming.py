@@ -110,3 +110,41 @@ def test_streamer_falls_back_to_one_chunk_with_host_processors():
     assert len(got) == 1 and got[0][0] == 0
     np.testing.assert_allclose(got[0][1].numpy(), want.cpu().numpy(), atol=1e-6)
     np.testing.assert_allclose(audio.cpu().numpy(), want.cpu().numpy(), atol=1e-6)
+
+
+def test_decode_beside_the_loop_without_a_streamer_and_with_a_cta_limit():
+    """generate() with model.overlap_decode_chunk_frames decodes finished chunks on the second stream while the loop runs
+    (streaming.SilentChunks) and returns the same waveform; the CTA limit of the persistent conv kernels
+    (ptts_dac_set_cta_limit, AudioChunkStreamer(decode_ctas=...)) changes the launch width only, not a sample."""
+    from parler_tts_b200 import cabi
+
+    model = _long_model()
+    ids, pids = _inputs(3, seed=4)
+    procs = [ptts.SuppressTokensAtOrAbove(32)]
+    want = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=procs)
+    model.overlap_decode_chunk_frames, model.overlap_decode_ctas = 16, 5
+    got = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=procs)
+    model.overlap_decode_chunk_frames, model.overlap_decode_ctas = 0, None
+    assert got.shape == want.shape
+    np.testing.assert_allclose(got.cpu().numpy(), want.cpu().numpy(), atol=1e-5)
+    lib = cabi.load()
+    assert lib.ptts_dac_set_cta_limit(0) == 0  # the pipeline restored the default after its launches
+    # the setter returns the previous value; a limited one-shot decode equals the unlimited one bit for bit
+    codes = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=procs,
+                           return_codes=True)
+    eng = model.audio_encoder.engine(model.decoder.impl)
+    full = eng.decode(codes)
+    assert lib.ptts_dac_set_cta_limit(3) == 0
+    try:
+        narrow = eng.decode(codes)
+    finally:
+        assert lib.ptts_dac_set_cta_limit(0) == 3
+    assert torch.equal(full, narrow)
+    # a streamer with a CTA limit and the timeline trace switched on
+    streamer = ptts.AudioChunkStreamer(chunk_frames=16, decode_ctas=7)
+    streamer.trace = True
+    audio = model.generate(input_ids=ids, prompt_input_ids=pids, do_sample=False, logits_processor=procs,
+                           streamer=streamer)
+    np.testing.assert_allclose(audio.cpu().numpy(), want.cpu().numpy(), atol=1e-5)
+    tl = streamer.timeline
+    assert len(tl["chunks"]) >= 1 and all(b >= a for _, _, _, a, b in tl["chunks"]) and tl["end_ms"] >= tl["loop_end_ms"]
