@@ -6,13 +6,17 @@
 // across a cluster): at M = 2112 (B=64 x 33 prefill positions) every weight tile is re-read 33 times and every token tile
 // 24 times from L2 - 312 MB of L2 traffic for a 13 GFLOP GEMM, 99 us per launch, 134 TFLOP/s
 // (profiles/r02_prefill_t5_kernels_v14.txt).  This is the plain tile kernel those shapes want:
-//   * CTA tile 128 token rows (tcgen05.mma M) x 128 weight rows (N), K in 64-element blocks through a 6-stage ring of
+//   * CTA tile 128 token rows (tcgen05.mma M) x 128 weight rows (N), K in 64-element blocks through a 5-stage ring of
 //     32 KB (A 16 KB + B 16 KB, cp.async.bulk.tensor 2-D box copies, SWIZZLE_128B);
 //   * persistent CTAs (one per SM), token tiles fastest so that the CTAs of a wave share weight tiles in L2;
 //   * warp 0 = TMA producer, warp 1 = MMA issuer (both a single elected lane), warps 2..5 = epilogue; two 128-column
 //     TMEM accumulators so that the epilogue of tile i runs under the MMAs of tile i + 1;
 //   * the fused epilogues of gemm_common.cuh (STORE: alpha / bias / activation / row mask / residual; SCATTER: q | k | v
-//     into their buffers and cache slots).
+//     into their buffers and cache slots), row by row: a TMEM lane is a token row, so a warp that stored straight from
+//     its registers wrote 32 different rows per instruction (one 4-byte pair per 32-byte sector; the epilogue, not the
+//     MMAs, set the kernel's time: ~57 us per launch at M = 2112 .. 3072).  Each epilogue warp therefore turns its
+//     32 x 64 block through a strip of shared memory and then walks the rows with lanes = consecutive column pairs:
+//     256-byte residual reads and 128-byte (bf16) / 256-byte (fp32) stores per instruction.
 #include <cuda.h>
 #include <string.h>
 
@@ -25,7 +29,9 @@ using namespace gemm;
 namespace {
 
 constexpr int GM = 128, GN = 128, GK = 64;
-constexpr int GSTAGES = 6;
+constexpr int GSTAGES = 5;
+constexpr int GSTRIP_PITCH = 64 + 4;                    // floats per strip row (the pad keeps float4 row writes at 4 wavefronts)
+constexpr int GSTRIP_BYTES = 32 * GSTRIP_PITCH * 4;     // one epilogue warp's 32 x 64 strip
 constexpr int GA_BYTES = GM * 128, GB_BYTES = GN * 128, GSTAGE_BYTES = GA_BYTES + GB_BYTES;
 constexpr int GTHREADS = 192;
 constexpr uint32_t GTMEM_COLS = 256;
@@ -170,19 +176,46 @@ gemm_big_kernel(const GemmParams p, int MT, int NT, const __grid_constant__ CUte
       const uint32_t buf = tt & 1u, use_acc = tt >> 1;
       big_wait<false>(acc_full + 8 * buf, use_acc & 1u);
       asm volatile("tcgen05.fence::after_thread_sync;\n" ::: "memory");
-      const int row = m0 + q * 32 + lane;
+      float* strip = reinterpret_cast<float*>(smem_raw + (sbase - smem_u32(smem_raw)) + GSTAGES * GSTAGE_BYTES) +
+                     (size_t)(warp - 2) * (GSTRIP_BYTES / 4);
 #pragma unroll 1
-      for (int c0 = 0; c0 < GN; c0 += 32) {
-        uint32_t v[32];
-        big_tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + buf * GN + c0, v);
-        asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
-        if (row < p.M) {
+      for (int c0 = 0; c0 < GN; c0 += 64) {
 #pragma unroll
-          for (int j = 0; j < 32; j += 2) {
-            const int col = n0 + c0 + j;
-            if (col < p.N) epilogue_pair<EPI>(p, row, col, 0, __uint_as_float(v[j]), __uint_as_float(v[j + 1]));
+        for (int h = 0; h < 2; ++h) {  // this lane's row, 2 x 32 columns -> strip[lane][..]
+          uint32_t v[32];
+          big_tmem_ld32(tmem_d + ((uint32_t)(q * 32) << 16) + buf * GN + c0 + 32 * h, v);
+          asm volatile("tcgen05.wait::ld.sync.aligned;\n" ::: "memory");
+#pragma unroll
+          for (int j = 0; j < 32; j += 4)
+            *reinterpret_cast<uint4*>(strip + lane * GSTRIP_PITCH + 32 * h + j) = make_uint4(v[j], v[j + 1], v[j + 2], v[j + 3]);
+        }
+        __syncwarp();
+        const int col = n0 + c0 + 2 * lane;  // lanes = consecutive column pairs of one row
+        if (col < p.N) {
+          bool has_res = false;
+          if constexpr (EPI == EPI_STORE) has_res = p.residual != nullptr;
+#pragma unroll 1
+          for (int r0 = 0; r0 < 32; r0 += 16) {
+            // the residual pairs of 16 rows are requested together (one L2 round trip instead of one per row)
+            float2 res[16];
+            if (has_res) {
+#pragma unroll
+              for (int u = 0; u < 16; ++u) {
+                const int row = m0 + q * 32 + r0 + u;
+                if (row < p.M) res[u] = __ldcg(reinterpret_cast<const float2*>(p.residual + (int64_t)row * p.N + col));
+              }
+            }
+#pragma unroll
+            for (int u = 0; u < 16; ++u) {
+              const int row = m0 + q * 32 + r0 + u;
+              if (row < p.M) {
+                const float2 a = *reinterpret_cast<const float2*>(strip + (r0 + u) * GSTRIP_PITCH + 2 * lane);
+                epilogue_pair<EPI>(p, row, col, 0, a.x, a.y, has_res ? &res[u] : nullptr);
+              }
+            }
           }
         }
+        __syncwarp();  // the strip is rewritten by the next 64 columns
       }
       asm volatile("tcgen05.fence::before_thread_sync;\n" ::: "memory");
       big_arrive(acc_empty + 8 * buf);
@@ -208,7 +241,7 @@ int launch_big(const GemmParams& p, cudaStream_t st) {
     if (g_sm_count <= 0) g_sm_count = 148;
   }
   const int MT = (p.M + GM - 1) / GM, NT = (p.N + GN - 1) / GN;
-  const size_t smem = (size_t)GSTAGES * GSTAGE_BYTES + 1024;
+  const size_t smem = (size_t)GSTAGES * GSTAGE_BYTES + 4 * GSTRIP_BYTES + 1024;
   static bool configured = false;
   if (!configured) {
     cudaFuncSetAttribute(gemm_big_kernel<EPI_STORE>, cudaFuncAttributeMaxDynamicSharedMemorySize, (int)smem);
