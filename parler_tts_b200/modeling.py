@@ -428,6 +428,12 @@ class SuppressTokensAtOrAbove:
         return scores
 
 
+def _drop_if_all_ones(mask):
+    """An attention mask without a zero masks nothing: None selects the kernels without the mask loads (the same sums
+    in the same order).  One small reduction + host read; callers do it before they queue long work."""
+    return None if mask is None or bool(mask.all()) else mask
+
+
 def _generate_codes(decoder, enc, enc_mask, prompt_table, prompt_ids, prompt_hidden, prompt_mask, decoder_input_ids,
                     gc, kwargs, logits_processor, stopping_criteria, streamer, impl, use_graph, seed, row_offset,
                     audio_engine=None):
@@ -723,6 +729,7 @@ class ParlerTTSForCausalLM(nn.Module):
                 prm_mask = torch.cat([prm_mask, torch.zeros_like(prm_mask)], dim=0)
             # encoder_hidden_states / encoder_attention_mask must already hold both halves (as in the reference,
             # where the composite model doubles them in _prepare_text_encoder_kwargs_for_generation)
+        enc_mask, prm_mask = _drop_if_all_ones(enc_mask), _drop_if_all_ones(prm_mask)
         if prm is not None:
             prm = prm.to(w.device, torch.float32).contiguous()
         if enc is None and prm is None:
@@ -930,6 +937,7 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         input_values = mk.pop("input_values", None)
         dev = self.device
         attention_mask = mk.pop("attention_mask", None)
+        mask_is_trivial = None  # True: every description position is attended (the decoder then runs without the mask)
         enc_out = mk.pop("encoder_outputs", None)
         if enc_out is not None:
             hs = enc_out[0] if isinstance(enc_out, (tuple, list)) else enc_out.last_hidden_state
@@ -943,7 +951,10 @@ class ParlerTTSForConditionalGeneration(nn.Module):
                     attention_mask = (input_ids != pad).long()
                 else:
                     attention_mask = torch.ones_like(input_ids)
+                    mask_is_trivial = True
             attention_mask = attention_mask.to(dev)
+            if mask_is_trivial is None:  # a caller's mask: looked at now, before the encoder is queued
+                mask_is_trivial = _drop_if_all_ones(attention_mask) is None
             with _nvtx("ptts.t5_encode"):
                 hs = self.encode_text(input_ids, attention_mask)
         B = hs.shape[0]
@@ -953,7 +964,7 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         cfg = gc.guidance_scale is not None and gc.guidance_scale > 1
         prompt_ids = mk.pop("prompt_input_ids", None)
         prompt_hidden = mk.pop("prompt_hidden_states", None)
-        prompt_mask = mk.pop("prompt_attention_mask", None)
+        prompt_mask = _drop_if_all_ones(mk.pop("prompt_attention_mask", None))
         dec_ids = mk.pop("decoder_input_ids", None)
         if input_values is not None:
             # audio-prompt continuation (modeling_parler_tts.py:2247-2292): the prompt's codes become decoder_input_ids
@@ -975,6 +986,11 @@ class ParlerTTSForConditionalGeneration(nn.Module):
             hs, attention_mask, prompt_ids, prompt_hidden, prompt_mask, dec_ids = map(
                 rep, (hs, attention_mask, prompt_ids, prompt_hidden, prompt_mask, dec_ids))
         enc = self.project_encoder(hs, attention_mask)
+        if attention_mask is not None and not cfg and (mask_is_trivial or _drop_if_all_ones(attention_mask) is None):
+            # all ones (the usual equal-length batch, modeling_parler_tts.py's ones_like default): the cross-attention of
+            # every decode step would load and test the mask for nothing - 1.259 against 1.203 ms per step at B=64
+            # (profiles/r02_e2e_phases_fine_v19.txt)
+            attention_mask = None
         prompt_table = None
         if prompt_hidden is not None:
             prompt_hidden, prompt_ids = prompt_hidden.to(dev, torch.float32).contiguous(), None
