@@ -98,6 +98,29 @@ def test_generate_masks_sampling_and_guidance_vs_oracle():
         assert np.array_equal(codes.cpu().numpy(), res["codes"]), kw
 
 
+def test_generate_masks_without_a_zero_equal_no_mask():
+    """An attention mask of ones masks nothing (the reference multiplies by it and adds a zero bias,
+    modeling_parler_tts.py:2010-2017): generate() hands the decoder no mask then, the mask-free kernels run, and the
+    codes equal those of a call without masks - also for a caller's explicit masks of ones, with and without guidance."""
+    model, dims, sd, dac_sd = _composite()
+    g = torch.Generator().manual_seed(6)
+    input_ids, prompt_ids = torch.randint(2, 100, (3, 6), generator=g).to(DEV), torch.randint(2, 100, (3, 5), generator=g).to(DEV)
+    for kw in (dict(do_sample=False), dict(do_sample=True, top_k=10, seed=4), dict(do_sample=False, guidance_scale=2.0)):
+        want = model.generate(input_ids=input_ids, prompt_input_ids=prompt_ids, max_length=20, return_codes=True, **kw)
+        got = model.generate(input_ids=input_ids, attention_mask=torch.ones_like(input_ids), prompt_input_ids=prompt_ids,
+                             prompt_attention_mask=torch.ones_like(prompt_ids).cpu(), max_length=20, return_codes=True, **kw)
+        assert torch.equal(got, want), kw
+        if not kw.get("guidance_scale"):
+            st = model.decoder._state_cache[1]
+            assert st.enc_mask is None and st.prompt_mask is None  # the loop ran without the mask loads
+    # the oracle (which applies the mask of ones) agrees
+    res, _ = _oracle_generate(model, dims, sd, dac_sd, input_ids.cpu(), prompt_ids.cpu(), torch.ones(3, 6, dtype=torch.int64),
+                              None, decode=False, max_length=20, do_sample=False)
+    codes = model.generate(input_ids=input_ids, attention_mask=torch.ones_like(input_ids), prompt_input_ids=prompt_ids,
+                           max_length=20, return_codes=True, do_sample=False)
+    assert np.array_equal(codes.cpu().numpy(), res["codes"])
+
+
 def test_generate_ragged_audio_and_out_of_range_codes():
     """Unsuppressed random-init generation emits EOS/unused ids: special ids route to the per-sample path with zero
     right-padding (modeling_parler_tts.py:2664-2680); an id >= codebook_size without any special id raises like the
