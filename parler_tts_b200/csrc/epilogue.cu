@@ -155,12 +155,31 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
     uint32_t thr = 0u;
     const int kk = top_k > 0 ? min(top_k, V) : V;
     if (top_k > 0) {
-      for (int bit = 31; bit >= 0; --bit) {
-        const uint32_t cand = thr | (1u << bit);
-        int cnt = 0;
-        for (int i = lane; i < V; i += 32) cnt += order_key(sc[i]) >= cand;
-        cnt = __reduce_add_sync(0xffffffffu, cnt);
-        if (cnt >= kk) thr = cand;
+      constexpr int KREG = 36;  // ordered keys a lane keeps in registers for the 32 search steps: rows of up to 1152 logits
+      if (V <= KREG * 32) {
+        uint32_t key[KREG];
+#pragma unroll
+        for (int t = 0; t < KREG; ++t) {
+          const int i = lane + 32 * t;
+          key[t] = i < V ? order_key(sc[i]) : 0u;  // 0 is below every candidate: slots past the row never count
+        }
+#pragma unroll 1
+        for (int bit = 31; bit >= 0; --bit) {
+          const uint32_t cand = thr | (1u << bit);
+          int cnt = 0;
+#pragma unroll
+          for (int t = 0; t < KREG; ++t) cnt += key[t] >= cand;
+          cnt = __reduce_add_sync(0xffffffffu, cnt);
+          if (cnt >= kk) thr = cand;
+        }
+      } else {
+        for (int bit = 31; bit >= 0; --bit) {
+          const uint32_t cand = thr | (1u << bit);
+          int cnt = 0;
+          for (int i = lane; i < V; i += 32) cnt += order_key(sc[i]) >= cand;
+          cnt = __reduce_add_sync(0xffffffffu, cnt);
+          if (cnt >= kk) thr = cand;
+        }
       }
     }
     // ordered compaction of the kept set
@@ -211,24 +230,48 @@ step_epilogue_kernel(const float* __restrict__ embed, const float* __restrict__ 
       __syncwarp();
     }
     int choice = 0;
-    if (lane == 0) {
-      float total = 0.f;
-      for (int j = 0; j < nk; ++j) total += expf(sc[kept[j]] - mx);  // fixed ascending-index fp32 order
-      uint32_t rnd[4];
-      const uint64_t grow = (uint64_t)(row_offset + r);
-      // the Philox key lives in the control block so that a captured graph can be replayed with a new seed
-      philox4x32_10((uint32_t)grow, (uint32_t)(len - T0), 0u, 0u, (uint32_t)ctrl->reserved[0],
-                    (uint32_t)ctrl->reserved[1], rnd);
-      const float u = (float)(((double)rnd[0] + 0.5) * 2.3283064365386963e-10);
-      const float thresh = u * total;
-      float acc = 0.f;
-      choice = kept[nk - 1];
+    uint32_t rnd[4];
+    const uint64_t grow = (uint64_t)(row_offset + r);
+    // the Philox key lives in the control block so that a captured graph can be replayed with a new seed
+    philox4x32_10((uint32_t)grow, (uint32_t)(len - T0), 0u, 0u, (uint32_t)ctrl->reserved[0], (uint32_t)ctrl->reserved[1],
+                  rnd);
+    const float u = (float)(((double)rnd[0] + 0.5) * 2.3283064365386963e-10);
+    if (nk <= 64 && V >= 64) {
+      // the usual top-k case.  The sums keep the fixed ascending-index fp32 order (the draw must not depend on the launch
+      // geometry), but the exponentials are taken by all lanes at once and the serial part is a chain of adds over a
+      // contiguous strip: every lane runs it (broadcast reads) and notes the prefix sums of its own two candidates
+      const int k0 = lane < nk ? kept[lane] : 0, k1 = lane + 32 < nk ? kept[lane + 32] : 0;
+      const float e0 = lane < nk ? expf(sc[k0] - mx) : 0.f, e1 = lane + 32 < nk ? expf(sc[k1] - mx) : 0.f;
+      __syncwarp();  // every score has been read: the head of the row becomes the strip
+      sc[lane] = e0;
+      sc[lane + 32] = e1;
+      __syncwarp();
+      float acc = 0.f, p0 = 0.f, p1 = 0.f;
       for (int j = 0; j < nk; ++j) {
-        acc += expf(sc[kept[j]] - mx);
-        if (acc > thresh) { choice = kept[j]; break; }
+        acc += sc[j];
+        if (j == lane) p0 = acc;
+        if (j == lane + 32) p1 = acc;
       }
+      const float thresh = u * acc;
+      const unsigned b0 = __ballot_sync(0xffffffffu, lane < nk && p0 > thresh);
+      const unsigned b1 = __ballot_sync(0xffffffffu, lane + 32 < nk && p1 > thresh);
+      const int pick = b0 ? __ffs(b0) - 1 : (b1 ? 32 + __ffs(b1) - 1 : nk - 1);
+      choice = pick < 32 ? __shfl_sync(0xffffffffu, k0, pick & 31) : __shfl_sync(0xffffffffu, k1, pick & 31);
+    } else {
+      if (lane == 0) {
+        float total = 0.f;
+        for (int j = 0; j < nk; ++j) total += expf(sc[kept[j]] - mx);  // fixed ascending-index fp32 order
+        const float thresh = u * total;
+        float acc = 0.f;
+        choice = kept[nk - 1];
+        for (int j = 0; j < nk; ++j) {
+          acc += expf(sc[kept[j]] - mx);
+          if (acc > thresh) { choice = kept[j]; break; }
+        }
+      }
+      choice = __shfl_sync(0xffffffffu, choice, 0);
     }
-    tok = __shfl_sync(0xffffffffu, choice, 0);
+    tok = choice;
   }
 
   // ---- EOS / PAD bookkeeping, token write, delay mask for the next input
