@@ -13,10 +13,12 @@
 //     TMEM accumulators so that the epilogue of tile i runs under the MMAs of tile i + 1;
 //   * the fused epilogues of gemm_common.cuh (STORE: alpha / bias / activation / row mask / residual; SCATTER: q | k | v
 //     into their buffers and cache slots), row by row: a TMEM lane is a token row, so a warp that stored straight from
-//     its registers wrote 32 different rows per instruction (one 4-byte pair per 32-byte sector; the epilogue, not the
-//     MMAs, set the kernel's time: ~57 us per launch at M = 2112 .. 3072).  Each epilogue warp therefore turns its
+//     its registers wrote 32 different rows per instruction (one 4-byte pair per 32-byte sector; with an fp32 residual
+//     that cost 27 us per launch at M = 2112: 48 against 21 us for the same shape without one).  Each epilogue warp turns its
 //     32 x 64 block through a strip of shared memory and then walks the rows with lanes = consecutive column pairs:
 //     256-byte residual reads and 128-byte (bf16) / 256-byte (fp32) stores per instruction.
+//   Known limit (profiles/r02_prefill_t5_launches_v19.txt): the operand stages arrive at ~13 bytes per clock per SM and the
+//   tensor pipe is busy 11 - 21 % of the time; ~200 - 300 TFLOP/s on the prefill shapes.  Once-per-call work (~1 % of a call).
 #include <cuda.h>
 #include <string.h>
 
