@@ -128,10 +128,12 @@ class DACModel(nn.Module):
 
     config_class = DACConfig
 
-    def __init__(self, config: DACConfig, state_dict=None, decoder_dim=1536, rates=(8, 8, 4, 2), codebook_dim=8):
+    def __init__(self, config: DACConfig, state_dict=None, decoder_dim=1536, rates=None, codebook_dim=8):
         super().__init__()
         self.config = config
-        self.rates = tuple(rates)
+        if rates is None:  # a checkpoint states its own up-sampling rates; random init takes the 44.1 kHz model's
+            rates = _dac_rates_of(state_dict) if state_dict is not None else (8, 8, 4, 2)
+        self.rates = tuple(int(r) for r in rates)
         self.model = _Node()
         if state_dict is None:
             state_dict = _random_dac_state(config, decoder_dim, self.rates, codebook_dim)
@@ -186,6 +188,24 @@ class DACModel(nn.Module):
 
     def forward(self, tensor):
         raise ValueError("`DACModel.forward` not implemented yet")
+
+
+def _dac_rates_of(state_dict):
+    """Up-sampling rates of a descript DAC decoder read from its checkpoint: block i holds a transposed conv
+    `decoder.model.{i}.block.1` whose kernel is twice its stride (descript DecoderBlock)."""
+    rates, i = [], 1
+    while True:
+        w = state_dict.get(f"decoder.model.{i}.block.1.weight_v", state_dict.get(f"decoder.model.{i}.block.1.weight"))
+        if w is None:
+            break
+        if w.dim() != 3 or w.shape[-1] % 2:
+            raise ValueError(f"decoder.model.{i}.block.1: expected a transposed conv with an even kernel, got "
+                             f"{tuple(w.shape)}")
+        rates.append(w.shape[-1] // 2)
+        i += 1
+    if not rates:
+        raise ValueError("no decoder.model.<i>.block.1 transposed conv in the DAC state dict: cannot infer the rates")
+    return tuple(rates)
 
 
 def _random_dac_state(config, decoder_dim, rates, codebook_dim, seed=0):

@@ -37,3 +37,28 @@ def test_window_is_complete_when_chunk_ready_columns_exist():
         assert max(hi + k + 1 for k in range(K)) == cols  # frame `hi` would need one more column
         win = np.stack([[applied[b * K + k, np.arange(hi) + k + 1] for k in range(K)] for b in range(B)])
         assert np.array_equal(win, full[:, :, :hi])
+
+
+def test_dac_rates_are_read_from_the_checkpoint():
+    """A DAC checkpoint states its own up-sampling rates (kernel of `decoder.model.{i}.block.1` = 2 x stride, descript
+    DecoderBlock): DACModel(state_dict=...) must not assume the 44.1 kHz model's (8, 8, 4, 2)."""
+    import pytest
+    import torch
+
+    import parler_tts_b200 as ptts
+    from oracle import dac_oracle
+    from parler_tts_b200.modeling import _dac_rates_of
+
+    for rates in ((8, 8, 4, 2), (2, 4, 5, 8), (4, 4)):
+        cfg = dict(n_codebooks=2, codebook_size=16, codebook_dim=4, latent_dim=32, decoder_dim=32, rates=rates)
+        sd = dac_oracle.random_dac_state(cfg, seed=1)
+        assert _dac_rates_of(sd) == rates
+        m = ptts.DACModel(ptts.DACConfig(num_codebooks=2, codebook_size=16, latent_dim=32), state_dict=sd)
+        assert m.rates == rates
+        # an explicit argument still wins, random init keeps the reference model's rates
+        assert ptts.DACModel(ptts.DACConfig(num_codebooks=2, codebook_size=16, latent_dim=32), state_dict=sd,
+                             rates=rates[::-1]).rates == rates[::-1]
+    assert ptts.DACModel(ptts.DACConfig(num_codebooks=2, codebook_size=16, latent_dim=32), decoder_dim=32,
+                         codebook_dim=4).rates == (8, 8, 4, 2)
+    with pytest.raises(ValueError):
+        _dac_rates_of({"decoder.model.0.weight_v": torch.zeros(4, 4, 7)})
