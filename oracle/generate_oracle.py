@@ -20,7 +20,10 @@ this file's inverse-CDF draw over a Philox4x32-10 uniform keyed by (seed, row, s
 epilogue uses ("parity unpinned" for the random stream itself; the candidate set, temperature and renormalisation
 follow the library's published algorithm).
 
-The loop itself is pinned against a probe that drives the reference decoder (tests/golden/loop_tiny.npz).
+The loop itself is pinned twice: against a probe that drives the reference decoder (tests/golden/loop_tiny.npz), and,
+live, against the installed transformers library's own `GenerationMixin.generate` / `_sample` loop over a stateless
+probe model (tests/test_oracle_vs_transformers_loop.py: EOS freeze + PAD fill, early stop, max_length stop, min_length /
+min_new_tokens, repetition penalty - raw sequences bit-identical).
 """
 import numpy as np
 import torch
