@@ -39,8 +39,10 @@ class _Probe(PreTrainedModel, GenerationMixin):
     main_input_name = "input_ids"
     _supports_cache_class = False
 
-    def __init__(self, config, rows, max_len, seed, eos_at):
+    def __init__(self, config, rows, max_len, seed, eos_at, guided=False):
         super().__init__(config)
+        self.guided = guided
+        rows = 2 * rows if guided else rows  # the second half plays the unconditional rows
         g = torch.Generator().manual_seed(seed)
         D = 24
         self.E = torch.nn.Parameter(torch.randn(V + 2, D, generator=g), requires_grad=False)
@@ -69,20 +71,27 @@ class _Probe(PreTrainedModel, GenerationMixin):
 
     def prepare_inputs_for_generation(self, input_ids, **kwargs):
         # modeling_parler_tts.py:2107: the mask is applied to the model's input, the loop keeps the raw tokens
-        applied = dp.apply_delay_pattern_mask(input_ids.numpy(), self.pattern)
-        return {"input_ids": torch.from_numpy(applied)}
+        applied = torch.from_numpy(dp.apply_delay_pattern_mask(input_ids.numpy(), self.pattern))
+        if self.guided:  # modeling_parler_tts.py:2108-2111: decoder args replicated across the batch dim
+            applied = applied.repeat((2, 1))
+        return {"input_ids": applied}
 
 
-def _run_both(B, max_length, eos_at, seed, **gen_kw):
+def _run_both(B, max_length, eos_at, seed, guidance_scale=None, **gen_kw):
     rows = B * K
-    probe = _Probe(_ProbeConfig(pad_token_id=PAD, eos_token_id=EOS, bos_token_id=BOS), rows, max_length, seed, eos_at)
+    probe = _Probe(_ProbeConfig(pad_token_id=PAD, eos_token_id=EOS, bos_token_id=BOS), rows, max_length, seed, eos_at,
+                   guided=guidance_scale is not None)
     probe.eval()
     start = np.full((rows, 1), BOS, dtype=np.int64)
     ids0, pattern = dp.build_delay_pattern_mask(start, BOS, PAD, max_length, K)
     probe.pattern = pattern
     assert ids0.shape == (rows, 1)
 
-    # the library's loop
+    # the library's loop (guidance as the reference wires it: its own batched processor appended to the caller's list,
+    # generation_config.guidance_scale left unset, modeling_parler_tts.py:2555-2558)
+    if guidance_scale is not None:
+        from transformers import ClassifierFreeGuidanceLogitsProcessor, LogitsProcessorList
+        gen_kw = dict(gen_kw, logits_processor=LogitsProcessorList([ClassifierFreeGuidanceLogitsProcessor(guidance_scale)]))
     with torch.no_grad():
         got = probe.generate(input_ids=torch.from_numpy(ids0), max_length=max_length, do_sample=False, num_beams=1,
                              use_cache=False, pad_token_id=PAD, eos_token_id=EOS, **gen_kw)
@@ -94,7 +103,8 @@ def _run_both(B, max_length, eos_at, seed, **gen_kw):
 
     enc = torch.zeros(B, 1, 1)
     okw = {k: v for k, v in gen_kw.items() if k in ("min_length", "min_new_tokens", "repetition_penalty")}
-    want = generate_oracle.generate_codes(None, DIMS, enc, max_length=max_length, do_sample=False, forward_fn=fwd, **okw)
+    want = generate_oracle.generate_codes(None, DIMS, enc, max_length=max_length, do_sample=False, forward_fn=fwd,
+                                          guidance_scale=guidance_scale, **okw)
     return got, want, probe
 
 
@@ -157,3 +167,14 @@ def test_final_codes_follow_from_the_library_sequences():
     start = np.full((2 * K, 1), BOS, dtype=np.int64)
     codes = dp.revert_delay_pattern(got, start, probe.pattern, BOS, PAD, K)
     assert np.array_equal(codes, want["codes"])
+
+
+def test_classifier_free_guidance_mixes_the_two_halves_like_the_library_processor():
+    """modeling_parler_tts.py:2108-2111 + 2555-2558: 2R logit rows in, transformers' ClassifierFreeGuidanceLogitsProcessor
+    mixes them to R score rows; EOS freeze and the stop rule act on the R rows."""
+    got, want, probe = _run_both(B=2, max_length=16, eos_at=[(2, 5)], seed=7, guidance_scale=3.0)
+    _assert_same(got, want)
+    assert got.shape[0] == 2 * K and probe.seen[-1].shape[0] == 4 * K
+    assert got[2, 6] == EOS and (got[2, 6:] == PAD).all()
+    other, _, _ = _run_both(B=2, max_length=16, eos_at=[(2, 5)], seed=7, guidance_scale=1.5)
+    assert not np.array_equal(other, got)  # the scale matters, so the mix was exercised
