@@ -350,10 +350,29 @@ def gen_c1(ref, seeds=(1234, 1235, 1236, 1237, 1238, 1239)):
     print(f"c1_mini.npz written: codes {res64['codes'].shape}, fp32-vs-fp64 reference logit error {err:.2e}")
 
 
+def gen_positions(ref):
+    """Known answers of the reference's position-table generator (modeling_parler_tts.py:200-213,
+    ParlerTTSSinusoidalPositionalEmbedding.get_embedding): small tables whole, the Mini table (4096 x 1024) as a
+    sample of rows plus an fp64 sum per row."""
+    from parler_tts.modeling_parler_tts import ParlerTTSSinusoidalPositionalEmbedding as Pos
+
+    out = {}
+    for n, d in ((64, 16), (37, 9), (5, 128)):
+        out[f"tab_{n}_{d}"] = Pos.get_embedding(n, d).numpy()
+    big = Pos.get_embedding(4096, 1024)
+    rows = np.array([0, 1, 2, 33, 466, 901, 2609, 4095])
+    out["mini_rows"] = rows
+    out["mini_sample"] = big[rows].numpy()
+    out["mini_row_sums"] = big.double().sum(dim=1).numpy()
+    np.savez_compressed(os.path.join(GOLD, "positions.npz"), **out)
+    print("positions.npz:", {k: v.shape for k, v in out.items()})
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = import_reference()
     gen_delay(ref)
+    gen_positions(ref)
     dims, sd, model = gen_decoder(ref)
     gen_loop(ref, dims, sd, model)
     gen_dac()
@@ -362,7 +381,9 @@ def main():
     gen_c1(ref)
 
 
-if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "c1":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "positions":
+    gen_positions(import_reference())
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "c1":
     gen_c1(import_reference())
 elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "t5":
     gen_t5()  # transformers only: does not need /root/reference

@@ -18,6 +18,22 @@ def test_delay_mask_docstring_kat():
     assert np.array_equal(mask, want)
 
 
+def test_position_table_vs_reference(golden_dir):
+    """ParlerTTSSinusoidalPositionalEmbedding.get_embedding (modeling_parler_tts.py:200-213): the table a random-init
+    model is built with - the host's generator and the oracle's - equals the reference's bit for bit (even and odd
+    widths; the 4096 x 1024 Mini table through sampled rows and a per-row fp64 sum)."""
+    from parler_tts_b200.modeling import sinusoidal_table as host_table
+
+    z = np.load(os.path.join(golden_dir, "positions.npz"))
+    for fn in (host_table, decoder_oracle.sinusoidal_table):
+        for n, d in ((64, 16), (37, 9), (5, 128)):
+            got = fn(n, d).numpy()
+            assert got.dtype == np.float32 and np.array_equal(got, z[f"tab_{n}_{d}"]), (fn.__module__, n, d)
+        big = fn(4096, 1024)
+        assert np.array_equal(big[torch.from_numpy(z["mini_rows"])].numpy(), z["mini_sample"])
+        assert np.array_equal(big.double().sum(dim=1).numpy(), z["mini_row_sums"])
+
+
 def test_delay_mask_vs_reference(golden_dir):
     z = np.load(os.path.join(golden_dir, "delay_patterns.npz"))
     for name in CASES:
