@@ -178,3 +178,46 @@ def test_classifier_free_guidance_mixes_the_two_halves_like_the_library_processo
     assert got[2, 6] == EOS and (got[2, 6:] == PAD).all()
     other, _, _ = _run_both(B=2, max_length=16, eos_at=[(2, 5)], seed=7, guidance_scale=1.5)
     assert not np.array_equal(other, got)  # the scale matters, so the mix was exercised
+
+
+def test_sampling_candidate_set_is_the_library_warpers_set():
+    """_get_logits_warper (modeling_parler_tts.py:2597): temperature, then top-k (ties with the k-th largest kept), then
+    top-p.  The library's processed scores of the first step (`output_scores`) are finite exactly on the oracle's
+    candidate set, and hold logits / temperature there; the draw itself (torch.multinomial) is not comparable."""
+    from transformers.generation import logits_process as lp
+
+    # class level, with ties at the k-th largest value
+    g = torch.Generator().manual_seed(0)
+    scores = torch.randn(5, V, generator=g)
+    scores[:, 7] = scores[:, 3]
+    scores[0, 3] = scores[0, 7] = scores[0].topk(4)[0][-1]  # row 0: a tie exactly at the k-th largest (k = 4)
+    for k in (1, 4, 50):
+        want = lp.TopKLogitsWarper(k)(None, scores.clone())
+        for r in range(5):
+            keep = generate_oracle.topk_candidates(scores[r].numpy(), k)
+            assert np.array_equal(keep, torch.isfinite(want[r]).numpy()), (k, r)
+
+    # loop level: what the library would sample from at step 0
+    B, max_length, temp, k, p = 2, 2, 0.7, 6, 0.8
+    rows = B * K
+    probe = _Probe(_ProbeConfig(pad_token_id=PAD, eos_token_id=EOS, bos_token_id=BOS), rows, max_length, 11, [])
+    probe.eval()
+    start = np.full((rows, 1), BOS, dtype=np.int64)
+    ids0, probe.pattern = dp.build_delay_pattern_mask(start, BOS, PAD, max_length, K)
+    torch.manual_seed(0)
+    with torch.no_grad():
+        out = probe.generate(input_ids=torch.from_numpy(ids0), max_length=max_length, do_sample=True, temperature=temp,
+                             top_k=k, top_p=p, use_cache=False, pad_token_id=PAD, eos_token_id=EOS, output_scores=True,
+                             return_dict_in_generate=True)
+    lib = out.scores[0]
+    raw = probe.logits_of(torch.from_numpy(ids0))[:, -1].float()
+    for r in range(rows):
+        s = (raw[r].numpy() / np.float32(temp)).astype(np.float32)
+        keep = generate_oracle.topp_candidates(s, generate_oracle.topk_candidates(s, k), p)
+        fin = torch.isfinite(lib[r]).numpy()
+        assert np.array_equal(keep, fin), r
+        assert 1 <= keep.sum() <= k
+        assert np.allclose(lib[r].numpy()[fin], s[fin], rtol=0, atol=1e-6)
+        # and the oracle's draw can only land inside that set
+        for u in (1e-6, 0.3, 0.999999):
+            assert keep[generate_oracle.sample_row(raw[r].numpy(), u, temperature=temp, top_k=k, top_p=p)]
