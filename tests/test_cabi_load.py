@@ -62,6 +62,20 @@ def test_reference_import_name_resolves():
     for name in ("ParlerTTSForConditionalGeneration", "ParlerTTSForCausalLM", "ParlerTTSConfig", "ParlerTTSDecoderConfig",
                  "DACConfig", "DACModel", "build_delay_pattern_mask", "apply_delay_pattern_mask"):
         assert getattr(parler_tts, name) is getattr(parler_tts_b200, name), name
+    # the reference's module paths resolve too (parler_tts/modeling_parler_tts.py, configuration_parler_tts.py, dac_wrapper/)
+    from parler_tts.configuration_parler_tts import ParlerTTSConfig, ParlerTTSDecoderConfig
+    from parler_tts.dac_wrapper import DACConfig, DACModel
+    from parler_tts.dac_wrapper.configuration_dac import DACConfig as C2
+    from parler_tts.dac_wrapper.modeling_dac import DACModel as M2
+    from parler_tts.modeling_parler_tts import (ParlerTTSForCausalLM, ParlerTTSForConditionalGeneration,
+                                                apply_delay_pattern_mask, build_delay_pattern_mask)
+
+    assert ParlerTTSConfig is parler_tts_b200.ParlerTTSConfig and ParlerTTSDecoderConfig is parler_tts_b200.ParlerTTSDecoderConfig
+    assert DACConfig is C2 is parler_tts_b200.DACConfig and DACModel is M2 is parler_tts_b200.DACModel
+    assert ParlerTTSForCausalLM is parler_tts_b200.ParlerTTSForCausalLM
+    assert ParlerTTSForConditionalGeneration is parler_tts_b200.ParlerTTSForConditionalGeneration
+    assert build_delay_pattern_mask is parler_tts_b200.build_delay_pattern_mask
+    assert apply_delay_pattern_mask is parler_tts_b200.apply_delay_pattern_mask
 
 
 def test_argument_errors_are_reported_without_a_gpu():
