@@ -170,11 +170,19 @@ def test_mini_architecture_fp32_greedy_token_exact_margin_gated():
     got = torch.stack(rec.scores)[:, :, :1024]
     ref = want["scores"][:, :, :1024]
     top2 = ref.topk(2, dim=-1).values
-    margin = float((top2[..., 0] - top2[..., 1]).min())
+    margins = top2[..., 0] - top2[..., 1]  # (steps, rows)
     err = float((got - ref).abs().max())
     assert err < 1e-3, err
-    if margin > 10 * err:
+    # every decision in front of the first one the oracle itself calls too close is compared UNCONDITIONALLY (greedy,
+    # ids >= 1024 suppressed: the chosen token is the argmax of the recorded scores); the first step always is
+    unsure = (margins <= 10 * err).any(dim=1)
+    n_sure = int(unsure.float().argmax()) if bool(unsure.any()) else margins.shape[0]
+    assert n_sure >= 1, (float(margins[0].min()), err)
+    assert torch.equal(got[:n_sure].argmax(-1), ref[:n_sure].argmax(-1))
+    if n_sure == margins.shape[0]:
         assert np.array_equal(codes.cpu().numpy(), want["codes"])
+    # (the unconditional full-length statement at this depth is test_gpu_baseline_configs.py, whose inputs were chosen
+    # for their margin against the reference decoder in float64)
 
 
 # ------------------------------------------------------------------------------------------------ epilogue
