@@ -62,3 +62,35 @@ def test_dac_rates_are_read_from_the_checkpoint():
                          codebook_dim=4).rates == (8, 8, 4, 2)
     with pytest.raises(ValueError):
         _dac_rates_of({"decoder.model.0.weight_v": torch.zeros(4, 4, 7)})
+
+
+def test_generation_length_and_mode_rules_follow_the_reference():
+    """Steps 1 and 6 of the reference generate (modeling_parler_tts.py:2416-2422, 2499-2521, 2575-2579): `max_new_tokens`
+    wins over `max_length` and counts from the decoder input length, an unset `max_length` is the library default 20,
+    `min_length > max_length` and beam search raise the reference's ValueErrors."""
+    import pytest
+    from transformers.generation.configuration_utils import GenerationConfig
+
+    from parler_tts_b200.modeling import _final_max_length, _gcv, _resolve_generation
+
+    base = GenerationConfig(max_length=2580, do_sample=True, pad_token_id=1024, eos_token_id=1024, bos_token_id=1025)
+    gc, rest = _resolve_generation(base, None, dict(max_new_tokens=30, prompt_input_ids="kept for the model"), None)
+    assert rest == {"prompt_input_ids": "kept for the model"} and base.max_new_tokens is None  # the caller's config is copied
+    assert _final_max_length(gc, {}, input_len=1) == 31
+    assert _final_max_length(_resolve_generation(base, None, dict(max_new_tokens=30), None)[0], {}, input_len=4) == 34
+    assert _final_max_length(_resolve_generation(base, None, {}, None)[0], {}, 1) == 2580
+    assert _final_max_length(_resolve_generation(base, None, dict(max_length=50), None)[0], {}, 1) == 50
+    bare = GenerationConfig()
+    bare.max_length = None
+    assert _final_max_length(_resolve_generation(bare, None, {}, None)[0], {}, 1) == 20
+    # an explicit generation_config replaces the model's; pad falls back to (the first) eos
+    other = GenerationConfig(max_length=77, eos_token_id=[5, 6])
+    gc, _ = _resolve_generation(base, other, {}, None)
+    assert gc.max_length == 77 and gc.pad_token_id == 5
+    # transformers <= 4.40 defaults for unset fields (top_k = 50 is the one that changes results)
+    assert _gcv(gc, "top_k") == 50 and _gcv(gc, "temperature") == 1.0 and _gcv(gc, "num_beams") == 1
+    with pytest.raises(ValueError, match="Unfeasible length constraints"):
+        _final_max_length(_resolve_generation(base, None, dict(max_length=10, min_length=11), None)[0], {}, 1)
+    for bad in (dict(num_beams=2), dict(num_beams=4, num_beam_groups=2, diversity_penalty=0.5)):
+        with pytest.raises(ValueError, match="incompatible mode for generation"):
+            _resolve_generation(base, None, bad, None)
