@@ -61,6 +61,42 @@ def gen_delay(ref):
     print("delay_patterns.npz:", len(specs), "cases")
 
 
+def gen_delay_random(ref, n=48, seed=20):
+    """Randomised cases of the same two reference functions (modeling_parler_tts.py:68-139): 1..9 codebooks, prompts of
+    every admissible length 1 <= T <= M - K + 1 (T = M - K + 1 is the "nothing left to fill" branch, :131-133), prompt
+    values that collide with BOS / PAD, M on both sides of 2K - 1 (the degenerate all -1 mask, :105-106)."""
+    rng = np.random.default_rng(seed)
+    cases, names = {}, []
+    for i in range(n):
+        K = int(rng.integers(1, 10))
+        B = int(rng.integers(1, 4))
+        degenerate = i % 8 == 7 and K >= 2
+        M = int(rng.integers(1, 2 * K - 1)) if degenerate else int(rng.integers(2 * K - 1, 2 * K + 40))
+        t_max = M if degenerate else M - K + 1
+        T = t_max if i % 6 == 5 else int(rng.integers(1, t_max + 1))
+        pad = int(rng.integers(8, 2000))
+        bos = pad + 1 if i % 3 else int(rng.integers(0, pad))
+        ids = rng.integers(0, pad + 2, size=(B * K, T)).astype(np.int64)
+        if i % 2 == 0:
+            ids[:, 0] = bos
+        out_ids, mask = ref.build_delay_pattern_mask(torch.from_numpy(ids), bos, pad, M, K)
+        name = f"r{i:02d}"
+        names.append(name)
+        cases[name + "_in"] = ids
+        cases[name + "_meta"] = np.array([B, K, M, T, bos, pad], dtype=np.int64)
+        cases[name + "_ids"] = out_ids.numpy()
+        cases[name + "_mask"] = mask.numpy()
+        gen = rng.integers(0, pad + 2, size=(B * K, int(rng.integers(1, M + 1)))).astype(np.int64)
+        cases[name + "_gen"] = gen
+        cases[name + "_applied"] = ref.apply_delay_pattern_mask(torch.from_numpy(gen), mask).numpy()
+    cases["names"] = np.array(names)
+    np.savez_compressed(os.path.join(GOLD, "delay_patterns_random.npz"), **cases)
+    print("delay_patterns_random.npz:", n, "cases;",
+          sum(1 for nm in names if (cases[nm + "_mask"] == -1).all()), "degenerate,",
+          sum(1 for nm in names if not (cases[nm + "_mask"][:: int(cases[nm + "_meta"][1])] == -1).any()),
+          "with nothing left to fill in the first codebook")
+
+
 def _ref_decoder(ref, dims, sd):
     cfg = ref.ParlerTTSDecoderConfig(
         vocab_size=dims.vocab_size, max_position_embeddings=dims.max_position_embeddings,
@@ -372,6 +408,7 @@ def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = import_reference()
     gen_delay(ref)
+    gen_delay_random(ref)
     gen_positions(ref)
     dims, sd, model = gen_decoder(ref)
     gen_loop(ref, dims, sd, model)
@@ -381,7 +418,9 @@ def main():
     gen_c1(ref)
 
 
-if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "positions":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "delay_random":
+    gen_delay_random(import_reference())
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "positions":
     gen_positions(import_reference())
 elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "c1":
     gen_c1(import_reference())

@@ -44,6 +44,19 @@ def test_delay_mask_bit_exact_vs_reference_fixture(golden_dir):
         assert np.array_equal(applied.cpu().numpy(), z[name + "_applied"]), name
 
 
+def test_delay_mask_bit_exact_vs_reference_randomised(golden_dir):
+    """48 randomised reference cases (oracle/gen_golden.py delay_random): 1..9 codebooks, every admissible prompt length,
+    prompt values colliding with BOS / PAD, the degenerate M < 2K - 1 mask."""
+    z = np.load(os.path.join(golden_dir, "delay_patterns_random.npz"))
+    for name in z["names"]:
+        B, K, M, T, bos, pad = (int(v) for v in z[name + "_meta"])
+        ids, mask = ptts.build_delay_pattern_mask(torch.from_numpy(z[name + "_in"]).to(DEV), bos, pad, M, K)
+        assert np.array_equal(mask.cpu().numpy(), z[name + "_mask"]), (name, B, K, M, T)
+        assert np.array_equal(ids.cpu().numpy(), z[name + "_ids"]), (name, B, K, M, T)
+        applied = ptts.apply_delay_pattern_mask(torch.from_numpy(z[name + "_gen"]).to(DEV), mask)
+        assert np.array_equal(applied.cpu().numpy(), z[name + "_applied"]), (name, B, K, M, T)
+
+
 def test_delay_mask_full_size_properties():
     # BASELINE config 2/5 sizes: B=64, K=9, M=869 and M=2609 - structure checked without the oracle
     for B, M in ((64, 869), (16, 2609)):

@@ -18,6 +18,20 @@ def test_delay_mask_docstring_kat():
     assert np.array_equal(mask, want)
 
 
+def test_delay_mask_vs_reference_randomised(golden_dir):
+    """48 randomised cases run through the reference (oracle/gen_golden.py delay_random): 1..9 codebooks, every prompt
+    length up to M - K + 1, prompt values colliding with BOS / PAD, the degenerate M < 2K - 1 mask."""
+    z = np.load(os.path.join(golden_dir, "delay_patterns_random.npz"))
+    assert len(z["names"]) == 48
+    for name in z["names"]:
+        B, K, M, T, bos, pad = z[name + "_meta"]
+        ids, mask = delay_pattern.build_delay_pattern_mask(z[name + "_in"], bos, pad, M, K)
+        assert np.array_equal(mask, z[name + "_mask"]), (name, z[name + "_meta"])
+        assert np.array_equal(ids, z[name + "_ids"]), (name, z[name + "_meta"])
+        applied = delay_pattern.apply_delay_pattern_mask(z[name + "_gen"], mask)
+        assert np.array_equal(applied, z[name + "_applied"]), (name, z[name + "_meta"])
+
+
 def test_position_table_vs_reference(golden_dir):
     """ParlerTTSSinusoidalPositionalEmbedding.get_embedding (modeling_parler_tts.py:200-213): the table a random-init
     model is built with - the host's generator and the oracle's - equals the reference's bit for bit (even and odd
