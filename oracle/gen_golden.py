@@ -149,6 +149,46 @@ def gen_decoder(ref):
     return dims, sd, model
 
 
+TINY2 = dict(
+    vocab_size=70, hidden_size=192, num_hidden_layers=3, num_attention_heads=3, ffn_dim=320, num_codebooks=5,
+    max_position_embeddings=48, pad_token_id=64, eos_token_id=64, bos_token_id=65,
+)
+
+
+def gen_decoder2(ref):
+    """A second decoder shape through the reference's forward (three heads, five codebooks, three layers, a hidden size
+    that is not a power of two, LayerNorm gains / biases away from 1 / 0): prefill and five cached steps with ragged
+    description and prompt masks (left- and right-padded), logits of every step and the whole final cache."""
+    dims = decoder_oracle.DecoderDims(**TINY2)
+    sd = decoder_oracle.random_decoder_state(dims, seed=23, ln_jitter=0.2)
+    model = _ref_decoder(ref, dims, sd)
+    g = torch.Generator().manual_seed(24)
+    B, S, P, K, n = 4, 7, 5, dims.num_codebooks, 5
+    enc = torch.randn(B, S, dims.hidden_size, generator=g)
+    prm = torch.randn(B, P, dims.hidden_size, generator=g) * 0.5
+    enc_mask = torch.tensor([[1, 1, 1, 1, 1, 1, 1], [1, 1, 1, 1, 0, 0, 0], [1, 0, 0, 0, 0, 0, 0], [1, 1, 1, 1, 1, 1, 0]])
+    prm_mask = torch.tensor([[1, 1, 1, 1, 1], [0, 0, 1, 1, 1], [1, 1, 1, 0, 0], [0, 1, 1, 1, 1]])
+    e = enc * enc_mask[..., None]
+    ids = torch.full((B * K, 1), dims.bos_token_id)
+    steps = torch.randint(0, dims.vocab_size, (n, B * K, 1), generator=g)
+    out = {"meta": np.array([B, S, P, n], dtype=np.int64), "enc": enc.numpy(), "prm": prm.numpy(),
+           "enc_mask": enc_mask.numpy(), "prm_mask": prm_mask.numpy(), "step_ids": steps.numpy()}
+    with torch.no_grad():
+        o = model(input_ids=ids, encoder_hidden_states=e, encoder_attention_mask=enc_mask, prompt_hidden_states=prm,
+                  prompt_attention_mask=prm_mask, use_cache=True)
+        out["prefill_logits"] = o.logits.numpy()
+        past = o.past_key_values
+        for t in range(n):
+            o = model(input_ids=steps[t], encoder_hidden_states=e, encoder_attention_mask=enc_mask,
+                      prompt_attention_mask=prm_mask, past_key_values=past, use_cache=True)
+            past = o.past_key_values
+            out[f"step{t}_logits"] = o.logits.numpy()
+    out["k_self_last"] = past[-1][0].numpy()
+    out["v_self_l0"] = past[0][1].numpy()
+    np.savez_compressed(os.path.join(GOLD, "decoder_tiny2.npz"), **out)
+    print("decoder_tiny2.npz written:", {k: v.shape for k, v in out.items() if k.endswith("logits")})
+
+
 def gen_loop(ref, dims, sd, model):
     """Drives the reference decoder + the reference mask functions through the restated loop (greedy), so that the
     fixture pins prepare_inputs/apply-mask/cache semantics end to end on the reference's own forward."""
@@ -411,6 +451,7 @@ def main():
     gen_delay_random(ref)
     gen_positions(ref)
     dims, sd, model = gen_decoder(ref)
+    gen_decoder2(ref)
     gen_loop(ref, dims, sd, model)
     gen_dac()
     gen_dac_encode()
@@ -418,7 +459,9 @@ def main():
     gen_c1(ref)
 
 
-if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "delay_random":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "decoder2":
+    gen_decoder2(import_reference())
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "delay_random":
     gen_delay_random(import_reference())
 elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "positions":
     gen_positions(import_reference())

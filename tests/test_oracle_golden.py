@@ -86,6 +86,30 @@ def test_decoder_forward_vs_reference(golden_dir):
     np.testing.assert_allclose(logits.numpy(), z["tf_logits"], atol=2e-5, rtol=1e-4)
 
 
+def test_decoder_forward_vs_reference_second_shape(golden_dir):
+    """Three heads, five codebooks, three layers, hidden 192, ragged left- / right-padded masks, five cached steps
+    (oracle/gen_golden.py gen_decoder2): logits of every step and the final self-attention cache."""
+    from oracle.gen_golden import TINY2
+
+    z = np.load(os.path.join(golden_dir, "decoder_tiny2.npz"))
+    dims = decoder_oracle.DecoderDims(**TINY2)
+    sd = decoder_oracle.random_decoder_state(dims, seed=23, ln_jitter=0.2)
+    B, S, P, n = (int(v) for v in z["meta"])
+    enc, prm = torch.from_numpy(z["enc"]), torch.from_numpy(z["prm"])
+    em, pm = torch.from_numpy(z["enc_mask"]), torch.from_numpy(z["prm_mask"])
+    e = enc * em[..., None]
+    ids = torch.full((B * dims.num_codebooks, 1), dims.bos_token_id)
+    logits, past = decoder_oracle.decoder_forward(sd, dims, ids, e, em, prm, pm, None)
+    np.testing.assert_allclose(logits.numpy(), z["prefill_logits"], atol=2e-5, rtol=1e-4)
+    steps = torch.from_numpy(z["step_ids"])
+    for t in range(n):
+        logits, past = decoder_oracle.decoder_forward(sd, dims, steps[t], e, em, None, pm, past)
+        np.testing.assert_allclose(logits.numpy(), z[f"step{t}_logits"], atol=2e-5, rtol=1e-4, err_msg=f"step {t}")
+    np.testing.assert_allclose(past[-1][0].numpy(), z["k_self_last"], atol=1e-5)
+    np.testing.assert_allclose(past[0][1].numpy(), z["v_self_l0"], atol=1e-5)
+    assert past[0][0].shape[2] == P + 1 + n
+
+
 def test_loop_vs_reference_driven_probe(golden_dir):
     z = np.load(os.path.join(golden_dir, "loop_tiny.npz"))
     dims, sd = _tiny()
