@@ -257,6 +257,61 @@ def test_forward_with_static_cache_matches_reference_fixture(golden_dir, impl):
         m(input_ids=ids[:, :1], past_key_values=((None,) * 4,))
 
 
+@pytest.mark.parametrize("impl", [cabi.IMPL_SIMPLE, cabi.IMPL_FAST])
+def test_cached_steps_match_the_reference_steps_masked_and_unmasked(golden_dir, impl):
+    """The reference's own cached decode steps (ParlerTTSForCausalLM.forward with its tuple cache, modeling_parler_tts.py:
+    292-304, 843-879; oracle/gen_golden.py gen_decoder) against prefill + three cached steps here, with and without
+    ragged description / prompt masks: logits of every step, fp32."""
+    z = np.load(os.path.join(golden_dir, "decoder_tiny.npz"))
+    dims, sd, m = _tiny_model(impl=impl)
+    enc, prm = torch.from_numpy(z["enc"]), torch.from_numpy(z["prm"])
+    B = enc.shape[0]
+    ids = torch.full((B * dims.num_codebooks, 1), dims.bos_token_id)
+    for tag in ("nomask", "masked"):
+        em = torch.from_numpy(z["enc_mask"]) if tag == "masked" else None
+        pm = torch.from_numpy(z["prm_mask"]) if tag == "masked" else None
+        e = enc if em is None else enc * em[..., None]
+        o = m(input_ids=ids.to(DEV), encoder_hidden_states=e.to(DEV), encoder_attention_mask=None if em is None else em.to(DEV),
+              prompt_hidden_states=prm.to(DEV), prompt_attention_mask=None if pm is None else pm.to(DEV), use_cache=True,
+              max_cache_len=8)
+        np.testing.assert_allclose(o.logits.cpu().numpy(), z[f"{tag}_prefill_logits"], atol=1e-4, rtol=1e-3)
+        steps = torch.from_numpy(z[f"{tag}_step_ids"])  # (3, B*K, 1)
+        past = o.past_key_values
+        for t in range(3):
+            o = m(input_ids=steps[t].to(DEV), past_key_values=past)
+            past = o.past_key_values
+            np.testing.assert_allclose(o.logits.cpu().numpy(), z[f"{tag}_step{t}_logits"], atol=1e-4, rtol=1e-3,
+                                       err_msg=f"{tag} step {t}")
+
+
+@pytest.mark.parametrize("impl", [cabi.IMPL_SIMPLE, cabi.IMPL_FAST])
+def test_second_decoder_shape_matches_the_reference(golden_dir, impl):
+    """Three heads, five codebooks, three layers, hidden 192 (not a power of two), ragged left- / right-padded description
+    and prompt masks: prefill + five cached steps against the reference's own logits (oracle/gen_golden.py gen_decoder2)."""
+    from oracle.gen_golden import TINY2
+
+    z = np.load(os.path.join(golden_dir, "decoder_tiny2.npz"))
+    dims = decoder_oracle.DecoderDims(**TINY2)
+    sd = decoder_oracle.random_decoder_state(dims, seed=23, ln_jitter=0.2)
+    m = ptts.ParlerTTSForCausalLM(ptts.ParlerTTSDecoderConfig(**TINY2), state_dict=sd).to(DEV)
+    m.impl = impl
+    B, S, P, n = (int(v) for v in z["meta"])
+    enc, prm = torch.from_numpy(z["enc"]), torch.from_numpy(z["prm"])
+    em, pm = torch.from_numpy(z["enc_mask"]), torch.from_numpy(z["prm_mask"])
+    e = enc * em[..., None]
+    ids = torch.full((B * dims.num_codebooks, 1), dims.bos_token_id)
+    o = m(input_ids=ids.to(DEV), encoder_hidden_states=e.to(DEV), encoder_attention_mask=em.to(DEV),
+          prompt_hidden_states=prm.to(DEV), prompt_attention_mask=pm.to(DEV), use_cache=True, max_cache_len=n + 2)
+    np.testing.assert_allclose(o.logits.cpu().numpy(), z["prefill_logits"], atol=1e-4, rtol=1e-3)
+    steps = torch.from_numpy(z["step_ids"])
+    past = o.past_key_values
+    for t in range(n):
+        o = m(input_ids=steps[t].to(DEV), past_key_values=past)
+        past = o.past_key_values
+        np.testing.assert_allclose(o.logits.cpu().numpy(), z[f"step{t}_logits"], atol=1e-4, rtol=1e-3, err_msg=f"step {t}")
+    assert past.get_seq_length() == P + 1 + n
+
+
 # ------------------------------------------------------------------------------------ fp8 KV cache kernels
 def _e4m3_to_float(u8):
     return u8.view(torch.float8_e4m3fn).float()
