@@ -246,7 +246,7 @@ PTTS_API int ptts_dac_dequant(const int64_t* codes, int32_t B, int32_t K, int32_
 PTTS_API int ptts_dac_conv1d(const float* x, int32_t B, int32_t Cin, int32_t T, const float* w, const float* bias,
                     int32_t Cout, int32_t ksize, int32_t dilation, const float* snake_alpha, const float* residual,
                     int32_t tanh_out, float* y, int32_t impl, ptts_stream_t s);
-/* y = conv_transpose1d(snake(x), w [Cin][Cout][2*stride], stride, padding ceil(stride/2)); stride in {2, 4, 8, 16} (the
+/* y = conv_transpose1d(snake(x), w [Cin][Cout][2*stride], stride, padding ceil(stride/2)); stride in {2, 4, 8} (the
  * 44.1 kHz codec of the reference uses 8, 8, 4, 2; an odd stride such as the 5 of descript's 16 / 24 kHz models is rejected
  * with an argument error, not approximated) */
 PTTS_API int ptts_dac_convtr1d(const float* x, int32_t B, int32_t Cin, int32_t T, const float* w, const float* bias,

@@ -26,3 +26,18 @@ for rates in ((4, 2, 8, 2), (2, 2, 2, 2), (8, 4), (16, 2, 2)):
             print(rates, "impl", impl, tuple(got.shape), "max abs err", float((got - want).abs().max()))
         except Exception as e:  # noqa: BLE001
             print(rates, "impl", impl, "ERROR", type(e).__name__, str(e)[:200])
+
+# the tcgen05 conv path (44.1 kHz widths: 1024 -> 1536 -> ... -> 96) with the rates permuted
+for rates in ((2, 4, 8, 8), (4, 8, 2, 8)):
+    cfg = dict(dac_oracle.DAC_44K, rates=rates)
+    sd = dac_oracle.random_dac_state(cfg, seed=2)
+    codes = torch.randint(0, 1024, (1, 9, 6), generator=torch.Generator().manual_seed(6))
+    want = dac_oracle.decode_codes(sd, codes, cfg).squeeze(1)
+    m = ptts.DACModel(ptts.DACConfig(), state_dict=sd).to(dev)
+    try:
+        eng = m.engine(cabi.IMPL_FAST)
+        got = eng.decode(codes.to(dev)).squeeze(1).cpu()
+        print("44k widths", rates, "fast family, tcgen05 path:", eng.nwc, tuple(got.shape), "max abs err",
+              float((got - want).abs().max()))
+    except Exception as e:  # noqa: BLE001
+        print("44k widths", rates, "ERROR", type(e).__name__, str(e)[:200])

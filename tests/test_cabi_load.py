@@ -85,6 +85,19 @@ def test_argument_errors_are_reported_without_a_gpu():
     assert b"null" in lib.ptts_last_error_string()
 
 
+def test_transposed_conv_rejects_strides_it_cannot_launch():
+    """descript's 16 / 24 kHz codecs use a stride of 5, and 16 would exceed the default dynamic shared memory: both are
+    argument errors with a message, not launch failures (checked before anything touches the device)."""
+    import ctypes
+
+    lib = cabi.load()
+    dummy = ctypes.c_void_p(256)  # never dereferenced: the stride check comes first
+    for stride in (5, 16, 3, 1, 0):
+        rc = lib.ptts_dac_convtr1d(dummy, 1, 32, 4, dummy, None, 16, stride, None, dummy, cabi.IMPL_SIMPLE, None)
+        assert rc == 1, stride
+        assert b"stride must be 2, 4 or 8" in lib.ptts_last_error_string()
+
+
 def test_no_cpu_fallback_in_public_api():
     import torch
 

@@ -197,6 +197,22 @@ def test_dac_44k_architecture_vs_oracle_waveform_1e3(impl):
     assert float((got.cpu() - want).abs().max()) < 1e-3
 
 
+@pytest.mark.parametrize("rates", [(4, 2, 8, 2), (2, 2, 2, 2), (8, 4)])
+def test_dac_rates_read_from_the_checkpoint_vs_oracle(rates):
+    """A codec whose up-sampling rates are not the 44.1 kHz model's: DACModel takes them from the checkpoint's transposed
+    convs (modeling.py _dac_rates_of) and the decode equals the oracle's waveform."""
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=64, decoder_dim=64, rates=rates)
+    sd = dac_oracle.random_dac_state(cfg, seed=5)
+    codes = torch.randint(0, 32, (2, 3, 9), generator=torch.Generator().manual_seed(1))
+    want = dac_oracle.decode_codes(sd, codes, cfg).squeeze(1)
+    m = ptts.DACModel(ptts.DACConfig(num_codebooks=3, codebook_size=32, latent_dim=64), state_dict=sd).to(DEV)
+    assert m.rates == rates
+    for impl in (cabi.IMPL_SIMPLE, cabi.IMPL_FAST):
+        got = m.engine(impl).decode(codes.to(DEV)).squeeze(1).cpu()
+        assert got.shape == want.shape == (2, 9 * int(np.prod(rates)))
+        assert float((got - want).abs().max()) < 1e-4
+
+
 def test_dac_chunked_decode_equals_one_shot_decode():
     """Streaming form of the DAC decode: chunks decoded with 16 frames of real context on
     both sides concatenate to the one-shot decode (the decoder's receptive field is 10 frames, see the oracle test)."""
