@@ -32,6 +32,38 @@ def test_delay_mask_vs_reference_randomised(golden_dir):
         assert np.array_equal(applied, z[name + "_applied"]), (name, z[name + "_meta"])
 
 
+def test_delay_then_dedelay_round_trip_property():
+    """Size-independent property of a1 / a2 / a14 (modeling_parler_tts.py:68-139, 2633-2648): lay codes (B, K, F) out in
+    the delay pattern (code f of codebook k in column f + k + 1, anything in the BOS / PAD triangles), and the de-delay
+    of that matrix returns the codes - for every K, and for matrices cut short (the loop stopped early)."""
+    rng = np.random.default_rng(5)
+    for _ in range(40):
+        K = int(rng.integers(1, 10))
+        B = int(rng.integers(1, 4))
+        F = int(rng.integers(K, 60))           # M = F + K >= 2K - 1
+        M, bos, pad = F + K, 1025, 1024
+        codes = rng.integers(0, 1024, size=(B, K, F)).astype(np.int64)
+        start = np.full((B * K, 1), bos, dtype=np.int64)
+        ids0, mask = delay_pattern.build_delay_pattern_mask(start, bos, pad, M, K)
+        assert ids0.shape == (B * K, 1) and mask.shape == (B * K, M)
+        raw = rng.integers(0, 1088, size=(B * K, M)).astype(np.int64)   # what the loop "selected" inside the triangles
+        for k in range(K):
+            raw[k::K, k + 1 : k + 1 + F] = codes[:, k]
+        got = delay_pattern.revert_delay_pattern(raw, start, mask, bos, pad, K)
+        assert got.shape == (B, K, F) and np.array_equal(got, codes)
+        # stopped early at Lout columns: frames 0 .. Lout - K - 1 come back when Lout >= 2K - 1, otherwise the reference
+        # keeps every column (its rebuilt mask is all -1)
+        Lout = int(rng.integers(max(2 * K - 1, K + 1), M + 1))
+        part = delay_pattern.revert_delay_pattern(raw[:, :Lout], start, mask, bos, pad, K)
+        assert part.shape == (B, K, Lout - K) and np.array_equal(part, codes[:, :, : Lout - K])
+        # frames holding an id outside the codebook are the ones the ragged path drops
+        bad = codes.copy()
+        bad[0, rng.integers(0, K), rng.integers(0, F)] = 1024
+        keep = delay_pattern.valid_frame_mask(bad, 1024)
+        assert keep.shape == (B, F) and int((~keep).sum()) == 1
+        assert delay_pattern.needs_sequential_decode(bad, bos, pad, pad) and not delay_pattern.needs_sequential_decode(codes, bos, pad, pad)
+
+
 def test_position_table_vs_reference(golden_dir):
     """ParlerTTSSinusoidalPositionalEmbedding.get_embedding (modeling_parler_tts.py:200-213): the table a random-init
     model is built with - the host's generator and the oracle's - equals the reference's bit for bit (even and odd
