@@ -117,7 +117,9 @@ def decode_latents(sd, z, cfg=DAC_44K, dtype=torch.float32, taps=None):
         p = f"decoder.model.{bi + 1}.block"
         x = snake(x, sd[p + ".0.alpha"].to(dtype))
         w, b = wn(sd, p + ".1", dtype)
-        x = F.conv_transpose1d(x, w, b, stride=s, padding=math.ceil(s / 2), output_padding=s % 2)
+        # no output_padding: an odd stride s yields s*T - 1 samples, as in transformers' DacDecoderBlock (the anchor for the
+        # un-vendored descript-audio-codec, models/dac/modeling_dac.py:243-249); the reference's codec has even strides only
+        x = F.conv_transpose1d(x, w, b, stride=s, padding=math.ceil(s / 2))
         if taps is not None:
             taps.append(x)
         for ri, dil in enumerate((1, 3, 9)):

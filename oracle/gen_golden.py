@@ -223,24 +223,27 @@ def gen_loop(ref, dims, sd, model):
     np.savez_compressed(os.path.join(GOLD, "loop_tiny.npz"), **out)
 
 
-def gen_dac():
-    """transformers' DacModel (arithmetic-equivalent to descript DAC) on the oracle's random weights."""
+def hf_dac_with_oracle_weights(cfg, sd):
+    """transformers' DacModel (arithmetic-equivalent to descript DAC) carrying the oracle's random decoder + quantizer
+    weights `sd` of the descript layout `cfg` (dac_oracle.random_dac_state); the encoder side keeps its random init."""
     from transformers import DacConfig, DacModel
 
-    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
-    sd = dac_oracle.random_dac_state(cfg, seed=31)
-    hf_cfg = DacConfig(encoder_hidden_size=8, downsampling_ratios=[2, 4, 8, 8], decoder_hidden_size=64,
-                       n_codebooks=3, codebook_size=32, codebook_dim=4, sampling_rate=44100)
-    assert hf_cfg.hidden_size == 128
+    rates, n_q = tuple(cfg["rates"]), cfg["n_codebooks"]
+    nb = len(rates)
+    assert cfg["latent_dim"] % 2 ** nb == 0
+    hf_cfg = DacConfig(encoder_hidden_size=cfg["latent_dim"] // 2 ** nb, downsampling_ratios=list(reversed(rates)),
+                       decoder_hidden_size=cfg["decoder_dim"], n_codebooks=n_q, codebook_size=cfg["codebook_size"],
+                       codebook_dim=cfg["codebook_dim"], sampling_rate=44100)
+    assert hf_cfg.hidden_size == cfg["latent_dim"] and list(hf_cfg.upsampling_ratios) == list(rates)
     hf = DacModel(hf_cfg).eval()
     new = {}
-    for i in range(3):
+    for i in range(n_q):
         new[f"quantizer.quantizers.{i}.codebook.weight"] = sd[f"quantizer.quantizers.{i}.codebook.weight"]
         w, b = dac_oracle.wn(sd, f"quantizer.quantizers.{i}.out_proj")
         new[f"quantizer.quantizers.{i}.out_proj.weight"], new[f"quantizer.quantizers.{i}.out_proj.bias"] = w, b
     w, b = dac_oracle.wn(sd, "decoder.model.0")
     new["decoder.conv1.weight"], new["decoder.conv1.bias"] = w, b
-    for bi in range(4):
+    for bi in range(nb):
         p, h = f"decoder.model.{bi + 1}.block", f"decoder.block.{bi}"
         new[h + ".snake1.alpha"] = sd[p + ".0.alpha"]
         w, b = dac_oracle.wn(sd, p + ".1")
@@ -252,13 +255,20 @@ def gen_dac():
             new[hr + ".conv1.weight"], new[hr + ".conv1.bias"] = w, b
             w, b = dac_oracle.wn(sd, r + ".3")
             new[hr + ".conv2.weight"], new[hr + ".conv2.bias"] = w, b
-    new["decoder.snake1.alpha"] = sd["decoder.model.5.alpha"]
-    w, b = dac_oracle.wn(sd, "decoder.model.6")
+    new["decoder.snake1.alpha"] = sd[f"decoder.model.{nb + 1}.alpha"]
+    w, b = dac_oracle.wn(sd, f"decoder.model.{nb + 2}")
     new["decoder.conv2.weight"], new["decoder.conv2.bias"] = w, b
     res = hf.load_state_dict(new, strict=False)
     assert not res.unexpected_keys, res.unexpected_keys
-    assert all(k.startswith(("encoder.", "quantizer.quantizers.0.in_proj", "quantizer.quantizers.1.in_proj",
-                             "quantizer.quantizers.2.in_proj")) for k in res.missing_keys), res.missing_keys
+    assert all(k.startswith("encoder.") or ".in_proj" in k for k in res.missing_keys), res.missing_keys
+    return hf
+
+
+def gen_dac():
+    """transformers' DacModel (arithmetic-equivalent to descript DAC) on the oracle's random weights."""
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+    sd = dac_oracle.random_dac_state(cfg, seed=31)
+    hf = hf_dac_with_oracle_weights(cfg, sd)
     g = torch.Generator().manual_seed(32)
     codes = torch.randint(0, 32, (2, 3, 7), generator=g)
     with torch.no_grad():

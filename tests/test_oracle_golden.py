@@ -250,6 +250,34 @@ def test_dac_decoder_receptive_field_is_ten_frames():
     assert err[10] == 0.0 and err[9] > 1e-7, err
 
 
+def test_dac_oracle_vs_transformers_live_on_other_shapes():
+    """The codec oracle against the installed transformers' DacModel (the arithmetic-equivalent of the un-vendored
+    descript-audio-codec), live, on shapes the committed fixture does not hold: other numbers of blocks and codebooks,
+    other widths, and descript's 24 kHz rate set with its ODD stride 5 (5 T - 1 samples from that block)."""
+    from oracle.gen_golden import hf_dac_with_oracle_weights
+
+    shapes = [
+        dict(n_codebooks=2, codebook_size=16, codebook_dim=4, latent_dim=64, decoder_dim=96, rates=(8, 5, 4, 2)),
+        dict(n_codebooks=4, codebook_size=64, codebook_dim=8, latent_dim=32, decoder_dim=32, rates=(2, 2)),
+        dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=64, decoder_dim=64, rates=(4, 2, 8, 2)),
+        dict(n_codebooks=1, codebook_size=8, codebook_dim=2, latent_dim=16, decoder_dim=48, rates=(3, 4, 4)),
+    ]
+    for i, cfg in enumerate(shapes):
+        sd = dac_oracle.random_dac_state(cfg, seed=40 + i)
+        hf = hf_dac_with_oracle_weights(cfg, sd)
+        codes = torch.randint(0, cfg["codebook_size"], (2, cfg["n_codebooks"], 6),
+                              generator=torch.Generator().manual_seed(i))
+        with torch.no_grad():
+            want = hf.decode(audio_codes=codes).audio_values
+            zq = hf.quantizer.from_codes(codes)[0]
+        got = dac_oracle.decode_codes(sd, codes, cfg).squeeze(1)
+        assert got.shape == want.shape, (cfg["rates"], got.shape, want.shape)
+        if all(r % 2 == 0 for r in cfg["rates"]):  # an odd stride s gives s * T - 1 samples in that block
+            assert got.shape == (2, 6 * int(np.prod(cfg["rates"])))
+        np.testing.assert_allclose(dac_oracle.from_codes(sd, codes, cfg).numpy(), zq.numpy(), atol=1e-5, rtol=1e-5)
+        np.testing.assert_allclose(got.numpy(), want.numpy(), atol=2e-5, rtol=1e-4, err_msg=str(cfg["rates"]))
+
+
 def test_oracle_processors_match_transformers_classes():
     """The oracle's top-p / repetition-penalty restatements against the installed transformers' own classes."""
     from transformers.generation import logits_process as lp
