@@ -94,3 +94,51 @@ def test_generation_length_and_mode_rules_follow_the_reference():
     for bad in (dict(num_beams=2), dict(num_beams=4, num_beam_groups=2, diversity_penalty=0.5)):
         with pytest.raises(ValueError, match="incompatible mode for generation"):
             _resolve_generation(base, None, bad, None)
+
+
+def test_generation_plan_routes_every_field_or_raises():
+    """`_Plan` = what the reference's `_get_logits_processor` / `_get_logits_warper` (modeling_parler_tts.py:2561-2567,
+    2597) would build, split into the fused epilogue's native knobs and transformers' own classes run between the forward
+    pass and the epilogue.  No field is dropped silently: it is native, or a python processor in the reference's order,
+    or an error."""
+    import pytest
+    from transformers.generation import logits_process as lp
+    from transformers.generation.configuration_utils import GenerationConfig
+
+    from parler_tts_b200.modeling import _Plan
+
+    def plan(user=(), cfg=False, T0=1, **kw):
+        gc = GenerationConfig(pad_token_id=1024, eos_token_id=1024, bos_token_id=1025, max_length=50)
+        gc.update(**kw)
+        return _Plan(gc, T0, list(user), cfg, 1024)
+
+    p = plan()  # greedy, nothing set
+    assert not p.slow and not p.do_sample and p.rep_penalty == 1.0 and p.min_length == 0
+    p = plan(min_new_tokens=5, T0=3, repetition_penalty=1.3, min_length=4)
+    assert not p.slow and p.min_length == 8 and p.rep_penalty == 1.3  # native: max(min_length, T0 + min_new_tokens)
+    p = plan(do_sample=True)
+    assert not p.slow and (p.temperature, p.top_k, p.top_p) == (1.0, 50, 1.0)  # transformers <= 4.40 default top_k = 50
+    p = plan(do_sample=True, temperature=0.7, top_k=20, top_p=0.9)
+    assert not p.slow and (p.temperature, p.top_k, p.top_p) == (0.7, 20, 0.9)
+    p = plan(do_sample=False, temperature=0.7, top_k=20, top_p=0.9)
+    assert not p.slow and (p.temperature, p.top_k, p.top_p) == (1.0, 0, 1.0)  # warpers exist for sampling only
+    # a warper the epilogue does not have: the whole warper chain runs as transformers' classes, in the library's order
+    p = plan(do_sample=True, temperature=0.7, top_k=20, top_p=0.9, typical_p=0.5)
+    assert p.slow and [type(w) for w in p.py_warpers] == [lp.TemperatureLogitsWarper, lp.TopKLogitsWarper,
+                                                          lp.TopPLogitsWarper, lp.TypicalLogitsWarper]
+    assert (p.temperature, p.top_k, p.top_p) == (1.0, 0, 1.0)  # and is not applied a second time natively
+    # a processor the epilogue does not have: every default processor moves to python, reference order, user's list last
+    user = [lambda ids, scores: scores]
+    # (min_length would join them as MinLengthLogitsProcessor on the CUDA device: covered by tests/test_gpu_api.py)
+    p = plan(user=user, no_repeat_ngram_size=2, repetition_penalty=1.2)
+    assert p.slow and [type(x) for x in p.py_procs[:2]] == [lp.RepetitionPenaltyLogitsProcessor,
+                                                           lp.NoRepeatNGramLogitsProcessor]
+    assert p.py_procs[2] is user[0] and p.rep_penalty == 1.0 and p.min_length == 0
+    assert plan(user=user, cfg=True).cfg_in_python and not plan(cfg=True).cfg_in_python
+    assert plan(renormalize_logits=True).slow
+    with pytest.raises(NotImplementedError):
+        plan(encoder_repetition_penalty=1.5)
+    with pytest.raises(ValueError):
+        plan(do_sample=True, temperature=0.0)
+    with pytest.raises(ValueError):
+        plan(do_sample=True, top_p=0.0)
