@@ -278,6 +278,36 @@ def test_dac_oracle_vs_transformers_live_on_other_shapes():
         np.testing.assert_allclose(got.numpy(), want.numpy(), atol=2e-5, rtol=1e-4, err_msg=str(cfg["rates"]))
 
 
+def test_t5_oracle_vs_transformers_live_on_other_shapes():
+    """The T5 encoder oracle against the installed transformers' T5EncoderModel, live, on shapes the committed fixture
+    does not hold: flan-t5-base's proportions (12 heads of d_kv = d_model / 12, gated-GELU, 3 layers here), a stack whose
+    heads do not tile d_model (d_kv * heads != d_model), few buckets with a short max_distance, and no mask at all."""
+    from oracle import t5_oracle
+    from oracle.gen_golden import hf_t5
+
+    base = dict(vocab_size=90, relative_attention_num_buckets=32, relative_attention_max_distance=128,
+                layer_norm_epsilon=1e-6)
+    shapes = [
+        dict(base, d_model=96, d_kv=8, num_heads=12, d_ff=256, num_layers=3, gated=True, dense_act_fn="gelu_new",
+             feed_forward_proj="gated-gelu"),
+        dict(base, d_model=48, d_kv=20, num_heads=3, d_ff=64, num_layers=2, gated=False, dense_act_fn="relu",
+             feed_forward_proj="relu", relative_attention_num_buckets=8, relative_attention_max_distance=16),
+    ]
+    for i, cfg in enumerate(shapes):
+        sd = t5_oracle.random_t5_state(cfg, seed=60 + i)
+        g = torch.Generator().manual_seed(i)
+        ids = torch.randint(0, cfg["vocab_size"], (3, 41), generator=g)
+        mask = torch.ones(3, 41, dtype=torch.long)
+        mask[0, 30:] = 0
+        mask[2, 1:] = 0
+        hf = hf_t5(cfg, sd)
+        for m in (mask, None):
+            with torch.no_grad():
+                want = hf(input_ids=ids, attention_mask=m).last_hidden_state
+            got = t5_oracle.t5_encode(sd, cfg, ids, m)
+            np.testing.assert_allclose(got.numpy(), want.numpy(), atol=2e-5, rtol=1e-4, err_msg=f"shape {i}, mask {m is not None}")
+
+
 def test_oracle_processors_match_transformers_classes():
     """The oracle's top-p / repetition-penalty restatements against the installed transformers' own classes."""
     from transformers.generation import logits_process as lp
