@@ -279,28 +279,29 @@ def gen_dac():
     print("dac_tiny.npz:", wav.shape)
 
 
-def gen_dac_encode():
-    """transformers' DacModel.encode (encoder + residual VQ) on the oracle's random weights -> tests/golden/dac_enc_tiny.npz."""
+def hf_dac_encoder_with_oracle_weights(cfg, sd):
+    """transformers' DacModel carrying the oracle's random ENCODER + quantizer weights (descript layout:
+    dac_oracle.random_dac_state + random_dac_encoder_state); the decoder keeps its random init."""
     from transformers import DacConfig, DacModel
 
-    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
-    sd = dict(dac_oracle.random_dac_state(cfg, seed=31))
-    sd.update(dac_oracle.random_dac_encoder_state(cfg, seed=31, encoder_dim=8))
-    hf_cfg = DacConfig(encoder_hidden_size=8, downsampling_ratios=[2, 4, 8, 8], decoder_hidden_size=64,
-                       n_codebooks=3, codebook_size=32, codebook_dim=4, sampling_rate=44100)
+    rates, n_q = tuple(cfg["rates"]), cfg["n_codebooks"]
+    nb = len(rates)
+    hf_cfg = DacConfig(encoder_hidden_size=cfg["latent_dim"] // 2 ** nb, downsampling_ratios=list(reversed(rates)),
+                       decoder_hidden_size=cfg["decoder_dim"], n_codebooks=n_q, codebook_size=cfg["codebook_size"],
+                       codebook_dim=cfg["codebook_dim"], sampling_rate=44100)
     hf = DacModel(hf_cfg).eval()
     new = {}
 
     def put(dst, src):
         new[dst + ".weight"], new[dst + ".bias"] = dac_oracle.wn(sd, src)
 
-    for i in range(3):
+    for i in range(n_q):
         q = f"quantizer.quantizers.{i}"
         new[q + ".codebook.weight"] = sd[q + ".codebook.weight"]
         put(q + ".out_proj", q + ".out_proj")
         put(q + ".in_proj", q + ".in_proj")
     put("encoder.conv1", "encoder.block.0")
-    for bi in range(4):
+    for bi in range(nb):
         p, h = f"encoder.block.{bi + 1}.block", f"encoder.block.{bi}"
         for ri in range(3):
             r, hr = f"{p}.{ri}.block", f"{h}.res_unit{ri + 1}"
@@ -309,10 +310,19 @@ def gen_dac_encode():
             put(hr + ".conv2", r + ".3")
         new[h + ".snake1.alpha"] = sd[p + ".3.alpha"]
         put(h + ".conv1", p + ".4")
-    new["encoder.snake1.alpha"] = sd["encoder.block.5.alpha"]
-    put("encoder.conv2", "encoder.block.6")
+    new["encoder.snake1.alpha"] = sd[f"encoder.block.{nb + 1}.alpha"]
+    put("encoder.conv2", f"encoder.block.{nb + 2}")
     res = hf.load_state_dict(new, strict=False)
     assert not res.unexpected_keys and all(k.startswith("decoder.") for k in res.missing_keys), res
+    return hf
+
+
+def gen_dac_encode():
+    """transformers' DacModel.encode (encoder + residual VQ) on the oracle's random weights -> tests/golden/dac_enc_tiny.npz."""
+    cfg = dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=128, decoder_dim=64, rates=(8, 8, 4, 2))
+    sd = dict(dac_oracle.random_dac_state(cfg, seed=31))
+    sd.update(dac_oracle.random_dac_encoder_state(cfg, seed=31, encoder_dim=8))
+    hf = hf_dac_encoder_with_oracle_weights(cfg, sd)
     g = torch.Generator().manual_seed(33)
     audio = torch.randn(2, 1, 512 * 9, generator=g) * 0.5
     with torch.no_grad():

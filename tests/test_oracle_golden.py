@@ -278,6 +278,35 @@ def test_dac_oracle_vs_transformers_live_on_other_shapes():
         np.testing.assert_allclose(got.numpy(), want.numpy(), atol=2e-5, rtol=1e-4, err_msg=str(cfg["rates"]))
 
 
+def test_dac_encode_oracle_vs_transformers_live_on_other_shapes():
+    """The codec ENCODE oracle (audio-prompt path, modeling_parler_tts.py:2247-2292 -> dac_wrapper/modeling_dac.py:25-96)
+    against the installed transformers' DacModel.encode, live, on shapes the committed fixture does not hold: latents to
+    1e-5, codes index-exact wherever the nearest-codebook margin is clear (and the margins are required to be clear)."""
+    from oracle.gen_golden import hf_dac_encoder_with_oracle_weights
+
+    shapes = [
+        (dict(n_codebooks=2, codebook_size=16, codebook_dim=4, latent_dim=64, decoder_dim=32, rates=(4, 2, 8, 2)), 4),
+        (dict(n_codebooks=4, codebook_size=64, codebook_dim=3, latent_dim=32, decoder_dim=32, rates=(2, 4)), 8),
+        (dict(n_codebooks=3, codebook_size=32, codebook_dim=4, latent_dim=48, decoder_dim=48, rates=(8, 5, 4, 2)), 3),
+    ]
+    for i, (cfg, enc_dim) in enumerate(shapes):
+        assert enc_dim * 2 ** len(cfg["rates"]) == cfg["latent_dim"]
+        sd = dict(dac_oracle.random_dac_state(cfg, seed=50 + i))
+        sd.update(dac_oracle.random_dac_encoder_state(cfg, seed=50 + i, encoder_dim=enc_dim))
+        hf = hf_dac_encoder_with_oracle_weights(cfg, sd)
+        hop = int(np.prod(cfg["rates"]))
+        audio = torch.randn(2, 1, hop * 7, generator=torch.Generator().manual_seed(i)) * 0.5
+        with torch.no_grad():
+            want_z = hf.encoder(audio)
+            want = hf.encode(audio).audio_codes
+        z = dac_oracle.encode_latents(sd, audio, cfg)
+        np.testing.assert_allclose(z.numpy(), want_z.numpy(), atol=1e-5, rtol=1e-4, err_msg=str(cfg["rates"]))
+        got, margins = dac_oracle.rvq_encode(sd, z, cfg, return_margins=True)
+        assert got.shape == want.shape == (2, cfg["n_codebooks"], 7)
+        sure = margins > 1e-5
+        assert float(sure.float().mean()) > 0.98 and torch.equal(got[sure], want[sure]), str(cfg["rates"])
+
+
 def test_t5_oracle_vs_transformers_live_on_other_shapes():
     """The T5 encoder oracle against the installed transformers' T5EncoderModel, live, on shapes the committed fixture
     does not hold: flan-t5-base's proportions (12 heads of d_kv = d_model / 12, gated-GELU, 3 layers here), a stack whose
