@@ -464,12 +464,35 @@ def gen_positions(ref):
     print("positions.npz:", {k: v.shape for k, v in out.items()})
 
 
+def gen_layout(ref):
+    """Checkpoint / config layout of the reference: state-dict key names and shapes of the reference's
+    ParlerTTSForCausalLM for two decoder shapes, and the default `to_dict()` of its three config classes."""
+    import json
+
+    from parler_tts.configuration_parler_tts import ParlerTTSDecoderConfig as RefDecCfg
+    from parler_tts.dac_wrapper.configuration_dac import DACConfig as RefDacCfg
+    from parler_tts.modeling_parler_tts import ParlerTTSForCausalLM as RefLM
+
+    out = {"decoder_state_dict": {}, "config_defaults": {}}
+    for name, kw in (("tiny", TINY), ("tiny2", TINY2)):
+        sd = RefLM(RefDecCfg(**kw)).state_dict()
+        out["decoder_state_dict"][name] = {k: list(v.shape) for k, v in sd.items()}
+    drop = ("transformers_version",)
+    out["config_defaults"]["decoder"] = {k: v for k, v in RefDecCfg().to_dict().items() if k not in drop}
+    out["config_defaults"]["dac"] = {k: v for k, v in RefDacCfg().to_dict().items() if k not in drop}
+    with open(os.path.join(GOLD, "layout.json"), "w") as f:
+        json.dump(out, f, indent=1, sort_keys=True, default=str)
+    print("layout.json:", {k: len(v) for k, v in out["decoder_state_dict"].items()}, "keys;",
+          len(out["config_defaults"]["decoder"]), "+", len(out["config_defaults"]["dac"]), "config fields")
+
+
 def main():
     os.makedirs(GOLD, exist_ok=True)
     ref = import_reference()
     gen_delay(ref)
     gen_delay_random(ref)
     gen_positions(ref)
+    gen_layout(ref)
     dims, sd, model = gen_decoder(ref)
     gen_decoder2(ref)
     gen_loop(ref, dims, sd, model)
@@ -479,7 +502,9 @@ def main():
     gen_c1(ref)
 
 
-if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "decoder2":
+if __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "layout":
+    gen_layout(import_reference())
+elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "decoder2":
     gen_decoder2(import_reference())
 elif __name__ == "__main__" and len(sys.argv) > 1 and sys.argv[1] == "delay_random":
     gen_delay_random(import_reference())
