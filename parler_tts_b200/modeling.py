@@ -189,6 +189,22 @@ class DACModel(nn.Module):
     def forward(self, tensor):
         raise ValueError("`DACModel.forward` not implemented yet")
 
+    # ---- checkpoint I/O as the reference's wrapper is stored (helpers/push_to_hub_scripts/push_dac_to_hub.py:9-13:
+    # config.json of DACConfig + the descript `DAC.state_dict()` under `model.*`)
+    def save_pretrained(self, path):
+        os.makedirs(path, exist_ok=True)
+        self.config.save_pretrained(path)
+        _save_state_file(self.state_dict(), path)
+
+    @classmethod
+    def from_pretrained(cls, path, **kwargs):
+        config = DACConfig.from_pretrained(path)
+        sd = _load_state_file(path)
+        bad = [k for k in sd if not k.startswith("model.")]
+        if bad:
+            raise RuntimeError(f"not a DACModel checkpoint: keys outside `model.*`, e.g. {bad[:3]}")
+        return cls(config, state_dict={k[len("model."):]: v for k, v in sd.items()})
+
 
 def _dac_rates_of(state_dict):
     """Up-sampling rates of a descript DAC decoder read from its checkpoint: block i holds a transposed conv
@@ -657,6 +673,28 @@ class ParlerTTSForCausalLM(nn.Module):
     def reset_engine(self):
         self._packed, self._state_cache = None, None
 
+    # ---- checkpoint I/O of the stand-alone decoder (config.json of ParlerTTSDecoderConfig + `model.decoder.*` /
+    # `lm_heads.*`), the form helpers/model_init_scripts/init_model_600M.py:44-45 saves before it assembles the composite
+    def save_pretrained(self, path):
+        os.makedirs(path, exist_ok=True)
+        self.config.save_pretrained(path)
+        _save_state_file(self.state_dict(), path)
+
+    @classmethod
+    def from_pretrained(cls, path, torch_dtype=None, config=None, **kwargs):
+        if config is None:
+            config = ParlerTTSDecoderConfig.from_pretrained(path)
+        if isinstance(config, ParlerTTSConfig):  # a composite checkpoint: take its decoder (modeling_parler_tts.py:1893-1894)
+            config = config.decoder
+        sd = _load_state_file(path)
+        if any(k.startswith("decoder.") for k in sd):
+            sd = {k[len("decoder."):]: v for k, v in sd.items() if k.startswith("decoder.")}
+        bad = [k for k in sd if not k.startswith(("model.", "lm_heads."))]
+        if bad:
+            raise RuntimeError(f"not a ParlerTTSForCausalLM checkpoint: unexpected keys, e.g. {bad[:3]}")
+        model = cls(config, state_dict=sd)
+        return model if torch_dtype is None else model.to(torch_dtype)
+
     def build_delay_pattern_mask(self, input_ids, bos_token_id, pad_token_id, max_length=None):
         max_length = max_length if max_length is not None else self.generation_config.max_length
         return build_delay_pattern_mask(input_ids, bos_token_id, pad_token_id, max_length, self.num_codebooks)
@@ -891,6 +929,44 @@ class ParlerTTSForConditionalGeneration(nn.Module):
         self.config.save_pretrained(path)
         self.generation_config.save_pretrained(path)
         _save_state_file(self.state_dict(), path)
+
+    @classmethod
+    def from_sub_models_pretrained(cls, text_encoder_pretrained_model_name_or_path=None,
+                                   audio_encoder_pretrained_model_name_or_path=None,
+                                   decoder_pretrained_model_name_or_path=None, *model_args, **kwargs):
+        """modeling_parler_tts.py:1722-1925: a text encoder, a DAC wrapper and a decoder from their own checkpoints (or
+        passed as `text_encoder_model=` / `audio_encoder_model=` / `decoder_model=`), `enc_to_dec_proj` and
+        `embed_prompts` freshly initialised; remaining kwargs (`vocab_size=...`) go to the composite config."""
+        def split(prefix):
+            own = {k[len(prefix):]: v for k, v in kwargs.items() if k.startswith(prefix)}
+            for k in own:
+                del kwargs[prefix + k]
+            return own
+
+        kw_text, kw_audio, kw_dec = split("text_encoder_"), split("audio_encoder_"), split("decoder_")
+        text_encoder = kw_text.pop("model", None)
+        if text_encoder is None:
+            if text_encoder_pretrained_model_name_or_path is None:
+                raise ValueError("If `text_encoder_model` is not defined as an argument, a "
+                                 "`text_encoder_pretrained_model_name_or_path` has to be defined.")
+            from transformers import AutoModelForTextEncoding
+
+            text_encoder = AutoModelForTextEncoding.from_pretrained(text_encoder_pretrained_model_name_or_path,
+                                                                    *model_args, **kw_text)
+        audio_encoder = kw_audio.pop("model", None)
+        if audio_encoder is None:
+            if audio_encoder_pretrained_model_name_or_path is None:
+                raise ValueError("If `audio_encoder_model` is not defined as an argument, an "
+                                 "`audio_encoder_pretrained_model_name_or_path` has to be defined.")
+            audio_encoder = DACModel.from_pretrained(audio_encoder_pretrained_model_name_or_path, **kw_audio)
+        decoder = kw_dec.pop("model", None)
+        if decoder is None:
+            if decoder_pretrained_model_name_or_path is None:
+                raise ValueError("If `decoder_model` is not defined as an argument, a "
+                                 "`decoder_pretrained_model_name_or_path` has to be defined.")
+            decoder = ParlerTTSForCausalLM.from_pretrained(decoder_pretrained_model_name_or_path, **kw_dec)
+        config = ParlerTTSConfig.from_sub_models_config(text_encoder.config, audio_encoder.config, decoder.config, **kwargs)
+        return cls(text_encoder=text_encoder, audio_encoder=audio_encoder, decoder=decoder, config=config)
 
     def prompt_table(self):
         t = self.embed_prompts.weight

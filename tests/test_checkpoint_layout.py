@@ -77,3 +77,64 @@ def test_save_pretrained_from_pretrained_round_trip(tmp_path):
     assert set(sd) == set(sd2) and all(torch.equal(sd[k], sd2[k]) for k in sd)
     assert m2.audio_encoder.rates == rates and m2.generation_config.max_length == 77
     assert m2.config.decoder.to_dict() == m.config.decoder.to_dict()
+
+
+def test_model_init_script_flow_from_sub_models_pretrained(tmp_path):
+    """The way the reference builds its random-init checkpoints (helpers/model_init_scripts/init_model_600M.py:24-70 -
+    the source of BASELINE.json's "random-init" configurations): a decoder from its config, saved alone; the composite
+    assembled from three checkpoints by `from_sub_models_pretrained(..., vocab_size=...)`; generation defaults set on
+    it; saved; loaded."""
+    import pytest
+    from transformers import T5Config, T5EncoderModel
+
+    t5_dir, dac_dir, dec_dir, out_dir = (str(tmp_path / n) for n in ("t5", "dac", "decoder", "parler"))
+    torch.manual_seed(1)
+    T5EncoderModel(T5Config(d_model=64, num_layers=2, d_ff=128, num_heads=2, d_kv=32, vocab_size=100)).save_pretrained(t5_dir)
+    dac_cfg = ptts.DACConfig(num_codebooks=4, codebook_size=32, latent_dim=128)
+    dac_sd = dac_oracle.random_dac_state(dict(n_codebooks=4, codebook_size=32, codebook_dim=4, latent_dim=128,
+                                              decoder_dim=64, rates=(8, 8, 4, 2)), seed=3)
+    ptts.DACModel(dac_cfg, state_dict=dac_sd).save_pretrained(dac_dir)
+    assert all(k.startswith("model.") for k in ptts.DACModel.from_pretrained(dac_dir).state_dict())
+
+    decoder_config = ptts.ParlerTTSDecoderConfig(**dict(TINY, vocab_size=32 + 64, pad_token_id=32, eos_token_id=32,
+                                                        bos_token_id=33))
+    decoder = ptts.ParlerTTSForCausalLM(decoder_config)
+    decoder.save_pretrained(dec_dir)
+    back = ptts.ParlerTTSForCausalLM.from_pretrained(dec_dir)
+    assert back.config.to_dict() == decoder.config.to_dict()
+    assert all(torch.equal(v, back.state_dict()[k]) for k, v in decoder.state_dict().items())
+
+    model = ptts.ParlerTTSForConditionalGeneration.from_sub_models_pretrained(
+        text_encoder_pretrained_model_name_or_path=t5_dir, audio_encoder_pretrained_model_name_or_path=dac_dir,
+        decoder_pretrained_model_name_or_path=dec_dir, vocab_size=100)
+    assert model.config.vocab_size == 100 and model.config.decoder.num_codebooks == TINY["num_codebooks"]
+    assert model.embed_prompts.weight.shape == (100, TINY["hidden_size"])
+    assert model.enc_to_dec_proj.weight.shape == (TINY["hidden_size"], 64)
+    assert all(torch.equal(v, model.decoder.state_dict()[k]) for k, v in decoder.state_dict().items())
+    model.generation_config.decoder_start_token_id = 33
+    model.generation_config.pad_token_id = 32
+    model.generation_config.eos_token_id = 32
+    model.generation_config.max_length = int(30 * model.audio_encoder.config.frame_rate)
+    model.generation_config.do_sample = True
+    model.generation_config.guidance_scale = 1
+    model.config.pad_token_id = 32
+    model.config.decoder_start_token_id = 33
+    model.save_pretrained(out_dir)
+    again = ptts.ParlerTTSForConditionalGeneration.from_pretrained(out_dir)
+    assert again.generation_config.max_length == 2580 and again.generation_config.do_sample is True
+    assert again.generation_config.decoder_start_token_id == 33
+    assert again.config.pad_token_id == 32 and again.config.decoder_start_token_id == 33
+    sd, sd2 = model.state_dict(), again.state_dict()
+    assert set(sd) == set(sd2) and all(torch.equal(sd[k], sd2[k]) for k in sd)
+    # a composite checkpoint also serves as the decoder's source (modeling_parler_tts.py:1893-1894)
+    dec2 = ptts.ParlerTTSForCausalLM.from_pretrained(out_dir)
+    assert all(torch.equal(v, dec2.state_dict()[k]) for k, v in decoder.state_dict().items())
+    # models handed over directly, and the reference's errors for a missing source
+    m3 = ptts.ParlerTTSForConditionalGeneration.from_sub_models_pretrained(
+        text_encoder_model=model.text_encoder, audio_encoder_model=model.audio_encoder, decoder_model=decoder, vocab_size=100)
+    assert m3.decoder is decoder
+    with pytest.raises(ValueError, match="text_encoder_pretrained_model_name_or_path"):
+        ptts.ParlerTTSForConditionalGeneration.from_sub_models_pretrained(decoder_pretrained_model_name_or_path=dec_dir)
+    with pytest.raises(ValueError, match="decoder_pretrained_model_name_or_path"):
+        ptts.ParlerTTSForConditionalGeneration.from_sub_models_pretrained(
+            text_encoder_pretrained_model_name_or_path=t5_dir, audio_encoder_pretrained_model_name_or_path=dac_dir)
